@@ -1,0 +1,382 @@
+#!/usr/bin/env python
+"""bench.py — GA fitness link-evaluations/sec of the LXY scaffolding scorer on N B200s.
+
+    python bench.py --gpus N --steps K --warmup W [--workload cfg3|cfg2] [--impl reference]
+
+A step = one generation's fitness pass: score every candidate ordering of the population against
+every Hi-C link record.  Workload (BASELINE.json configs[2], the one the metric's "at 1/2/4/8 B200"
+is quoted on): synthetic 5,000 contigs / 200M link records, population 1024, population-sharded
+(strong scaling: the population is split across ranks, links replicated).  One evaluation = one link
+record scored for one candidate, so a step is P x L evaluations.
+
+  value  device-resident: the population is already in HBM; timed with CUDA events on the stream
+         the kernels run on; max over ranks.
+  e2e    through the C ABI with HOST buffers (lxy_scaff_score_batch): host->device copy of the
+         population and device->host copy of the scores inside the timed region; wall clock, max
+         over ranks.
+  --impl reference   the reference's own CPU algorithm (the oracle's line-for-line restatement of
+         scaff.score + Links.Get; the Go toolchain is absent) on the host cores.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (contigs, link records, population, link seed, population seed)
+    "cfg2": (500, 5_000_000, 128, 2, 102),
+    "cfg3": (5_000, 200_000_000, 1024, 3, 103),
+    "tiny": (300, 200_000, 64, 9, 109),
+}
+METRIC = "ga_fitness_link_evals_per_sec"
+UNIT = "link-evals/s"
+
+
+# ------------------------------------------------------------------------------------------------
+# synthetic inputs (torch is plumbing here: device RNG + memory)
+# ------------------------------------------------------------------------------------------------
+def gen_links(n, L, seed, device):
+    """contig pairs with P(a,b) ~ 1/|i-j| in a hidden true order plus 10 % uniform
+    noise pairs; one record per read pair (weight 1).  Returns int32 tensors a, b, order."""
+    import torch
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    order = torch.randperm(n, generator=g, device=device, dtype=torch.int64)
+    d = torch.arange(1, n, device=device, dtype=torch.float64)
+    pmf = (n - d) / d
+    cdf = torch.cumsum(pmf / pmf.sum(), 0)
+    a = torch.empty(L, dtype=torch.int32, device=device)
+    b = torch.empty(L, dtype=torch.int32, device=device)
+    chunk = 1 << 24
+    for lo in range(0, L, chunk):
+        m = min(chunk, L - lo)
+        u = torch.rand(m, generator=g, device=device, dtype=torch.float64)
+        dist = (torch.searchsorted(cdf, u, right=True) + 1).clamp_(1, n - 1)
+        i = (torch.rand(m, generator=g, device=device, dtype=torch.float64) * (n - dist)).long()
+        x, y = order[i], order[i + dist]
+        noise = torch.rand(m, generator=g, device=device) < 0.1
+        nx = torch.randint(0, n, (m,), generator=g, device=device)
+        ny = (nx + torch.randint(1, n, (m,), generator=g, device=device)) % n
+        x = torch.where(noise, nx, x)
+        y = torch.where(noise, ny, y)
+        flip = torch.rand(m, generator=g, device=device) < 0.5
+        a[lo:lo + m] = torch.where(flip, y, x).int()
+        b[lo:lo + m] = torch.where(flip, x, y).int()
+    return a, b, order
+
+
+def gen_population(n, P, seed, order):
+    """The true order, its reverse, k-swap neighbours of it, random permutations (int32 [P][n])."""
+    rng = np.random.default_rng(seed)
+    order = np.asarray(order, np.int32)
+    pop = np.empty((P, n), np.int32)
+    for p in range(P):
+        if p == 0:
+            g = order.copy()
+        elif p == 1:
+            g = order[::-1].copy()
+        elif p % 2 == 0:
+            g = order.copy()
+            for _ in range(int(rng.integers(1, max(2, n // 8)))):
+                x, y = rng.integers(0, n, 2)
+                g[x], g[y] = g[y], g[x]
+        else:
+            g = rng.permutation(n).astype(np.int32)
+        pop[p] = g
+    return pop
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks during the timed region (NVML)
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap",
+               0x8: "hw_slowdown", 0x10: "sync_boost", 0x20: "sw_thermal_slowdown",
+               0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown",
+               0x100: "display_clock_setting"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._t = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if mask & bit and name != "gpu_idle":
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+
+    def start(self):
+        if self.nv:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join()
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+def measured_peak_hbm():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU legs (the oracle is the checker / baseline only)
+# ------------------------------------------------------------------------------------------------
+def cpu_link_streaming_baseline(n, a_host, b_host, perms, seconds=10.0):
+    """The oracle's link-centric port (same algorithm as the GPU kernels) on all host cores, on a
+    bounded sample: the first records x the first candidates, sized for ~`seconds` of work."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _oracle as O
+    cores = os.cpu_count() or 1
+    Ls, Ps = min(len(a_host), 2_000_000), min(len(perms), 2 * cores)
+    w = np.ones(Ls, np.float64)
+    t0 = time.perf_counter()
+    O.scaff_score_links_batch(n, a_host[:Ls], b_host[:Ls], w, perms[:Ps], nthreads=cores)
+    t1 = time.perf_counter() - t0
+    reps = max(1, int(seconds / max(t1, 1e-3)) - 1)
+    reps = min(reps, 20)
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        O.scaff_score_links_batch(n, a_host[:Ls], b_host[:Ls], w, perms[:Ps], nthreads=cores)
+    dt = (time.perf_counter() - t0) / reps
+    return {"value": Ls * Ps / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"oracle link-streaming port (C++ restatement; Go toolchain absent): first "
+                      f"{Ls} records x first {Ps} candidates, {reps} reps, all {cores} host threads"}
+
+
+def run_reference(args, name, n, L, P):
+    """--impl reference: the reference's algorithm (scaff.score's 12N-90 Links.Get look-ups per
+    candidate against the map-of-maps table, scaff.go:246-310 / links.go:190-221) as restated by
+    the oracle, all host threads.  Its cost does not depend on the number of records, so
+    link-evals/s = candidates/s x L (equivalent evaluations)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import torch
+    import _oracle as O
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    dev = "cuda" if torch.cuda.is_available() else "cpu"
+    seed, pseed = WORKLOADS[name][3], WORKLOADS[name][4]
+    a, b, order = gen_links(n, L, seed, dev)
+    # Links.Add per record == add the per-pair counts once (links.go:149-177); aggregate with torch
+    # so that building the table stays bounded (the table is built once, outside the timed steps).
+    lo, hi = torch.minimum(a, b).long(), torch.maximum(a, b).long()
+    keys, counts = torch.unique(lo * n + hi, return_counts=True)
+    ua = (keys // n).cpu().numpy().astype(np.uint32)
+    ub = (keys % n).cpu().numpy().astype(np.uint32)
+    uw = counts.cpu().numpy().astype(np.float64)
+    del a, b, lo, hi, keys, counts
+    table = O.Links.from_records(n, ua, ub, uw)
+    perms = gen_population(n, P, pseed, order.cpu().numpy())
+    Ps = min(P, max(cores, 16))                       # bounded sample of the population per step
+    for _ in range(args.warmup):
+        table.scaff_score_batch(perms[:Ps], nthreads=cores)
+    t0 = time.perf_counter()
+    for s in range(args.steps):
+        table.scaff_score_batch(perms[(s * Ps) % (P - Ps + 1):][:Ps], nthreads=cores)
+    dt = time.perf_counter() - t0
+    cand_per_s = Ps * args.steps / dt
+    value = cand_per_s * L
+    sample = (f"{Ps} of {P} candidates per step against the full aggregated table "
+              f"({len(ua)} pairs from {L} records), {cores} host threads; "
+              f"value = candidates/s x L (the reference's cost is 12N-90 look-ups per candidate, "
+              f"independent of L)")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "candidates_per_sec": cand_per_s,
+        "config": {"workload": f"{name}: {n} contigs / {L} links / population {P}"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+# ------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    n, L, P, seed, pseed = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        return run_reference(args, args.workload, n, L, P)
+
+    import torch
+    import lxy_b200._native as N
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (lxy_b200 has no CPU fallback)")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    # ---- inputs: links replicated on every rank, the population sharded ----
+    a, b, order = gen_links(n, L, seed, dev)
+    perms_all = gen_population(n, P, pseed, order.cpu().numpy())
+    P_loc = P // world
+    perms = np.ascontiguousarray(perms_all[rank * P_loc:(rank + 1) * P_loc])
+    torch.cuda.synchronize()
+    ctx = N.Context(local)
+    t0 = time.perf_counter()
+    ctx.set_links_dev(n, L, a.data_ptr(), b.data_ptr(), None)
+    t_build = time.perf_counter() - t0
+    a_host = a[:2_000_000].cpu().numpy().astype(np.uint32) if rank == 0 else None
+    b_host = b[:2_000_000].cpu().numpy().astype(np.uint32) if rank == 0 else None
+    del a, b
+    torch.cuda.empty_cache()
+
+    perm_dev = torch.from_numpy(perms).to(dev)
+    out_dev = torch.zeros(P_loc, dtype=torch.float64, device=dev)
+    x100_dev = torch.zeros(P_loc, dtype=torch.int64, device=dev)
+    gathered = torch.zeros(P, dtype=torch.float64, device=dev)
+    torch.cuda.synchronize()
+    stream = torch.cuda.ExternalStream(ctx.stream(), device=dev)
+
+    def step_device():
+        ctx.scaff_score_batch_dev(perm_dev.data_ptr(), P_loc, out_dev.data_ptr(), x100_dev.data_ptr())
+        if dist is not None:   # only the score vector moves between GPUs
+            dist.all_gather_into_tensor(gathered, out_dev)
+
+    def bracket():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- value: device-resident ----
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    sampler = ClockSampler(local)
+    bracket()
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    ms_score, ms_layout, ms_finish = [], [], []
+    launches = 0
+    for _ in range(args.steps):
+        step_device()
+        t = ctx.timing()
+        ms_score.append(t["ms_score"]); ms_layout.append(t["ms_layout"]); ms_finish.append(t["ms_finish"])
+        launches += t["launches"]
+    if dist is not None:
+        torch.cuda.current_stream().synchronize()
+    ev1.record(stream)
+    bracket()
+    clocks = sampler.stop()
+    ms_dev = ev0.elapsed_time(ev1)
+    timing = ctx.timing()
+
+    # ---- e2e: host buffers through the C ABI ----
+    for _ in range(2):
+        ctx.scaff_score_batch(perms)
+    bracket()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        host_scores = ctx.scaff_score_batch(perms)
+        if dist is not None:
+            out_dev.copy_(torch.from_numpy(host_scores))
+            dist.all_gather_into_tensor(gathered, out_dev)
+            torch.cuda.synchronize()
+    bracket()
+    ms_e2e = 1e3 * (time.perf_counter() - t0)
+
+    if dist is not None:
+        tt = torch.tensor([ms_dev, ms_e2e], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_dev, ms_e2e = float(tt[0]), float(tt[1])
+    evals_per_step = float(P_loc * world) * float(L)
+    value = evals_per_step * args.steps / (ms_dev * 1e-3)
+    e2e_value = evals_per_step * args.steps / (ms_e2e * 1e-3)
+
+    if rank == 0:
+        peak, peak_src = measured_peak_hbm()
+        # algorithmic bytes of one k_scaff_score launch: every record once (2 B),
+        # both placement tables of every local candidate once, the per-CTA partial sums once
+        cand = 128 if P_loc > 64 else (64 if P_loc > 32 else 32)
+        groups = (P_loc + cand - 1) // cand
+        alg_bytes = 2.0 * L + 2.0 * 2 * groups * cand * n + 8.0 * timing["grid"] * 2 * cand
+        k_ms = float(np.mean(ms_score))
+        achieved = alg_bytes / (k_ms * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "int64 (exact integer accumulation of 100*T*w; fitness = -x/100 in f64)",
+            "data": "synthetic",
+            "config": {"workload": f"{args.workload}: {n} contigs / {L} link records / population {P} "
+                                   f"(BASELINE.json configs[{2 if args.workload == 'cfg3' else 1}])",
+                       "parallelism": f"population-sharded x{world}, links replicated",
+                       "population_per_gpu": P_loc,
+                       "l2_policy": f"inputs larger than L2 ({2 * L / 1e6:.0f} MB of records per pass)"
+                                    if 2 * L > 130e6 else "records fit L2; no flush (steady-state GA loop)",
+                       "link_store_build_s": round(t_build, 3)},
+            "candidates_per_sec": P_loc * world * args.steps / (ms_dev * 1e-3),
+            "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
+                    "h2d_bytes_per_step": int(perms.nbytes), "d2h_bytes_per_step": int(16 * P_loc)},
+            "gpu_launches": int(launches),
+            "kernel_ms": {"k_scaff_score": k_ms, "layout+check": float(np.mean(ms_layout)),
+                          "head+finish": float(np.mean(ms_finish))},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "kernel": "k_scaff_score", "algorithmic_bytes_per_launch": alg_bytes,
+                         "note": "each record byte is reused by every local candidate "
+                                 f"({P_loc} evaluations per 2-byte record), so the kernel sits on "
+                                 "the shared-memory-gather/issue roof, not the HBM roof; see "
+                                 "DESIGN.md §4 and profiles/"},
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_link_streaming_baseline(n, a_host, b_host, perms_all)
+        print(json.dumps(line))
+    ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

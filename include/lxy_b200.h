@@ -1,0 +1,144 @@
+/* lxy_b200.h — C ABI of liblxyb200.so: LXY's GA fitness evaluation on one B200 (sm_100a).
+ *
+ * This is the drop-in boundary.  The reference has no FFI; the hooks it exposes for this path are
+ * the two package-private Go functions handed to the genomes as `sfunc`
+ *     func score(g *GAOrderedIntGenome) float64         /root/reference/src/lxy/scaff/scaff.go:246-310
+ *     func score(g *GAFixedBitstringGenome) float64     /root/reference/src/lxy/phase/phase.go:171-207
+ * reached through Genome.Score()  (scaff/genome.go:153-159, phase/genome.go:87-93), both reading
+ * the link table sequtil.Links through Links.Get (src/sequtil/links.go:190-221).  A cgo shim binds
+ * the entry points below (see INTEGRATION.md for the Go side).
+ *
+ * Conventions: every function returns 0 (LXY_OK) or a negative lxy_status; nothing throws or
+ * aborts across the boundary; the message of the last failure on the calling thread is
+ * lxy_last_error().  All pointers are HOST pointers unless the name ends in _dev.  The library
+ * copies what it needs before returning and never retains caller memory (cgo pointer rule).
+ * A context belongs to one CUDA device; entry points take the context mutex, so concurrent
+ * callers (go-galib runs Score() from 7 goroutines, scaff.go:88) are serialised, not corrupted.
+ * There is NO CPU fallback: without a CUDA device lxy_ctx_create fails with LXY_ERR_CUDA.
+ */
+#ifndef LXY_B200_H_
+#define LXY_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LXY_ABI_VERSION 1
+
+typedef enum lxy_status {
+  LXY_OK = 0,
+  LXY_ERR_ARG = -1,      /* null pointer, negative size, id out of range                     */
+  LXY_ERR_CUDA = -2,     /* a CUDA runtime call failed (message holds cudaGetErrorString)     */
+  LXY_ERR_STATE = -3,    /* e.g. scoring before links were set                                */
+  LXY_ERR_BAD_GENE = -4, /* a row of the population is not a permutation of 0..n-1 / not 0,1  */
+  LXY_ERR_RANGE = -5,    /* value does not fit the device format (n too large, overflow)      */
+  LXY_ERR_NOMEM = -6
+} lxy_status;
+
+/* accumulation mode of the scaffolding scorers */
+#define LXY_ACC_AUTO 0 /* exact integers when every weight is integral (|w| < 2^31), else fp64 */
+#define LXY_ACC_F64 1  /* always fp64 accumulation                                            */
+#define LXY_ACC_INT 2  /* require integral weights (error otherwise)                          */
+
+#define LXY_FLAG_NO_VALIDATE 1u /* skip the on-device permutation / bit check                  */
+
+typedef struct lxy_cfg {
+  int32_t device;   /* CUDA ordinal                                                          */
+  int32_t acc_mode; /* LXY_ACC_*                                                             */
+  uint32_t flags;   /* LXY_FLAG_*                                                            */
+  int32_t reserved;
+} lxy_cfg;
+
+typedef struct lxy_ctx lxy_ctx;
+
+/* Device time of the most recent scoring call, measured with CUDA events on the context's own
+ * stream (bench.py reads these; they are the roofline numerators' denominators). */
+typedef struct lxy_timing {
+  float ms_total;    /* first kernel start -> last kernel end (excludes host<->device copies)  */
+  float ms_layout;   /* ordering -> placement tables (inverse permutation / prefix scan)       */
+  float ms_score;    /* the link-streaming fitness kernel (the dominant kernel)                */
+  float ms_finish;   /* head-of-ordering correction + fixed-order reduction                    */
+  float ms_h2d;      /* host->device copy of the population (0 for *_dev entry points)         */
+  float ms_d2h;      /* device->host copy of the scores                                        */
+  int32_t launches;  /* kernels launched by the call                                           */
+  int32_t grid;      /* CTAs of the dominant kernel                                            */
+  int64_t link_bytes; /* bytes of link records the dominant kernel read per pass              */
+  int64_t table_bytes; /* bytes of placement tables it staged into shared memory              */
+} lxy_timing;
+
+int lxy_abi_version(void);
+const char* lxy_last_error(void);
+int lxy_device_count(int32_t* count);
+
+int lxy_ctx_create(const lxy_cfg* cfg, lxy_ctx** out);
+void lxy_ctx_destroy(lxy_ctx* ctx);
+int lxy_ctx_get_timing(lxy_ctx* ctx, lxy_timing* out);
+int lxy_ctx_stream(lxy_ctx* ctx, void** cuda_stream); /* cudaStream_t the kernels run on       */
+int lxy_ctx_sync(lxy_ctx* ctx);
+
+/* ---- scaffolding, R-profile = the reference scorer (scaff.go:246-310) -------------------------
+ * Link records (a, b, w): ids in [0, n_ids), w nullable (= 1 per record, what
+ * ScaffoldLinksFromSam adds per read pair, src/sequtil/alignment.go:656-660).  Records of the same
+ * pair accumulate (Links.Add, links.go:149-177); (a,b) == (b,a) (links.go:130-132,162-164).
+ * fitness(p) = - sum_records w * T[|pos a - pos b|] * (1 + [min(pos a, pos b) > 0]),
+ * T = {1:1, 2:.5, 3:.33, 5:.2, 11:.1, 20:.05}, pos = inverse of the ordering. */
+int lxy_ctx_set_links(lxy_ctx* ctx, int32_t n_ids, int64_t n_links, const uint32_t* a,
+                      const uint32_t* b, const double* w);
+/* Same, with a_dev / b_dev / w_dev already resident on the context's device (e.g. produced by a
+ * device-side SAM -> links step); the arrays are read, not retained. */
+int lxy_ctx_set_links_dev(lxy_ctx* ctx, int32_t n_ids, int64_t n_links, const uint32_t* a_dev,
+                          const uint32_t* b_dev, const double* w_dev);
+/* population perm[P][n_ids] row-major (Gene of GAOrderedIntGenome, genome.go:20-26, narrowed to
+ * int32); out[P] fitness (lower is better, scaff.go:308); x100 (nullable) receives the exact
+ * integer sum_records 100*T*w*m when the context runs in integer mode, INT64_MIN otherwise. */
+int lxy_scaff_score_batch(lxy_ctx* ctx, const int32_t* perm, int32_t P, double* out,
+                          int64_t* x100);
+int lxy_scaff_score_batch_dev(lxy_ctx* ctx, const int32_t* perm_dev, int32_t P, double* out_dev,
+                              int64_t* x100_dev);
+/* Integer checks: pos[P][n_ids] (placement offset of every contig = its ordering index in the
+ * R-profile) and, for ONE candidate, |pos a - pos b| of caller-supplied records in their order. */
+int lxy_scaff_positions(lxy_ctx* ctx, const int32_t* perm, int32_t P, int32_t* pos);
+int lxy_scaff_link_distances(lxy_ctx* ctx, int32_t n_ids, int64_t n_links, const uint32_t* a,
+                             const uint32_t* b, const int32_t* perm, int64_t* dist);
+/* Aggregated pair weight as Links.Get returns it (links.go:190-221): 0 for an absent pair,
+ * LXY_ERR_ARG (and *out = -1) for an unknown id. */
+int lxy_links_get(lxy_ctx* ctx, int32_t id1, int32_t id2, double* out);
+
+/* ---- scaffolding, G-profile (north_star generalisation; no reference counterpart) -------------
+ * contig lengths len[n_ids], records (a, xa, b, xb, w) with in-contig offsets, per-candidate
+ * orientation bytes ori[P][n_ids] indexed by ORDERING POSITION (nullable = all forward).
+ * start = exclusive prefix sum of len over the ordering; coord = start + (ori ? len-1-x : x);
+ * bucket = |coord a - coord b| / unit; fitness as above with T[bucket].  len==1, x==0, unit==1
+ * reproduces the R-profile bit for bit. */
+int lxy_ctx_set_links_g(lxy_ctx* ctx, int32_t n_ids, int64_t n_links, const uint32_t* a,
+                        const uint32_t* xa, const uint32_t* b, const uint32_t* xb,
+                        const double* w, const uint32_t* len, uint32_t unit);
+int lxy_scaffg_score_batch(lxy_ctx* ctx, const int32_t* perm, const uint8_t* ori, int32_t P,
+                           double* out, int64_t* x100);
+int lxy_scaffg_layout(lxy_ctx* ctx, const int32_t* perm, int32_t P, uint64_t* start_by_pos,
+                      int32_t* pos_by_contig);
+int lxy_scaffg_link_distances(lxy_ctx* ctx, int64_t n_links, const uint32_t* a,
+                              const uint32_t* xa, const uint32_t* b, const uint32_t* xb,
+                              const int32_t* perm, const uint8_t* ori, uint64_t* dist);
+
+/* ---- phasing (phase.go:171-207) ---------------------------------------------------------------
+ * ids are gene indices (phase.go:185); records (a, b, w) with signed integral w (read-pair counts,
+ * links.go:401-412).  genes[P][n_ids] bytes, 0 = false.
+ * fitness(p) = - sum_{records, |a-b| in steps} w * (g[a]==g[b] ? +1 : -1) * (1 + [min(a,b) > 0]),
+ * steps = {1..11, 15, 20, 25, 30}.  out_i64 is exact; out_f64 = (double)out_i64. */
+int lxy_ctx_set_phase_links(lxy_ctx* ctx, int32_t n_ids, int64_t n_links, const uint32_t* a,
+                            const uint32_t* b, const double* w);
+int lxy_phase_score_batch(lxy_ctx* ctx, const uint8_t* genes, int32_t P, int64_t* out_i64,
+                          double* out_f64);
+int lxy_phase_score_batch_dev(lxy_ctx* ctx, const uint8_t* genes_dev, int32_t P,
+                              int64_t* out_i64_dev, double* out_f64_dev);
+
+/* ---- rank / elite (go-galib sorts by Score(); lower is better, ties keep population order) --- */
+int lxy_rank(const double* scores, int32_t P, int32_t* order);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LXY_B200_H_ */

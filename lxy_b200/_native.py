@@ -1,0 +1,271 @@
+"""ctypes binding of liblxyb200.so (the C ABI declared in include/lxy_b200.h).
+
+The library is built in-tree (lxy_b200/_lib/liblxyb200.so) by `make -C lxy_b200/csrc` for sm_100a.
+There is no CPU fallback anywhere in this package: if the library is missing, or no CUDA device
+is present when a context is created, the call raises.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_lib", "liblxyb200.so")
+CSRC = os.path.join(_HERE, "csrc")
+INT64_MIN = -(1 << 63)
+
+# every symbol include/lxy_b200.h declares (tests check the library exports each of them)
+SYMBOLS = [
+    "lxy_abi_version", "lxy_last_error", "lxy_device_count", "lxy_ctx_create", "lxy_ctx_destroy",
+    "lxy_ctx_get_timing", "lxy_ctx_stream", "lxy_ctx_sync", "lxy_ctx_set_links",
+    "lxy_ctx_set_links_dev",
+    "lxy_scaff_score_batch", "lxy_scaff_score_batch_dev", "lxy_scaff_positions",
+    "lxy_scaff_link_distances", "lxy_links_get", "lxy_ctx_set_links_g", "lxy_scaffg_score_batch",
+    "lxy_scaffg_layout", "lxy_scaffg_link_distances", "lxy_ctx_set_phase_links",
+    "lxy_phase_score_batch", "lxy_phase_score_batch_dev", "lxy_rank",
+]
+
+ACC_AUTO, ACC_F64, ACC_INT = 0, 1, 2
+FLAG_NO_VALIDATE = 1
+
+
+class LxyError(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__(f"liblxyb200 status {status}: {message}")
+        self.status = status
+
+
+class Cfg(C.Structure):
+    _fields_ = [("device", C.c_int32), ("acc_mode", C.c_int32), ("flags", C.c_uint32),
+                ("reserved", C.c_int32)]
+
+
+class Timing(C.Structure):
+    _fields_ = [("ms_total", C.c_float), ("ms_layout", C.c_float), ("ms_score", C.c_float),
+                ("ms_finish", C.c_float), ("ms_h2d", C.c_float), ("ms_d2h", C.c_float),
+                ("launches", C.c_int32), ("grid", C.c_int32), ("link_bytes", C.c_int64),
+                ("table_bytes", C.c_int64)]
+
+    def asdict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+def build(verbose=False):
+    """Compile the CUDA library in-tree (cross-compiles for sm_100a without a GPU)."""
+    out = None if verbose else subprocess.DEVNULL
+    subprocess.run(["make", "-C", CSRC, "-j4"], check=True, stdout=out)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: build it with `make -C {CSRC}` (or __graft_entry__.build()). "
+            "lxy_b200 has no CPU fallback.")
+    L = C.CDLL(LIB_PATH)
+    vp, i32, i64, u32, f64 = C.c_void_p, C.c_int32, C.c_int64, C.c_uint32, C.c_double
+    sig = {
+        "lxy_abi_version": (i32, []),
+        "lxy_last_error": (C.c_char_p, []),
+        "lxy_device_count": (i32, [C.POINTER(i32)]),
+        "lxy_ctx_create": (i32, [C.POINTER(Cfg), C.POINTER(vp)]),
+        "lxy_ctx_destroy": (None, [vp]),
+        "lxy_ctx_get_timing": (i32, [vp, C.POINTER(Timing)]),
+        "lxy_ctx_stream": (i32, [vp, C.POINTER(vp)]),
+        "lxy_ctx_sync": (i32, [vp]),
+        "lxy_ctx_set_links": (i32, [vp, i32, i64, vp, vp, vp]),
+        "lxy_ctx_set_links_dev": (i32, [vp, i32, i64, vp, vp, vp]),
+        "lxy_scaff_score_batch": (i32, [vp, vp, i32, vp, vp]),
+        "lxy_scaff_score_batch_dev": (i32, [vp, vp, i32, vp, vp]),
+        "lxy_scaff_positions": (i32, [vp, vp, i32, vp]),
+        "lxy_scaff_link_distances": (i32, [vp, i32, i64, vp, vp, vp, vp]),
+        "lxy_links_get": (i32, [vp, i32, i32, C.POINTER(f64)]),
+        "lxy_ctx_set_links_g": (i32, [vp, i32, i64, vp, vp, vp, vp, vp, vp, u32]),
+        "lxy_scaffg_score_batch": (i32, [vp, vp, vp, i32, vp, vp]),
+        "lxy_scaffg_layout": (i32, [vp, vp, i32, vp, vp]),
+        "lxy_scaffg_link_distances": (i32, [vp, i64, vp, vp, vp, vp, vp, vp, vp]),
+        "lxy_ctx_set_phase_links": (i32, [vp, i32, i64, vp, vp, vp]),
+        "lxy_phase_score_batch": (i32, [vp, vp, i32, vp, vp]),
+        "lxy_phase_score_batch_dev": (i32, [vp, vp, i32, vp, vp]),
+        "lxy_rank": (i32, [vp, i32, vp]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype, fn.argtypes = res, args
+    _lib = L
+    return L
+
+
+def _check(rc):
+    if rc != 0:
+        raise LxyError(rc, lib().lxy_last_error().decode(errors="replace"))
+
+
+def _p(arr):
+    return None if arr is None else arr.ctypes.data_as(C.c_void_p)
+
+
+def _c(arr, dtype):
+    return None if arr is None else np.ascontiguousarray(arr, dtype=dtype)
+
+
+def device_count():
+    n = C.c_int32(0)
+    rc = lib().lxy_device_count(C.byref(n))
+    return n.value if rc == 0 else 0
+
+
+def rank(scores):
+    s = _c(scores, np.float64)
+    order = np.zeros(len(s), np.int32)
+    _check(lib().lxy_rank(_p(s), len(s), _p(order)))
+    return order
+
+
+class Context:
+    """One lxy_ctx: a CUDA device, its stream, the resident link stores."""
+
+    def __init__(self, device=0, acc_mode=ACC_AUTO, flags=0):
+        self._h = C.c_void_p()
+        cfg = Cfg(device, acc_mode, flags, 0)
+        _check(lib().lxy_ctx_create(C.byref(cfg), C.byref(self._h)))
+        self.device = device
+        self.n = 0
+        self.phase_n = 0
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib().lxy_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # -- plumbing --------------------------------------------------------------------------
+    def timing(self):
+        t = Timing()
+        _check(lib().lxy_ctx_get_timing(self._h, C.byref(t)))
+        return t.asdict()
+
+    def stream(self):
+        s = C.c_void_p()
+        _check(lib().lxy_ctx_stream(self._h, C.byref(s)))
+        return s.value or 0
+
+    def sync(self):
+        _check(lib().lxy_ctx_sync(self._h))
+
+    # -- scaffolding -----------------------------------------------------------------------
+    def set_links(self, n_ids, a, b, w=None):
+        a, b, w = _c(a, np.uint32), _c(b, np.uint32), _c(w, np.float64)
+        if len(a) != len(b) or (w is not None and len(w) != len(a)):
+            raise ValueError("a, b, w must have equal length")
+        _check(lib().lxy_ctx_set_links(self._h, n_ids, len(a), _p(a), _p(b), _p(w)))
+        self.n = n_ids
+
+    def set_links_dev(self, n_ids, n_links, a_ptr, b_ptr, w_ptr=None):
+        """a_ptr / b_ptr / w_ptr: device addresses (uint32, uint32, float64) on this device."""
+        _check(lib().lxy_ctx_set_links_dev(self._h, n_ids, n_links, C.c_void_p(a_ptr),
+                                           C.c_void_p(b_ptr),
+                                           C.c_void_p(w_ptr) if w_ptr else None))
+        self.n = n_ids
+
+    def scaff_score_batch(self, perms, want_x100=False):
+        perms = _c(perms, np.int32)
+        if perms.ndim != 2 or perms.shape[1] != self.n:
+            raise ValueError(f"perms must be [P][{self.n}]")
+        P = perms.shape[0]
+        out = np.zeros(P, np.float64)
+        x100 = np.zeros(P, np.int64)
+        _check(lib().lxy_scaff_score_batch(self._h, _p(perms), P, _p(out), _p(x100)))
+        return (out, x100) if want_x100 else out
+
+    def scaff_score_batch_dev(self, perm_ptr, P, out_ptr, x100_ptr=None):
+        _check(lib().lxy_scaff_score_batch_dev(self._h, C.c_void_p(perm_ptr), P,
+                                               C.c_void_p(out_ptr),
+                                               C.c_void_p(x100_ptr) if x100_ptr else None))
+
+    def scaff_positions(self, perms):
+        perms = _c(perms, np.int32)
+        pos = np.zeros_like(perms)
+        _check(lib().lxy_scaff_positions(self._h, _p(perms), perms.shape[0], _p(pos)))
+        return pos
+
+    def scaff_link_distances(self, n_ids, a, b, perm):
+        a, b, perm = _c(a, np.uint32), _c(b, np.uint32), _c(perm, np.int32)
+        dist = np.zeros(len(a), np.int64)
+        _check(lib().lxy_scaff_link_distances(self._h, n_ids, len(a), _p(a), _p(b), _p(perm),
+                                              _p(dist)))
+        return dist
+
+    def links_get(self, id1, id2):
+        out = C.c_double()
+        rc = lib().lxy_links_get(self._h, id1, id2, C.byref(out))
+        return out.value, rc
+
+    # -- G-profile -------------------------------------------------------------------------
+    def set_links_g(self, lens, unit, a, xa, b, xb, w=None):
+        lens = _c(lens, np.uint32)
+        a, xa, b, xb = (_c(v, np.uint32) for v in (a, xa, b, xb))
+        w = _c(w, np.float64)
+        _check(lib().lxy_ctx_set_links_g(self._h, len(lens), len(a), _p(a), _p(xa), _p(b), _p(xb),
+                                         _p(w), _p(lens), unit))
+        self.n = len(lens)
+
+    def scaffg_score_batch(self, perms, oris=None, want_x100=False):
+        perms, oris = _c(perms, np.int32), _c(oris, np.uint8)
+        P = perms.shape[0]
+        out, x100 = np.zeros(P, np.float64), np.zeros(P, np.int64)
+        _check(lib().lxy_scaffg_score_batch(self._h, _p(perms), _p(oris), P, _p(out), _p(x100)))
+        return (out, x100) if want_x100 else out
+
+    def scaffg_layout(self, perms):
+        perms = _c(perms, np.int32)
+        start = np.zeros(perms.shape, np.uint64)
+        pos = np.zeros(perms.shape, np.int32)
+        _check(lib().lxy_scaffg_layout(self._h, _p(perms), perms.shape[0], _p(start), _p(pos)))
+        return start, pos
+
+    def scaffg_link_distances(self, a, xa, b, xb, perm, ori=None):
+        a, xa, b, xb = (_c(v, np.uint32) for v in (a, xa, b, xb))
+        perm, ori = _c(perm, np.int32), _c(ori, np.uint8)
+        dist = np.zeros(len(a), np.uint64)
+        _check(lib().lxy_scaffg_link_distances(self._h, len(a), _p(a), _p(xa), _p(b), _p(xb),
+                                               _p(perm), _p(ori), _p(dist)))
+        return dist
+
+    # -- phasing ---------------------------------------------------------------------------
+    def set_phase_links(self, n_ids, a, b, w):
+        a, b, w = _c(a, np.uint32), _c(b, np.uint32), _c(w, np.float64)
+        _check(lib().lxy_ctx_set_phase_links(self._h, n_ids, len(a), _p(a), _p(b), _p(w)))
+        self.phase_n = n_ids
+
+    def phase_score_batch(self, genes):
+        genes = _c(genes, np.uint8)
+        if genes.ndim != 2 or genes.shape[1] != self.phase_n:
+            raise ValueError(f"genes must be [P][{self.phase_n}]")
+        P = genes.shape[0]
+        oi, of = np.zeros(P, np.int64), np.zeros(P, np.float64)
+        _check(lib().lxy_phase_score_batch(self._h, _p(genes), P, _p(oi), _p(of)))
+        return oi, of
+
+    def phase_score_batch_dev(self, genes_ptr, P, out_i64_ptr, out_f64_ptr):
+        _check(lib().lxy_phase_score_batch_dev(self._h, C.c_void_p(genes_ptr), P,
+                                               C.c_void_p(out_i64_ptr) if out_i64_ptr else None,
+                                               C.c_void_p(out_f64_ptr) if out_f64_ptr else None))

@@ -1,0 +1,363 @@
+// api.cu — the extern "C" boundary of liblxyb200.so (declared in include/lxy_b200.h).
+#include <algorithm>
+#include <cstring>
+#include <numeric>
+#include <vector>
+
+#include "common.cuh"
+
+namespace lxy {
+
+static thread_local std::string g_err;
+
+void set_error(const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+}
+
+int pin_reserve(lxy_ctx* c, size_t bytes) {
+  if (bytes <= c->h_pin_cap) return LXY_OK;
+  if (c->h_pin) cudaFreeHost(c->h_pin);
+  c->h_pin = nullptr;
+  c->h_pin_cap = 0;
+  size_t want = bytes + (bytes >> 2) + 4096;
+  LXY_CUDA(cudaMallocHost(&c->h_pin, want));
+  c->h_pin_cap = want;
+  return LXY_OK;
+}
+
+struct Guard {  // context mutex + device selection for one entry point
+  std::lock_guard<std::mutex> lk;
+  bool ok;
+  explicit Guard(lxy_ctx* c) : lk(c->mu), ok(cudaSetDevice(c->cfg.device) == cudaSuccess) {
+    if (!ok) set_error("cudaSetDevice(%d) failed", c->cfg.device);
+  }
+};
+
+static float ev_ms(cudaEvent_t a, cudaEvent_t b) {
+  float ms = 0.f;
+  if (cudaEventElapsedTime(&ms, a, b) != cudaSuccess) { cudaGetLastError(); return 0.f; }
+  return ms;
+}
+
+}  // namespace lxy
+
+using namespace lxy;
+
+#define CHECK_CTX(c)                                                    \
+  if (!(c)) { set_error("null context"); return LXY_ERR_ARG; }          \
+  Guard guard_(c);                                                      \
+  if (!guard_.ok) return LXY_ERR_CUDA;
+
+static void collect_timing(lxy_ctx* c, bool host_copies) {
+  c->timing.ms_layout = ev_ms(c->ev[0], c->ev[1]);
+  c->timing.ms_score = ev_ms(c->ev[1], c->ev[2]);
+  c->timing.ms_finish = ev_ms(c->ev[2], c->ev[3]);
+  c->timing.ms_total = ev_ms(c->ev[0], c->ev[3]);
+  c->timing.ms_h2d = host_copies ? ev_ms(c->ev[4], c->ev[0]) : 0.f;
+  c->timing.ms_d2h = host_copies ? ev_ms(c->ev[3], c->ev[5]) : 0.f;
+}
+
+extern "C" {
+
+int lxy_abi_version(void) { return LXY_ABI_VERSION; }
+const char* lxy_last_error(void) { return g_err.c_str(); }
+
+int lxy_device_count(int32_t* count) {
+  if (!count) { set_error("null count"); return LXY_ERR_ARG; }
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) {
+    *count = 0;
+    set_error("cudaGetDeviceCount failed: %s", cudaGetErrorString(e));
+    cudaGetLastError();
+    return LXY_ERR_CUDA;
+  }
+  *count = n;
+  return LXY_OK;
+}
+
+int lxy_ctx_create(const lxy_cfg* cfg, lxy_ctx** out) {
+  if (!out) { set_error("null out"); return LXY_ERR_ARG; }
+  *out = nullptr;
+  lxy_cfg cf{};
+  if (cfg) cf = *cfg;
+  if (cf.acc_mode < LXY_ACC_AUTO || cf.acc_mode > LXY_ACC_INT) { set_error("bad acc_mode"); return LXY_ERR_ARG; }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev <= 0) {
+    set_error("no CUDA device (%s); liblxyb200 has no CPU fallback",
+              e != cudaSuccess ? cudaGetErrorString(e) : "count 0");
+    cudaGetLastError();
+    return LXY_ERR_CUDA;
+  }
+  if (cf.device < 0 || cf.device >= ndev) { set_error("device %d out of range [0,%d)", cf.device, ndev); return LXY_ERR_ARG; }
+  LXY_CUDA(cudaSetDevice(cf.device));
+  cudaDeviceProp prop;
+  LXY_CUDA(cudaGetDeviceProperties(&prop, cf.device));
+  if (prop.major < 10) {
+    set_error("device %d is sm_%d%d; liblxyb200 is built for sm_100a only", cf.device, prop.major, prop.minor);
+    return LXY_ERR_CUDA;
+  }
+  lxy_ctx* c = new (std::nothrow) lxy_ctx();
+  if (!c) { set_error("out of memory"); return LXY_ERR_NOMEM; }
+  c->cfg = cf;
+  c->sm_count = prop.multiProcessorCount;
+  c->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
+  if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    set_error("cudaStreamCreate failed");
+    delete c;
+    return LXY_ERR_CUDA;
+  }
+  for (auto& ev : c->ev) {
+    if (cudaEventCreate(&ev) != cudaSuccess) { set_error("cudaEventCreate failed"); lxy_ctx_destroy(c); return LXY_ERR_CUDA; }
+  }
+  *out = c;
+  return LXY_OK;
+}
+
+void lxy_ctx_destroy(lxy_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->cfg.device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  DevBuf* bufs[] = {&c->scaff.rec, &c->scaff.w, &c->scaff.tile_start, &c->scaff.len, &c->scaff.xa, &c->scaff.xb,
+                    &c->phase.rec, &c->phase.w, &c->d_perm, &c->d_ori, &c->d_out, &c->d_x100,
+                    &c->d_posA, &c->d_posB, &c->d_partial, &c->d_corr, &c->d_flag, &c->d_genes,
+                    &c->d_gbits, &c->d_tmp0, &c->d_tmp1, &c->d_tmp2, &c->d_tmp3, &c->d_start};
+  for (DevBuf* b : bufs) b->release();
+  if (c->h_pin) cudaFreeHost(c->h_pin);
+  for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+int lxy_ctx_get_timing(lxy_ctx* c, lxy_timing* out) {
+  if (!c || !out) { set_error("null argument"); return LXY_ERR_ARG; }
+  CHECK_CTX(c);
+  if (c->timing_pending) {
+    LXY_CUDA(cudaEventSynchronize(c->ev[c->timing_pending == 2 ? 5 : 3]));
+    collect_timing(c, c->timing_pending == 2);
+    c->timing_pending = 0;
+  }
+  *out = c->timing;
+  return LXY_OK;
+}
+
+int lxy_ctx_stream(lxy_ctx* c, void** s) {
+  if (!c || !s) { set_error("null argument"); return LXY_ERR_ARG; }
+  *s = (void*)c->stream;
+  return LXY_OK;
+}
+
+int lxy_ctx_sync(lxy_ctx* c) {
+  CHECK_CTX(c);
+  LXY_CUDA(cudaStreamSynchronize(c->stream));
+  return LXY_OK;
+}
+
+// ---- scaffolding --------------------------------------------------------------------------------
+int lxy_ctx_set_links(lxy_ctx* c, int32_t n_ids, int64_t n_links, const uint32_t* a,
+                      const uint32_t* b, const double* w) {
+  CHECK_CTX(c);
+  LinkInput in;
+  in.n = n_ids; in.L = n_links; in.a = a; in.b = b; in.w = w;
+  return build_scaff_links(c, in);
+}
+
+int lxy_ctx_set_links_dev(lxy_ctx* c, int32_t n_ids, int64_t n_links, const uint32_t* a_dev,
+                          const uint32_t* b_dev, const double* w_dev) {
+  CHECK_CTX(c);
+  LinkInput in;
+  in.n = n_ids; in.L = n_links; in.a = a_dev; in.b = b_dev; in.w = w_dev; in.on_device = true;
+  return build_scaff_links(c, in);
+}
+
+static int finish_flags(lxy_ctx* c, const char* what) {
+  int flag = 0;
+  LXY_CUDA(cudaMemcpyAsync(&flag, c->d_flag.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  LXY_CUDA(cudaStreamSynchronize(c->stream));
+  if (flag & 1) { set_error("%s: gene value outside [0, n)", what); return LXY_ERR_BAD_GENE; }
+  if (flag & 2) { set_error("%s: a population row is not a permutation", what); return LXY_ERR_BAD_GENE; }
+  if (flag & 4) { set_error("%s: placement offsets overflow the device format", what); return LXY_ERR_RANGE; }
+  return LXY_OK;
+}
+
+
+int lxy_scaff_score_batch_dev(lxy_ctx* c, const int32_t* perm_dev, int32_t P, double* out_dev,
+                              int64_t* x100_dev) {
+  CHECK_CTX(c);
+  if (P < 0 || (P > 0 && (!perm_dev || !out_dev))) { set_error("score_batch_dev: bad argument"); return LXY_ERR_ARG; }
+  if (P == 0) return LXY_OK;
+  LXY_TRY(scaff_score(c, perm_dev, nullptr, P, out_dev, x100_dev));
+  c->timing_pending = 1;
+  // With LXY_FLAG_NO_VALIDATE nothing has to come back to the host: the call is asynchronous on
+  // the context's stream (lxy_ctx_sync / lxy_ctx_get_timing wait for it).
+  if (c->cfg.flags & LXY_FLAG_NO_VALIDATE) return LXY_OK;
+  return finish_flags(c, "scaff score");
+}
+
+int lxy_scaff_score_batch(lxy_ctx* c, const int32_t* perm, int32_t P, double* out, int64_t* x100) {
+  CHECK_CTX(c);
+  if (P < 0 || (P > 0 && (!perm || !out))) { set_error("score_batch: bad argument"); return LXY_ERR_ARG; }
+  if (!c->scaff.ready) { set_error("score_batch: links not set"); return LXY_ERR_STATE; }
+  if (P == 0) return LXY_OK;
+  const size_t n = (size_t)c->scaff.n;
+  const size_t pbytes = sizeof(int32_t) * n * (size_t)P;
+  const size_t obytes = 16 * (size_t)P;
+  LXY_TRY(pin_reserve(c, pbytes + obytes));
+  LXY_TRY(c->d_perm.reserve(pbytes));
+  LXY_TRY(c->d_out.reserve(8 * (size_t)P));
+  LXY_TRY(c->d_x100.reserve(8 * (size_t)P));
+  // pinned staging: the copy below is then a true async DMA (and the caller's memory is not
+  // retained — cgo rule)
+  std::memcpy(c->h_pin, perm, pbytes);
+  LXY_CUDA(cudaEventRecord(c->ev[4], c->stream));
+  LXY_CUDA(cudaMemcpyAsync(c->d_perm.p, c->h_pin, pbytes, cudaMemcpyHostToDevice, c->stream));
+  LXY_TRY(scaff_score(c, c->d_perm.as<int32_t>(), nullptr, P, c->d_out.as<double>(), c->d_x100.as<int64_t>()));
+  char* hout = (char*)c->h_pin + pbytes;
+  LXY_CUDA(cudaMemcpyAsync(hout, c->d_out.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, c->stream));
+  LXY_CUDA(cudaMemcpyAsync(hout + 8 * (size_t)P, c->d_x100.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, c->stream));
+  LXY_CUDA(cudaEventRecord(c->ev[5], c->stream));
+  c->timing_pending = 2;
+  LXY_TRY(finish_flags(c, "scaff score"));
+  std::memcpy(out, hout, 8 * (size_t)P);
+  if (x100) std::memcpy(x100, hout + 8 * (size_t)P, 8 * (size_t)P);
+  return LXY_OK;
+}
+
+int lxy_scaff_positions(lxy_ctx* c, const int32_t* perm, int32_t P, int32_t* pos) {
+  CHECK_CTX(c);
+  if (!c->scaff.ready) { set_error("positions: links not set"); return LXY_ERR_STATE; }
+  if (P < 0 || (P > 0 && (!perm || !pos))) { set_error("positions: bad argument"); return LXY_ERR_ARG; }
+  if (P == 0) return LXY_OK;
+  const size_t bytes = sizeof(int32_t) * (size_t)c->scaff.n * (size_t)P;
+  LXY_TRY(c->d_perm.reserve(bytes));
+  LXY_TRY(c->d_tmp0.reserve(bytes));
+  LXY_CUDA(cudaMemcpyAsync(c->d_perm.p, perm, bytes, cudaMemcpyHostToDevice, c->stream));
+  LXY_CUDA(cudaMemsetAsync(c->d_tmp0.p, 0xFF, bytes, c->stream));
+  LXY_TRY(scaff_positions(c, c->d_perm.as<int32_t>(), P, c->scaff.n, c->d_tmp0.as<int32_t>()));
+  LXY_CUDA(cudaMemcpyAsync(pos, c->d_tmp0.p, bytes, cudaMemcpyDeviceToHost, c->stream));
+  return finish_flags(c, "positions");
+}
+
+int lxy_scaff_link_distances(lxy_ctx* c, int32_t n, int64_t L, const uint32_t* a, const uint32_t* b,
+                             const int32_t* perm, int64_t* dist) {
+  CHECK_CTX(c);
+  if (n <= 0 || L < 0 || !perm || (L > 0 && (!a || !b || !dist))) { set_error("link_distances: bad argument"); return LXY_ERR_ARG; }
+  LXY_TRY(c->d_perm.reserve(sizeof(int32_t) * (size_t)n));
+  LXY_TRY(c->d_tmp0.reserve(4 * (size_t)L + 16));
+  LXY_TRY(c->d_tmp1.reserve(4 * (size_t)L + 16));
+  LXY_TRY(c->d_tmp2.reserve(8 * (size_t)L + 16));
+  LXY_CUDA(cudaMemcpyAsync(c->d_perm.p, perm, sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+  if (L > 0) {
+    LXY_CUDA(cudaMemcpyAsync(c->d_tmp0.p, a, 4 * (size_t)L, cudaMemcpyHostToDevice, c->stream));
+    LXY_CUDA(cudaMemcpyAsync(c->d_tmp1.p, b, 4 * (size_t)L, cudaMemcpyHostToDevice, c->stream));
+  }
+  LXY_TRY(scaff_link_distances(c, n, L, c->d_tmp0.as<uint32_t>(), c->d_tmp1.as<uint32_t>(),
+                               c->d_perm.as<int32_t>(), c->d_tmp2.as<int64_t>()));
+  if (L > 0) LXY_CUDA(cudaMemcpyAsync(dist, c->d_tmp2.p, 8 * (size_t)L, cudaMemcpyDeviceToHost, c->stream));
+  return finish_flags(c, "link_distances");
+}
+
+int lxy_links_get(lxy_ctx* c, int32_t id1, int32_t id2, double* out) {
+  CHECK_CTX(c);
+  if (!out) { set_error("links_get: null out"); return LXY_ERR_ARG; }
+  return links_get(c, id1, id2, out);
+}
+
+// ---- G-profile ----------------------------------------------------------------------------------
+int lxy_ctx_set_links_g(lxy_ctx* c, int32_t n_ids, int64_t n_links, const uint32_t* a,
+                        const uint32_t* xa, const uint32_t* b, const uint32_t* xb, const double* w,
+                        const uint32_t* len, uint32_t unit) {
+  CHECK_CTX(c);
+  if (!len) { set_error("set_links_g: null len"); return LXY_ERR_ARG; }
+  LinkInput in;
+  in.n = n_ids; in.L = n_links; in.a = a; in.b = b; in.w = w; in.xa = xa; in.xb = xb;
+  in.len = len; in.unit = unit;
+  return build_scaff_links(c, in);
+}
+
+int lxy_scaffg_score_batch(lxy_ctx* c, const int32_t* perm, const uint8_t* ori, int32_t P,
+                           double* out, int64_t* x100) {
+  CHECK_CTX(c);
+  (void)perm; (void)ori; (void)P; (void)out; (void)x100;
+  set_error("scaffg_score_batch: not implemented in this build");
+  return LXY_ERR_STATE;
+}
+
+int lxy_scaffg_layout(lxy_ctx* c, const int32_t* perm, int32_t P, uint64_t* start_by_pos,
+                      int32_t* pos_by_contig) {
+  CHECK_CTX(c);
+  (void)perm; (void)P; (void)start_by_pos; (void)pos_by_contig;
+  set_error("scaffg_layout: not implemented in this build");
+  return LXY_ERR_STATE;
+}
+
+int lxy_scaffg_link_distances(lxy_ctx* c, int64_t n_links, const uint32_t* a, const uint32_t* xa,
+                              const uint32_t* b, const uint32_t* xb, const int32_t* perm,
+                              const uint8_t* ori, uint64_t* dist) {
+  CHECK_CTX(c);
+  (void)n_links; (void)a; (void)xa; (void)b; (void)xb; (void)perm; (void)ori; (void)dist;
+  set_error("scaffg_link_distances: not implemented in this build");
+  return LXY_ERR_STATE;
+}
+
+// ---- phasing ------------------------------------------------------------------------------------
+int lxy_ctx_set_phase_links(lxy_ctx* c, int32_t n_ids, int64_t n_links, const uint32_t* a,
+                            const uint32_t* b, const double* w) {
+  CHECK_CTX(c);
+  return build_phase_links(c, n_ids, n_links, a, b, w);
+}
+
+int lxy_phase_score_batch_dev(lxy_ctx* c, const uint8_t* genes_dev, int32_t P, int64_t* out_i64_dev,
+                              double* out_f64_dev) {
+  CHECK_CTX(c);
+  if (P < 0 || (P > 0 && (!genes_dev || (!out_i64_dev && !out_f64_dev)))) { set_error("phase_score_batch_dev: bad argument"); return LXY_ERR_ARG; }
+  if (P == 0) return LXY_OK;
+  LXY_TRY(phase_score(c, genes_dev, P, out_i64_dev, out_f64_dev));
+  c->timing_pending = 1;
+  if (c->cfg.flags & LXY_FLAG_NO_VALIDATE) return LXY_OK;
+  return finish_flags(c, "phase score");
+}
+
+int lxy_phase_score_batch(lxy_ctx* c, const uint8_t* genes, int32_t P, int64_t* out_i64,
+                          double* out_f64) {
+  CHECK_CTX(c);
+  if (P < 0 || (P > 0 && (!genes || (!out_i64 && !out_f64)))) { set_error("phase_score_batch: bad argument"); return LXY_ERR_ARG; }
+  if (!c->phase.ready) { set_error("phase_score_batch: links not set"); return LXY_ERR_STATE; }
+  if (P == 0) return LXY_OK;
+  const size_t gbytes = (size_t)c->phase.n * (size_t)P;
+  LXY_TRY(pin_reserve(c, gbytes + 16 * (size_t)P));
+  LXY_TRY(c->d_genes.reserve(gbytes));
+  LXY_TRY(c->d_out.reserve(8 * (size_t)P));
+  LXY_TRY(c->d_x100.reserve(8 * (size_t)P));
+  std::memcpy(c->h_pin, genes, gbytes);
+  LXY_CUDA(cudaEventRecord(c->ev[4], c->stream));
+  LXY_CUDA(cudaMemcpyAsync(c->d_genes.p, c->h_pin, gbytes, cudaMemcpyHostToDevice, c->stream));
+  LXY_TRY(phase_score(c, c->d_genes.as<uint8_t>(), P, c->d_x100.as<int64_t>(), c->d_out.as<double>()));
+  char* hout = (char*)c->h_pin + gbytes;
+  LXY_CUDA(cudaMemcpyAsync(hout, c->d_out.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, c->stream));
+  LXY_CUDA(cudaMemcpyAsync(hout + 8 * (size_t)P, c->d_x100.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, c->stream));
+  LXY_CUDA(cudaEventRecord(c->ev[5], c->stream));
+  c->timing_pending = 2;
+  LXY_TRY(finish_flags(c, "phase score"));
+  if (out_f64) std::memcpy(out_f64, hout, 8 * (size_t)P);
+  if (out_i64) std::memcpy(out_i64, hout + 8 * (size_t)P, 8 * (size_t)P);
+  return LXY_OK;
+}
+
+// ---- rank ---------------------------------------------------------------------------------------
+int lxy_rank(const double* s, int32_t P, int32_t* order) {
+  if (P < 0 || (P > 0 && (!s || !order))) { set_error("rank: bad argument"); return LXY_ERR_ARG; }
+  std::vector<int32_t> idx((size_t)P);
+  std::iota(idx.begin(), idx.end(), 0);
+  std::stable_sort(idx.begin(), idx.end(), [&](int32_t x, int32_t y) { return s[x] < s[y]; });
+  if (P) std::memcpy(order, idx.data(), sizeof(int32_t) * (size_t)P);
+  return LXY_OK;
+}
+
+}  // extern "C"

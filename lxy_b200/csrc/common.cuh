@@ -1,0 +1,133 @@
+// common.cuh — shared declarations of liblxyb200 (context, error plumbing, device formats).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <mutex>
+#include <string>
+
+#include "../../include/lxy_b200.h"
+
+namespace lxy {
+
+// ---- error plumbing ---------------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+#define LXY_CUDA(expr)                                                                     \
+  do {                                                                                     \
+    cudaError_t e_ = (expr);                                                               \
+    if (e_ != cudaSuccess) {                                                               \
+      ::lxy::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__,   \
+                       __LINE__);                                                          \
+      return LXY_ERR_CUDA;                                                                 \
+    }                                                                                      \
+  } while (0)
+#define LXY_TRY(expr)          \
+  do {                         \
+    int rc_ = (expr);          \
+    if (rc_ != LXY_OK) return rc_; \
+  } while (0)
+
+// ---- device formats ---------------------------------------------------------------------------
+// Contigs are grouped into blocks of kBlk consecutive ids; a link (a < b) lives in tile
+// (a / kBlk, b / kBlk) and is stored as the two block-local ids, one byte each.
+constexpr int kBlk = 256;
+constexpr int kBlkShift = 8;
+// The decay table T of scaff.go:252-302 times 100 (exact integers), indexed by d + kBias where
+// d = pos a - pos b in [-20, 20]; everything else clamps to kMiss.
+constexpr int kBias = 20;
+constexpr int kMiss = 41;
+constexpr int kLutLen = 48;  // u8 entries, padded
+
+enum WeightMode : int { W_UNIT = 0, W_INT32 = 1, W_F64 = 2 };
+
+// A growable device buffer (never shrinks; freed with the context).
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes);
+  void release();
+  template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+// Tile-sorted link store of the scaffolding scorers.
+struct ScaffLinks {
+  bool ready = false;
+  bool gprofile = false;
+  int32_t n = 0;            // ids
+  int64_t L = 0;            // records
+  int32_t nblk = 0;         // ceil(n / kBlk)
+  int64_t ntiles = 0;       // nblk * (nblk + 1) / 2
+  int wmode = W_UNIT;
+  bool wide_pos = false;    // positions need 32 bits (n > kMaxN16)
+  DevBuf rec;               // R: uint16 (a_loc << 8 | b_loc) sorted by (tile, a_loc, b_loc)
+                            // G: uint2 {a_loc << 8 | b_loc | ..., xa, xb} see scaffg
+  DevBuf w;                 // int32 or double per record (absent for W_UNIT)
+  DevBuf tile_start;        // int64[ntiles + 1]
+  // G-profile only
+  DevBuf len;               // uint32[n]
+  DevBuf xa, xb;            // uint32 in-contig offsets per record, same order as rec
+  uint32_t unit = 1;
+  uint64_t total_len = 0;
+};
+
+struct PhaseLinks {
+  bool ready = false;
+  int32_t n = 0;
+  int64_t L = 0;            // records kept (valid step only)
+  int64_t L_in = 0;
+  DevBuf rec;               // uint32 (lo << 5 | stepcode) sorted by lo, see phase_kernels.cu
+  DevBuf w;                 // int32 w * m
+  int64_t sum_w = 0;        // sum of w * m over kept records
+};
+
+}  // namespace lxy
+
+struct lxy_ctx {
+  lxy_cfg cfg{};
+  std::mutex mu;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[8]{};
+  int sm_count = 0;
+  int max_smem_optin = 0;
+  lxy_timing timing{};
+  int timing_pending = 0;     // 1: device-only call, 2: call with host copies (events not read yet)
+  lxy::ScaffLinks scaff;
+  lxy::PhaseLinks phase;
+  // per-call scratch
+  lxy::DevBuf d_perm, d_ori, d_out, d_x100, d_posA, d_posB, d_partial, d_corr, d_flag, d_genes,
+      d_gbits, d_tmp0, d_tmp1, d_tmp2, d_tmp3, d_start;
+  void* h_pin = nullptr;      // pinned staging for populations / scores
+  size_t h_pin_cap = 0;
+};
+
+namespace lxy {
+int pin_reserve(lxy_ctx* c, size_t bytes);
+
+// link_store.cu
+struct LinkInput {
+  int32_t n = 0;
+  int64_t L = 0;
+  const uint32_t *a = nullptr, *b = nullptr, *xa = nullptr, *xb = nullptr;
+  const double* w = nullptr;
+  const uint32_t* len = nullptr;  // host pointer; non-null selects the G-profile
+  uint32_t unit = 1;
+  bool on_device = false;         // a, b, w, xa, xb are device pointers
+};
+int build_scaff_links(lxy_ctx* c, const LinkInput& in);
+int build_phase_links(lxy_ctx* c, int32_t n, int64_t L, const uint32_t* a, const uint32_t* b,
+                      const double* w);
+int links_get(lxy_ctx* c, int32_t id1, int32_t id2, double* out);
+
+// scaff_kernels.cu
+int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int32_t P,
+                double* out_dev, int64_t* x100_dev);
+int scaff_positions(lxy_ctx* c, const int32_t* perm_dev, int32_t P, int32_t n, int32_t* pos_dev);
+int scaff_link_distances(lxy_ctx* c, int32_t n, int64_t L, const uint32_t* a_dev,
+                         const uint32_t* b_dev, const int32_t* perm_dev, int64_t* dist_dev);
+
+// phase_kernels.cu
+int phase_score(lxy_ctx* c, const uint8_t* genes_dev, int32_t P, int64_t* out_i64_dev,
+                double* out_f64_dev);
+}  // namespace lxy

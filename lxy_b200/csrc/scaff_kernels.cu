@@ -1,0 +1,585 @@
+// scaff_kernels.cu — scaffolding fitness on sm_100a (R-profile = /root/reference/src/lxy/scaff/
+// scaff.go:246-310 in its link-centric form, derivation in DESIGN.md §2).
+//
+// Pipeline of one lxy_scaff_score_batch call:
+//   k_scaff_layout   ordering -> placement tables (inverse permutation; offsets = ordering index)
+//   k_scaff_score    the link-streaming kernel: tables for kCand candidates x 2 contig blocks are
+//                    staged in shared memory by TMA bulk copies, 2-byte link records are streamed
+//                    with 128-bit loads, one lane owns CPL candidates, so every record byte is
+//                    reused by kCand candidates and the table gathers are bank-conflict free.
+//   k_scaff_head     the reference's `i-k > 0` quirk (scaff.go:256): pairs whose earlier member is
+//                    at ordering index 0 count once, everything else twice.  Instead of testing it
+//                    per evaluation the main kernel sums every record once and this kernel looks up
+//                    the six pairs (g[0], g[k]) in the sorted tiles.
+//   k_scaff_finish   fixed-order reduction of the per-CTA partials, fitness = -(2S - head)/100.
+#include "common.cuh"
+
+namespace lxy {
+namespace {
+
+constexpr int kThreads = 512;
+constexpr int kWarps = kThreads / 32;
+constexpr int kPacket = 8;  // records per 128-bit load
+
+__constant__ uint8_t c_lut100[kLutLen];  // T*100 by (d + kBias), 0 elsewhere
+__constant__ int c_steps[6] = {1, 2, 3, 5, 11, 20};
+__constant__ int c_w100[6] = {100, 50, 33, 20, 10, 5};
+
+const uint8_t h_lut100[kLutLen] = {
+    /* d=-20 */ 5, 0, 0, 0, 0, 0, 0, 0, 0, /* -11 */ 10, 0, 0, 0, 0, 0, /* -5 */ 20, 0,
+    /* -3 */ 33, /* -2 */ 50, /* -1 */ 100, /* 0 */ 0, 100, 50, 33, 0, 20, 0, 0, 0, 0, 0,
+    /* 11 */ 10, 0, 0, 0, 0, 0, 0, 0, 0, /* 20 */ 5, /* miss */ 0, 0, 0, 0, 0, 0, 0};
+
+// ---- PTX helpers (mbarrier + TMA bulk copy, sm_90+) ---------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_bulk_g2s(void* dst_smem, const void* src, uint32_t bytes,
+                                             uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+          "r"(smem_u32(dst_smem)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ uint4 ldg_stream_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+
+__host__ __device__ inline int64_t tile_row_start(int64_t I, int64_t nblk) {
+  return I * nblk - I * (I - 1) / 2;
+}
+
+// ---- k_scaff_layout -----------------------------------------------------------------------------
+// Tables are stored group-major: tab[g][contig][cand] with kCand = 32*CPL candidates per group, so
+// the rows of one contig block are one contiguous TMA bulk copy.  Narrow (u16) tables hold
+// posA = pos + 0x8000 + kBias and posB = pos: one 32-bit subtract then yields, in each half-word,
+// 0x8000 + kBias + (pos a - pos b) with no borrow between the halves (needs pos + kBias < 0x8000).
+template <bool WIDE>
+__global__ void k_scaff_layout(const int32_t* __restrict__ perm, int32_t P, int32_t Ppad, int32_t n,
+                               int32_t cand, void* __restrict__ tabA, void* __restrict__ tabB,
+                               int* __restrict__ flag) {
+  int64_t total = (int64_t)Ppad * n;
+  int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; idx < total; idx += stride) {
+    int32_t p = (int32_t)(idx / n), i = (int32_t)(idx - (int64_t)p * n);
+    int32_t cid = (p < P) ? perm[idx] : i;  // pad candidates = identity ordering (discarded)
+    if ((uint32_t)cid >= (uint32_t)n) {
+      atomicOr(flag, 1);
+      continue;
+    }
+    int32_t g = p / cand, pc = p - g * cand;
+    size_t at = ((size_t)g * n + cid) * cand + pc;
+    if (WIDE) {
+      ((uint32_t*)tabA)[at] = (uint32_t)i + kBias;
+      ((uint32_t*)tabB)[at] = (uint32_t)i;
+    } else {
+      ((uint16_t*)tabA)[at] = (uint16_t)(i + 0x8000 + kBias);
+      ((uint16_t*)tabB)[at] = (uint16_t)i;
+    }
+  }
+}
+
+// pos[perm[i]] == i for every i  <=>  the row is a permutation (given the range check above).
+template <bool WIDE>
+__global__ void k_scaff_check(const int32_t* __restrict__ perm, int32_t P, int32_t n, int32_t cand,
+                              const void* __restrict__ tabB, int* __restrict__ flag) {
+  int64_t total = (int64_t)P * n;
+  int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; idx < total; idx += stride) {
+    int32_t p = (int32_t)(idx / n), i = (int32_t)(idx - (int64_t)p * n);
+    int32_t cid = perm[idx];
+    if ((uint32_t)cid >= (uint32_t)n) continue;
+    int32_t g = p / cand, pc = p - g * cand;
+    size_t at = ((size_t)g * n + cid) * cand + pc;
+    uint32_t got = WIDE ? ((const uint32_t*)tabB)[at] : ((const uint16_t*)tabB)[at];
+    if (got != (uint32_t)i) atomicOr(flag, 2);
+  }
+}
+
+// ---- k_scaff_score ------------------------------------------------------------------------------
+struct ScoreParams {
+  const uint16_t* rec;        // sorted records
+  const void* w;              // sorted weights (int32 / double) or null
+  const int64_t* tile_start;  // [ntiles + 1]
+  const void* tabA;           // [groups][n][cand]
+  const void* tabB;
+  void* partial;              // [units][cand] int64 / double
+  int64_t L;
+  int32_t n, nblk;
+  int32_t groups, splits;     // units = groups * splits
+};
+
+template <int WM> struct Acc;          // per-lane accumulator type
+template <> struct Acc<W_UNIT> { typedef int64_t type; };
+template <> struct Acc<W_INT32> { typedef int64_t type; };
+template <> struct Acc<W_F64> { typedef double type; };
+
+// One record against CPL candidates of this lane.
+template <int CPL, bool WIDE, int WM>
+struct Eval {
+  // rowA/rowB: this lane's slice of the contig rows in shared memory
+  __device__ __forceinline__ static void run(const uint8_t* rowA, const uint8_t* rowB,
+                                             const uint8_t* lut, const double* lutd,
+                                             int32_t wi, double wd, int32_t (&acc32)[CPL],
+                                             int64_t (&acc64)[CPL], double (&accd)[CPL]) {
+    uint32_t idx[CPL];
+    if (WIDE) {
+      uint32_t A[CPL], B[CPL];
+      if (CPL == 4) {
+        uint4 a = *(const uint4*)rowA, b = *(const uint4*)rowB;
+        A[0] = a.x; A[1] = a.y; A[2 % CPL] = a.z; A[3 % CPL] = a.w;
+        B[0] = b.x; B[1] = b.y; B[2 % CPL] = b.z; B[3 % CPL] = b.w;
+      } else if (CPL == 2) {
+        uint2 a = *(const uint2*)rowA, b = *(const uint2*)rowB;
+        A[0] = a.x; A[1 % CPL] = a.y; B[0] = b.x; B[1 % CPL] = b.y;
+      } else {
+        A[0] = *(const uint32_t*)rowA; B[0] = *(const uint32_t*)rowB;
+      }
+#pragma unroll
+      for (int j = 0; j < CPL; ++j) idx[j] = min(A[j] - B[j], (uint32_t)kMiss);
+    } else {
+      uint32_t D[(CPL + 1) / 2];
+      if (CPL == 8) {
+        uint4 a = *(const uint4*)rowA, b = *(const uint4*)rowB;
+        D[0] = a.x - b.x; D[1 % ((CPL + 1) / 2)] = a.y - b.y;
+        D[2 % ((CPL + 1) / 2)] = a.z - b.z; D[3 % ((CPL + 1) / 2)] = a.w - b.w;
+      } else if (CPL == 4) {
+        uint2 a = *(const uint2*)rowA, b = *(const uint2*)rowB;
+        D[0] = a.x - b.x; D[1 % ((CPL + 1) / 2)] = a.y - b.y;
+      } else if (CPL == 2) {
+        D[0] = *(const uint32_t*)rowA - *(const uint32_t*)rowB;
+      } else {
+        D[0] = (uint32_t)(*(const uint16_t*)rowA) - (uint32_t)(*(const uint16_t*)rowB);
+      }
+#pragma unroll
+      for (int j = 0; j < CPL; ++j) {
+        uint32_t d = D[j / 2] ^ 0x80008000u;
+        uint32_t h = (j & 1) ? (d >> 16) : (d & 0xFFFFu);
+        idx[j] = min(h, (uint32_t)kMiss);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < CPL; ++j) {
+      if (WM == W_UNIT) acc32[j] += lut[idx[j]];
+      else if (WM == W_INT32) acc64[j] += (int64_t)((int32_t)lut[idx[j]]) * (int64_t)wi;
+      else accd[j] += lutd[idx[j]] * wd;
+    }
+  }
+};
+
+template <int CPL, bool WIDE, int WM>
+__global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
+  constexpr int CAND = 32 * CPL;
+  constexpr int ES = WIDE ? 4 : 2;
+  constexpr int ROWB = CAND * ES;           // bytes per contig row
+  constexpr int TABB = kBlk * ROWB;         // bytes per table
+  typedef typename Acc<WM>::type acc_t;
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + TABB;
+  __shared__ uint64_t bar;
+  __shared__ __align__(8) uint8_t s_lut[kLutLen];
+  __shared__ __align__(8) double s_lutd[kLutLen];
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid < kLutLen) {
+    s_lut[tid] = c_lut100[tid];
+    s_lutd[tid] = (double)c_lut100[tid];
+  }
+  if (tid == 0) {
+    mbar_init(&bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  uint32_t parity = 0;
+
+  const int units = prm.groups * prm.splits;
+  const int64_t npk = (prm.L + kPacket - 1) / kPacket;  // packets overall
+  for (int u = blockIdx.x; u < units; u += gridDim.x) {
+    const int g = u / prm.splits, s = u - g * prm.splits;
+    // even split of the packets, so every boundary is 16-byte aligned
+    const int64_t pk_lo = npk * s / prm.splits, pk_hi = npk * (s + 1) / prm.splits;
+    const int64_t lo = pk_lo * kPacket, hi = min(pk_hi * kPacket, prm.L);
+
+    int32_t acc32[CPL];
+    int64_t acc64[CPL];
+    double accd[CPL];
+#pragma unroll
+    for (int j = 0; j < CPL; ++j) { acc32[j] = 0; acc64[j] = 0; accd[j] = 0.0; }
+
+    if (lo < hi) {
+      // tile containing record `lo`: largest t with tile_start[t] <= lo
+      int64_t ntiles = (int64_t)prm.nblk * (prm.nblk + 1) / 2;
+      int64_t tl = 0, th = ntiles;  // invariant: tile_start[tl] <= lo < tile_start[th]
+      while (th - tl > 1) {
+        int64_t mid = (tl + th) >> 1;
+        if (prm.tile_start[mid] <= lo) tl = mid; else th = mid;
+      }
+      int64_t t = tl;
+      // (I, J) of tile t
+      int32_t I = 0;
+      {
+        int32_t a = 0, b = prm.nblk;  // tile_row_start(a) <= t < tile_row_start(b)
+        while (b - a > 1) {
+          int32_t m = (a + b) >> 1;
+          if (tile_row_start(m, prm.nblk) <= t) a = m; else b = m;
+        }
+        I = a;
+      }
+      int32_t J = I + (int32_t)(t - tile_row_start(I, prm.nblk));
+
+      int64_t cur = lo;
+      while (cur < hi) {
+        int64_t tend = prm.tile_start[t + 1];
+        if (tend <= cur) {  // empty tile (or finished): next
+          ++t; ++J;
+          if (J == prm.nblk) { ++I; J = I; }
+          continue;
+        }
+        const int64_t seg_end = min(hi, tend);
+        // ---- stage the two contig-block tables of tile (I, J) for group g ----
+        __syncthreads();  // everyone is done with the previous tables
+        if (tid == 0) {
+          const int rowsA = min(kBlk, prm.n - I * kBlk), rowsB = min(kBlk, prm.n - J * kBlk);
+          const uint8_t* gA = (const uint8_t*)prm.tabA + ((size_t)g * prm.n + (size_t)I * kBlk) * ROWB;
+          const uint8_t* gB = (const uint8_t*)prm.tabB + ((size_t)g * prm.n + (size_t)J * kBlk) * ROWB;
+          fence_proxy_async();
+          mbar_expect_tx(&bar, (uint32_t)(rowsA + rowsB) * ROWB);
+          tma_bulk_g2s(sA, gA, (uint32_t)rowsA * ROWB, &bar);
+          tma_bulk_g2s(sB, gB, (uint32_t)rowsB * ROWB, &bar);
+        }
+        mbar_wait(&bar, parity);
+        parity ^= 1;
+
+        // ---- stream the records of [cur, seg_end) ----
+        const uint8_t* laneA = sA + lane * (CPL * ES);
+        const uint8_t* laneB = sB + lane * (CPL * ES);
+        const int64_t p_first = cur / kPacket, p_last = (seg_end - 1) / kPacket;
+        for (int64_t pk = p_first + warp; pk <= p_last; pk += kWarps) {
+          const int64_t base = pk * kPacket;
+          uint4 v = ldg_stream_v4(prm.rec + base);
+          const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+          const bool full = (base >= cur) && (base + kPacket <= seg_end);
+          int32_t wi[kPacket];
+          double wd[kPacket];
+          if (WM == W_INT32) {
+            const int32_t* wp = (const int32_t*)prm.w + base;
+#pragma unroll
+            for (int k = 0; k < kPacket; ++k) wi[k] = (base + k < prm.L) ? wp[k] : 0;
+          } else if (WM == W_F64) {
+            const double* wp = (const double*)prm.w + base;
+#pragma unroll
+            for (int k = 0; k < kPacket; ++k) wd[k] = (base + k < prm.L) ? wp[k] : 0.0;
+          }
+#pragma unroll
+          for (int k = 0; k < kPacket; ++k) {
+            if (!full && (base + k < cur || base + k >= seg_end)) continue;
+            const uint32_t r = (words[k >> 1] >> (16 * (k & 1))) & 0xFFFFu;
+            const uint8_t* rowA = laneA + (r >> 8) * ROWB;
+            const uint8_t* rowB = laneB + (r & 0xFFu) * ROWB;
+            Eval<CPL, WIDE, WM>::run(rowA, rowB, s_lut, s_lutd, WM == W_INT32 ? wi[k] : 0,
+                                     WM == W_F64 ? wd[k] : 0.0, acc32, acc64, accd);
+          }
+          if (WM == W_UNIT && ((pk - p_first) / kWarps & 0xFFFF) == 0xFFFF) {
+#pragma unroll
+            for (int j = 0; j < CPL; ++j) { acc64[j] += acc32[j]; acc32[j] = 0; }
+          }
+        }
+        cur = seg_end;
+      }
+    }
+    if (WM == W_UNIT) {
+#pragma unroll
+      for (int j = 0; j < CPL; ++j) acc64[j] += acc32[j];
+    }
+    // ---- cross-warp reduction in the (now idle) table area, fixed order ----
+    __syncthreads();
+    acc_t* red = (acc_t*)smem;  // [kWarps][CAND]
+#pragma unroll
+    for (int j = 0; j < CPL; ++j) {
+      acc_t v;
+      if (WM == W_F64) v = (acc_t)accd[j]; else v = (acc_t)acc64[j];
+      red[warp * CAND + lane * CPL + j] = v;
+    }
+    __syncthreads();
+    if (tid < CAND) {
+      acc_t sum = 0;
+      for (int wq = 0; wq < kWarps; ++wq) sum += red[wq * CAND + tid];
+      ((acc_t*)prm.partial)[(size_t)u * CAND + tid] = sum;
+    }
+  }
+}
+
+// ---- k_scaff_head -------------------------------------------------------------------------------
+// head[p] = sum_k 100*T[k] * W(g[0], g[k]) with W the summed weight of the records of that pair:
+// exactly the evaluations the reference's `i-k > 0` test drops (scaff.go:256,264,...,299).
+// One warp per candidate, lane k < 6 looks one pair up by binary search in its sorted tile.
+template <int WM>
+__global__ void k_scaff_head(const int32_t* __restrict__ perm, int32_t P, int32_t n, int32_t nblk,
+                             const uint16_t* __restrict__ rec, const void* __restrict__ w,
+                             const int64_t* __restrict__ tile_start, void* __restrict__ head) {
+  typedef typename Acc<WM>::type acc_t;
+  const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (p >= P) return;
+  acc_t term = 0;
+  if (lane < 6 && c_steps[lane] < n) {
+    const uint32_t z = (uint32_t)perm[(size_t)p * n], y = (uint32_t)perm[(size_t)p * n + c_steps[lane]];
+    if (z < (uint32_t)n && y < (uint32_t)n && z != y) {
+      const uint32_t lo = min(z, y), hi = max(z, y);
+      const int64_t I = lo >> kBlkShift, J = hi >> kBlkShift;
+      const int64_t t = tile_row_start(I, nblk) + (J - I);
+      const uint32_t key = ((lo & (kBlk - 1)) << 8) | (hi & (kBlk - 1));
+      int64_t a = tile_start[t], b = tile_start[t + 1];
+      const int64_t end = b;
+      while (a < b) {  // lower bound of key
+        int64_t m = (a + b) >> 1;
+        if (rec[m] < key) a = m + 1; else b = m;
+      }
+      acc_t sum = 0;
+      for (int64_t i = a; i < end && rec[i] == key; ++i) {
+        if (WM == W_UNIT) sum += 1;
+        else if (WM == W_INT32) sum += ((const int32_t*)w)[i];
+        else sum += ((const double*)w)[i];
+      }
+      term = sum * (acc_t)c_w100[lane];
+    }
+  }
+  // fixed-order sum over the six lanes
+  acc_t tot = 0;
+  for (int k = 0; k < 6; ++k) {
+    acc_t v;
+    if (WM == W_F64) v = (acc_t)__shfl_sync(0xffffffffu, (double)term, k);
+    else v = (acc_t)__shfl_sync(0xffffffffu, (long long)term, k);
+    tot += v;
+  }
+  if (lane == 0) ((acc_t*)head)[p] = tot;
+}
+
+// ---- k_scaff_finish -----------------------------------------------------------------------------
+template <int WM>
+__global__ void k_scaff_finish(int32_t P, int32_t cand, int32_t splits,
+                               const void* __restrict__ partial, const void* __restrict__ head,
+                               double* __restrict__ out, int64_t* __restrict__ x100) {
+  typedef typename Acc<WM>::type acc_t;
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= P) return;
+  const int g = p / cand, pc = p - g * cand;
+  acc_t S = 0;
+  for (int s = 0; s < splits; ++s) S += ((const acc_t*)partial)[((size_t)g * splits + s) * cand + pc];
+  const acc_t tot = S + S - ((const acc_t*)head)[p];  // every pair twice, head-of-ordering pairs once
+  if (WM == W_F64) {
+    out[p] = -((double)tot / 100.0);
+    if (x100) x100[p] = INT64_MIN;
+  } else {
+    out[p] = -((double)(int64_t)tot / 100.0);
+    if (x100) x100[p] = (int64_t)tot;
+  }
+}
+
+// ---- integer checks -----------------------------------------------------------------------------
+__global__ void k_positions(const int32_t* __restrict__ perm, int32_t P, int32_t n,
+                            int32_t* __restrict__ pos, int* __restrict__ flag) {
+  int64_t total = (int64_t)P * n;
+  int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; idx < total; idx += stride) {
+    int32_t p = (int32_t)(idx / n), i = (int32_t)(idx - (int64_t)p * n);
+    int32_t cid = perm[idx];
+    if ((uint32_t)cid >= (uint32_t)n) { atomicOr(flag, 1); continue; }
+    pos[(size_t)p * n + cid] = i;
+  }
+}
+__global__ void k_link_dist(int64_t L, const uint32_t* __restrict__ a, const uint32_t* __restrict__ b,
+                            const int32_t* __restrict__ pos, int32_t n, int64_t* __restrict__ dist,
+                            int* __restrict__ flag) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < L; i += stride) {
+    uint32_t x = a[i], y = b[i];
+    if (x >= (uint32_t)n || y >= (uint32_t)n) { atomicOr(flag, 1); continue; }
+    int64_t d = (int64_t)pos[x] - (int64_t)pos[y];
+    dist[i] = d < 0 ? -d : d;
+  }
+}
+
+inline int grid_for(int64_t n, int threads, int sm) {
+  int64_t g = (n + threads - 1) / threads;
+  int64_t cap = (int64_t)sm * 16;
+  return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+template <int CPL, bool WIDE, int WM>
+int launch_score(lxy_ctx* c, const ScoreParams& prm, int grid) {
+  constexpr int smem = 2 * kBlk * 32 * CPL * (WIDE ? 4 : 2);
+  static bool configured[64] = {};
+  if (!configured[c->cfg.device & 63]) {
+    LXY_CUDA(cudaFuncSetAttribute(k_scaff_score<CPL, WIDE, WM>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured[c->cfg.device & 63] = true;
+  }
+  k_scaff_score<CPL, WIDE, WM><<<grid, kThreads, smem, c->stream>>>(prm);
+  LXY_CUDA(cudaGetLastError());
+  return LXY_OK;
+}
+
+template <bool WIDE, int WM>
+int launch_score_cpl(lxy_ctx* c, int cpl, const ScoreParams& prm, int grid) {
+  switch (cpl) {
+    case 1: return launch_score<1, WIDE, WM>(c, prm, grid);
+    case 2: return launch_score<2, WIDE, WM>(c, prm, grid);
+    default: return WIDE ? launch_score<2, WIDE, WM>(c, prm, grid)
+                         : launch_score<4, WIDE, WM>(c, prm, grid);
+  }
+}
+
+}  // namespace
+
+static bool g_lut_loaded[64] = {};
+
+int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int32_t P,
+                double* out_dev, int64_t* x100_dev) {
+  ScaffLinks& S = c->scaff;
+  if (!S.ready) { set_error("scaff score: links not set"); return LXY_ERR_STATE; }
+  if (S.gprofile) { set_error("scaff score: G-profile context"); return LXY_ERR_STATE; }
+  (void)ori_dev;
+  if (P <= 0) return LXY_OK;
+  cudaStream_t st = c->stream;
+  const int n = S.n;
+  const bool wide = (n + kBias >= 0x8000);
+  // candidates per lane: 4 (narrow) / 2 (wide) fill 128 KB of tables; small populations use less
+  int cpl = wide ? 2 : 4;
+  while (cpl > 1 && P <= 32 * (cpl / 2)) cpl /= 2;
+  const int cand = 32 * cpl;
+  const int groups = (P + cand - 1) / cand;
+  const int Ppad = groups * cand;
+  const size_t es = wide ? 4 : 2;
+  LXY_TRY(c->d_posA.reserve((size_t)Ppad * n * es));
+  LXY_TRY(c->d_posB.reserve((size_t)Ppad * n * es));
+  LXY_TRY(c->d_flag.reserve(64));
+  LXY_TRY(c->d_corr.reserve(8 * (size_t)P));
+  if (!g_lut_loaded[c->cfg.device & 63]) {
+    LXY_CUDA(cudaMemcpyToSymbolAsync(c_lut100, h_lut100, kLutLen, 0, cudaMemcpyHostToDevice, st));
+    g_lut_loaded[c->cfg.device & 63] = true;
+  }
+  LXY_CUDA(cudaMemsetAsync(c->d_flag.p, 0, 64, st));
+  int launches = 0;
+
+  LXY_CUDA(cudaEventRecord(c->ev[0], st));
+  const int lg = grid_for((int64_t)Ppad * n, 256, c->sm_count);
+  if (wide) k_scaff_layout<true><<<lg, 256, 0, st>>>(perm_dev, P, Ppad, n, cand, c->d_posA.p, c->d_posB.p, c->d_flag.as<int>());
+  else k_scaff_layout<false><<<lg, 256, 0, st>>>(perm_dev, P, Ppad, n, cand, c->d_posA.p, c->d_posB.p, c->d_flag.as<int>());
+  ++launches;
+  if (!(c->cfg.flags & LXY_FLAG_NO_VALIDATE)) {
+    if (wide) k_scaff_check<true><<<lg, 256, 0, st>>>(perm_dev, P, n, cand, c->d_posB.p, c->d_flag.as<int>());
+    else k_scaff_check<false><<<lg, 256, 0, st>>>(perm_dev, P, n, cand, c->d_posB.p, c->d_flag.as<int>());
+    ++launches;
+  }
+  LXY_CUDA(cudaGetLastError());
+  LXY_CUDA(cudaEventRecord(c->ev[1], st));
+
+  // work units: groups x splits, about two waves of one CTA per SM
+  const int64_t npk = (S.L + kPacket - 1) / kPacket;
+  int splits = (2 * c->sm_count + groups - 1) / groups;
+  if (splits < 1) splits = 1;
+  const int64_t min_pk = 64;  // do not split below 512 records per unit
+  if ((int64_t)splits * min_pk > npk) splits = (int)(npk / min_pk > 0 ? npk / min_pk : 1);
+  const int units = groups * splits;
+  const int grid = units < c->sm_count ? units : c->sm_count;
+  LXY_TRY(c->d_partial.reserve(8 * (size_t)units * cand));
+  ScoreParams prm;
+  prm.rec = S.rec.as<uint16_t>();
+  prm.w = S.w.p;
+  prm.tile_start = S.tile_start.as<int64_t>();
+  prm.tabA = c->d_posA.p;
+  prm.tabB = c->d_posB.p;
+  prm.partial = c->d_partial.p;
+  prm.L = S.L;
+  prm.n = n;
+  prm.nblk = S.nblk;
+  prm.groups = groups;
+  prm.splits = splits;
+  int rc;
+  if (wide) {
+    rc = S.wmode == W_UNIT ? launch_score_cpl<true, W_UNIT>(c, cpl, prm, grid)
+       : S.wmode == W_INT32 ? launch_score_cpl<true, W_INT32>(c, cpl, prm, grid)
+                            : launch_score_cpl<true, W_F64>(c, cpl, prm, grid);
+  } else {
+    rc = S.wmode == W_UNIT ? launch_score_cpl<false, W_UNIT>(c, cpl, prm, grid)
+       : S.wmode == W_INT32 ? launch_score_cpl<false, W_INT32>(c, cpl, prm, grid)
+                            : launch_score_cpl<false, W_F64>(c, cpl, prm, grid);
+  }
+  LXY_TRY(rc);
+  ++launches;
+  LXY_CUDA(cudaEventRecord(c->ev[2], st));
+
+  const int hb = (P * 32 + 255) / 256;
+  if (S.wmode == W_UNIT) {
+    k_scaff_head<W_UNIT><<<hb, 256, 0, st>>>(perm_dev, P, n, S.nblk, prm.rec, prm.w, prm.tile_start, c->d_corr.p);
+    k_scaff_finish<W_UNIT><<<(P + 127) / 128, 128, 0, st>>>(P, cand, splits, c->d_partial.p, c->d_corr.p, out_dev, x100_dev);
+  } else if (S.wmode == W_INT32) {
+    k_scaff_head<W_INT32><<<hb, 256, 0, st>>>(perm_dev, P, n, S.nblk, prm.rec, prm.w, prm.tile_start, c->d_corr.p);
+    k_scaff_finish<W_INT32><<<(P + 127) / 128, 128, 0, st>>>(P, cand, splits, c->d_partial.p, c->d_corr.p, out_dev, x100_dev);
+  } else {
+    k_scaff_head<W_F64><<<hb, 256, 0, st>>>(perm_dev, P, n, S.nblk, prm.rec, prm.w, prm.tile_start, c->d_corr.p);
+    k_scaff_finish<W_F64><<<(P + 127) / 128, 128, 0, st>>>(P, cand, splits, c->d_partial.p, c->d_corr.p, out_dev, x100_dev);
+  }
+  launches += 2;
+  LXY_CUDA(cudaGetLastError());
+  LXY_CUDA(cudaEventRecord(c->ev[3], st));
+
+  c->timing.launches = launches;
+  c->timing.grid = grid;
+  c->timing.link_bytes = (int64_t)groups * S.L * (2 + (S.wmode == W_INT32 ? 4 : S.wmode == W_F64 ? 8 : 0));
+  c->timing.table_bytes = 0;
+  return LXY_OK;
+}
+
+int scaff_positions(lxy_ctx* c, const int32_t* perm_dev, int32_t P, int32_t n, int32_t* pos_dev) {
+  LXY_TRY(c->d_flag.reserve(64));
+  LXY_CUDA(cudaMemsetAsync(c->d_flag.p, 0, 64, c->stream));
+  k_positions<<<grid_for((int64_t)P * n, 256, c->sm_count), 256, 0, c->stream>>>(perm_dev, P, n, pos_dev, c->d_flag.as<int>());
+  LXY_CUDA(cudaGetLastError());
+  return LXY_OK;
+}
+
+int scaff_link_distances(lxy_ctx* c, int32_t n, int64_t L, const uint32_t* a_dev,
+                         const uint32_t* b_dev, const int32_t* perm_dev, int64_t* dist_dev) {
+  LXY_TRY(c->d_start.reserve(sizeof(int32_t) * (size_t)n));
+  LXY_TRY(scaff_positions(c, perm_dev, 1, n, c->d_start.as<int32_t>()));
+  if (L > 0) {
+    k_link_dist<<<grid_for(L, 256, c->sm_count), 256, 0, c->stream>>>(L, a_dev, b_dev, c->d_start.as<int32_t>(), n, dist_dev, c->d_flag.as<int>());
+    LXY_CUDA(cudaGetLastError());
+  }
+  return LXY_OK;
+}
+
+}  // namespace lxy

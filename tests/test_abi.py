@@ -1,0 +1,62 @@
+"""CPU-side checks of the C-ABI boundary: the library builds, loads, exports every symbol that
+include/lxy_b200.h declares, and refuses to work without a CUDA device (no CPU fallback)."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+import lxy_b200._native as N
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def native():
+    if not os.path.exists(N.LIB_PATH):
+        N.build()
+    return N.lib()
+
+
+def _header_functions():
+    text = open(os.path.join(ROOT, "include", "lxy_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(lxy_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_and_binding_agree():
+    assert _header_functions() == sorted(N.SYMBOLS)
+
+
+def test_library_exports_every_declared_symbol(native):
+    for name in _header_functions():
+        assert hasattr(native, name), name
+
+
+def test_abi_version(native):
+    assert native.lxy_abi_version() == 1
+
+
+def test_rank_is_stable_ascending(native):
+    s = np.array([3.0, -1.0, 3.0, -7.5, -1.0, 0.0])
+    assert N.rank(s).tolist() == [3, 1, 4, 5, 0, 2]
+    assert N.rank(np.zeros(0)).tolist() == []
+
+
+def test_no_cpu_fallback_without_a_device(native):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(N.LxyError) as e:
+        N.Context(0)
+    assert e.value.status == -2          # LXY_ERR_CUDA
+    assert "no CPU fallback" in str(e.value)
+
+
+def test_product_package_never_touches_the_oracle():
+    pkg = os.path.join(ROOT, "lxy_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "lxy_oracle" not in src and "_oracle" not in src, os.path.join(dirpath, f)
