@@ -21,14 +21,14 @@ constexpr int kThreads = 512;
 constexpr int kWarps = kThreads / 32;
 constexpr int kPacket = 8;  // records per 128-bit load
 
-__constant__ uint8_t c_lut100[kLutLen];  // T*100 by (d + kBias), 0 elsewhere
+__constant__ uint8_t c_lut100[kLutLen];  // T*100 by v = d + kBias + 1; 0 at the far entries 0, 42
 __constant__ int c_steps[6] = {1, 2, 3, 5, 11, 20};
 __constant__ int c_w100[6] = {100, 50, 33, 20, 10, 5};
 
 const uint8_t h_lut100[kLutLen] = {
-    /* d=-20 */ 5, 0, 0, 0, 0, 0, 0, 0, 0, /* -11 */ 10, 0, 0, 0, 0, 0, /* -5 */ 20, 0,
+    /* far */ 0, /* d=-20 */ 5, 0, 0, 0, 0, 0, 0, 0, 0, /* -11 */ 10, 0, 0, 0, 0, 0, /* -5 */ 20, 0,
     /* -3 */ 33, /* -2 */ 50, /* -1 */ 100, /* 0 */ 0, 100, 50, 33, 0, 20, 0, 0, 0, 0, 0,
-    /* 11 */ 10, 0, 0, 0, 0, 0, 0, 0, 0, /* 20 */ 5, /* miss */ 0, 0, 0, 0, 0, 0, 0};
+    /* 11 */ 10, 0, 0, 0, 0, 0, 0, 0, 0, /* 20 */ 5, /* far */ 0, 0, 0, 0, 0, 0};
 
 // ---- PTX helpers (mbarrier + TMA bulk copy, sm_90+) ---------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -78,9 +78,9 @@ __host__ __device__ inline int64_t tile_row_start(int64_t I, int64_t nblk) {
 
 // ---- k_scaff_layout -----------------------------------------------------------------------------
 // Tables are stored group-major: tab[g][contig][cand] with kCand = 32*CPL candidates per group, so
-// the rows of one contig block are one contiguous TMA bulk copy.  Narrow (u16) tables hold
-// posA = pos + 0x8000 + kBias and posB = pos: one 32-bit subtract then yields, in each half-word,
-// 0x8000 + kBias + (pos a - pos b) with no borrow between the halves (needs pos + kBias < 0x8000).
+// the rows of one contig block are one contiguous TMA bulk copy.  tabA holds pos + kBias + 1 and
+// tabB holds -pos (16-bit two's complement when n + kBias < 2^15, else 32-bit): the kernel's
+// VIADDMNMX then yields clamp(pos a - pos b + kBias + 1, 0, kMiss + 1) per candidate.
 template <bool WIDE>
 __global__ void k_scaff_layout(const int32_t* __restrict__ perm, int32_t P, int32_t Ppad, int32_t n,
                                int32_t cand, void* __restrict__ tabA, void* __restrict__ tabB,
@@ -98,11 +98,11 @@ __global__ void k_scaff_layout(const int32_t* __restrict__ perm, int32_t P, int3
     int32_t g = p / cand, pc = p - g * cand;
     size_t at = ((size_t)g * n + cid) * cand + pc;
     if (WIDE) {
-      ((uint32_t*)tabA)[at] = (uint32_t)i + kBias;
-      ((uint32_t*)tabB)[at] = (uint32_t)i;
+      ((uint32_t*)tabA)[at] = (uint32_t)(i + kBias + 1);
+      ((uint32_t*)tabB)[at] = (uint32_t)(-i);
     } else {
-      ((uint16_t*)tabA)[at] = (uint16_t)(i + 0x8000 + kBias);
-      ((uint16_t*)tabB)[at] = (uint16_t)i;
+      ((uint16_t*)tabA)[at] = (uint16_t)(i + kBias + 1);
+      ((uint16_t*)tabB)[at] = (uint16_t)(-i);
     }
   }
 }
@@ -120,8 +120,9 @@ __global__ void k_scaff_check(const int32_t* __restrict__ perm, int32_t P, int32
     if ((uint32_t)cid >= (uint32_t)n) continue;
     int32_t g = p / cand, pc = p - g * cand;
     size_t at = ((size_t)g * n + cid) * cand + pc;
-    uint32_t got = WIDE ? ((const uint32_t*)tabB)[at] : ((const uint16_t*)tabB)[at];
-    if (got != (uint32_t)i) atomicOr(flag, 2);
+    const uint32_t got = WIDE ? ((const uint32_t*)tabB)[at] : ((const uint16_t*)tabB)[at];
+    const uint32_t want = WIDE ? (uint32_t)(-i) : (uint32_t)(uint16_t)(-i);
+    if (got != want) atomicOr(flag, 2);
   }
 }
 
@@ -143,58 +144,119 @@ template <> struct Acc<W_UNIT> { typedef int64_t type; };
 template <> struct Acc<W_INT32> { typedef int64_t type; };
 template <> struct Acc<W_F64> { typedef double type; };
 
-// One record against CPL candidates of this lane.
-template <int CPL, bool WIDE, int WM>
-struct Eval {
-  // rowA/rowB: this lane's slice of the contig rows in shared memory
-  __device__ __forceinline__ static void run(const uint8_t* rowA, const uint8_t* rowB,
-                                             const uint8_t* lut, const double* lutd,
-                                             int32_t wi, double wd, int32_t (&acc32)[CPL],
-                                             int64_t (&acc64)[CPL], double (&accd)[CPL]) {
-    uint32_t idx[CPL];
-    if (WIDE) {
-      uint32_t A[CPL], B[CPL];
-      if (CPL == 4) {
-        uint4 a = *(const uint4*)rowA, b = *(const uint4*)rowB;
-        A[0] = a.x; A[1] = a.y; A[2 % CPL] = a.z; A[3 % CPL] = a.w;
-        B[0] = b.x; B[1] = b.y; B[2 % CPL] = b.z; B[3 % CPL] = b.w;
-      } else if (CPL == 2) {
-        uint2 a = *(const uint2*)rowA, b = *(const uint2*)rowB;
-        A[0] = a.x; A[1 % CPL] = a.y; B[0] = b.x; B[1 % CPL] = b.y;
-      } else {
-        A[0] = *(const uint32_t*)rowA; B[0] = *(const uint32_t*)rowB;
-      }
+// Per-lane state of the streaming loop: CPL candidates, their running sums.
+template <int CPL, int WM>
+struct Lane {
+  int32_t a32[CPL];   // W_UNIT: 100*T summed per record (flushed into a64 before it can overflow)
+  int64_t a64[CPL];
+  double ad[CPL];
+  __device__ __forceinline__ void clear() {
 #pragma unroll
-      for (int j = 0; j < CPL; ++j) idx[j] = min(A[j] - B[j], (uint32_t)kMiss);
-    } else {
-      uint32_t D[(CPL + 1) / 2];
-      if (CPL == 8) {
-        uint4 a = *(const uint4*)rowA, b = *(const uint4*)rowB;
-        D[0] = a.x - b.x; D[1 % ((CPL + 1) / 2)] = a.y - b.y;
-        D[2 % ((CPL + 1) / 2)] = a.z - b.z; D[3 % ((CPL + 1) / 2)] = a.w - b.w;
-      } else if (CPL == 4) {
-        uint2 a = *(const uint2*)rowA, b = *(const uint2*)rowB;
-        D[0] = a.x - b.x; D[1 % ((CPL + 1) / 2)] = a.y - b.y;
-      } else if (CPL == 2) {
-        D[0] = *(const uint32_t*)rowA - *(const uint32_t*)rowB;
-      } else {
-        D[0] = (uint32_t)(*(const uint16_t*)rowA) - (uint32_t)(*(const uint16_t*)rowB);
-      }
+    for (int j = 0; j < CPL; ++j) { a32[j] = 0; a64[j] = 0; ad[j] = 0.0; }
+  }
+  __device__ __forceinline__ void flush() {
+    if (WM == W_UNIT) {
 #pragma unroll
-      for (int j = 0; j < CPL; ++j) {
-        uint32_t d = D[j / 2] ^ 0x80008000u;
-        uint32_t h = (j & 1) ? (d >> 16) : (d & 0xFFFFu);
-        idx[j] = min(h, (uint32_t)kMiss);
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < CPL; ++j) {
-      if (WM == W_UNIT) acc32[j] += lut[idx[j]];
-      else if (WM == W_INT32) acc64[j] += (int64_t)((int32_t)lut[idx[j]]) * (int64_t)wi;
-      else accd[j] += lutd[idx[j]] * wd;
+      for (int j = 0; j < CPL; ++j) { a64[j] += a32[j]; a32[j] = 0; }
     }
   }
 };
+
+// One record against the CPL candidates of this lane.
+//   narrow tables (u16): A = pos + kBias + 1, B = -pos; VIADDMNMX.S16x2.RELU gives, per half-word,
+//   v = clamp(pos a - pos b + kBias + 1, 0, kMiss + 1): one instruction for two candidates.
+//   wide tables (u32): the same with VIADDMNMX.RELU on full words.
+// v indexes the decay table: v in [1, 41] <=> |d| <= 20; 0 and 42 are the two "far" entries.
+template <int CPL, bool WIDE, int WM>
+__device__ __forceinline__ void eval_record(const uint8_t* rowA, const uint8_t* rowB,
+                                            const uint8_t* lut, const double* lutd, int32_t wi,
+                                            double wd, Lane<CPL, WM>& L) {
+  constexpr uint32_t kHi = kMiss + 1;  // 42
+  uint32_t idx[CPL];
+  if (WIDE) {
+    uint32_t A[4], B[4];
+    if (CPL == 4) {
+      const uint4 a = *(const uint4*)rowA, b = *(const uint4*)rowB;
+      A[0] = a.x; A[1] = a.y; A[2] = a.z; A[3] = a.w; B[0] = b.x; B[1] = b.y; B[2] = b.z; B[3] = b.w;
+    } else if (CPL == 2) {
+      const uint2 a = *(const uint2*)rowA, b = *(const uint2*)rowB;
+      A[0] = a.x; A[1] = a.y; B[0] = b.x; B[1] = b.y;
+    } else {
+      A[0] = *(const uint32_t*)rowA; B[0] = *(const uint32_t*)rowB;
+    }
+#pragma unroll
+    for (int j = 0; j < CPL; ++j) idx[j] = (uint32_t)__viaddmin_s32_relu((int)A[j], (int)B[j], (int)kHi);
+  } else {
+    uint32_t A[4], B[4];
+    if (CPL == 8) {
+      const uint4 a = *(const uint4*)rowA, b = *(const uint4*)rowB;
+      A[0] = a.x; A[1] = a.y; A[2] = a.z; A[3] = a.w; B[0] = b.x; B[1] = b.y; B[2] = b.z; B[3] = b.w;
+    } else if (CPL == 4) {
+      const uint2 a = *(const uint2*)rowA, b = *(const uint2*)rowB;
+      A[0] = a.x; A[1] = a.y; B[0] = b.x; B[1] = b.y;
+    } else if (CPL == 2) {
+      A[0] = *(const uint32_t*)rowA; B[0] = *(const uint32_t*)rowB;
+    } else {
+      A[0] = *(const uint16_t*)rowA; B[0] = *(const uint16_t*)rowB;
+    }
+#pragma unroll
+    for (int q = 0; q < (CPL + 1) / 2; ++q) {
+      const uint32_t m = __viaddmin_s16x2_relu(A[q], B[q], kHi | (kHi << 16));
+      idx[2 * q] = m & 0xFFFFu;
+      if (2 * q + 1 < CPL) idx[2 * q + 1] = m >> 16;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < CPL; ++j) {
+    if (WM == W_UNIT) L.a32[j] += lut[idx[j]];
+    else if (WM == W_INT32) L.a64[j] += (int64_t)((int32_t)lut[idx[j]]) * (int64_t)wi;
+    else L.ad[j] += lutd[idx[j]] * wd;
+  }
+}
+
+// Records k in [k0, k1) of one 8-record packet (k0 = 0, k1 = 8 compiles to straight-line code).
+template <int CPL, bool WIDE, int WM>
+__device__ __forceinline__ void eval_packet(const uint4 v, const uint8_t* laneA, const uint8_t* laneB,
+                                            uint32_t lane_off, const uint8_t* lut, const double* lutd,
+                                            const int32_t* wi, const double* wd, int k0, int k1,
+                                            Lane<CPL, WM>& L) {
+  constexpr int ROWB = 32 * CPL * (WIDE ? 4 : 2);
+  const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int k = 0; k < kPacket; ++k) {
+    if (k < k0 || k >= k1) continue;
+    const uint32_t wv = words[k >> 1];
+    const uint8_t *rowA, *rowB;
+    if (ROWB == 256) {
+      // one PRMT builds (a_loc << 8 | lane_off): lane_off < 256 occupies byte 0 only
+      const uint32_t oa = __byte_perm(wv, lane_off, (k & 1) ? 0x7634 : 0x7614);
+      const uint32_t ob = __byte_perm(wv, lane_off, (k & 1) ? 0x7624 : 0x7604);
+      rowA = laneA - lane_off + oa;
+      rowB = laneB - lane_off + ob;
+    } else {
+      const uint32_t r = (k & 1) ? (wv >> 16) : (wv & 0xFFFFu);
+      rowA = laneA + (r >> 8) * ROWB;
+      rowB = laneB + (r & 0xFFu) * ROWB;
+    }
+    eval_record<CPL, WIDE, WM>(rowA, rowB, lut, lutd, WM == W_INT32 ? wi[k] : 0,
+                               WM == W_F64 ? wd[k] : 0.0, L);
+  }
+}
+
+template <int WM>
+__device__ __forceinline__ void load_weights(const void* w, int64_t base, int32_t (&wi)[kPacket],
+                                             double (&wd)[kPacket]) {
+  // the weight arrays are padded past L with zeros (link_store.cu), so whole packets are readable
+  if (WM == W_INT32) {
+    const uint4* p = reinterpret_cast<const uint4*>((const int32_t*)w + base);
+    const uint4 x = __ldg(p), y = __ldg(p + 1);
+    wi[0] = x.x; wi[1] = x.y; wi[2] = x.z; wi[3] = x.w; wi[4] = y.x; wi[5] = y.y; wi[6] = y.z; wi[7] = y.w;
+  } else if (WM == W_F64) {
+    const double2* p = reinterpret_cast<const double2*>((const double*)w + base);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { const double2 d = __ldg(p + q); wd[2 * q] = d.x; wd[2 * q + 1] = d.y; }
+  }
+}
 
 template <int CPL, bool WIDE, int WM>
 __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
@@ -203,12 +265,13 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
   constexpr int ROWB = CAND * ES;           // bytes per contig row
   constexpr int TABB = kBlk * ROWB;         // bytes per table
   typedef typename Acc<WM>::type acc_t;
+  // dynamic shared memory: table A | table B | decay tables (u8 and f64) | mbarrier
   extern __shared__ __align__(128) uint8_t smem[];
   uint8_t* sA = smem;
   uint8_t* sB = smem + TABB;
-  __shared__ uint64_t bar;
-  __shared__ __align__(8) uint8_t s_lut[kLutLen];
-  __shared__ __align__(8) double s_lutd[kLutLen];
+  uint8_t* s_lut = smem + 2 * TABB;                       // kLutLen bytes
+  double* s_lutd = (double*)(smem + 2 * TABB + 64);       // kLutLen doubles
+  uint64_t* bar = (uint64_t*)(smem + 2 * TABB + 64 + 8 * kLutLen);
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid < kLutLen) {
@@ -216,41 +279,39 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
     s_lutd[tid] = (double)c_lut100[tid];
   }
   if (tid == 0) {
-    mbar_init(&bar, 1);
+    mbar_init(bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
   uint32_t parity = 0;
+  const uint32_t lane_off = lane * (CPL * ES);
+  const uint8_t* laneA = sA + lane_off;
+  const uint8_t* laneB = sB + lane_off;
 
   const int units = prm.groups * prm.splits;
-  const int64_t npk = (prm.L + kPacket - 1) / kPacket;  // packets overall
+  const int64_t npk_all = (prm.L + kPacket - 1) / kPacket;  // packets overall
+  const int64_t ntiles = (int64_t)prm.nblk * (prm.nblk + 1) / 2;
   for (int u = blockIdx.x; u < units; u += gridDim.x) {
     const int g = u / prm.splits, s = u - g * prm.splits;
-    // even split of the packets, so every boundary is 16-byte aligned
-    const int64_t pk_lo = npk * s / prm.splits, pk_hi = npk * (s + 1) / prm.splits;
-    const int64_t lo = pk_lo * kPacket, hi = min(pk_hi * kPacket, prm.L);
-
-    int32_t acc32[CPL];
-    int64_t acc64[CPL];
-    double accd[CPL];
-#pragma unroll
-    for (int j = 0; j < CPL; ++j) { acc32[j] = 0; acc64[j] = 0; accd[j] = 0.0; }
+    // even split of the packets, so every unit boundary is 16-byte aligned
+    const int64_t lo = (npk_all * s / prm.splits) * kPacket;
+    const int64_t hi = min((npk_all * (s + 1) / prm.splits) * kPacket, prm.L);
+    Lane<CPL, WM> acc;
+    acc.clear();
 
     if (lo < hi) {
       // tile containing record `lo`: largest t with tile_start[t] <= lo
-      int64_t ntiles = (int64_t)prm.nblk * (prm.nblk + 1) / 2;
       int64_t tl = 0, th = ntiles;  // invariant: tile_start[tl] <= lo < tile_start[th]
       while (th - tl > 1) {
-        int64_t mid = (tl + th) >> 1;
+        const int64_t mid = (tl + th) >> 1;
         if (prm.tile_start[mid] <= lo) tl = mid; else th = mid;
       }
       int64_t t = tl;
-      // (I, J) of tile t
       int32_t I = 0;
       {
         int32_t a = 0, b = prm.nblk;  // tile_row_start(a) <= t < tile_row_start(b)
         while (b - a > 1) {
-          int32_t m = (a + b) >> 1;
+          const int32_t m = (a + b) >> 1;
           if (tile_row_start(m, prm.nblk) <= t) a = m; else b = m;
         }
         I = a;
@@ -259,75 +320,87 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
 
       int64_t cur = lo;
       while (cur < hi) {
-        int64_t tend = prm.tile_start[t + 1];
+        const int64_t tend = prm.tile_start[t + 1];
         if (tend <= cur) {  // empty tile (or finished): next
           ++t; ++J;
           if (J == prm.nblk) { ++I; J = I; }
           continue;
         }
         const int64_t seg_end = min(hi, tend);
-        // ---- stage the two contig-block tables of tile (I, J) for group g ----
+        // ---- stage the two contig-block tables of tile (I, J) for group g (TMA bulk copies) ----
         __syncthreads();  // everyone is done with the previous tables
         if (tid == 0) {
           const int rowsA = min(kBlk, prm.n - I * kBlk), rowsB = min(kBlk, prm.n - J * kBlk);
           const uint8_t* gA = (const uint8_t*)prm.tabA + ((size_t)g * prm.n + (size_t)I * kBlk) * ROWB;
           const uint8_t* gB = (const uint8_t*)prm.tabB + ((size_t)g * prm.n + (size_t)J * kBlk) * ROWB;
           fence_proxy_async();
-          mbar_expect_tx(&bar, (uint32_t)(rowsA + rowsB) * ROWB);
-          tma_bulk_g2s(sA, gA, (uint32_t)rowsA * ROWB, &bar);
-          tma_bulk_g2s(sB, gB, (uint32_t)rowsB * ROWB, &bar);
+          mbar_expect_tx(bar, (uint32_t)(rowsA + rowsB) * ROWB);
+          tma_bulk_g2s(sA, gA, (uint32_t)rowsA * ROWB, bar);
+          tma_bulk_g2s(sB, gB, (uint32_t)rowsB * ROWB, bar);
         }
-        mbar_wait(&bar, parity);
+        mbar_wait(bar, parity);
         parity ^= 1;
 
-        // ---- stream the records of [cur, seg_end) ----
-        const uint8_t* laneA = sA + lane * (CPL * ES);
-        const uint8_t* laneB = sB + lane * (CPL * ES);
+        // ---- stream the records of [cur, seg_end): 8-record packets, one 128-bit load each ----
         const int64_t p_first = cur / kPacket, p_last = (seg_end - 1) / kPacket;
-        for (int64_t pk = p_first + warp; pk <= p_last; pk += kWarps) {
-          const int64_t base = pk * kPacket;
-          uint4 v = ldg_stream_v4(prm.rec + base);
-          const uint32_t words[4] = {v.x, v.y, v.z, v.w};
-          const bool full = (base >= cur) && (base + kPacket <= seg_end);
-          int32_t wi[kPacket];
-          double wd[kPacket];
-          if (WM == W_INT32) {
-            const int32_t* wp = (const int32_t*)prm.w + base;
-#pragma unroll
-            for (int k = 0; k < kPacket; ++k) wi[k] = (base + k < prm.L) ? wp[k] : 0;
-          } else if (WM == W_F64) {
-            const double* wp = (const double*)prm.w + base;
-#pragma unroll
-            for (int k = 0; k < kPacket; ++k) wd[k] = (base + k < prm.L) ? wp[k] : 0.0;
-          }
-#pragma unroll
-          for (int k = 0; k < kPacket; ++k) {
-            if (!full && (base + k < cur || base + k >= seg_end)) continue;
-            const uint32_t r = (words[k >> 1] >> (16 * (k & 1))) & 0xFFFFu;
-            const uint8_t* rowA = laneA + (r >> 8) * ROWB;
-            const uint8_t* rowB = laneB + (r & 0xFFu) * ROWB;
-            Eval<CPL, WIDE, WM>::run(rowA, rowB, s_lut, s_lutd, WM == W_INT32 ? wi[k] : 0,
-                                     WM == W_F64 ? wd[k] : 0.0, acc32, acc64, accd);
-          }
-          if (WM == W_UNIT && ((pk - p_first) / kWarps & 0xFFFF) == 0xFFFF) {
-#pragma unroll
-            for (int j = 0; j < CPL; ++j) { acc64[j] += acc32[j]; acc32[j] = 0; }
+        const bool head_partial = (p_first * kPacket < cur);
+        const bool tail_partial = ((p_last + 1) * kPacket > seg_end);
+        int32_t wi[kPacket];
+        double wd[kPacket];
+        // boundary packets (shared with a neighbouring tile / unit): masked, one warp each
+        if (head_partial && warp == 0) {
+          const int64_t base = p_first * kPacket;
+          const uint4 v = ldg_stream_v4(prm.rec + base);
+          load_weights<WM>(prm.w, base, wi, wd);
+          const int k0 = (int)(cur - base), k1 = (int)min((int64_t)kPacket, seg_end - base);
+#pragma unroll 1
+          for (int k = k0; k < k1; ++k)
+            eval_packet<CPL, WIDE, WM>(v, laneA, laneB, lane_off, s_lut, s_lutd, wi, wd, k, k + 1, acc);
+        }
+        if (tail_partial && warp == 1 && !(head_partial && p_last == p_first)) {
+          const int64_t base = p_last * kPacket;
+          const uint4 v = ldg_stream_v4(prm.rec + base);
+          load_weights<WM>(prm.w, base, wi, wd);
+          const int k1 = (int)(seg_end - base);
+#pragma unroll 1
+          for (int k = 0; k < k1; ++k)
+            eval_packet<CPL, WIDE, WM>(v, laneA, laneB, lane_off, s_lut, s_lutd, wi, wd, k, k + 1, acc);
+        }
+        // full packets: straight-line code, next packet's load in flight while this one is scored
+        const int64_t f0 = p_first + (head_partial ? 1 : 0);
+        const int64_t f1 = p_last - (tail_partial ? 1 : 0);  // inclusive
+        const int64_t nfull = f1 - f0 + 1;
+        if (nfull > 0) {
+          const uint16_t* recp = prm.rec + f0 * kPacket;
+          const int64_t wbase = f0 * kPacket;
+          // chunks bound the int32 accumulators: 2^16 packets * 8 records * 100 < 2^31
+          for (int64_t c0 = 0; c0 < nfull; c0 += (int64_t)kWarps << 16) {
+            const int32_t cnt = (int32_t)min((int64_t)kWarps << 16, nfull - c0);
+            const uint16_t* rp = recp + c0 * kPacket;
+            int32_t it = warp;
+            uint4 vn = make_uint4(0, 0, 0, 0);
+            if (it < cnt) vn = ldg_stream_v4(rp + (size_t)it * kPacket);
+#pragma unroll 1
+            for (; it < cnt; it += kWarps) {
+              const uint4 v = vn;
+              if (it + kWarps < cnt) vn = ldg_stream_v4(rp + (size_t)(it + kWarps) * kPacket);
+              load_weights<WM>(prm.w, wbase + (c0 + it) * kPacket, wi, wd);
+              eval_packet<CPL, WIDE, WM>(v, laneA, laneB, lane_off, s_lut, s_lutd, wi, wd, 0, kPacket, acc);
+            }
+            acc.flush();
           }
         }
         cur = seg_end;
       }
     }
-    if (WM == W_UNIT) {
-#pragma unroll
-      for (int j = 0; j < CPL; ++j) acc64[j] += acc32[j];
-    }
+    acc.flush();
     // ---- cross-warp reduction in the (now idle) table area, fixed order ----
     __syncthreads();
     acc_t* red = (acc_t*)smem;  // [kWarps][CAND]
 #pragma unroll
     for (int j = 0; j < CPL; ++j) {
       acc_t v;
-      if (WM == W_F64) v = (acc_t)accd[j]; else v = (acc_t)acc64[j];
+      if (WM == W_F64) v = (acc_t)acc.ad[j]; else v = (acc_t)acc.a64[j];
       red[warp * CAND + lane * CPL + j] = v;
     }
     __syncthreads();
@@ -342,7 +415,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
 // ---- k_scaff_head -------------------------------------------------------------------------------
 // head[p] = sum_k 100*T[k] * W(g[0], g[k]) with W the summed weight of the records of that pair:
 // exactly the evaluations the reference's `i-k > 0` test drops (scaff.go:256,264,...,299).
-// One warp per candidate, lane k < 6 looks one pair up by binary search in its sorted tile.
+// One warp per candidate; the six pairs are taken in turn: two binary searches bound the run of
+// equal keys in the sorted tile, unit weights need only its length, otherwise the warp sums the
+// run with coalesced loads (lane-strided, then a fixed-order shuffle tree: deterministic).
 template <int WM>
 __global__ void k_scaff_head(const int32_t* __restrict__ perm, int32_t P, int32_t n, int32_t nblk,
                              const uint16_t* __restrict__ rec, const void* __restrict__ w,
@@ -350,36 +425,45 @@ __global__ void k_scaff_head(const int32_t* __restrict__ perm, int32_t P, int32_
   typedef typename Acc<WM>::type acc_t;
   const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (p >= P) return;
-  acc_t term = 0;
-  if (lane < 6 && c_steps[lane] < n) {
-    const uint32_t z = (uint32_t)perm[(size_t)p * n], y = (uint32_t)perm[(size_t)p * n + c_steps[lane]];
-    if (z < (uint32_t)n && y < (uint32_t)n && z != y) {
-      const uint32_t lo = min(z, y), hi = max(z, y);
-      const int64_t I = lo >> kBlkShift, J = hi >> kBlkShift;
-      const int64_t t = tile_row_start(I, nblk) + (J - I);
-      const uint32_t key = ((lo & (kBlk - 1)) << 8) | (hi & (kBlk - 1));
-      int64_t a = tile_start[t], b = tile_start[t + 1];
-      const int64_t end = b;
-      while (a < b) {  // lower bound of key
-        int64_t m = (a + b) >> 1;
-        if (rec[m] < key) a = m + 1; else b = m;
-      }
-      acc_t sum = 0;
-      for (int64_t i = a; i < end && rec[i] == key; ++i) {
-        if (WM == W_UNIT) sum += 1;
-        else if (WM == W_INT32) sum += ((const int32_t*)w)[i];
-        else sum += ((const double*)w)[i];
-      }
-      term = sum * (acc_t)c_w100[lane];
-    }
-  }
-  // fixed-order sum over the six lanes
   acc_t tot = 0;
+  const uint32_t z = (uint32_t)perm[(size_t)p * n];
+#pragma unroll 1
   for (int k = 0; k < 6; ++k) {
-    acc_t v;
-    if (WM == W_F64) v = (acc_t)__shfl_sync(0xffffffffu, (double)term, k);
-    else v = (acc_t)__shfl_sync(0xffffffffu, (long long)term, k);
-    tot += v;
+    if (c_steps[k] >= n) break;
+    const uint32_t y = (uint32_t)perm[(size_t)p * n + c_steps[k]];
+    if (z >= (uint32_t)n || y >= (uint32_t)n || z == y) continue;  // invalid rows are flagged elsewhere
+    const uint32_t lo = min(z, y), hi = max(z, y);
+    const int64_t I = lo >> kBlkShift, J = hi >> kBlkShift;
+    const int64_t t = tile_row_start(I, nblk) + (J - I);
+    const uint32_t key = ((lo & (kBlk - 1)) << 8) | (hi & (kBlk - 1));
+    const int64_t t0 = tile_start[t], t1 = tile_start[t + 1];
+    int64_t a = t0, b = t1;
+    while (a < b) {  // first record >= key
+      int64_t m = (a + b) >> 1;
+      if (rec[m] < key) a = m + 1; else b = m;
+    }
+    const int64_t first = a;
+    b = t1;
+    while (a < b) {  // first record > key
+      int64_t m = (a + b) >> 1;
+      if (rec[m] <= key) a = m + 1; else b = m;
+    }
+    const int64_t last = a;
+    acc_t sum = 0;
+    if (WM == W_UNIT) {
+      sum = (acc_t)(last - first);
+    } else {
+      for (int64_t i = first + lane; i < last; i += 32) {
+        if (WM == W_INT32) sum += (acc_t)((const int32_t*)w)[i];
+        else sum += (acc_t)((const double*)w)[i];
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        if (WM == W_F64) sum += (acc_t)__shfl_xor_sync(0xffffffffu, (double)sum, o);
+        else sum += (acc_t)__shfl_xor_sync(0xffffffffu, (long long)sum, o);
+      }
+    }
+    tot += sum * (acc_t)c_w100[k];
   }
   if (lane == 0) ((acc_t*)head)[p] = tot;
 }
@@ -439,7 +523,7 @@ inline int grid_for(int64_t n, int threads, int sm) {
 
 template <int CPL, bool WIDE, int WM>
 int launch_score(lxy_ctx* c, const ScoreParams& prm, int grid) {
-  constexpr int smem = 2 * kBlk * 32 * CPL * (WIDE ? 4 : 2);
+  constexpr int smem = 2 * kBlk * 32 * CPL * (WIDE ? 4 : 2) + 64 + 8 * kLutLen + 16;
   static bool configured[64] = {};
   if (!configured[c->cfg.device & 63]) {
     LXY_CUDA(cudaFuncSetAttribute(k_scaff_score<CPL, WIDE, WM>,
@@ -456,8 +540,9 @@ int launch_score_cpl(lxy_ctx* c, int cpl, const ScoreParams& prm, int grid) {
   switch (cpl) {
     case 1: return launch_score<1, WIDE, WM>(c, prm, grid);
     case 2: return launch_score<2, WIDE, WM>(c, prm, grid);
-    default: return WIDE ? launch_score<2, WIDE, WM>(c, prm, grid)
-                         : launch_score<4, WIDE, WM>(c, prm, grid);
+    default:
+      if constexpr (WIDE) return launch_score<2, WIDE, WM>(c, prm, grid);
+      else return launch_score<4, WIDE, WM>(c, prm, grid);
   }
 }
 
@@ -474,7 +559,7 @@ int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int
   if (P <= 0) return LXY_OK;
   cudaStream_t st = c->stream;
   const int n = S.n;
-  const bool wide = (n + kBias >= 0x8000);
+  const bool wide = (n + kBias + 1 >= 0x8000);
   // candidates per lane: 4 (narrow) / 2 (wide) fill 128 KB of tables; small populations use less
   int cpl = wide ? 2 : 4;
   while (cpl > 1 && P <= 32 * (cpl / 2)) cpl /= 2;
