@@ -113,6 +113,12 @@ int lxy_ctx_create(const lxy_cfg* cfg, lxy_ctx** out) {
     delete c;
     return LXY_ERR_CUDA;
   }
+  if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+    set_error("cudaStreamCreate failed");
+    lxy_ctx_destroy(c);
+    return LXY_ERR_CUDA;
+  }
   for (auto& ev : c->ev) {
     if (cudaEventCreate(&ev) != cudaSuccess) { set_error("cudaEventCreate failed"); lxy_ctx_destroy(c); return LXY_ERR_CUDA; }
   }
@@ -124,6 +130,7 @@ void lxy_ctx_destroy(lxy_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->cfg.device);
   if (c->stream) cudaStreamSynchronize(c->stream);
+  if (c->stream2) cudaStreamSynchronize(c->stream2);
   DevBuf* bufs[] = {&c->scaff.rec, &c->scaff.w, &c->scaff.tile_start, &c->scaff.len, &c->scaff.xa, &c->scaff.xb,
                     &c->phase.rec, &c->phase.w, &c->d_perm, &c->d_ori, &c->d_out, &c->d_x100,
                     &c->d_posA, &c->d_posB, &c->d_partial, &c->d_corr, &c->d_flag, &c->d_genes,
@@ -131,6 +138,8 @@ void lxy_ctx_destroy(lxy_ctx* c) {
   for (DevBuf* b : bufs) b->release();
   if (c->h_pin) cudaFreeHost(c->h_pin);
   for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
+  if (c->ev_join) cudaEventDestroy(c->ev_join);
+  if (c->stream2) cudaStreamDestroy(c->stream2);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }

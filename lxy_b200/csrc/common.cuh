@@ -88,6 +88,8 @@ struct lxy_ctx {
   lxy_cfg cfg{};
   std::mutex mu;
   cudaStream_t stream = nullptr;
+  cudaStream_t stream2 = nullptr;   // side stream (head-of-ordering look-ups)
+  cudaEvent_t ev_join = nullptr;
   cudaEvent_t ev[8]{};
   int sm_count = 0;
   int max_smem_optin = 0;

@@ -415,9 +415,10 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
 // ---- k_scaff_head -------------------------------------------------------------------------------
 // head[p] = sum_k 100*T[k] * W(g[0], g[k]) with W the summed weight of the records of that pair:
 // exactly the evaluations the reference's `i-k > 0` test drops (scaff.go:256,264,...,299).
-// One warp per candidate; the six pairs are taken in turn: two binary searches bound the run of
-// equal keys in the sorted tile, unit weights need only its length, otherwise the warp sums the
-// run with coalesced loads (lane-strided, then a fixed-order shuffle tree: deterministic).
+// One warp per candidate; lane k < 6 bounds the run of pair (g[0], g[step k]) in its sorted tile
+// with two binary searches (the six dependent-load chains run side by side).  Unit weights need
+// only the run length; otherwise the warp sums each run with coalesced loads (lane-strided, then
+// a fixed-order shuffle tree: deterministic).
 template <int WM>
 __global__ void k_scaff_head(const int32_t* __restrict__ perm, int32_t P, int32_t n, int32_t nblk,
                              const uint16_t* __restrict__ rec, const void* __restrict__ w,
@@ -425,35 +426,40 @@ __global__ void k_scaff_head(const int32_t* __restrict__ perm, int32_t P, int32_
   typedef typename Acc<WM>::type acc_t;
   const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (p >= P) return;
+  int64_t first = 0, last = 0;
+  if (lane < 6 && c_steps[lane] < n) {
+    const uint32_t z = (uint32_t)perm[(size_t)p * n];
+    const uint32_t y = (uint32_t)perm[(size_t)p * n + c_steps[lane]];
+    if (z < (uint32_t)n && y < (uint32_t)n && z != y) {  // invalid rows are flagged by k_scaff_check
+      const uint32_t lo = min(z, y), hi = max(z, y);
+      const int64_t I = lo >> kBlkShift, J = hi >> kBlkShift;
+      const int64_t t = tile_row_start(I, nblk) + (J - I);
+      const uint32_t key = ((lo & (kBlk - 1)) << 8) | (hi & (kBlk - 1));
+      const int64_t t1 = tile_start[t + 1];
+      int64_t a = tile_start[t], b = t1;
+      while (a < b) {  // first record >= key
+        const int64_t m = (a + b) >> 1;
+        if (rec[m] < key) a = m + 1; else b = m;
+      }
+      first = a;
+      b = t1;
+      while (a < b) {  // first record > key
+        const int64_t m = (a + b) >> 1;
+        if (rec[m] <= key) a = m + 1; else b = m;
+      }
+      last = a;
+    }
+  }
   acc_t tot = 0;
-  const uint32_t z = (uint32_t)perm[(size_t)p * n];
 #pragma unroll 1
   for (int k = 0; k < 6; ++k) {
-    if (c_steps[k] >= n) break;
-    const uint32_t y = (uint32_t)perm[(size_t)p * n + c_steps[k]];
-    if (z >= (uint32_t)n || y >= (uint32_t)n || z == y) continue;  // invalid rows are flagged elsewhere
-    const uint32_t lo = min(z, y), hi = max(z, y);
-    const int64_t I = lo >> kBlkShift, J = hi >> kBlkShift;
-    const int64_t t = tile_row_start(I, nblk) + (J - I);
-    const uint32_t key = ((lo & (kBlk - 1)) << 8) | (hi & (kBlk - 1));
-    const int64_t t0 = tile_start[t], t1 = tile_start[t + 1];
-    int64_t a = t0, b = t1;
-    while (a < b) {  // first record >= key
-      int64_t m = (a + b) >> 1;
-      if (rec[m] < key) a = m + 1; else b = m;
-    }
-    const int64_t first = a;
-    b = t1;
-    while (a < b) {  // first record > key
-      int64_t m = (a + b) >> 1;
-      if (rec[m] <= key) a = m + 1; else b = m;
-    }
-    const int64_t last = a;
+    const int64_t f = __shfl_sync(0xffffffffu, (long long)first, k);
+    const int64_t l = __shfl_sync(0xffffffffu, (long long)last, k);
     acc_t sum = 0;
     if (WM == W_UNIT) {
-      sum = (acc_t)(last - first);
+      sum = (acc_t)(l - f);
     } else {
-      for (int64_t i = first + lane; i < last; i += 32) {
+      for (int64_t i = f + lane; i < l; i += 32) {
         if (WM == W_INT32) sum += (acc_t)((const int32_t*)w)[i];
         else sum += (acc_t)((const double*)w)[i];
       }
@@ -469,16 +475,24 @@ __global__ void k_scaff_head(const int32_t* __restrict__ perm, int32_t P, int32_
 }
 
 // ---- k_scaff_finish -----------------------------------------------------------------------------
+// One warp per candidate: lane-strided sum of the per-unit partials, then a fixed shuffle tree
+// (the order does not depend on timing, so fp64 results are reproducible run to run).
 template <int WM>
 __global__ void k_scaff_finish(int32_t P, int32_t cand, int32_t splits,
                                const void* __restrict__ partial, const void* __restrict__ head,
                                double* __restrict__ out, int64_t* __restrict__ x100) {
   typedef typename Acc<WM>::type acc_t;
-  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (p >= P) return;
   const int g = p / cand, pc = p - g * cand;
   acc_t S = 0;
-  for (int s = 0; s < splits; ++s) S += ((const acc_t*)partial)[((size_t)g * splits + s) * cand + pc];
+  for (int s = lane; s < splits; s += 32) S += ((const acc_t*)partial)[((size_t)g * splits + s) * cand + pc];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    if (WM == W_F64) S += (acc_t)__shfl_xor_sync(0xffffffffu, (double)S, o);
+    else S += (acc_t)__shfl_xor_sync(0xffffffffu, (long long)S, o);
+  }
+  if (lane != 0) return;
   const acc_t tot = S + S - ((const acc_t*)head)[p];  // every pair twice, head-of-ordering pairs once
   if (WM == W_F64) {
     out[p] = -((double)tot / 100.0);
@@ -579,6 +593,20 @@ int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int
   int launches = 0;
 
   LXY_CUDA(cudaEventRecord(c->ev[0], st));
+  // The head-of-ordering look-ups only need the population and the link store: they run on a side
+  // stream next to the layout and streaming kernels and are joined before k_scaff_finish.
+  {
+    cudaStream_t s2 = c->stream2;
+    LXY_CUDA(cudaStreamWaitEvent(s2, c->ev[0], 0));
+    const int hb = (P * 32 + 255) / 256;
+    const uint16_t* rec = S.rec.as<uint16_t>();
+    const int64_t* ts = S.tile_start.as<int64_t>();
+    if (S.wmode == W_UNIT) k_scaff_head<W_UNIT><<<hb, 256, 0, s2>>>(perm_dev, P, n, S.nblk, rec, S.w.p, ts, c->d_corr.p);
+    else if (S.wmode == W_INT32) k_scaff_head<W_INT32><<<hb, 256, 0, s2>>>(perm_dev, P, n, S.nblk, rec, S.w.p, ts, c->d_corr.p);
+    else k_scaff_head<W_F64><<<hb, 256, 0, s2>>>(perm_dev, P, n, S.nblk, rec, S.w.p, ts, c->d_corr.p);
+    LXY_CUDA(cudaGetLastError());
+    LXY_CUDA(cudaEventRecord(c->ev_join, s2));
+  }
   const int lg = grid_for((int64_t)Ppad * n, 256, c->sm_count);
   if (wide) k_scaff_layout<true><<<lg, 256, 0, st>>>(perm_dev, P, Ppad, n, cand, c->d_posA.p, c->d_posB.p, c->d_flag.as<int>());
   else k_scaff_layout<false><<<lg, 256, 0, st>>>(perm_dev, P, Ppad, n, cand, c->d_posA.p, c->d_posB.p, c->d_flag.as<int>());
@@ -626,17 +654,10 @@ int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int
   ++launches;
   LXY_CUDA(cudaEventRecord(c->ev[2], st));
 
-  const int hb = (P * 32 + 255) / 256;
-  if (S.wmode == W_UNIT) {
-    k_scaff_head<W_UNIT><<<hb, 256, 0, st>>>(perm_dev, P, n, S.nblk, prm.rec, prm.w, prm.tile_start, c->d_corr.p);
-    k_scaff_finish<W_UNIT><<<(P + 127) / 128, 128, 0, st>>>(P, cand, splits, c->d_partial.p, c->d_corr.p, out_dev, x100_dev);
-  } else if (S.wmode == W_INT32) {
-    k_scaff_head<W_INT32><<<hb, 256, 0, st>>>(perm_dev, P, n, S.nblk, prm.rec, prm.w, prm.tile_start, c->d_corr.p);
-    k_scaff_finish<W_INT32><<<(P + 127) / 128, 128, 0, st>>>(P, cand, splits, c->d_partial.p, c->d_corr.p, out_dev, x100_dev);
-  } else {
-    k_scaff_head<W_F64><<<hb, 256, 0, st>>>(perm_dev, P, n, S.nblk, prm.rec, prm.w, prm.tile_start, c->d_corr.p);
-    k_scaff_finish<W_F64><<<(P + 127) / 128, 128, 0, st>>>(P, cand, splits, c->d_partial.p, c->d_corr.p, out_dev, x100_dev);
-  }
+  LXY_CUDA(cudaStreamWaitEvent(st, c->ev_join, 0));
+  if (S.wmode == W_UNIT) k_scaff_finish<W_UNIT><<<(P + 7) / 8, 256, 0, st>>>(P, cand, splits, c->d_partial.p, c->d_corr.p, out_dev, x100_dev);
+  else if (S.wmode == W_INT32) k_scaff_finish<W_INT32><<<(P + 7) / 8, 256, 0, st>>>(P, cand, splits, c->d_partial.p, c->d_corr.p, out_dev, x100_dev);
+  else k_scaff_finish<W_F64><<<(P + 7) / 8, 256, 0, st>>>(P, cand, splits, c->d_partial.p, c->d_corr.p, out_dev, x100_dev);
   launches += 2;
   LXY_CUDA(cudaGetLastError());
   LXY_CUDA(cudaEventRecord(c->ev[3], st));
