@@ -117,6 +117,8 @@ int lxy_ctx_set_links_g(lxy_ctx* ctx, int32_t n_ids, int64_t n_links, const uint
                         const double* w, const uint32_t* len, uint32_t unit);
 int lxy_scaffg_score_batch(lxy_ctx* ctx, const int32_t* perm, const uint8_t* ori, int32_t P,
                            double* out, int64_t* x100);
+int lxy_scaffg_score_batch_dev(lxy_ctx* ctx, const int32_t* perm_dev, const uint8_t* ori_dev,
+                               int32_t P, double* out_dev, int64_t* x100_dev);
 int lxy_scaffg_layout(lxy_ctx* ctx, const int32_t* perm, int32_t P, uint64_t* start_by_pos,
                       int32_t* pos_by_contig);
 int lxy_scaffg_link_distances(lxy_ctx* ctx, int64_t n_links, const uint32_t* a,

@@ -22,6 +22,8 @@ SYMBOLS = [
     "lxy_ctx_set_links_dev",
     "lxy_scaff_score_batch", "lxy_scaff_score_batch_dev", "lxy_scaff_positions",
     "lxy_scaff_link_distances", "lxy_links_get", "lxy_ctx_set_links_g", "lxy_scaffg_score_batch",
+    "lxy_scaffg_score_batch_dev",
+    "lxy_scaffg_score_batch_dev",
     "lxy_scaffg_layout", "lxy_scaffg_link_distances", "lxy_ctx_set_phase_links",
     "lxy_phase_score_batch", "lxy_phase_score_batch_dev", "lxy_rank",
 ]
@@ -89,6 +91,7 @@ def lib():
         "lxy_links_get": (i32, [vp, i32, i32, C.POINTER(f64)]),
         "lxy_ctx_set_links_g": (i32, [vp, i32, i64, vp, vp, vp, vp, vp, vp, u32]),
         "lxy_scaffg_score_batch": (i32, [vp, vp, vp, i32, vp, vp]),
+        "lxy_scaffg_score_batch_dev": (i32, [vp, vp, vp, i32, vp, vp]),
         "lxy_scaffg_layout": (i32, [vp, vp, i32, vp, vp]),
         "lxy_scaffg_link_distances": (i32, [vp, i64, vp, vp, vp, vp, vp, vp, vp]),
         "lxy_ctx_set_phase_links": (i32, [vp, i32, i64, vp, vp, vp]),
@@ -234,6 +237,12 @@ class Context:
         out, x100 = np.zeros(P, np.float64), np.zeros(P, np.int64)
         _check(lib().lxy_scaffg_score_batch(self._h, _p(perms), _p(oris), P, _p(out), _p(x100)))
         return (out, x100) if want_x100 else out
+
+    def scaffg_score_batch_dev(self, perm_ptr, ori_ptr, P, out_ptr, x100_ptr=None):
+        _check(lib().lxy_scaffg_score_batch_dev(self._h, C.c_void_p(perm_ptr),
+                                                C.c_void_p(ori_ptr) if ori_ptr else None, P,
+                                                C.c_void_p(out_ptr),
+                                                C.c_void_p(x100_ptr) if x100_ptr else None))
 
     def scaffg_layout(self, perms):
         perms = _c(perms, np.int32)

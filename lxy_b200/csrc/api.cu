@@ -293,26 +293,92 @@ int lxy_ctx_set_links_g(lxy_ctx* c, int32_t n_ids, int64_t n_links, const uint32
 int lxy_scaffg_score_batch(lxy_ctx* c, const int32_t* perm, const uint8_t* ori, int32_t P,
                            double* out, int64_t* x100) {
   CHECK_CTX(c);
-  (void)perm; (void)ori; (void)P; (void)out; (void)x100;
-  set_error("scaffg_score_batch: not implemented in this build");
-  return LXY_ERR_STATE;
+  if (P < 0 || (P > 0 && (!perm || !out))) { set_error("scaffg_score_batch: bad argument"); return LXY_ERR_ARG; }
+  if (!c->scaff.ready || !c->scaff.gprofile) { set_error("scaffg_score_batch: G-profile links not set"); return LXY_ERR_STATE; }
+  if (P == 0) return LXY_OK;
+  const size_t n = (size_t)c->scaff.n;
+  const size_t pbytes = sizeof(int32_t) * n * (size_t)P, obytes = ori ? n * (size_t)P : 0;
+  const size_t ooff = (pbytes + obytes + 15) & ~(size_t)15;
+  LXY_TRY(pin_reserve(c, ooff + 16 * (size_t)P));
+  LXY_TRY(c->d_perm.reserve(pbytes));
+  LXY_TRY(c->d_ori.reserve(obytes + 16));
+  LXY_TRY(c->d_out.reserve(8 * (size_t)P));
+  LXY_TRY(c->d_x100.reserve(8 * (size_t)P));
+  std::memcpy(c->h_pin, perm, pbytes);
+  if (ori) std::memcpy((char*)c->h_pin + pbytes, ori, obytes);
+  LXY_CUDA(cudaEventRecord(c->ev[4], c->stream));
+  LXY_CUDA(cudaMemcpyAsync(c->d_perm.p, c->h_pin, pbytes, cudaMemcpyHostToDevice, c->stream));
+  if (ori) LXY_CUDA(cudaMemcpyAsync(c->d_ori.p, (char*)c->h_pin + pbytes, obytes, cudaMemcpyHostToDevice, c->stream));
+  LXY_TRY(scaffg_score(c, c->d_perm.as<int32_t>(), ori ? c->d_ori.as<uint8_t>() : nullptr, P,
+                       c->d_out.as<double>(), c->d_x100.as<int64_t>()));
+  char* hout = (char*)c->h_pin + ooff;
+  LXY_CUDA(cudaMemcpyAsync(hout, c->d_out.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, c->stream));
+  LXY_CUDA(cudaMemcpyAsync(hout + 8 * (size_t)P, c->d_x100.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, c->stream));
+  LXY_CUDA(cudaEventRecord(c->ev[5], c->stream));
+  c->timing_pending = 2;
+  LXY_TRY(finish_flags(c, "scaffg score"));
+  std::memcpy(out, hout, 8 * (size_t)P);
+  if (x100) std::memcpy(x100, hout + 8 * (size_t)P, 8 * (size_t)P);
+  return LXY_OK;
+}
+
+int lxy_scaffg_score_batch_dev(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int32_t P,
+                               double* out_dev, int64_t* x100_dev) {
+  CHECK_CTX(c);
+  if (P < 0 || (P > 0 && (!perm_dev || !out_dev))) { set_error("scaffg_score_batch_dev: bad argument"); return LXY_ERR_ARG; }
+  if (P == 0) return LXY_OK;
+  LXY_TRY(scaffg_score(c, perm_dev, ori_dev, P, out_dev, x100_dev));
+  c->timing_pending = 1;
+  if (c->cfg.flags & LXY_FLAG_NO_VALIDATE) return LXY_OK;
+  return finish_flags(c, "scaffg score");
 }
 
 int lxy_scaffg_layout(lxy_ctx* c, const int32_t* perm, int32_t P, uint64_t* start_by_pos,
                       int32_t* pos_by_contig) {
   CHECK_CTX(c);
-  (void)perm; (void)P; (void)start_by_pos; (void)pos_by_contig;
-  set_error("scaffg_layout: not implemented in this build");
-  return LXY_ERR_STATE;
+  if (!c->scaff.ready || !c->scaff.gprofile) { set_error("scaffg_layout: G-profile links not set"); return LXY_ERR_STATE; }
+  if (P < 0 || (P > 0 && (!perm || !start_by_pos || !pos_by_contig))) { set_error("scaffg_layout: bad argument"); return LXY_ERR_ARG; }
+  if (P == 0) return LXY_OK;
+  const size_t cnt = (size_t)c->scaff.n * (size_t)P;
+  LXY_TRY(c->d_perm.reserve(4 * cnt));
+  LXY_TRY(c->d_tmp0.reserve(8 * cnt));
+  LXY_TRY(c->d_tmp1.reserve(4 * cnt));
+  LXY_CUDA(cudaMemcpyAsync(c->d_perm.p, perm, 4 * cnt, cudaMemcpyHostToDevice, c->stream));
+  LXY_CUDA(cudaMemsetAsync(c->d_tmp1.p, 0xFF, 4 * cnt, c->stream));
+  LXY_TRY(scaffg_layout64(c, c->d_perm.as<int32_t>(), P, c->d_tmp0.as<uint64_t>(), c->d_tmp1.as<int32_t>()));
+  LXY_CUDA(cudaMemcpyAsync(start_by_pos, c->d_tmp0.p, 8 * cnt, cudaMemcpyDeviceToHost, c->stream));
+  LXY_CUDA(cudaMemcpyAsync(pos_by_contig, c->d_tmp1.p, 4 * cnt, cudaMemcpyDeviceToHost, c->stream));
+  return finish_flags(c, "scaffg_layout");
 }
 
-int lxy_scaffg_link_distances(lxy_ctx* c, int64_t n_links, const uint32_t* a, const uint32_t* xa,
+int lxy_scaffg_link_distances(lxy_ctx* c, int64_t L, const uint32_t* a, const uint32_t* xa,
                               const uint32_t* b, const uint32_t* xb, const int32_t* perm,
                               const uint8_t* ori, uint64_t* dist) {
   CHECK_CTX(c);
-  (void)n_links; (void)a; (void)xa; (void)b; (void)xb; (void)perm; (void)ori; (void)dist;
-  set_error("scaffg_link_distances: not implemented in this build");
-  return LXY_ERR_STATE;
+  if (!c->scaff.ready || !c->scaff.gprofile) { set_error("scaffg_link_distances: G-profile links not set"); return LXY_ERR_STATE; }
+  if (L < 0 || !perm || (L > 0 && (!a || !xa || !b || !xb || !dist))) { set_error("scaffg_link_distances: bad argument"); return LXY_ERR_ARG; }
+  const size_t n = (size_t)c->scaff.n;
+  LXY_TRY(c->d_perm.reserve(4 * n));
+  LXY_TRY(c->d_ori.reserve(n + 16));
+  LXY_TRY(c->d_posA.reserve(8 * n));
+  LXY_TRY(c->d_posB.reserve(4 * n));
+  LXY_TRY(c->d_tmp0.reserve(16 * (size_t)L + 64));
+  LXY_TRY(c->d_tmp2.reserve(8 * (size_t)L + 64));
+  LXY_CUDA(cudaMemcpyAsync(c->d_perm.p, perm, 4 * n, cudaMemcpyHostToDevice, c->stream));
+  if (ori) LXY_CUDA(cudaMemcpyAsync(c->d_ori.p, ori, n, cudaMemcpyHostToDevice, c->stream));
+  LXY_TRY(scaffg_layout64(c, c->d_perm.as<int32_t>(), 1, c->d_posA.as<uint64_t>(), c->d_posB.as<int32_t>()));
+  uint32_t* da = c->d_tmp0.as<uint32_t>();
+  if (L > 0) {
+    LXY_CUDA(cudaMemcpyAsync(da, a, 4 * (size_t)L, cudaMemcpyHostToDevice, c->stream));
+    LXY_CUDA(cudaMemcpyAsync(da + L, xa, 4 * (size_t)L, cudaMemcpyHostToDevice, c->stream));
+    LXY_CUDA(cudaMemcpyAsync(da + 2 * L, b, 4 * (size_t)L, cudaMemcpyHostToDevice, c->stream));
+    LXY_CUDA(cudaMemcpyAsync(da + 3 * L, xb, 4 * (size_t)L, cudaMemcpyHostToDevice, c->stream));
+  }
+  LXY_TRY(scaffg_link_distances(c, L, da, da + L, da + 2 * L, da + 3 * L, c->d_posA.as<uint64_t>(),
+                                c->d_posB.as<int32_t>(), ori ? c->d_ori.as<uint8_t>() : nullptr,
+                                c->d_tmp2.as<uint64_t>()));
+  if (L > 0) LXY_CUDA(cudaMemcpyAsync(dist, c->d_tmp2.p, 8 * (size_t)L, cudaMemcpyDeviceToHost, c->stream));
+  return finish_flags(c, "scaffg_link_distances");
 }
 
 // ---- phasing ------------------------------------------------------------------------------------

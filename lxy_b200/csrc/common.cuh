@@ -129,6 +129,15 @@ int scaff_positions(lxy_ctx* c, const int32_t* perm_dev, int32_t P, int32_t n, i
 int scaff_link_distances(lxy_ctx* c, int32_t n, int64_t L, const uint32_t* a_dev,
                          const uint32_t* b_dev, const int32_t* perm_dev, int64_t* dist_dev);
 
+// scaffg_kernels.cu
+int scaffg_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int32_t P,
+                 double* out_dev, int64_t* x100_dev);
+int scaffg_layout64(lxy_ctx* c, const int32_t* perm_dev, int32_t P, uint64_t* start_dev,
+                    int32_t* pos_dev);
+int scaffg_link_distances(lxy_ctx* c, int64_t L, const uint32_t* a, const uint32_t* xa,
+                          const uint32_t* b, const uint32_t* xb, const uint64_t* start_dev,
+                          const int32_t* pos_dev, const uint8_t* ori_dev, uint64_t* dist_dev);
+
 // phase_kernels.cu
 int phase_score(lxy_ctx* c, const uint8_t* genes_dev, int32_t P, int64_t* out_i64_dev,
                 double* out_f64_dev);

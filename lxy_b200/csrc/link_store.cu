@@ -175,6 +175,11 @@ int build_scaff_links(lxy_ctx* c, const LinkInput& in) {
       tot += in.len[i];
     }
     S.total_len = tot;
+    if (tot > 0xFFFFFFFFull) {
+      set_error("set_links_g: total scaffold length %llu exceeds the 32-bit coordinate format",
+                (unsigned long long)tot);
+      return LXY_ERR_RANGE;
+    }
     LXY_TRY(S.len.reserve(sizeof(uint32_t) * (size_t)n));
     LXY_CUDA(cudaMemcpyAsync(S.len.p, in.len, sizeof(uint32_t) * (size_t)n, cudaMemcpyHostToDevice, st));
   }

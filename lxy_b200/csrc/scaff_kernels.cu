@@ -13,6 +13,7 @@
 //                    the six pairs (g[0], g[k]) in the sorted tiles.
 //   k_scaff_finish   fixed-order reduction of the per-CTA partials, fitness = -(2S - head)/100.
 #include "common.cuh"
+#include "device_utils.cuh"
 
 namespace lxy {
 namespace {
@@ -29,52 +30,6 @@ const uint8_t h_lut100[kLutLen] = {
     /* far */ 0, /* d=-20 */ 5, 0, 0, 0, 0, 0, 0, 0, 0, /* -11 */ 10, 0, 0, 0, 0, 0, /* -5 */ 20, 0,
     /* -3 */ 33, /* -2 */ 50, /* -1 */ 100, /* 0 */ 0, 100, 50, 33, 0, 20, 0, 0, 0, 0, 0,
     /* 11 */ 10, 0, 0, 0, 0, 0, 0, 0, 0, /* 20 */ 5, /* far */ 0, 0, 0, 0, 0, 0};
-
-// ---- PTX helpers (mbarrier + TMA bulk copy, sm_90+) ---------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-  return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
-               "r"(bytes)
-               : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "WAIT_%=:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra DONE_%=;\n\t"
-      "bra WAIT_%=;\n\t"
-      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
-      "r"(parity)
-      : "memory");
-}
-__device__ __forceinline__ void tma_bulk_g2s(void* dst_smem, const void* src, uint32_t bytes,
-                                             uint64_t* bar) {
-  asm volatile(
-      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
-          "r"(smem_u32(dst_smem)),
-      "l"(src), "r"(bytes), "r"(smem_u32(bar))
-      : "memory");
-}
-__device__ __forceinline__ void fence_proxy_async() {
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-}
-__device__ __forceinline__ uint4 ldg_stream_v4(const void* p) {
-  uint4 r;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-               : "l"(p));
-  return r;
-}
-
-__host__ __device__ inline int64_t tile_row_start(int64_t I, int64_t nblk) {
-  return I * nblk - I * (I - 1) / 2;
-}
 
 // ---- k_scaff_layout -----------------------------------------------------------------------------
 // Tables are stored group-major: tab[g][contig][cand] with kCand = 32*CPL candidates per group, so
@@ -138,11 +93,6 @@ struct ScoreParams {
   int32_t n, nblk;
   int32_t groups, splits;     // units = groups * splits
 };
-
-template <int WM> struct Acc;          // per-lane accumulator type
-template <> struct Acc<W_UNIT> { typedef int64_t type; };
-template <> struct Acc<W_INT32> { typedef int64_t type; };
-template <> struct Acc<W_F64> { typedef double type; };
 
 // Per-lane state of the streaming loop: CPL candidates, their running sums.
 template <int CPL, int WM>
@@ -527,12 +477,6 @@ __global__ void k_link_dist(int64_t L, const uint32_t* __restrict__ a, const uin
     int64_t d = (int64_t)pos[x] - (int64_t)pos[y];
     dist[i] = d < 0 ? -d : d;
   }
-}
-
-inline int grid_for(int64_t n, int threads, int sm) {
-  int64_t g = (n + threads - 1) / threads;
-  int64_t cap = (int64_t)sm * 16;
-  return (int)(g < 1 ? 1 : (g > cap ? cap : g));
 }
 
 template <int CPL, bool WIDE, int WM>

@@ -1,0 +1,486 @@
+// scaffg_kernels.cu — scaffolding fitness, G-profile: the generalisation BASELINE.json's north_star
+// describes (contig lengths, orientations, per-link in-contig offsets, genomic distance -> decay).
+// It has no counterpart in the reference; oracle/lxy_oracle.cpp (scaffg_*) defines it, constrained
+// to collapse to scaff.go:246-310 bit for bit when len == 1, x == 0, unit == 1.
+//
+//   k_scaffg_layout  one warp per candidate: warp prefix scan (shuffle-up) of the permuted contig
+//                    lengths -> placement offsets; writes the origin table
+//                    origin[g][contig][cand] = start (forward) | start + len - 1 (reversed) and the
+//                    per-contig bit rows {reversed?, first in the ordering?} of the 64 candidates.
+//   k_scaffg_score   same streaming structure as k_scaff_score (tiles of 256 x 256 contigs, tables
+//                    staged by TMA bulk copies, 2-byte records + their two in-contig offsets
+//                    streamed with 128-bit loads, lane = candidate):
+//                    coord = origin -/+ x, d = |coord a - coord b|, bucket = d / unit by a 64-bit
+//                    multiply-high (exact for 32-bit d), decay table, integer / fp64 sums.  The
+//                    `i-k > 0` multiplicity (pairs touching the first contig count once) is kept as
+//                    a second running sum that is only touched when a record's row has a "first"
+//                    bit set for some candidate of the group (a warp-uniform test).
+//   k_scaffg_finish  fixed-order reduction, fitness = -(2 S - H) / 100.
+#include "common.cuh"
+#include "device_utils.cuh"
+
+namespace lxy {
+namespace {
+
+constexpr int kThreads = 512;
+constexpr int kWarps = kThreads / 32;
+constexpr int kPacket = 8;
+constexpr int kCandG = 64;                 // candidates per group: lane l owns l and l + 32
+constexpr int kRowG = kCandG * 4;          // bytes per contig row of the origin table
+constexpr int kTabG = kBlk * kRowG;        // 64 KB
+constexpr int kBitsG = kBlk * 16;          // uint4 {rev[0..31], rev[32..63], first[0..31], first[32..63]}
+constexpr int kLutG = 24;
+
+__constant__ uint8_t c_lutg[kLutG] = {0, 100, 50, 33, 0, 20, 0, 0, 0, 0, 0, 10,
+                                      0, 0,   0,  0,  0, 0,  0, 0, 5, 0, 0, 0};
+
+// ---- layout ---------------------------------------------------------------------------------
+__global__ void k_scaffg_layout(const int32_t* __restrict__ perm, const uint8_t* __restrict__ ori,
+                                const uint32_t* __restrict__ len, int32_t P, int32_t Ppad, int32_t n,
+                                uint32_t* __restrict__ origin, uint32_t* __restrict__ bits,
+                                int32_t* __restrict__ pos, int* __restrict__ flag) {
+  const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (p >= Ppad) return;
+  const int g = p / kCandG, pc = p - g * kCandG;
+  uint32_t carry = 0;
+  for (int i0 = 0; i0 < n; i0 += 32) {
+    const int i = i0 + lane;
+    int32_t cid = -1;
+    uint32_t l = 0;
+    if (i < n) {
+      cid = (p < P) ? perm[(size_t)p * n + i] : i;  // pad candidates: identity, forward
+      if ((uint32_t)cid >= (uint32_t)n) { atomicOr(flag, 1); cid = -1; }
+      else l = len[cid];
+    }
+    // inclusive warp scan of the lengths (Hillis-Steele over shuffle-up)
+    uint32_t s = l;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, s, o);
+      if (lane >= o) s += v;
+    }
+    const uint32_t start = carry + s - l;            // exclusive
+    carry += __shfl_sync(0xffffffffu, s, 31);
+    if (cid >= 0) {
+      const bool rev = (p < P) && ori && ori[(size_t)p * n + i] != 0;
+      origin[((size_t)g * n + cid) * kCandG + pc] = rev ? start + l - 1 : start;
+      uint32_t* row = bits + ((size_t)g * n + cid) * 4;
+      if (rev) atomicOr(row + (pc >> 5), 1u << (pc & 31));
+      if (i == 0) atomicOr(row + 2 + (pc >> 5), 1u << (pc & 31));
+      if (p < P) pos[(size_t)p * n + cid] = i;
+    }
+  }
+}
+
+__global__ void k_scaffg_check(const int32_t* __restrict__ perm, int32_t P, int32_t n,
+                               const int32_t* __restrict__ pos, int* __restrict__ flag) {
+  int64_t total = (int64_t)P * n;
+  int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; idx < total; idx += stride) {
+    const int32_t p = (int32_t)(idx / n), i = (int32_t)(idx - (int64_t)p * n);
+    const int32_t cid = perm[idx];
+    if ((uint32_t)cid >= (uint32_t)n) continue;
+    if (pos[(size_t)p * n + cid] != i) atomicOr(flag, 2);
+  }
+}
+
+// 64-bit layout for the API's integer check (lxy_scaffg_layout): one warp per candidate.
+__global__ void k_scaffg_layout64(const int32_t* __restrict__ perm, const uint32_t* __restrict__ len,
+                                  int32_t P, int32_t n, uint64_t* __restrict__ start_by_pos,
+                                  int32_t* __restrict__ pos_by_contig, int* __restrict__ flag) {
+  const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (p >= P) return;
+  uint64_t carry = 0;
+  for (int i0 = 0; i0 < n; i0 += 32) {
+    const int i = i0 + lane;
+    int32_t cid = -1;
+    uint64_t l = 0;
+    if (i < n) {
+      cid = perm[(size_t)p * n + i];
+      if ((uint32_t)cid >= (uint32_t)n) { atomicOr(flag, 1); cid = -1; }
+      else l = len[cid];
+    }
+    uint64_t s = l;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint64_t v = __shfl_up_sync(0xffffffffu, s, o);
+      if (lane >= o) s += v;
+    }
+    if (i < n) start_by_pos[(size_t)p * n + i] = carry + s - l;
+    if (cid >= 0) pos_by_contig[(size_t)p * n + cid] = i;
+    carry += __shfl_sync(0xffffffffu, s, 31);
+  }
+}
+
+__global__ void k_scaffg_link_dist(int64_t L, const uint32_t* __restrict__ a, const uint32_t* __restrict__ xa,
+                                   const uint32_t* __restrict__ b, const uint32_t* __restrict__ xb,
+                                   const uint32_t* __restrict__ len, const uint64_t* __restrict__ start,
+                                   const int32_t* __restrict__ pos, const uint8_t* __restrict__ ori,
+                                   int32_t n, uint64_t* __restrict__ dist, int* __restrict__ flag) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < L; i += stride) {
+    const uint32_t x = a[i], y = b[i];
+    if (x >= (uint32_t)n || y >= (uint32_t)n) { atomicOr(flag, 1); continue; }
+    const int32_t pa = pos[x], pb = pos[y];
+    const bool ra = ori && ori[pa], rb = ori && ori[pb];
+    const uint64_t ca = start[pa] + (ra ? (uint64_t)len[x] - 1 - xa[i] : (uint64_t)xa[i]);
+    const uint64_t cb = start[pb] + (rb ? (uint64_t)len[y] - 1 - xb[i] : (uint64_t)xb[i]);
+    dist[i] = ca > cb ? ca - cb : cb - ca;
+  }
+}
+
+// ---- score ----------------------------------------------------------------------------------
+struct GParams {
+  const uint16_t* rec;
+  const uint32_t* xa;
+  const uint32_t* xb;
+  const void* w;
+  const int64_t* tile_start;
+  const uint32_t* origin;     // [groups][n][64]
+  const uint32_t* bits;       // [groups][n][4]
+  void* partial;              // [units][2][64]: S then H
+  int64_t L;
+  int32_t n, nblk;
+  int32_t groups, splits;
+  uint32_t unit;
+  uint32_t m_lo, m_hi;        // floor(2^64 / unit) + 1 (unused when unit == 1)
+};
+
+template <int WM>
+struct GLane {
+  int32_t s32[2], h32[2];
+  int64_t s64[2], h64[2];
+  double sd[2], hd[2];
+  __device__ __forceinline__ void clear() {
+#pragma unroll
+    for (int j = 0; j < 2; ++j) { s32[j] = h32[j] = 0; s64[j] = h64[j] = 0; sd[j] = hd[j] = 0.0; }
+  }
+  __device__ __forceinline__ void flush() {
+    if (WM == W_UNIT) {
+#pragma unroll
+      for (int j = 0; j < 2; ++j) { s64[j] += s32[j]; h64[j] += h32[j]; s32[j] = h32[j] = 0; }
+    }
+  }
+};
+
+template <int WM>
+__device__ __forceinline__ void g_eval_record(uint32_t r, uint32_t xa, uint32_t xb, int32_t wi, double wd,
+                                              const uint8_t* sA, const uint8_t* sB, const uint8_t* sBitsA,
+                                              const uint8_t* sBitsB, const uint8_t* lut, int lane,
+                                              const GParams& prm, bool unit_is_one, GLane<WM>& L) {
+  const uint32_t aloc = r >> 8, bloc = r & 0xFFu;
+  const uint8_t* rowA = sA + aloc * kRowG + lane * 4;
+  const uint8_t* rowB = sB + bloc * kRowG + lane * 4;
+  const uint4 ba = *(const uint4*)(sBitsA + aloc * 16);   // warp-uniform address: broadcast
+  const uint4 bb = *(const uint4*)(sBitsB + bloc * 16);
+  const uint32_t revA[2] = {ba.x, ba.y}, revB[2] = {bb.x, bb.y};
+  const uint32_t first[2] = {ba.z | bb.z, ba.w | bb.w};
+  uint32_t t[2];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const uint32_t oa = *(const uint32_t*)(rowA + 128 * j), ob = *(const uint32_t*)(rowB + 128 * j);
+    const uint32_t ca = ((revA[j] >> lane) & 1u) ? oa - xa : oa + xa;
+    const uint32_t cb = ((revB[j] >> lane) & 1u) ? ob - xb : ob + xb;
+    const uint32_t d = ca > cb ? ca - cb : cb - ca;
+    uint32_t q;
+    if (unit_is_one) {
+      q = d;
+    } else {  // floor(d / unit) = (d * M) >> 64, exact for every 32-bit d
+      const uint64_t x = (uint64_t)d * prm.m_lo;
+      const uint64_t y = (uint64_t)d * prm.m_hi + (x >> 32);
+      q = (uint32_t)(y >> 32);
+    }
+    t[j] = lut[min(q, 21u)];
+  }
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    if (WM == W_UNIT) L.s32[j] += (int32_t)t[j];
+    else if (WM == W_INT32) L.s64[j] += (int64_t)(int32_t)t[j] * (int64_t)wi;
+    else L.sd[j] += (double)t[j] * wd;
+  }
+  if ((first[0] | first[1]) != 0) {   // rare: some candidate of the group has this contig first
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      if ((first[j] >> lane) & 1u) {
+        if (WM == W_UNIT) L.h32[j] += (int32_t)t[j];
+        else if (WM == W_INT32) L.h64[j] += (int64_t)(int32_t)t[j] * (int64_t)wi;
+        else L.hd[j] += (double)t[j] * wd;
+      }
+    }
+  }
+}
+
+template <int WM>
+__global__ void __launch_bounds__(kThreads, 1) k_scaffg_score(GParams prm) {
+  typedef typename Acc<WM>::type acc_t;
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + kTabG;
+  uint8_t* sBitsA = smem + 2 * kTabG;
+  uint8_t* sBitsB = sBitsA + kBitsG;
+  uint8_t* s_lut = sBitsB + kBitsG;
+  uint64_t* bar = (uint64_t*)(s_lut + 32);
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid < kLutG) s_lut[tid] = c_lutg[tid];
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  uint32_t parity = 0;
+  const bool unit_is_one = (prm.unit == 1);
+
+  const int units = prm.groups * prm.splits;
+  const int64_t npk_all = (prm.L + kPacket - 1) / kPacket;
+  const int64_t ntiles = (int64_t)prm.nblk * (prm.nblk + 1) / 2;
+  for (int u = blockIdx.x; u < units; u += gridDim.x) {
+    const int g = u / prm.splits, s = u - g * prm.splits;
+    const int64_t lo = (npk_all * s / prm.splits) * kPacket;
+    const int64_t hi = min((npk_all * (s + 1) / prm.splits) * kPacket, prm.L);
+    GLane<WM> acc;
+    acc.clear();
+    if (lo < hi) {
+      int64_t tl = 0, th = ntiles;
+      while (th - tl > 1) {
+        const int64_t mid = (tl + th) >> 1;
+        if (prm.tile_start[mid] <= lo) tl = mid; else th = mid;
+      }
+      int64_t t = tl;
+      int32_t I = 0;
+      {
+        int32_t a = 0, b = prm.nblk;
+        while (b - a > 1) {
+          const int32_t m = (a + b) >> 1;
+          if (tile_row_start(m, prm.nblk) <= t) a = m; else b = m;
+        }
+        I = a;
+      }
+      int32_t J = I + (int32_t)(t - tile_row_start(I, prm.nblk));
+      int64_t cur = lo;
+      while (cur < hi) {
+        const int64_t tend = prm.tile_start[t + 1];
+        if (tend <= cur) {
+          ++t; ++J;
+          if (J == prm.nblk) { ++I; J = I; }
+          continue;
+        }
+        const int64_t seg_end = min(hi, tend);
+        __syncthreads();
+        if (tid == 0) {
+          const int rowsA = min(kBlk, prm.n - I * kBlk), rowsB = min(kBlk, prm.n - J * kBlk);
+          const size_t ra = (size_t)g * prm.n + (size_t)I * kBlk, rb = (size_t)g * prm.n + (size_t)J * kBlk;
+          fence_proxy_async();
+          mbar_expect_tx(bar, (uint32_t)(rowsA + rowsB) * (kRowG + 16));
+          tma_bulk_g2s(sA, prm.origin + ra * kCandG, (uint32_t)rowsA * kRowG, bar);
+          tma_bulk_g2s(sB, prm.origin + rb * kCandG, (uint32_t)rowsB * kRowG, bar);
+          tma_bulk_g2s(sBitsA, prm.bits + ra * 4, (uint32_t)rowsA * 16, bar);
+          tma_bulk_g2s(sBitsB, prm.bits + rb * 4, (uint32_t)rowsB * 16, bar);
+        }
+        mbar_wait(bar, parity);
+        parity ^= 1;
+
+        const int64_t p_first = cur / kPacket, p_last = (seg_end - 1) / kPacket;
+        int64_t done = 0;  // packets this warp has scored since the last flush
+        for (int64_t pk = p_first + warp; pk <= p_last; pk += kWarps) {
+          const int64_t base = pk * kPacket;
+          const uint4 v = ldg_stream_v4(prm.rec + base);
+          const uint4 xa0 = ldg_stream_v4(prm.xa + base), xa1 = ldg_stream_v4(prm.xa + base + 4);
+          const uint4 xb0 = ldg_stream_v4(prm.xb + base), xb1 = ldg_stream_v4(prm.xb + base + 4);
+          const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+          const uint32_t xav[8] = {xa0.x, xa0.y, xa0.z, xa0.w, xa1.x, xa1.y, xa1.z, xa1.w};
+          const uint32_t xbv[8] = {xb0.x, xb0.y, xb0.z, xb0.w, xb1.x, xb1.y, xb1.z, xb1.w};
+          int32_t wi[kPacket];
+          double wd[kPacket];
+          if (WM == W_INT32) {
+            const uint4* wp = reinterpret_cast<const uint4*>((const int32_t*)prm.w + base);
+            const uint4 x = __ldg(wp), y = __ldg(wp + 1);
+            wi[0] = x.x; wi[1] = x.y; wi[2] = x.z; wi[3] = x.w; wi[4] = y.x; wi[5] = y.y; wi[6] = y.z; wi[7] = y.w;
+          } else if (WM == W_F64) {
+            const double2* wp = reinterpret_cast<const double2*>((const double*)prm.w + base);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { const double2 d2 = __ldg(wp + q); wd[2 * q] = d2.x; wd[2 * q + 1] = d2.y; }
+          }
+          const int k0 = (int)max((int64_t)0, cur - base), k1 = (int)min((int64_t)kPacket, seg_end - base);
+#pragma unroll
+          for (int k = 0; k < kPacket; ++k) {
+            if (k < k0 || k >= k1) continue;
+            const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
+            g_eval_record<WM>(r, xav[k], xbv[k], WM == W_INT32 ? wi[k] : 0, WM == W_F64 ? wd[k] : 0.0,
+                              sA, sB, sBitsA, sBitsB, s_lut, lane, prm, unit_is_one, acc);
+          }
+          if (WM == W_UNIT && (++done & 0xFFFF) == 0) acc.flush();
+        }
+        cur = seg_end;
+      }
+    }
+    acc.flush();
+    __syncthreads();
+    acc_t* red = (acc_t*)smem;  // [kWarps][2][64]
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      acc_t sv, hv;
+      if (WM == W_F64) { sv = (acc_t)acc.sd[j]; hv = (acc_t)acc.hd[j]; }
+      else { sv = (acc_t)acc.s64[j]; hv = (acc_t)acc.h64[j]; }
+      red[(warp * 2 + 0) * kCandG + lane + 32 * j] = sv;
+      red[(warp * 2 + 1) * kCandG + lane + 32 * j] = hv;
+    }
+    __syncthreads();
+    if (tid < 2 * kCandG) {
+      acc_t sum = 0;
+      for (int wq = 0; wq < kWarps; ++wq) sum += red[wq * 2 * kCandG + tid];
+      ((acc_t*)prm.partial)[(size_t)u * 2 * kCandG + tid] = sum;
+    }
+  }
+}
+
+template <int WM>
+__global__ void k_scaffg_finish(int32_t P, int32_t splits, const void* __restrict__ partial,
+                                double* __restrict__ out, int64_t* __restrict__ x100) {
+  typedef typename Acc<WM>::type acc_t;
+  const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (p >= P) return;
+  const int g = p / kCandG, pc = p - g * kCandG;
+  acc_t S = 0, H = 0;
+  for (int s = lane; s < splits; s += 32) {
+    const acc_t* row = (const acc_t*)partial + ((size_t)g * splits + s) * 2 * kCandG;
+    S += row[pc];
+    H += row[kCandG + pc];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    if (WM == W_F64) {
+      S += (acc_t)__shfl_xor_sync(0xffffffffu, (double)S, o);
+      H += (acc_t)__shfl_xor_sync(0xffffffffu, (double)H, o);
+    } else {
+      S += (acc_t)__shfl_xor_sync(0xffffffffu, (long long)S, o);
+      H += (acc_t)__shfl_xor_sync(0xffffffffu, (long long)H, o);
+    }
+  }
+  if (lane != 0) return;
+  const acc_t tot = S + S - H;
+  if (WM == W_F64) {
+    out[p] = -((double)tot / 100.0);
+    if (x100) x100[p] = INT64_MIN;
+  } else {
+    out[p] = -((double)(int64_t)tot / 100.0);
+    if (x100) x100[p] = (int64_t)tot;
+  }
+}
+
+template <int WM>
+int launch_g(lxy_ctx* c, const GParams& prm, int grid) {
+  constexpr int smem = 2 * kTabG + 2 * kBitsG + 32 + 16;
+  static bool configured[64] = {};
+  if (!configured[c->cfg.device & 63]) {
+    LXY_CUDA(cudaFuncSetAttribute(k_scaffg_score<WM>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured[c->cfg.device & 63] = true;
+  }
+  k_scaffg_score<WM><<<grid, kThreads, smem, c->stream>>>(prm);
+  LXY_CUDA(cudaGetLastError());
+  return LXY_OK;
+}
+
+}  // namespace
+
+int scaffg_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int32_t P,
+                 double* out_dev, int64_t* x100_dev) {
+  ScaffLinks& S = c->scaff;
+  if (!S.ready || !S.gprofile) { set_error("scaffg score: G-profile links not set"); return LXY_ERR_STATE; }
+  if (P <= 0) return LXY_OK;
+  cudaStream_t st = c->stream;
+  const int n = S.n;
+  const int groups = (P + kCandG - 1) / kCandG;
+  const int Ppad = groups * kCandG;
+  LXY_TRY(c->d_posA.reserve(4 * (size_t)Ppad * n));           // origin table
+  LXY_TRY(c->d_posB.reserve(16 * (size_t)groups * n));        // bit rows
+  LXY_TRY(c->d_start.reserve(4 * (size_t)P * n));             // pos (validation)
+  LXY_TRY(c->d_flag.reserve(64));
+  LXY_CUDA(cudaMemsetAsync(c->d_flag.p, 0, 64, st));
+  LXY_CUDA(cudaEventRecord(c->ev[0], st));
+  LXY_CUDA(cudaMemsetAsync(c->d_posB.p, 0, 16 * (size_t)groups * n, st));
+  int launches = 0;
+  k_scaffg_layout<<<(Ppad * 32 + 255) / 256, 256, 0, st>>>(perm_dev, ori_dev, S.len.as<uint32_t>(), P, Ppad, n,
+                                                          c->d_posA.as<uint32_t>(), c->d_posB.as<uint32_t>(),
+                                                          c->d_start.as<int32_t>(), c->d_flag.as<int>());
+  ++launches;
+  if (!(c->cfg.flags & LXY_FLAG_NO_VALIDATE)) {
+    k_scaffg_check<<<grid_for((int64_t)P * n, 256, c->sm_count), 256, 0, st>>>(perm_dev, P, n, c->d_start.as<int32_t>(), c->d_flag.as<int>());
+    ++launches;
+  }
+  LXY_CUDA(cudaGetLastError());
+  LXY_CUDA(cudaEventRecord(c->ev[1], st));
+
+  const int64_t npk = (S.L + kPacket - 1) / kPacket;
+  int splits = (2 * c->sm_count + groups - 1) / groups;
+  if (splits < 1) splits = 1;
+  if ((int64_t)splits * 64 > npk) splits = (int)(npk / 64 > 0 ? npk / 64 : 1);
+  const int units = groups * splits;
+  const int grid = units < c->sm_count ? units : c->sm_count;
+  LXY_TRY(c->d_partial.reserve(8 * (size_t)units * 2 * kCandG));
+  GParams prm;
+  prm.rec = S.rec.as<uint16_t>();
+  prm.xa = S.xa.as<uint32_t>();
+  prm.xb = S.xb.as<uint32_t>();
+  prm.w = S.w.p;
+  prm.tile_start = S.tile_start.as<int64_t>();
+  prm.origin = c->d_posA.as<uint32_t>();
+  prm.bits = c->d_posB.as<uint32_t>();
+  prm.partial = c->d_partial.p;
+  prm.L = S.L;
+  prm.n = n;
+  prm.nblk = S.nblk;
+  prm.groups = groups;
+  prm.splits = splits;
+  prm.unit = S.unit;
+  uint64_t M = 0;
+  if (S.unit > 1) M = (~(uint64_t)0) / S.unit + 1;  // floor((2^64 - 1) / u) + 1 == floor(2^64 / u) + 1 unless u | 2^64
+  if (S.unit > 1 && (S.unit & (S.unit - 1)) == 0) M = ((uint64_t)1 << 63) / (S.unit >> 1);  // power of two: exact 2^64 / u
+  prm.m_lo = (uint32_t)M;
+  prm.m_hi = (uint32_t)(M >> 32);
+  if (S.L > 0) {
+    int rc = S.wmode == W_UNIT ? launch_g<W_UNIT>(c, prm, grid)
+           : S.wmode == W_INT32 ? launch_g<W_INT32>(c, prm, grid) : launch_g<W_F64>(c, prm, grid);
+    LXY_TRY(rc);
+    ++launches;
+  } else {
+    LXY_CUDA(cudaMemsetAsync(c->d_partial.p, 0, 8 * (size_t)units * 2 * kCandG, st));
+  }
+  LXY_CUDA(cudaEventRecord(c->ev[2], st));
+  if (S.wmode == W_UNIT) k_scaffg_finish<W_UNIT><<<(P + 7) / 8, 256, 0, st>>>(P, splits, c->d_partial.p, out_dev, x100_dev);
+  else if (S.wmode == W_INT32) k_scaffg_finish<W_INT32><<<(P + 7) / 8, 256, 0, st>>>(P, splits, c->d_partial.p, out_dev, x100_dev);
+  else k_scaffg_finish<W_F64><<<(P + 7) / 8, 256, 0, st>>>(P, splits, c->d_partial.p, out_dev, x100_dev);
+  ++launches;
+  LXY_CUDA(cudaGetLastError());
+  LXY_CUDA(cudaEventRecord(c->ev[3], st));
+  c->timing.launches = launches;
+  c->timing.grid = grid;
+  c->timing.link_bytes = (int64_t)groups * S.L * (10 + (S.wmode == W_INT32 ? 4 : S.wmode == W_F64 ? 8 : 0));
+  c->timing.table_bytes = 0;
+  return LXY_OK;
+}
+
+int scaffg_layout64(lxy_ctx* c, const int32_t* perm_dev, int32_t P, uint64_t* start_dev, int32_t* pos_dev) {
+  ScaffLinks& S = c->scaff;
+  if (!S.ready || !S.gprofile) { set_error("scaffg layout: G-profile links not set"); return LXY_ERR_STATE; }
+  LXY_TRY(c->d_flag.reserve(64));
+  LXY_CUDA(cudaMemsetAsync(c->d_flag.p, 0, 64, c->stream));
+  k_scaffg_layout64<<<(P * 32 + 255) / 256, 256, 0, c->stream>>>(perm_dev, S.len.as<uint32_t>(), P, S.n, start_dev, pos_dev, c->d_flag.as<int>());
+  LXY_CUDA(cudaGetLastError());
+  return LXY_OK;
+}
+
+int scaffg_link_distances(lxy_ctx* c, int64_t L, const uint32_t* a, const uint32_t* xa, const uint32_t* b,
+                          const uint32_t* xb, const uint64_t* start_dev, const int32_t* pos_dev,
+                          const uint8_t* ori_dev, uint64_t* dist_dev) {
+  ScaffLinks& S = c->scaff;
+  if (L > 0) {
+    k_scaffg_link_dist<<<grid_for(L, 256, c->sm_count), 256, 0, c->stream>>>(L, a, xa, b, xb, S.len.as<uint32_t>(), start_dev, pos_dev, ori_dev, S.n, dist_dev, c->d_flag.as<int>());
+    LXY_CUDA(cudaGetLastError());
+  }
+  return LXY_OK;
+}
+
+}  // namespace lxy
