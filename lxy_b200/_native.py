@@ -23,7 +23,6 @@ SYMBOLS = [
     "lxy_scaff_score_batch", "lxy_scaff_score_batch_dev", "lxy_scaff_positions",
     "lxy_scaff_link_distances", "lxy_links_get", "lxy_ctx_set_links_g", "lxy_scaffg_score_batch",
     "lxy_scaffg_score_batch_dev",
-    "lxy_scaffg_score_batch_dev",
     "lxy_scaffg_layout", "lxy_scaffg_link_distances", "lxy_ctx_set_phase_links",
     "lxy_phase_score_batch", "lxy_phase_score_batch_dev", "lxy_rank",
 ]
