@@ -1,6 +1,6 @@
 // scaffg_kernels.cu — scaffolding fitness, G-profile: the generalisation BASELINE.json's north_star
 // describes (contig lengths, orientations, per-link in-contig offsets, genomic distance -> decay).
-// It has no counterpart in the reference; oracle/lxy_oracle.cpp (scaffg_*) defines it, constrained
+// It has no counterpart in the reference; the CPU checker under oracle/ (its scaffg_* functions) defines it, constrained
 // to collapse to scaff.go:246-310 bit for bit when len == 1, x == 0, unit == 1.
 //
 //   k_scaffg_layout  one warp per candidate: warp prefix scan (shuffle-up) of the permuted contig
