@@ -1,0 +1,61 @@
+"""The reference-facing host interface on the GPU: genomes scored through ScaffScorer / PhaseScorer
+(the `sfunc` of the reference) and the per-generation ScoreBatch pre-pass, against the oracle run
+on the reference's own fixture files."""
+import random
+
+import numpy as np
+import pytest
+
+import _oracle as O
+from lxy_b200 import host as H
+
+pytestmark = pytest.mark.gpu
+
+
+def test_scaffold_fixture_through_the_reference_interface(golden, golden_files):
+    links = H.LoadLinks(golden_files["test_ctg"])            # scaff/_testdata/test.ctg.links
+    ref = O.Links.load(golden_files["test_ctg"])
+    sc = H.ScaffScorer(links)
+    genome = H.NewOrderedIntGenome(links.IntIDs(), sc.score)  # scaff.go:89-92
+    genome.data = links
+    assert genome.Score() == pytest.approx(-319.2999999999998, rel=1e-12)
+    rng = random.Random(7)
+    pop = []
+    for _ in range(40):                                        # gao.Init(40, genome), scaff.go:94
+        g = genome.Copy()
+        g.Randomize(rng)
+        pop.append(g)
+    assert sc.ScoreBatch(pop) == 40 and all(g.hasscore for g in pop)
+    before = sc.scores
+    for g in pop:
+        assert g.Score() == pytest.approx(ref.scaff_score(g.Gene), rel=1e-9)
+    assert sc.scores == before                                 # memo hits: no further device calls
+    child, _ = pop[0].Crossover(pop[1], 2, 6)
+    assert not child.hasscore and sc.ScoreBatch(pop + [child]) == 1
+    assert child.Score() == pytest.approx(ref.scaff_score(child.Gene), rel=1e-9)
+    best = H.Rank(pop)[0]
+    assert best.Score() == min(g.Score() for g in pop)
+    bad = H.NewOrderedIntGenome([0] * links.Size(), sc.score)  # not a permutation
+    assert bad.Score() == float("inf")                         # worst fitness, never elite
+    sc.close()
+
+
+def test_phasing_fixture_through_the_reference_interface(golden_files):
+    links = H.LoadLinks(golden_files["test_var"])             # phase/_testdata/test.var.links
+    ref = O.Links.load(golden_files["test_var"])
+    sc = H.PhaseScorer(links)
+    g = H.NewFixedBitstringGenome([False] * links.Size(), sc.score)   # phase.go:59
+    assert g.Score() == -265.0
+    truth = [c == "A" for c in "AABAAAAAABA"]
+    t = H.NewFixedBitstringGenome(truth, sc.score)
+    assert t.Score() == -679.0
+    rng = random.Random(3)
+    pop = []
+    for _ in range(10):                                        # gao.Init(10, genome), phase.go:63
+        c = g.Copy()
+        c.Randomize(rng)
+        pop.append(c)
+    sc.ScoreBatch(pop)
+    for c in pop:
+        assert c.Score() == ref.phase_score([int(b) for b in c.Gene])
+    sc.close()
