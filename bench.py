@@ -365,12 +365,14 @@ def main():
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                          "kernel": "k_scaff_score", "algorithmic_bytes_per_launch": alg_bytes,
                          "smem_wavefront": {
-                             "what": "the roof that binds: 8 shared-memory wavefronts per 128 "
-                                     "evaluations, one wavefront/cycle/SM -> 16 evals/cycle/SM",
-                             "peak_evals_per_s": 16.0 * 148 * (clocks["sm_mhz"] or 1965.0) * 1e6,
+                             "what": "the roof that binds: per record-warp (128 evaluations) 2 "
+                                     "wavefronts for row B + 4 decay-table look-ups + 2/8 for row A "
+                                     "(gathered once per 8-record packet) = 6.25 shared-memory "
+                                     "wavefronts, one wavefront/cycle/SM -> 20.48 evals/cycle/SM",
+                             "peak_evals_per_s": 20.48 * 148 * (clocks["sm_mhz"] or 1965.0) * 1e6,
                              "achieved_evals_per_s": float(P_loc) * L / (k_ms * 1e-3),
                              "frac": float(P_loc) * L / (k_ms * 1e-3)
-                                     / (16.0 * 148 * (clocks["sm_mhz"] or 1965.0) * 1e6)},
+                                     / (20.48 * 148 * (clocks["sm_mhz"] or 1965.0) * 1e6)},
                          "note": "each record byte is reused by every local candidate "
                                  f"({P_loc} evaluations per 2-byte record), so the kernel sits on "
                                  "the shared-memory-gather/issue roof, not the HBM roof; see "

@@ -112,43 +112,39 @@ struct Lane {
   }
 };
 
-// One record against the CPL candidates of this lane.
+// This lane's slice of one table row (CPL candidates) as up to four 32-bit words.
+template <int CPL, bool WIDE>
+__device__ __forceinline__ void load_row(const uint8_t* row, uint32_t (&X)[4]) {
+  constexpr int BYTES = CPL * (WIDE ? 4 : 2);
+  if (BYTES == 16) {
+    const uint4 a = *(const uint4*)row;
+    X[0] = a.x; X[1] = a.y; X[2] = a.z; X[3] = a.w;
+  } else if (BYTES == 8) {
+    const uint2 a = *(const uint2*)row;
+    X[0] = a.x; X[1] = a.y;
+  } else if (BYTES == 4) {
+    X[0] = *(const uint32_t*)row;
+  } else {
+    X[0] = *(const uint16_t*)row;
+  }
+}
+
+// One record against the CPL candidates of this lane, row A already in registers.
 //   narrow tables (u16): A = pos + kBias + 1, B = -pos; VIADDMNMX.S16x2.RELU gives, per half-word,
 //   v = clamp(pos a - pos b + kBias + 1, 0, kMiss + 1): one instruction for two candidates.
 //   wide tables (u32): the same with VIADDMNMX.RELU on full words.
 // v indexes the decay table: v in [1, 41] <=> |d| <= 20; 0 and 42 are the two "far" entries.
 template <int CPL, bool WIDE, int WM>
-__device__ __forceinline__ void eval_record(const uint8_t* rowA, const uint8_t* rowB,
+__device__ __forceinline__ void eval_record(const uint32_t (&A)[4], const uint8_t* rowB,
                                             const uint8_t* lut, const double* lutd, int32_t wi,
                                             double wd, Lane<CPL, WM>& L) {
   constexpr uint32_t kHi = kMiss + 1;  // 42
-  uint32_t idx[CPL];
+  uint32_t idx[CPL], B[4];
+  load_row<CPL, WIDE>(rowB, B);
   if (WIDE) {
-    uint32_t A[4], B[4];
-    if (CPL == 4) {
-      const uint4 a = *(const uint4*)rowA, b = *(const uint4*)rowB;
-      A[0] = a.x; A[1] = a.y; A[2] = a.z; A[3] = a.w; B[0] = b.x; B[1] = b.y; B[2] = b.z; B[3] = b.w;
-    } else if (CPL == 2) {
-      const uint2 a = *(const uint2*)rowA, b = *(const uint2*)rowB;
-      A[0] = a.x; A[1] = a.y; B[0] = b.x; B[1] = b.y;
-    } else {
-      A[0] = *(const uint32_t*)rowA; B[0] = *(const uint32_t*)rowB;
-    }
 #pragma unroll
     for (int j = 0; j < CPL; ++j) idx[j] = (uint32_t)__viaddmin_s32_relu((int)A[j], (int)B[j], (int)kHi);
   } else {
-    uint32_t A[4], B[4];
-    if (CPL == 8) {
-      const uint4 a = *(const uint4*)rowA, b = *(const uint4*)rowB;
-      A[0] = a.x; A[1] = a.y; A[2] = a.z; A[3] = a.w; B[0] = b.x; B[1] = b.y; B[2] = b.z; B[3] = b.w;
-    } else if (CPL == 4) {
-      const uint2 a = *(const uint2*)rowA, b = *(const uint2*)rowB;
-      A[0] = a.x; A[1] = a.y; B[0] = b.x; B[1] = b.y;
-    } else if (CPL == 2) {
-      A[0] = *(const uint32_t*)rowA; B[0] = *(const uint32_t*)rowB;
-    } else {
-      A[0] = *(const uint16_t*)rowA; B[0] = *(const uint16_t*)rowB;
-    }
 #pragma unroll
     for (int q = 0; q < (CPL + 1) / 2; ++q) {
       const uint32_t m = __viaddmin_s16x2_relu(A[q], B[q], kHi | (kHi << 16));
@@ -165,13 +161,20 @@ __device__ __forceinline__ void eval_record(const uint8_t* rowA, const uint8_t* 
 }
 
 // Records k in [k0, k1) of one 8-record packet (k0 = 0, k1 = 8 compiles to straight-line code).
-template <int CPL, bool WIDE, int WM>
+// SAME_A: every record of the packet has the same a (records are sorted by (a, b) inside a tile,
+// so this is the common case): row A is gathered once for the whole packet.
+template <int CPL, bool WIDE, int WM, bool SAME_A>
 __device__ __forceinline__ void eval_packet(const uint4 v, const uint8_t* laneA, const uint8_t* laneB,
                                             uint32_t lane_off, const uint8_t* lut, const double* lutd,
                                             const int32_t* wi, const double* wd, int k0, int k1,
                                             Lane<CPL, WM>& L) {
   constexpr int ROWB = 32 * CPL * (WIDE ? 4 : 2);
   const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+  uint32_t A[4] = {0, 0, 0, 0};
+  if (SAME_A) {
+    if (ROWB == 256) load_row<CPL, WIDE>(laneA - lane_off + __byte_perm(v.x, lane_off, 0x7614), A);
+    else load_row<CPL, WIDE>(laneA + ((v.x >> 8) & 0xFFu) * ROWB, A);
+  }
 #pragma unroll
   for (int k = 0; k < kPacket; ++k) {
     if (k < k0 || k >= k1) continue;
@@ -188,7 +191,8 @@ __device__ __forceinline__ void eval_packet(const uint4 v, const uint8_t* laneA,
       rowA = laneA + (r >> 8) * ROWB;
       rowB = laneB + (r & 0xFFu) * ROWB;
     }
-    eval_record<CPL, WIDE, WM>(rowA, rowB, lut, lutd, WM == W_INT32 ? wi[k] : 0,
+    if (!SAME_A) load_row<CPL, WIDE>(rowA, A);
+    eval_record<CPL, WIDE, WM>(A, rowB, lut, lutd, WM == W_INT32 ? wi[k] : 0,
                                WM == W_F64 ? wd[k] : 0.0, L);
   }
 }
@@ -305,7 +309,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
           const int k0 = (int)(cur - base), k1 = (int)min((int64_t)kPacket, seg_end - base);
 #pragma unroll 1
           for (int k = k0; k < k1; ++k)
-            eval_packet<CPL, WIDE, WM>(v, laneA, laneB, lane_off, s_lut, s_lutd, wi, wd, k, k + 1, acc);
+            eval_packet<CPL, WIDE, WM, false>(v, laneA, laneB, lane_off, s_lut, s_lutd, wi, wd, k, k + 1, acc);
         }
         if (tail_partial && warp == 1 && !(head_partial && p_last == p_first)) {
           const int64_t base = p_last * kPacket;
@@ -314,7 +318,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
           const int k1 = (int)(seg_end - base);
 #pragma unroll 1
           for (int k = 0; k < k1; ++k)
-            eval_packet<CPL, WIDE, WM>(v, laneA, laneB, lane_off, s_lut, s_lutd, wi, wd, k, k + 1, acc);
+            eval_packet<CPL, WIDE, WM, false>(v, laneA, laneB, lane_off, s_lut, s_lutd, wi, wd, k, k + 1, acc);
         }
         // full packets: straight-line code, next packet's load in flight while this one is scored
         const int64_t f0 = p_first + (head_partial ? 1 : 0);
@@ -335,7 +339,11 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
               const uint4 v = vn;
               if (it + kWarps < cnt) vn = ldg_stream_v4(rp + (size_t)(it + kWarps) * kPacket);
               load_weights<WM>(prm.w, wbase + (c0 + it) * kPacket, wi, wd);
-              eval_packet<CPL, WIDE, WM>(v, laneA, laneB, lane_off, s_lut, s_lutd, wi, wd, 0, kPacket, acc);
+              // sorted by (a, b): first a == last a  <=>  one a for the whole packet (warp-uniform)
+              if (((v.x >> 8) & 0xFFu) == (v.w >> 24))
+                eval_packet<CPL, WIDE, WM, true>(v, laneA, laneB, lane_off, s_lut, s_lutd, wi, wd, 0, kPacket, acc);
+              else
+                eval_packet<CPL, WIDE, WM, false>(v, laneA, laneB, lane_off, s_lut, s_lutd, wi, wd, 0, kPacket, acc);
             }
             acc.flush();
           }
