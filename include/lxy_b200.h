@@ -44,11 +44,17 @@ typedef enum lxy_status {
 
 #define LXY_FLAG_NO_VALIDATE 1u /* skip the on-device permutation / bit check                  */
 
+/* which kernel scores the R-profile (lxy_scaff_score_batch*) */
+#define LXY_PATH_STREAM 0 /* stream every record for every candidate (north_star design; default)  */
+#define LXY_PATH_PAIRS 1  /* aggregate the records into a dense pair table at set_links and score a  \
+                             candidate with the reference's own 6n table gathers (cost independent  \
+                             of the number of records; same results)                                */
+
 typedef struct lxy_cfg {
   int32_t device;   /* CUDA ordinal                                                          */
   int32_t acc_mode; /* LXY_ACC_*                                                             */
   uint32_t flags;   /* LXY_FLAG_*                                                            */
-  int32_t reserved;
+  int32_t path;     /* LXY_PATH_*                                                            */
 } lxy_cfg;
 
 typedef struct lxy_ctx lxy_ctx;

@@ -28,6 +28,7 @@ SYMBOLS = [
 ]
 
 ACC_AUTO, ACC_F64, ACC_INT = 0, 1, 2
+PATH_STREAM, PATH_PAIRS = 0, 1
 FLAG_NO_VALIDATE = 1
 
 
@@ -39,7 +40,7 @@ class LxyError(RuntimeError):
 
 class Cfg(C.Structure):
     _fields_ = [("device", C.c_int32), ("acc_mode", C.c_int32), ("flags", C.c_uint32),
-                ("reserved", C.c_int32)]
+                ("path", C.c_int32)]
 
 
 class Timing(C.Structure):
@@ -134,9 +135,9 @@ def rank(scores):
 class Context:
     """One lxy_ctx: a CUDA device, its stream, the resident link stores."""
 
-    def __init__(self, device=0, acc_mode=ACC_AUTO, flags=0):
+    def __init__(self, device=0, acc_mode=ACC_AUTO, flags=0, path=PATH_STREAM):
         self._h = C.c_void_p()
-        cfg = Cfg(device, acc_mode, flags, 0)
+        cfg = Cfg(device, acc_mode, flags, path)
         _check(lib().lxy_ctx_create(C.byref(cfg), C.byref(self._h)))
         self.device = device
         self.n = 0

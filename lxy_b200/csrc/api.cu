@@ -87,6 +87,7 @@ int lxy_ctx_create(const lxy_cfg* cfg, lxy_ctx** out) {
   lxy_cfg cf{};
   if (cfg) cf = *cfg;
   if (cf.acc_mode < LXY_ACC_AUTO || cf.acc_mode > LXY_ACC_INT) { set_error("bad acc_mode"); return LXY_ERR_ARG; }
+  if (cf.path != LXY_PATH_STREAM && cf.path != LXY_PATH_PAIRS) { set_error("bad path"); return LXY_ERR_ARG; }
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || ndev <= 0) {
@@ -131,7 +132,7 @@ void lxy_ctx_destroy(lxy_ctx* c) {
   cudaSetDevice(c->cfg.device);
   if (c->stream) cudaStreamSynchronize(c->stream);
   if (c->stream2) cudaStreamSynchronize(c->stream2);
-  DevBuf* bufs[] = {&c->scaff.rec, &c->scaff.w, &c->scaff.tile_start, &c->scaff.len, &c->scaff.xa, &c->scaff.xb,
+  DevBuf* bufs[] = {&c->scaff.rec, &c->scaff.w, &c->scaff.tile_start, &c->scaff.len, &c->scaff.xa, &c->scaff.xb, &c->scaff.dense,
                     &c->phase.rec, &c->phase.w, &c->d_perm, &c->d_ori, &c->d_out, &c->d_x100,
                     &c->d_posA, &c->d_posB, &c->d_partial, &c->d_corr, &c->d_flag, &c->d_genes,
                     &c->d_gbits, &c->d_tmp0, &c->d_tmp1, &c->d_tmp2, &c->d_tmp3, &c->d_start};
@@ -174,7 +175,8 @@ int lxy_ctx_set_links(lxy_ctx* c, int32_t n_ids, int64_t n_links, const uint32_t
   CHECK_CTX(c);
   LinkInput in;
   in.n = n_ids; in.L = n_links; in.a = a; in.b = b; in.w = w;
-  return build_scaff_links(c, in);
+  LXY_TRY(build_scaff_links(c, in));
+  return c->cfg.path == LXY_PATH_PAIRS ? build_pair_table(c) : LXY_OK;
 }
 
 int lxy_ctx_set_links_dev(lxy_ctx* c, int32_t n_ids, int64_t n_links, const uint32_t* a_dev,
@@ -182,7 +184,8 @@ int lxy_ctx_set_links_dev(lxy_ctx* c, int32_t n_ids, int64_t n_links, const uint
   CHECK_CTX(c);
   LinkInput in;
   in.n = n_ids; in.L = n_links; in.a = a_dev; in.b = b_dev; in.w = w_dev; in.on_device = true;
-  return build_scaff_links(c, in);
+  LXY_TRY(build_scaff_links(c, in));
+  return c->cfg.path == LXY_PATH_PAIRS ? build_pair_table(c) : LXY_OK;
 }
 
 static int finish_flags(lxy_ctx* c, const char* what) {
@@ -196,12 +199,17 @@ static int finish_flags(lxy_ctx* c, const char* what) {
 }
 
 
+static int scaff_dispatch(lxy_ctx* c, const int32_t* perm_dev, int32_t P, double* out_dev, int64_t* x100_dev) {
+  if (c->cfg.path == LXY_PATH_PAIRS) return pairs_score(c, perm_dev, P, out_dev, x100_dev);
+  return scaff_score(c, perm_dev, nullptr, P, out_dev, x100_dev);
+}
+
 int lxy_scaff_score_batch_dev(lxy_ctx* c, const int32_t* perm_dev, int32_t P, double* out_dev,
                               int64_t* x100_dev) {
   CHECK_CTX(c);
   if (P < 0 || (P > 0 && (!perm_dev || !out_dev))) { set_error("score_batch_dev: bad argument"); return LXY_ERR_ARG; }
   if (P == 0) return LXY_OK;
-  LXY_TRY(scaff_score(c, perm_dev, nullptr, P, out_dev, x100_dev));
+  LXY_TRY(scaff_dispatch(c, perm_dev, P, out_dev, x100_dev));
   c->timing_pending = 1;
   // With LXY_FLAG_NO_VALIDATE nothing has to come back to the host: the call is asynchronous on
   // the context's stream (lxy_ctx_sync / lxy_ctx_get_timing wait for it).
@@ -226,7 +234,7 @@ int lxy_scaff_score_batch(lxy_ctx* c, const int32_t* perm, int32_t P, double* ou
   std::memcpy(c->h_pin, perm, pbytes);
   LXY_CUDA(cudaEventRecord(c->ev[4], c->stream));
   LXY_CUDA(cudaMemcpyAsync(c->d_perm.p, c->h_pin, pbytes, cudaMemcpyHostToDevice, c->stream));
-  LXY_TRY(scaff_score(c, c->d_perm.as<int32_t>(), nullptr, P, c->d_out.as<double>(), c->d_x100.as<int64_t>()));
+  LXY_TRY(scaff_dispatch(c, c->d_perm.as<int32_t>(), P, c->d_out.as<double>(), c->d_x100.as<int64_t>()));
   char* hout = (char*)c->h_pin + pbytes;
   LXY_CUDA(cudaMemcpyAsync(hout, c->d_out.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, c->stream));
   LXY_CUDA(cudaMemcpyAsync(hout + 8 * (size_t)P, c->d_x100.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, c->stream));

@@ -70,6 +70,9 @@ struct ScaffLinks {
   DevBuf xa, xb;            // uint32 in-contig offsets per record, same order as rec
   uint32_t unit = 1;
   uint64_t total_len = 0;
+  // pair-table path (cfg.path == LXY_PATH_PAIRS): dense symmetric n x n table, int32 or double
+  DevBuf dense;
+  bool dense_ready = false;
 };
 
 struct PhaseLinks {
@@ -137,6 +140,10 @@ int scaffg_layout64(lxy_ctx* c, const int32_t* perm_dev, int32_t P, uint64_t* st
 int scaffg_link_distances(lxy_ctx* c, int64_t L, const uint32_t* a, const uint32_t* xa,
                           const uint32_t* b, const uint32_t* xb, const uint64_t* start_dev,
                           const int32_t* pos_dev, const uint8_t* ori_dev, uint64_t* dist_dev);
+
+// pair_kernels.cu
+int build_pair_table(lxy_ctx* c);
+int pairs_score(lxy_ctx* c, const int32_t* perm_dev, int32_t P, double* out_dev, int64_t* x100_dev);
 
 // phase_kernels.cu
 int phase_score(lxy_ctx* c, const uint8_t* genes_dev, int32_t P, int64_t* out_i64_dev,

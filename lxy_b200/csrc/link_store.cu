@@ -146,6 +146,7 @@ __global__ void k_iota(int64_t L, uint32_t* __restrict__ out) {
 int build_scaff_links(lxy_ctx* c, const LinkInput& in) {
   ScaffLinks& S = c->scaff;
   S.ready = false;
+  S.dense_ready = false;
   const int32_t n = in.n;
   const int64_t L = in.L;
   const bool G = (in.len != nullptr);
