@@ -234,6 +234,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the pair-table / G-profile / phasing side measurements")
     args = ap.parse_args()
     n, L, P, seed, pseed = WORKLOADS[args.workload]
     if args.impl == "reference":
@@ -267,20 +269,12 @@ def main():
     t_build = time.perf_counter() - t0
     a_host = a[:2_000_000].cpu().numpy().astype(np.uint32) if rank == 0 else None
     b_host = b[:2_000_000].cpu().numpy().astype(np.uint32) if rank == 0 else None
-    del a, b
-    torch.cuda.empty_cache()
 
     perm_dev = torch.from_numpy(perms).to(dev)
     out_dev = torch.zeros(P_loc, dtype=torch.float64, device=dev)
     x100_dev = torch.zeros(P_loc, dtype=torch.int64, device=dev)
     gathered = torch.zeros(P, dtype=torch.float64, device=dev)
     torch.cuda.synchronize()
-    stream = torch.cuda.ExternalStream(ctx.stream(), device=dev)
-
-    def step_device():
-        ctx.scaff_score_batch_dev(perm_dev.data_ptr(), P_loc, out_dev.data_ptr(), x100_dev.data_ptr())
-        if dist is not None:   # only the score vector moves between GPUs
-            dist.all_gather_into_tensor(gathered, out_dev)
 
     def bracket():
         torch.cuda.synchronize()
@@ -288,47 +282,159 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- value: device-resident ----
-    for _ in range(max(args.warmup, 3)):
-        step_device()
-    sampler = ClockSampler(local)
-    bracket()
-    sampler.start()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record(stream)
-    ms_score, ms_layout, ms_finish = [], [], []
-    launches = 0
-    for _ in range(args.steps):
-        step_device()
-        t = ctx.timing()
-        ms_score.append(t["ms_score"]); ms_layout.append(t["ms_layout"]); ms_finish.append(t["ms_finish"])
-        launches += t["launches"]
-    if dist is not None:
-        torch.cuda.current_stream().synchronize()
-    ev1.record(stream)
-    bracket()
-    clocks = sampler.stop()
-    ms_dev = ev0.elapsed_time(ev1)
-    timing = ctx.timing()
+    def time_path(cx, dev_call, host_call, steps, sample_clocks=False):
+        """K device-resident steps (CUDA events on the context's stream) and K host-buffer steps
+        (wall clock); every step ends with the all-gather of the score vector when N > 1."""
+        stream = torch.cuda.ExternalStream(cx.stream(), device=dev)
 
-    # ---- e2e: host buffers through the C ABI ----
-    for _ in range(2):
-        ctx.scaff_score_batch(perms)
-    bracket()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        host_scores = ctx.scaff_score_batch(perms)
+        def step_device():
+            dev_call()
+            if dist is not None:   # only the score vector moves between GPUs
+                dist.all_gather_into_tensor(gathered, out_dev)
+
+        for _ in range(max(args.warmup, 3)):
+            step_device()
+        sampler = ClockSampler(local) if sample_clocks else None
+        bracket()
+        if sampler:
+            sampler.start()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(stream)
+        tms = {"ms_score": [], "ms_layout": [], "ms_finish": []}
+        launches = 0
+        for _ in range(steps):
+            step_device()
+            t = cx.timing()
+            for k in tms:
+                tms[k].append(t[k])
+            launches += t["launches"]
         if dist is not None:
-            out_dev.copy_(torch.from_numpy(host_scores))
-            dist.all_gather_into_tensor(gathered, out_dev)
-            torch.cuda.synchronize()
-    bracket()
-    ms_e2e = 1e3 * (time.perf_counter() - t0)
+            torch.cuda.current_stream().synchronize()
+        ev1.record(stream)
+        bracket()
+        clk = sampler.stop() if sampler else None
+        ms_d = ev0.elapsed_time(ev1)
+        last = cx.timing()
+        for _ in range(2):
+            host_call()
+        bracket()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            host_scores = host_call()
+            if dist is not None:
+                out_dev.copy_(torch.from_numpy(host_scores))
+                dist.all_gather_into_tensor(gathered, out_dev)
+                torch.cuda.synchronize()
+        bracket()
+        ms_h = 1e3 * (time.perf_counter() - t0)
+        if dist is not None:
+            tt = torch.tensor([ms_d, ms_h], dtype=torch.float64, device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ms_d, ms_h = float(tt[0]), float(tt[1])
+        return {"ms_dev": ms_d, "ms_e2e": ms_h, "launches": launches, "clocks": clk, "last": last,
+                "kernel_ms": {k: float(np.mean(v)) for k, v in tms.items()}}
 
-    if dist is not None:
-        tt = torch.tensor([ms_dev, ms_e2e], dtype=torch.float64, device=dev)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        ms_dev, ms_e2e = float(tt[0]), float(tt[1])
+    # ---- the headline path: streaming kernel, R-profile ----
+    main = time_path(ctx, lambda: ctx.scaff_score_batch_dev(perm_dev.data_ptr(), P_loc, out_dev.data_ptr(),
+                                                            x100_dev.data_ptr()),
+                     lambda: ctx.scaff_score_batch(perms), args.steps, sample_clocks=True)
+    ms_dev, ms_e2e, launches, clocks, timing = (main["ms_dev"], main["ms_e2e"], main["launches"],
+                                                main["clocks"], main["last"])
+    ms_score, ms_layout, ms_finish = ([main["kernel_ms"]["ms_score"]], [main["kernel_ms"]["ms_layout"]],
+                                      [main["kernel_ms"]["ms_finish"]])
+    stream_x100 = x100_dev.clone()
+
+    extras = {}
+    if not args.no_extras:
+        # ---- pair-table path (same inputs, same results; cost independent of L) ----
+        pctx = N.Context(local, path=N.PATH_PAIRS)
+        t0 = time.perf_counter()
+        pctx.set_links_dev(n, L, a.data_ptr(), b.data_ptr(), None)
+        t_pbuild = time.perf_counter() - t0
+        pr = time_path(pctx, lambda: pctx.scaff_score_batch_dev(perm_dev.data_ptr(), P_loc, out_dev.data_ptr(),
+                                                                x100_dev.data_ptr()),
+                       lambda: pctx.scaff_score_batch(perms), args.steps)
+        same = bool((x100_dev == stream_x100).all().item())
+        pctx.close()
+        extras["pair_table_path"] = {
+            "what": "LXY_PATH_PAIRS: records aggregated per pair at set_links (Links.Add), 6n table "
+                    "gathers per candidate - the reference's algorithm on the GPU; value = "
+                    "candidates/s x L (the convention of the reference arm)",
+            "value": float(P) * L * args.steps / (pr["ms_dev"] * 1e-3), "unit": UNIT,
+            "candidates_per_sec": float(P) * args.steps / (pr["ms_dev"] * 1e-3),
+            "ms_per_step": pr["ms_dev"] / args.steps,
+            "e2e": {"value": float(P) * L * args.steps / (pr["ms_e2e"] * 1e-3), "unit": UNIT,
+                    "ms_per_step": pr["ms_e2e"] / args.steps},
+            "kernel_ms": pr["kernel_ms"], "table_bytes": 4 * n * n, "table_build_s": round(t_pbuild, 3),
+            "gather_sector_GBps": 6.0 * P_loc * n * 32 / (pr["kernel_ms"]["ms_score"] * 1e-3) / 1e9,
+            "identical_x100_to_streaming_path": same}
+
+        # ---- G-profile (north_star's generalisation): lengths, orientations, in-contig offsets ----
+        g = torch.Generator(device=dev)
+        g.manual_seed(seed + 17)
+        lens_t = torch.exp(torch.randn(n, generator=g, device=dev, dtype=torch.float64) * 0.6
+                           + float(np.log(min(1_000_000, 3_000_000_000 // n)))).clamp_(1000).long()
+        xa = (torch.rand(L, generator=g, device=dev, dtype=torch.float64) * lens_t[a.long()]).int()
+        xb = (torch.rand(L, generator=g, device=dev, dtype=torch.float64) * lens_t[b.long()]).int()
+        ori_host = (np.random.default_rng(pseed + 31).random((P_loc, n)) < 0.5).astype(np.uint8)
+        ori_dev = torch.from_numpy(ori_host).to(dev)
+        unit = int(lens_t.double().median().item())
+        gctx = N.Context(local)
+        gctx.set_links_g_dev(lens_t.cpu().numpy().astype(np.uint32), unit, L, a.data_ptr(), xa.data_ptr(),
+                             b.data_ptr(), xb.data_ptr(), None)
+        del xa, xb
+        gr = time_path(gctx, lambda: gctx.scaffg_score_batch_dev(perm_dev.data_ptr(), ori_dev.data_ptr(), P_loc,
+                                                                 out_dev.data_ptr(), x100_dev.data_ptr()),
+                       lambda: gctx.scaffg_score_batch(perms, ori_host), args.steps)
+        gctx.close()
+        extras["g_profile"] = {
+            "what": "contig lengths (log-normal), per-candidate orientations, per-record in-contig "
+                    "offsets; bucket = genomic distance / unit (unit = median contig length)",
+            "value": float(P) * L * args.steps / (gr["ms_dev"] * 1e-3), "unit": UNIT,
+            "ms_per_step": gr["ms_dev"] / args.steps,
+            "e2e": {"value": float(P) * L * args.steps / (gr["ms_e2e"] * 1e-3), "unit": UNIT,
+                    "ms_per_step": gr["ms_e2e"] / args.steps},
+            "kernel_ms": gr["kernel_ms"], "record_bytes": 10}
+        # ---- phasing (BASELINE.json configs[4]): simvarblocks-style blocks, integer-exact ----
+        if world == 1:
+            from lxy_b200 import synth as SY
+            pn, pP = 300_000, 1024
+            pa, pb, pw, truth = SY.phase_links(pn, 5)
+            genes = SY.phase_population(pn, pP, 105, truth)
+            hctx = N.Context(local)
+            hctx.set_phase_links(pn, pa, pb, pw)
+            genes_dev = torch.from_numpy(genes).to(dev)
+            oi = torch.zeros(pP, dtype=torch.int64, device=dev)
+            of = torch.zeros(pP, dtype=torch.float64, device=dev)
+            torch.cuda.synchronize()
+            for _ in range(3):
+                hctx.phase_score_batch_dev(genes_dev.data_ptr(), pP, oi.data_ptr(), of.data_ptr())
+            hstream = torch.cuda.ExternalStream(hctx.stream(), device=dev)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(hstream)
+            for _ in range(args.steps):
+                hctx.phase_score_batch_dev(genes_dev.data_ptr(), pP, oi.data_ptr(), of.data_ptr())
+            e1.record(hstream)
+            torch.cuda.synchronize()
+            pms = e0.elapsed_time(e1) / args.steps
+            pt = hctx.timing()
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                hctx.phase_score_batch(genes)
+            pms_h = 1e3 * (time.perf_counter() - t0) / args.steps
+            hctx.close()
+            extras["phasing"] = {
+                "what": f"phase.score over {pn} simulated variant blocks, {len(pa)} block-pair records, "
+                        f"population {pP}; int64 exact",
+                "value": float(pP) * len(pa) / (pms * 1e-3), "unit": UNIT, "ms_per_step": pms,
+                "e2e": {"value": float(pP) * len(pa) / (pms_h * 1e-3), "unit": UNIT, "ms_per_step": pms_h,
+                        "h2d_bytes_per_step": int(genes.nbytes), "d2h_bytes_per_step": 16 * pP},
+                "kernel_ms": {"k_phase_score": pt["ms_score"], "k_phase_bits": pt["ms_layout"]}}
+            del genes_dev
+    del a, b
+    torch.cuda.empty_cache()
+
     evals_per_step = float(P_loc * world) * float(L)
     value = evals_per_step * args.steps / (ms_dev * 1e-3)
     e2e_value = evals_per_step * args.steps / (ms_e2e * 1e-3)
@@ -379,6 +485,7 @@ def main():
                                  "DESIGN.md §4 and profiles/"},
             "clocks": clocks,
         }
+        line.update(extras)
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_link_streaming_baseline(n, a_host, b_host, perms_all)
         print(json.dumps(line))

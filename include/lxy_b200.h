@@ -121,6 +121,10 @@ int lxy_links_get(lxy_ctx* ctx, int32_t id1, int32_t id2, double* out);
 int lxy_ctx_set_links_g(lxy_ctx* ctx, int32_t n_ids, int64_t n_links, const uint32_t* a,
                         const uint32_t* xa, const uint32_t* b, const uint32_t* xb,
                         const double* w, const uint32_t* len, uint32_t unit);
+/* Same with the record arrays already on the device (len stays a host array of n_ids entries). */
+int lxy_ctx_set_links_g_dev(lxy_ctx* ctx, int32_t n_ids, int64_t n_links, const uint32_t* a_dev,
+                            const uint32_t* xa_dev, const uint32_t* b_dev, const uint32_t* xb_dev,
+                            const double* w_dev, const uint32_t* len, uint32_t unit);
 int lxy_scaffg_score_batch(lxy_ctx* ctx, const int32_t* perm, const uint8_t* ori, int32_t P,
                            double* out, int64_t* x100);
 int lxy_scaffg_score_batch_dev(lxy_ctx* ctx, const int32_t* perm_dev, const uint8_t* ori_dev,

@@ -21,7 +21,8 @@ SYMBOLS = [
     "lxy_ctx_get_timing", "lxy_ctx_stream", "lxy_ctx_sync", "lxy_ctx_set_links",
     "lxy_ctx_set_links_dev",
     "lxy_scaff_score_batch", "lxy_scaff_score_batch_dev", "lxy_scaff_positions",
-    "lxy_scaff_link_distances", "lxy_links_get", "lxy_ctx_set_links_g", "lxy_scaffg_score_batch",
+    "lxy_scaff_link_distances", "lxy_links_get", "lxy_ctx_set_links_g", "lxy_ctx_set_links_g_dev",
+    "lxy_scaffg_score_batch",
     "lxy_scaffg_score_batch_dev",
     "lxy_scaffg_layout", "lxy_scaffg_link_distances", "lxy_ctx_set_phase_links",
     "lxy_phase_score_batch", "lxy_phase_score_batch_dev", "lxy_rank",
@@ -90,6 +91,7 @@ def lib():
         "lxy_scaff_link_distances": (i32, [vp, i32, i64, vp, vp, vp, vp]),
         "lxy_links_get": (i32, [vp, i32, i32, C.POINTER(f64)]),
         "lxy_ctx_set_links_g": (i32, [vp, i32, i64, vp, vp, vp, vp, vp, vp, u32]),
+        "lxy_ctx_set_links_g_dev": (i32, [vp, i32, i64, vp, vp, vp, vp, vp, vp, u32]),
         "lxy_scaffg_score_batch": (i32, [vp, vp, vp, i32, vp, vp]),
         "lxy_scaffg_score_batch_dev": (i32, [vp, vp, vp, i32, vp, vp]),
         "lxy_scaffg_layout": (i32, [vp, vp, i32, vp, vp]),
@@ -229,6 +231,14 @@ class Context:
         w = _c(w, np.float64)
         _check(lib().lxy_ctx_set_links_g(self._h, len(lens), len(a), _p(a), _p(xa), _p(b), _p(xb),
                                          _p(w), _p(lens), unit))
+        self.n = len(lens)
+
+    def set_links_g_dev(self, lens, unit, n_links, a_ptr, xa_ptr, b_ptr, xb_ptr, w_ptr=None):
+        lens = _c(lens, np.uint32)
+        _check(lib().lxy_ctx_set_links_g_dev(self._h, len(lens), n_links, C.c_void_p(a_ptr),
+                                             C.c_void_p(xa_ptr), C.c_void_p(b_ptr),
+                                             C.c_void_p(xb_ptr),
+                                             C.c_void_p(w_ptr) if w_ptr else None, _p(lens), unit))
         self.n = len(lens)
 
     def scaffg_score_batch(self, perms, oris=None, want_x100=False):

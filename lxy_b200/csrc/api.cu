@@ -298,6 +298,17 @@ int lxy_ctx_set_links_g(lxy_ctx* c, int32_t n_ids, int64_t n_links, const uint32
   return build_scaff_links(c, in);
 }
 
+int lxy_ctx_set_links_g_dev(lxy_ctx* c, int32_t n_ids, int64_t n_links, const uint32_t* a_dev,
+                            const uint32_t* xa_dev, const uint32_t* b_dev, const uint32_t* xb_dev,
+                            const double* w_dev, const uint32_t* len, uint32_t unit) {
+  CHECK_CTX(c);
+  if (!len) { set_error("set_links_g_dev: null len"); return LXY_ERR_ARG; }
+  LinkInput in;
+  in.n = n_ids; in.L = n_links; in.a = a_dev; in.b = b_dev; in.w = w_dev; in.xa = xa_dev; in.xb = xb_dev;
+  in.len = len; in.unit = unit; in.on_device = true;
+  return build_scaff_links(c, in);
+}
+
 int lxy_scaffg_score_batch(lxy_ctx* c, const int32_t* perm, const uint8_t* ori, int32_t P,
                            double* out, int64_t* x100) {
   CHECK_CTX(c);
