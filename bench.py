@@ -373,7 +373,7 @@ def main():
         g = torch.Generator(device=dev)
         g.manual_seed(seed + 17)
         lens_t = torch.exp(torch.randn(n, generator=g, device=dev, dtype=torch.float64) * 0.6
-                           + float(np.log(min(1_000_000, 3_000_000_000 // n)))).clamp_(1000).long()
+                           + float(np.log(min(1_000_000, 1_600_000_000 // n)))).clamp_(1000).long()
         xa = (torch.rand(L, generator=g, device=dev, dtype=torch.float64) * lens_t[a.long()]).int()
         xb = (torch.rand(L, generator=g, device=dev, dtype=torch.float64) * lens_t[b.long()]).int()
         ori_host = (np.random.default_rng(pseed + 31).random((P_loc, n)) < 0.5).astype(np.uint8)
@@ -394,7 +394,10 @@ def main():
             "ms_per_step": gr["ms_dev"] / args.steps,
             "e2e": {"value": float(P) * L * args.steps / (gr["ms_e2e"] * 1e-3), "unit": UNIT,
                     "ms_per_step": gr["ms_e2e"] / args.steps},
-            "kernel_ms": gr["kernel_ms"], "record_bytes": 10}
+            "kernel_ms": gr["kernel_ms"], "record_bytes": 10,
+            "total_length_bp": int(lens_t.sum().item()), "unit_bp": unit,
+            "coordinate_mode": "signed 32-bit origins (total < 2^31)" if int(lens_t.sum().item()) < 0x7FFFFFF0
+                               else "unsigned 32-bit origins + orientation bits"}
         # ---- phasing (BASELINE.json configs[4]): simvarblocks-style blocks, integer-exact ----
         if world == 1:
             from lxy_b200 import synth as SY

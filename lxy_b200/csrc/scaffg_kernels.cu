@@ -37,7 +37,7 @@ __constant__ uint8_t c_lutg[kLutG] = {0, 100, 50, 33, 0, 20, 0, 0, 0, 0, 0, 10,
 // ---- layout ---------------------------------------------------------------------------------
 __global__ void k_scaffg_layout(const int32_t* __restrict__ perm, const uint8_t* __restrict__ ori,
                                 const uint32_t* __restrict__ len, int32_t P, int32_t Ppad, int32_t n,
-                                uint32_t* __restrict__ origin, uint32_t* __restrict__ bits,
+                                int sgn, uint32_t* __restrict__ origin, uint32_t* __restrict__ bits,
                                 int32_t* __restrict__ pos, int* __restrict__ flag) {
   const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (p >= Ppad) return;
@@ -63,7 +63,9 @@ __global__ void k_scaffg_layout(const int32_t* __restrict__ perm, const uint8_t*
     carry += __shfl_sync(0xffffffffu, s, 31);
     if (cid >= 0) {
       const bool rev = (p < P) && ori && ori[(size_t)p * n + i] != 0;
-      origin[((size_t)g * n + cid) * kCandG + pc] = rev ? start + l - 1 : start;
+      // sgn: orientation in the sign (coord = |v + x|); else unsigned origin + orientation bit
+      const uint32_t e = start + l - 1;
+      origin[((size_t)g * n + cid) * kCandG + pc] = rev ? (sgn ? (uint32_t)(-(int32_t)e) : e) : start;
       uint32_t* row = bits + ((size_t)g * n + cid) * 4;
       if (rev) atomicOr(row + (pc >> 5), 1u << (pc & 31));
       if (i == 0) atomicOr(row + 2 + (pc >> 5), 1u << (pc & 31));
@@ -145,7 +147,8 @@ struct GParams {
   int32_t n, nblk;
   int32_t groups, splits;
   uint32_t unit;
-  uint32_t m_lo, m_hi;        // floor(2^64 / unit) + 1 (unused when unit == 1)
+  uint32_t m_lo, m_hi;        // floor(2^64 / unit) + 1 (general units)
+  uint32_t shift;             // log2(unit) when unit is a power of two
 };
 
 template <int WM>
@@ -165,29 +168,53 @@ struct GLane {
   }
 };
 
-template <int WM>
-__device__ __forceinline__ void g_eval_record(uint32_t r, uint32_t xa, uint32_t xb, int32_t wi, double wd,
-                                              const uint8_t* sA, const uint8_t* sB, const uint8_t* sBitsA,
-                                              const uint8_t* sBitsB, const uint8_t* lut, int lane,
-                                              const GParams& prm, bool unit_is_one, GLane<WM>& L) {
-  const uint32_t aloc = r >> 8, bloc = r & 0xFFu;
-  const uint8_t* rowA = sA + aloc * kRowG + lane * 4;
-  const uint8_t* rowB = sB + bloc * kRowG + lane * 4;
-  const uint4 ba = *(const uint4*)(sBitsA + aloc * 16);   // warp-uniform address: broadcast
-  const uint4 bb = *(const uint4*)(sBitsB + bloc * 16);
-  const uint32_t revA[2] = {ba.x, ba.y}, revB[2] = {bb.x, bb.y};
-  const uint32_t first[2] = {ba.z | bb.z, ba.w | bb.w};
+// Row A of a record (or of a whole packet when all its records share one a): the two origins of
+// this lane's candidates and the bit words of the row.
+struct GRowA {
+  uint32_t o[2], rev[2], first[2];
+};
+
+template <bool SGN>
+__device__ __forceinline__ void g_load_row(const uint8_t* tab, const uint8_t* bits, uint32_t loc, int lane,
+                                           GRowA& R) {
+  const uint8_t* row = tab + loc * kRowG + lane * 4;
+  R.o[0] = *(const uint32_t*)row;
+  R.o[1] = *(const uint32_t*)(row + 128);
+  if (SGN) {  // orientation lives in the sign of the origin: only the "first" words are needed
+    const uint2 f = *(const uint2*)(bits + loc * 16 + 8);   // warp-uniform address: broadcast
+    R.first[0] = f.x; R.first[1] = f.y; R.rev[0] = R.rev[1] = 0;
+  } else {
+    const uint4 b = *(const uint4*)(bits + loc * 16);
+    R.rev[0] = b.x; R.rev[1] = b.y; R.first[0] = b.z; R.first[1] = b.w;
+  }
+}
+
+// One record against the two candidates of this lane.
+//   SGN  (total length < 2^31): the table holds v = start (forward) or -(start + len - 1) (reversed),
+//        so coord = |v + x| and d = |coord a - coord b|: four IADD/IABS, no orientation bits.
+//   !SGN (total length < 2^32): unsigned origins, orientation from the bit rows.
+//   POW2: unit is a power of two -> bucket = d >> shift; otherwise bucket = (d * M) >> 64 with
+//        M = floor(2^64 / unit) + 1 (two IMAD.HI.U32), exact for every 32-bit d.
+template <int WM, bool SGN, bool POW2>
+__device__ __forceinline__ void g_eval(const GRowA& A, const GRowA& B, uint32_t xa, uint32_t xb, int32_t wi,
+                                       double wd, const uint8_t* lut, int lane, const GParams& prm,
+                                       GLane<WM>& L) {
   uint32_t t[2];
 #pragma unroll
   for (int j = 0; j < 2; ++j) {
-    const uint32_t oa = *(const uint32_t*)(rowA + 128 * j), ob = *(const uint32_t*)(rowB + 128 * j);
-    const uint32_t ca = ((revA[j] >> lane) & 1u) ? oa - xa : oa + xa;
-    const uint32_t cb = ((revB[j] >> lane) & 1u) ? ob - xb : ob + xb;
-    const uint32_t d = ca > cb ? ca - cb : cb - ca;
+    uint32_t d;
+    if (SGN) {
+      const int ca = abs((int)A.o[j] + (int)xa), cb = abs((int)B.o[j] + (int)xb);
+      d = (uint32_t)abs(ca - cb);
+    } else {
+      const uint32_t ca = ((A.rev[j] >> lane) & 1u) ? A.o[j] - xa : A.o[j] + xa;
+      const uint32_t cb = ((B.rev[j] >> lane) & 1u) ? B.o[j] - xb : B.o[j] + xb;
+      d = ca > cb ? ca - cb : cb - ca;
+    }
     uint32_t q;
-    if (unit_is_one) {
-      q = d;
-    } else {  // floor(d / unit) = (d * M) >> 64, exact for every 32-bit d
+    if (POW2) {
+      q = d >> prm.shift;
+    } else {
       const uint64_t x = (uint64_t)d * prm.m_lo;
       const uint64_t y = (uint64_t)d * prm.m_hi + (x >> 32);
       q = (uint32_t)(y >> 32);
@@ -200,10 +227,12 @@ __device__ __forceinline__ void g_eval_record(uint32_t r, uint32_t xa, uint32_t 
     else if (WM == W_INT32) L.s64[j] += (int64_t)(int32_t)t[j] * (int64_t)wi;
     else L.sd[j] += (double)t[j] * wd;
   }
-  if ((first[0] | first[1]) != 0) {   // rare: some candidate of the group has this contig first
+  const uint32_t f0 = A.first[0] | B.first[0], f1 = A.first[1] | B.first[1];
+  if ((f0 | f1) != 0) {   // rare and warp-uniform: some candidate of the group has this contig first
+    const uint32_t f[2] = {f0, f1};
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-      if ((first[j] >> lane) & 1u) {
+      if ((f[j] >> lane) & 1u) {
         if (WM == W_UNIT) L.h32[j] += (int32_t)t[j];
         else if (WM == W_INT32) L.h64[j] += (int64_t)(int32_t)t[j] * (int64_t)wi;
         else L.hd[j] += (double)t[j] * wd;
@@ -212,7 +241,54 @@ __device__ __forceinline__ void g_eval_record(uint32_t r, uint32_t xa, uint32_t 
   }
 }
 
+struct GPacket {
+  uint4 rec, xa0, xa1, xb0, xb1;
+};
+__device__ __forceinline__ GPacket g_load_packet(const GParams& prm, int64_t base) {
+  GPacket p;
+  p.rec = ldg_stream_v4(prm.rec + base);
+  p.xa0 = ldg_stream_v4(prm.xa + base); p.xa1 = ldg_stream_v4(prm.xa + base + 4);
+  p.xb0 = ldg_stream_v4(prm.xb + base); p.xb1 = ldg_stream_v4(prm.xb + base + 4);
+  return p;
+}
+
+// Records k in [k0, k1) of one packet; SAME_A: one a for the whole packet (sorted records).
+template <int WM, bool SGN, bool POW2, bool SAME_A>
+__device__ __forceinline__ void g_eval_packet(const GPacket& pk, const int32_t* wi, const double* wd, int k0,
+                                              int k1, const uint8_t* sA, const uint8_t* sB,
+                                              const uint8_t* sBitsA, const uint8_t* sBitsB, const uint8_t* lut,
+                                              int lane, const GParams& prm, GLane<WM>& L) {
+  const uint32_t words[4] = {pk.rec.x, pk.rec.y, pk.rec.z, pk.rec.w};
+  const uint32_t xav[8] = {pk.xa0.x, pk.xa0.y, pk.xa0.z, pk.xa0.w, pk.xa1.x, pk.xa1.y, pk.xa1.z, pk.xa1.w};
+  const uint32_t xbv[8] = {pk.xb0.x, pk.xb0.y, pk.xb0.z, pk.xb0.w, pk.xb1.x, pk.xb1.y, pk.xb1.z, pk.xb1.w};
+  GRowA A, B;
+  if (SAME_A) g_load_row<SGN>(sA, sBitsA, (words[0] >> 8) & 0xFFu, lane, A);
+#pragma unroll
+  for (int k = 0; k < kPacket; ++k) {
+    if (k < k0 || k >= k1) continue;
+    const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
+    if (!SAME_A) g_load_row<SGN>(sA, sBitsA, r >> 8, lane, A);
+    g_load_row<SGN>(sB, sBitsB, r & 0xFFu, lane, B);
+    g_eval<WM, SGN, POW2>(A, B, xav[k], xbv[k], WM == W_INT32 ? wi[k] : 0, WM == W_F64 ? wd[k] : 0.0, lut,
+                          lane, prm, L);
+  }
+}
+
 template <int WM>
+__device__ __forceinline__ void g_load_weights(const void* w, int64_t base, int32_t (&wi)[kPacket],
+                                               double (&wd)[kPacket]) {
+  if (WM == W_INT32) {
+    const uint4* wp = reinterpret_cast<const uint4*>((const int32_t*)w + base);
+    const uint4 x = __ldg(wp), y = __ldg(wp + 1);
+    wi[0] = x.x; wi[1] = x.y; wi[2] = x.z; wi[3] = x.w; wi[4] = y.x; wi[5] = y.y; wi[6] = y.z; wi[7] = y.w;
+  } else if (WM == W_F64) {
+    const double2* wp = reinterpret_cast<const double2*>((const double*)w + base);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { const double2 d2 = __ldg(wp + q); wd[2 * q] = d2.x; wd[2 * q + 1] = d2.y; }
+  }
+}
+
+template <int WM, bool SGN, bool POW2>
 __global__ void __launch_bounds__(kThreads, 1) k_scaffg_score(GParams prm) {
   typedef typename Acc<WM>::type acc_t;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -231,7 +307,6 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaffg_score(GParams prm) {
   }
   __syncthreads();
   uint32_t parity = 0;
-  const bool unit_is_one = (prm.unit == 1);
 
   const int units = prm.groups * prm.splits;
   const int64_t npk_all = (prm.L + kPacket - 1) / kPacket;
@@ -283,35 +358,50 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaffg_score(GParams prm) {
         parity ^= 1;
 
         const int64_t p_first = cur / kPacket, p_last = (seg_end - 1) / kPacket;
-        int64_t done = 0;  // packets this warp has scored since the last flush
-        for (int64_t pk = p_first + warp; pk <= p_last; pk += kWarps) {
-          const int64_t base = pk * kPacket;
-          const uint4 v = ldg_stream_v4(prm.rec + base);
-          const uint4 xa0 = ldg_stream_v4(prm.xa + base), xa1 = ldg_stream_v4(prm.xa + base + 4);
-          const uint4 xb0 = ldg_stream_v4(prm.xb + base), xb1 = ldg_stream_v4(prm.xb + base + 4);
-          const uint32_t words[4] = {v.x, v.y, v.z, v.w};
-          const uint32_t xav[8] = {xa0.x, xa0.y, xa0.z, xa0.w, xa1.x, xa1.y, xa1.z, xa1.w};
-          const uint32_t xbv[8] = {xb0.x, xb0.y, xb0.z, xb0.w, xb1.x, xb1.y, xb1.z, xb1.w};
-          int32_t wi[kPacket];
-          double wd[kPacket];
-          if (WM == W_INT32) {
-            const uint4* wp = reinterpret_cast<const uint4*>((const int32_t*)prm.w + base);
-            const uint4 x = __ldg(wp), y = __ldg(wp + 1);
-            wi[0] = x.x; wi[1] = x.y; wi[2] = x.z; wi[3] = x.w; wi[4] = y.x; wi[5] = y.y; wi[6] = y.z; wi[7] = y.w;
-          } else if (WM == W_F64) {
-            const double2* wp = reinterpret_cast<const double2*>((const double*)prm.w + base);
-#pragma unroll
-            for (int q = 0; q < 4; ++q) { const double2 d2 = __ldg(wp + q); wd[2 * q] = d2.x; wd[2 * q + 1] = d2.y; }
+        const bool head_partial = (p_first * kPacket < cur);
+        const bool tail_partial = ((p_last + 1) * kPacket > seg_end);
+        int32_t wi[kPacket];
+        double wd[kPacket];
+        if (head_partial && warp == 0) {   // boundary packets: masked, one warp each
+          const int64_t base = p_first * kPacket;
+          const GPacket pk = g_load_packet(prm, base);
+          g_load_weights<WM>(prm.w, base, wi, wd);
+          const int k0 = (int)(cur - base), k1 = (int)min((int64_t)kPacket, seg_end - base);
+#pragma unroll 1
+          for (int k = k0; k < k1; ++k)
+            g_eval_packet<WM, SGN, POW2, false>(pk, wi, wd, k, k + 1, sA, sB, sBitsA, sBitsB, s_lut, lane, prm, acc);
+        }
+        if (tail_partial && warp == 1 && !(head_partial && p_last == p_first)) {
+          const int64_t base = p_last * kPacket;
+          const GPacket pk = g_load_packet(prm, base);
+          g_load_weights<WM>(prm.w, base, wi, wd);
+          const int k1 = (int)(seg_end - base);
+#pragma unroll 1
+          for (int k = 0; k < k1; ++k)
+            g_eval_packet<WM, SGN, POW2, false>(pk, wi, wd, k, k + 1, sA, sB, sBitsA, sBitsB, s_lut, lane, prm, acc);
+        }
+        const int64_t f0 = p_first + (head_partial ? 1 : 0);
+        const int64_t f1 = p_last - (tail_partial ? 1 : 0);  // inclusive
+        const int64_t nfull = f1 - f0 + 1;
+        if (nfull > 0) {
+          for (int64_t c0 = 0; c0 < nfull; c0 += (int64_t)kWarps << 16) {
+            const int32_t cnt = (int32_t)min((int64_t)kWarps << 16, nfull - c0);
+            const int64_t pbase = (f0 + c0) * kPacket;
+            int32_t it = warp;
+            GPacket nx;
+            if (it < cnt) nx = g_load_packet(prm, pbase + (int64_t)it * kPacket);
+#pragma unroll 1
+            for (; it < cnt; it += kWarps) {
+              const GPacket pk = nx;
+              if (it + kWarps < cnt) nx = g_load_packet(prm, pbase + (int64_t)(it + kWarps) * kPacket);
+              g_load_weights<WM>(prm.w, pbase + (int64_t)it * kPacket, wi, wd);
+              if (((pk.rec.x >> 8) & 0xFFu) == (pk.rec.w >> 24))
+                g_eval_packet<WM, SGN, POW2, true>(pk, wi, wd, 0, kPacket, sA, sB, sBitsA, sBitsB, s_lut, lane, prm, acc);
+              else
+                g_eval_packet<WM, SGN, POW2, false>(pk, wi, wd, 0, kPacket, sA, sB, sBitsA, sBitsB, s_lut, lane, prm, acc);
+            }
+            acc.flush();
           }
-          const int k0 = (int)max((int64_t)0, cur - base), k1 = (int)min((int64_t)kPacket, seg_end - base);
-#pragma unroll
-          for (int k = 0; k < kPacket; ++k) {
-            if (k < k0 || k >= k1) continue;
-            const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
-            g_eval_record<WM>(r, xav[k], xbv[k], WM == W_INT32 ? wi[k] : 0, WM == W_F64 ? wd[k] : 0.0,
-                              sA, sB, sBitsA, sBitsB, s_lut, lane, prm, unit_is_one, acc);
-          }
-          if (WM == W_UNIT && (++done & 0xFFFF) == 0) acc.flush();
         }
         cur = seg_end;
       }
@@ -370,17 +460,22 @@ __global__ void k_scaffg_finish(int32_t P, int32_t splits, const void* __restric
   }
 }
 
-template <int WM>
-int launch_g(lxy_ctx* c, const GParams& prm, int grid) {
+template <int WM, bool SGN, bool POW2>
+int launch_g3(lxy_ctx* c, const GParams& prm, int grid) {
   constexpr int smem = 2 * kTabG + 2 * kBitsG + 32 + 16;
   static bool configured[64] = {};
   if (!configured[c->cfg.device & 63]) {
-    LXY_CUDA(cudaFuncSetAttribute(k_scaffg_score<WM>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    LXY_CUDA(cudaFuncSetAttribute(k_scaffg_score<WM, SGN, POW2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured[c->cfg.device & 63] = true;
   }
-  k_scaffg_score<WM><<<grid, kThreads, smem, c->stream>>>(prm);
+  k_scaffg_score<WM, SGN, POW2><<<grid, kThreads, smem, c->stream>>>(prm);
   LXY_CUDA(cudaGetLastError());
   return LXY_OK;
+}
+template <int WM>
+int launch_g(lxy_ctx* c, const GParams& prm, int grid, bool sgn, bool pow2) {
+  if (sgn) return pow2 ? launch_g3<WM, true, true>(c, prm, grid) : launch_g3<WM, true, false>(c, prm, grid);
+  return pow2 ? launch_g3<WM, false, true>(c, prm, grid) : launch_g3<WM, false, false>(c, prm, grid);
 }
 
 }  // namespace
@@ -402,7 +497,9 @@ int scaffg_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, in
   LXY_CUDA(cudaEventRecord(c->ev[0], st));
   LXY_CUDA(cudaMemsetAsync(c->d_posB.p, 0, 16 * (size_t)groups * n, st));
   int launches = 0;
-  k_scaffg_layout<<<(Ppad * 32 + 255) / 256, 256, 0, st>>>(perm_dev, ori_dev, S.len.as<uint32_t>(), P, Ppad, n,
+  const bool sgn = S.total_len < 0x7FFFFFF0ull;               // coordinates fit a signed 32-bit word
+  const bool pow2 = (S.unit & (S.unit - 1)) == 0;
+  k_scaffg_layout<<<(Ppad * 32 + 255) / 256, 256, 0, st>>>(perm_dev, ori_dev, S.len.as<uint32_t>(), P, Ppad, n, sgn ? 1 : 0,
                                                           c->d_posA.as<uint32_t>(), c->d_posB.as<uint32_t>(),
                                                           c->d_start.as<int32_t>(), c->d_flag.as<int>());
   ++launches;
@@ -440,9 +537,12 @@ int scaffg_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, in
   if (S.unit > 1 && (S.unit & (S.unit - 1)) == 0) M = ((uint64_t)1 << 63) / (S.unit >> 1);  // power of two: exact 2^64 / u
   prm.m_lo = (uint32_t)M;
   prm.m_hi = (uint32_t)(M >> 32);
+  prm.shift = 0;
+  while (pow2 && (1u << prm.shift) < S.unit) ++prm.shift;
   if (S.L > 0) {
-    int rc = S.wmode == W_UNIT ? launch_g<W_UNIT>(c, prm, grid)
-           : S.wmode == W_INT32 ? launch_g<W_INT32>(c, prm, grid) : launch_g<W_F64>(c, prm, grid);
+    int rc = S.wmode == W_UNIT ? launch_g<W_UNIT>(c, prm, grid, sgn, pow2)
+           : S.wmode == W_INT32 ? launch_g<W_INT32>(c, prm, grid, sgn, pow2)
+                                : launch_g<W_F64>(c, prm, grid, sgn, pow2);
     LXY_TRY(rc);
     ++launches;
   } else {

@@ -1,0 +1,44 @@
+#!/usr/bin/env python
+"""Small fixed workloads for ncu: `python tools/prof_workload.py {r|g|pairs|phase} [steps]`.
+cfg2-sized (500 contigs, 5 M records, population 128); phase: 100k blocks, population 256."""
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import lxy_b200._native as N
+from lxy_b200 import synth as S
+
+mode = sys.argv[1] if len(sys.argv) > 1 else "r"
+steps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+n, L, P = 500, 5_000_000, 128
+if mode == "phase":
+    pn, pP = 100_000, 256
+    a, b, w, truth = S.phase_links(pn, 5)
+    genes = S.phase_population(pn, pP, 105, truth)
+    with N.Context(0) as ctx:
+        ctx.set_phase_links(pn, a, b, w)
+        for _ in range(steps):
+            ctx.phase_score_batch(genes)
+        print(ctx.timing())
+    sys.exit(0)
+a, b, w = S.scaff_links(n, L, 2)
+perms = S.scaff_population(n, P, 102)
+if mode == "g":
+    lens = S.contig_lengths(n, 2)
+    rng = np.random.default_rng(31)
+    xa = (rng.random(L) * lens[a]).astype(np.uint32)
+    xb = (rng.random(L) * lens[b]).astype(np.uint32)
+    oris = S.orientations(n, P, 2)
+    with N.Context(0) as ctx:
+        ctx.set_links_g(lens, int(np.median(lens)), a, xa, b, xb, None)
+        for _ in range(steps):
+            ctx.scaffg_score_batch(perms, oris)
+        print(ctx.timing())
+else:
+    with N.Context(0, path=N.PATH_PAIRS if mode == "pairs" else N.PATH_STREAM) as ctx:
+        ctx.set_links(n, a, b, None)
+        for _ in range(steps):
+            ctx.scaff_score_batch(perms)
+        print(ctx.timing())
