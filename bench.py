@@ -34,7 +34,11 @@ WORKLOADS = {
     "cfg2": (500, 5_000_000, 128, 2, 102),
     "cfg3": (5_000, 200_000_000, 1024, 3, 103),
     "tiny": (300, 200_000, 64, 9, 109),
+    # link-sharded (BASELINE.json configs[3]): records split across ranks, NCCL all-reduce of partials
+    "cfg4": (50_000, 2_000_000_000, 1024, 4, 104),
+    "cfg4s": (50_000, 64_000_000, 256, 4, 104),
 }
+LINK_SHARDED = {"cfg4", "cfg4s"}
 METRIC = "ga_fitness_link_evals_per_sec"
 UNIT = "link-evals/s"
 
@@ -42,13 +46,15 @@ UNIT = "link-evals/s"
 # ------------------------------------------------------------------------------------------------
 # synthetic inputs (torch is plumbing here: device RNG + memory)
 # ------------------------------------------------------------------------------------------------
-def gen_links(n, L, seed, device):
+def gen_links(n, L, seed, device, stream_seed=None):
     """contig pairs with P(a,b) ~ 1/|i-j| in a hidden true order plus 10 % uniform
     noise pairs; one record per read pair (weight 1).  Returns int32 tensors a, b, order."""
     import torch
     g = torch.Generator(device=device)
     g.manual_seed(seed)
     order = torch.randperm(n, generator=g, device=device, dtype=torch.int64)
+    if stream_seed is not None:      # same hidden order on every rank, a different record stream
+        g.manual_seed(stream_seed)
     d = torch.arange(1, n, device=device, dtype=torch.float64)
     pmf = (n - d) / d
     cdf = torch.cumsum(pmf / pmf.sum(), 0)
@@ -258,14 +264,21 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     # ---- inputs: links replicated on every rank, the population sharded ----
-    a, b, order = gen_links(n, L, seed, dev)
-    perms_all = gen_population(n, P, pseed, order.cpu().numpy())
-    P_loc = P // world
-    perms = np.ascontiguousarray(perms_all[rank * P_loc:(rank + 1) * P_loc])
+    link_mode = args.workload in LINK_SHARDED
+    if link_mode:       # records sharded, the whole population on every rank
+        L_loc, P_loc = L // world, P
+        a, b, order = gen_links(n, L_loc, seed, dev, stream_seed=seed * 1000 + rank)
+        perms_all = gen_population(n, P, pseed, order.cpu().numpy())
+        perms = perms_all
+    else:               # links replicated, the population sharded
+        L_loc, P_loc = L, P // world
+        a, b, order = gen_links(n, L, seed, dev)
+        perms_all = gen_population(n, P, pseed, order.cpu().numpy())
+        perms = np.ascontiguousarray(perms_all[rank * P_loc:(rank + 1) * P_loc])
     torch.cuda.synchronize()
     ctx = N.Context(local)
     t0 = time.perf_counter()
-    ctx.set_links_dev(n, L, a.data_ptr(), b.data_ptr(), None)
+    ctx.set_links_dev(n, L_loc, a.data_ptr(), b.data_ptr(), None)
     t_build = time.perf_counter() - t0
     a_host = a[:2_000_000].cpu().numpy().astype(np.uint32) if rank == 0 else None
     b_host = b[:2_000_000].cpu().numpy().astype(np.uint32) if rank == 0 else None
@@ -289,7 +302,10 @@ def main():
 
         def step_device():
             dev_call()
-            if dist is not None:   # only the score vector moves between GPUs
+            if dist is not None and link_mode:      # partial exact sums -> all-reduce, then -x/100
+                dist.all_reduce(x100_dev, op=dist.ReduceOp.SUM)
+                torch.div(x100_dev.double(), -100.0, out=out_dev)
+            elif dist is not None:                  # only the score vector moves between GPUs
                 dist.all_gather_into_tensor(gathered, out_dev)
 
         for _ in range(max(args.warmup, 3)):
@@ -321,7 +337,11 @@ def main():
         t0 = time.perf_counter()
         for _ in range(steps):
             host_scores = host_call()
-            if dist is not None:
+            if dist is not None and link_mode:
+                x100_dev.copy_(torch.from_numpy(host_scores[1]))
+                dist.all_reduce(x100_dev, op=dist.ReduceOp.SUM)
+                final = (x100_dev.double() / -100.0).cpu()
+            elif dist is not None:
                 out_dev.copy_(torch.from_numpy(host_scores))
                 dist.all_gather_into_tensor(gathered, out_dev)
                 torch.cuda.synchronize()
@@ -337,7 +357,8 @@ def main():
     # ---- the headline path: streaming kernel, R-profile ----
     main = time_path(ctx, lambda: ctx.scaff_score_batch_dev(perm_dev.data_ptr(), P_loc, out_dev.data_ptr(),
                                                             x100_dev.data_ptr()),
-                     lambda: ctx.scaff_score_batch(perms), args.steps, sample_clocks=True)
+                     lambda: ctx.scaff_score_batch(perms, want_x100=link_mode), args.steps,
+                     sample_clocks=True)
     ms_dev, ms_e2e, launches, clocks, timing = (main["ms_dev"], main["ms_e2e"], main["launches"],
                                                 main["clocks"], main["last"])
     ms_score, ms_layout, ms_finish = ([main["kernel_ms"]["ms_score"]], [main["kernel_ms"]["ms_layout"]],
@@ -345,7 +366,7 @@ def main():
     stream_x100 = x100_dev.clone()
 
     extras = {}
-    if not args.no_extras:
+    if not args.no_extras and not link_mode:
         # ---- pair-table path (same inputs, same results; cost independent of L) ----
         pctx = N.Context(local, path=N.PATH_PAIRS)
         t0 = time.perf_counter()
@@ -438,7 +459,7 @@ def main():
     del a, b
     torch.cuda.empty_cache()
 
-    evals_per_step = float(P_loc * world) * float(L)
+    evals_per_step = float(P) * float(L_loc * world)
     value = evals_per_step * args.steps / (ms_dev * 1e-3)
     e2e_value = evals_per_step * args.steps / (ms_e2e * 1e-3)
 
@@ -446,9 +467,15 @@ def main():
         peak, peak_src = measured_peak_hbm()
         # algorithmic bytes of one k_scaff_score launch: every record once (2 B),
         # both placement tables of every local candidate once, the per-CTA partial sums once
-        cand = 128 if P_loc > 64 else (64 if P_loc > 32 else 32)
+        wide = n + 21 >= 0x8000                       # 32-bit placement tables (scaff_kernels.cu)
+        cmax = 64 if wide else 128
+        cand = cmax if P_loc > cmax // 2 else (cmax // 2 if P_loc > cmax // 4 else cmax // 4)
         groups = (P_loc + cand - 1) // cand
-        alg_bytes = 2.0 * L + 2.0 * 2 * groups * cand * n + 8.0 * timing["grid"] * 2 * cand
+        es = 4 if wide else 2
+        alg_bytes = 2.0 * L_loc + es * 2.0 * groups * cand * n + 8.0 * timing["grid"] * 2 * cand
+        # shared-memory wavefronts per record-warp: row B + decay look-ups + row A / 8 (per packet)
+        evals_per_cycle = (64 / 4.25) if wide else (128 / 6.25)
+        cfg_index = {"cfg2": 1, "cfg3": 2, "cfg4": 3}.get(args.workload)
         k_ms = float(np.mean(ms_score))
         achieved = alg_bytes / (k_ms * 1e-3) / 1e9
         line = {
@@ -457,14 +484,17 @@ def main():
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "int64 (exact integer accumulation of 100*T*w; fitness = -x/100 in f64)",
             "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {n} contigs / {L} link records / population {P} "
-                                   f"(BASELINE.json configs[{2 if args.workload == 'cfg3' else 1}])",
-                       "parallelism": f"population-sharded x{world}, links replicated",
-                       "population_per_gpu": P_loc,
-                       "l2_policy": f"inputs larger than L2 ({2 * L / 1e6:.0f} MB of records per pass)"
-                                    if 2 * L > 130e6 else "records fit L2; no flush (steady-state GA loop)",
+            "config": {"workload": f"{args.workload}: {n} contigs / {L_loc * world} link records / "
+                                   f"population {P}"
+                                   + (f" (BASELINE.json configs[{cfg_index}])" if cfg_index else ""),
+                       "parallelism": (f"link-sharded x{world} (NCCL all-reduce of exact int64 partials), "
+                                       "population replicated") if link_mode
+                                      else f"population-sharded x{world}, links replicated",
+                       "population_per_gpu": P_loc, "records_per_gpu": L_loc,
+                       "l2_policy": f"inputs larger than L2 ({2 * L_loc / 1e6:.0f} MB of records per pass)"
+                                    if 2 * L_loc > 130e6 else "records fit L2; no flush (steady-state GA loop)",
                        "link_store_build_s": round(t_build, 3)},
-            "candidates_per_sec": P_loc * world * args.steps / (ms_dev * 1e-3),
+            "candidates_per_sec": P * args.steps / (ms_dev * 1e-3),
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                     "h2d_bytes_per_step": int(perms.nbytes), "d2h_bytes_per_step": int(16 * P_loc)},
             "gpu_launches": int(launches),
@@ -474,14 +504,15 @@ def main():
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                          "kernel": "k_scaff_score", "algorithmic_bytes_per_launch": alg_bytes,
                          "smem_wavefront": {
-                             "what": "the roof that binds: per record-warp (128 evaluations) 2 "
-                                     "wavefronts for row B + 4 decay-table look-ups + 2/8 for row A "
-                                     "(gathered once per 8-record packet) = 6.25 shared-memory "
-                                     "wavefronts, one wavefront/cycle/SM -> 20.48 evals/cycle/SM",
-                             "peak_evals_per_s": 20.48 * 148 * (clocks["sm_mhz"] or 1965.0) * 1e6,
-                             "achieved_evals_per_s": float(P_loc) * L / (k_ms * 1e-3),
-                             "frac": float(P_loc) * L / (k_ms * 1e-3)
-                                     / (20.48 * 148 * (clocks["sm_mhz"] or 1965.0) * 1e6)},
+                             "what": "the roof that binds: per record-warp (128 evaluations; 64 with "
+                                     "32-bit tables) 2 wavefronts for row B + 4 (2) decay-table "
+                                     "look-ups + 2/8 for row A (gathered once per 8-record packet) "
+                                     "= 6.25 (4.25) shared-memory wavefronts, one wavefront/cycle/SM",
+                             "evals_per_cycle_per_sm": evals_per_cycle,
+                             "peak_evals_per_s": evals_per_cycle * 148 * (clocks["sm_mhz"] or 1965.0) * 1e6,
+                             "achieved_evals_per_s": float(P_loc) * L_loc / (k_ms * 1e-3),
+                             "frac": float(P_loc) * L_loc / (k_ms * 1e-3)
+                                     / (evals_per_cycle * 148 * (clocks["sm_mhz"] or 1965.0) * 1e6)},
                          "note": "each record byte is reused by every local candidate "
                                  f"({P_loc} evaluations per 2-byte record), so the kernel sits on "
                                  "the shared-memory-gather/issue roof, not the HBM roof; see "

@@ -573,7 +573,7 @@ int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int
 
   // work units: groups x splits, about two waves of one CTA per SM
   const int64_t npk = (S.L + kPacket - 1) / kPacket;
-  int splits = (2 * c->sm_count + groups - 1) / groups;
+  int splits = (2 * c->sm_count) / groups;  // two full waves of one CTA per SM, never a third
   if (splits < 1) splits = 1;
   const int64_t min_pk = 64;  // do not split below 512 records per unit
   if ((int64_t)splits * min_pk > npk) splits = (int)(npk / min_pk > 0 ? npk / min_pk : 1);

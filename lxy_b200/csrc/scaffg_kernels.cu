@@ -511,7 +511,7 @@ int scaffg_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, in
   LXY_CUDA(cudaEventRecord(c->ev[1], st));
 
   const int64_t npk = (S.L + kPacket - 1) / kPacket;
-  int splits = (2 * c->sm_count + groups - 1) / groups;
+  int splits = (2 * c->sm_count) / groups;  // two full waves of one CTA per SM, never a third
   if (splits < 1) splits = 1;
   if ((int64_t)splits * 64 > npk) splits = (int)(npk / 64 > 0 ? npk / 64 : 1);
   const int units = groups * splits;

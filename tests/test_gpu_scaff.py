@@ -210,3 +210,52 @@ def test_full_size_config2_properties(ctx):
     _, ox = O.scaff_score_links_batch(n, a, b, w, perms[:8], nthreads=8)
     assert xf[:8].tolist() == ox.tolist()
     assert N.rank(full)[0] in (0, 1)                 # the hidden true order (or its reverse) wins
+
+
+def test_link_sharding_identity_with_32bit_tables(ctx):
+    """BASELINE config 4's shape in small: n = 50,000 (32-bit placement tables), records split in
+    two shards; the exact integer partials add up to the unsharded result (what the NCCL
+    all-reduce relies on), and agree with the oracle."""
+    n, L, P = 50_000, 3_000_000, 70
+    a, b, w = S.scaff_links(n, L, 81)
+    perms = S.scaff_population(n, P, 181)
+    ctx.set_links(n, a, b, None)
+    _, full = ctx.scaff_score_batch(perms, want_x100=True)
+    cut = L // 3 + 5
+    ctx.set_links(n, a[:cut], b[:cut], None)
+    _, p1 = ctx.scaff_score_batch(perms, want_x100=True)
+    ctx.set_links(n, a[cut:], b[cut:], None)
+    _, p2 = ctx.scaff_score_batch(perms, want_x100=True)
+    assert (p1 + p2).tolist() == full.tolist()
+    _, ox = O.scaff_score_links_batch(n, a, b, w, perms[:6], nthreads=6)
+    assert full[:6].tolist() == ox.tolist()
+
+
+def test_full_size_config3_properties():
+    """BASELINE config 3 at full size (5,000 contigs / 200 M records), population 128: records
+    generated on the device (bench.gen_links), (i) both halves of the record stream add up to the
+    whole, (ii) the pair-table path gives the same exact integers, (iii) two candidates agree with
+    the oracle run over all 200 M records."""
+    import torch
+    import bench
+    n, L, P = 5_000, 200_000_000, 128
+    dev = torch.device("cuda", 0)
+    a, b, order = bench.gen_links(n, L, 3, dev)
+    perms = bench.gen_population(n, P, 103, order.cpu().numpy())
+    torch.cuda.synchronize()
+    with N.Context(0) as c, N.Context(0, path=N.PATH_PAIRS) as pc:
+        c.set_links_dev(n, L, a.data_ptr(), b.data_ptr())
+        full, xf = c.scaff_score_batch(perms, want_x100=True)
+        pc.set_links_dev(n, L, a.data_ptr(), b.data_ptr())
+        _, xp = pc.scaff_score_batch(perms, want_x100=True)
+        assert xp.tolist() == xf.tolist()
+        h = L // 2 + 3
+        c.set_links_dev(n, h, a.data_ptr(), b.data_ptr())
+        _, x1 = c.scaff_score_batch(perms, want_x100=True)
+        c.set_links_dev(n, L - h, a[h:].data_ptr(), b[h:].data_ptr())
+        _, x2 = c.scaff_score_batch(perms, want_x100=True)
+        assert (x1 + x2).tolist() == xf.tolist()
+    ah, bh = a.cpu().numpy().astype(np.uint32), b.cpu().numpy().astype(np.uint32)
+    _, ox = O.scaff_score_links_batch(n, ah, bh, np.ones(L), perms[:2], nthreads=2)
+    assert xf[:2].tolist() == ox.tolist()
+    assert N.rank(full)[0] in (0, 1)
