@@ -366,6 +366,47 @@ def main():
     stream_x100 = x100_dev.clone()
 
     extras = {}
+    if not args.no_extras and not link_mode and world == 1:
+        # ---- streaming regime: a lone Score() call (the reference's literal boundary hands ONE
+        # ordering to score(), scaff/genome.go:153-159).  No cross-candidate reuse, so this pass is
+        # HBM-bound: k_scaff_stream1 reads every 2-byte record once and scores it once. ----
+        peak_s, peak_src_s = measured_peak_hbm()
+        sweep = {}
+        for ps in (1, 2, 4, 8):
+            pdev = perm_dev[:ps].contiguous()
+            call = lambda: ctx.scaff_score_batch_dev(pdev.data_ptr(), ps, out_dev.data_ptr(), x100_dev.data_ptr())
+            for _ in range(3):
+                call()
+            stream = torch.cuda.ExternalStream(ctx.stream(), device=dev)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            reps = max(args.steps, 10)
+            kms = []
+            e0.record(stream)
+            for _ in range(reps):
+                call()
+                kms.append(ctx.timing()["ms_score"])
+            e1.record(stream)
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / reps
+            k = float(np.mean(kms))
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                ctx.scaff_score_batch(perms[:ps])
+            ms_h = 1e3 * (time.perf_counter() - t0) / reps
+            alg = 2.0 * L_loc + 4.0 * n * ps            # every record once + the orderings once
+            sweep[f"P={ps}"] = {
+                "value": ps * float(L_loc) / (ms * 1e-3), "unit": UNIT, "ms_per_call": ms,
+                "e2e": {"value": ps * float(L_loc) / (ms_h * 1e-3), "unit": UNIT, "ms_per_call": ms_h},
+                "k_scaff_stream1_ms": k,
+                "roofline": {"bound": "hbm", "achieved": alg / (k * 1e-3) / 1e9, "peak": peak_s,
+                             "unit": "GB/s", "frac": alg / (k * 1e-3) / 1e9 / peak_s,
+                             "algorithmic_bytes_per_launch": alg, "peak_source": peak_src_s}}
+        extras["streaming_regime"] = {
+            "what": "lone Score() calls / tiny batches on the same resident link store: lane = record, "
+                    "the whole placement table in shared memory (k_scaff_stream1); P=1 is the "
+                    "HBM-bound case north_star's '% of HBM roofline' refers to",
+            "sweep": sweep}
     if not args.no_extras and not link_mode:
         # ---- pair-table path (same inputs, same results; cost independent of L) ----
         pctx = N.Context(local, path=N.PATH_PAIRS)

@@ -43,6 +43,8 @@ typedef enum lxy_status {
 #define LXY_ACC_INT 2  /* require integral weights (error otherwise)                          */
 
 #define LXY_FLAG_NO_VALIDATE 1u /* skip the on-device permutation / bit check                  */
+#define LXY_FLAG_NO_STREAM1 2u  /* score batches of <= 8 orderings with the batch kernel too    \
+                                   (default: the lane = record streaming kernel, HBM-bound)     */
 
 /* which kernel scores the R-profile (lxy_scaff_score_batch*) */
 #define LXY_PATH_STREAM 0 /* stream every record for every candidate (north_star design; default)  */

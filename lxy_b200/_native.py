@@ -11,7 +11,7 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "_lib", "liblxyb200.so")
+LIB_PATH = os.environ.get("LXY_B200_LIB") or os.path.join(_HERE, "_lib", "liblxyb200.so")
 CSRC = os.path.join(_HERE, "csrc")
 INT64_MIN = -(1 << 63)
 
@@ -31,6 +31,7 @@ SYMBOLS = [
 ACC_AUTO, ACC_F64, ACC_INT = 0, 1, 2
 PATH_STREAM, PATH_PAIRS = 0, 1
 FLAG_NO_VALIDATE = 1
+FLAG_NO_STREAM1 = 2
 
 
 class LxyError(RuntimeError):

@@ -41,9 +41,12 @@ __device__ __forceinline__ void tma_bulk_g2s(void* dst_smem, const void* src, ui
 __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
+#ifndef LXY_LDG_STREAM
+#define LXY_LDG_STREAM "ld.global.nc.L1::no_allocate.v4.u32"
+#endif
 __device__ __forceinline__ uint4 ldg_stream_v4(const void* p) {
   uint4 r;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+  asm volatile(LXY_LDG_STREAM " {%0,%1,%2,%3}, [%4];"
                : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
                : "l"(p));
   return r;

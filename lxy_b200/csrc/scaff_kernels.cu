@@ -461,6 +461,8 @@ __global__ void k_scaff_finish(int32_t P, int32_t cand, int32_t splits,
   }
 }
 
+#include "scaff_stream1.cuh"
+
 // ---- integer checks -----------------------------------------------------------------------------
 __global__ void k_positions(const int32_t* __restrict__ perm, int32_t P, int32_t n,
                             int32_t* __restrict__ pos, int* __restrict__ flag) {
@@ -494,6 +496,8 @@ int launch_score(lxy_ctx* c, const ScoreParams& prm, int grid) {
   if (!configured[c->cfg.device & 63]) {
     LXY_CUDA(cudaFuncSetAttribute(k_scaff_score<CPL, WIDE, WM>,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    LXY_CUDA(cudaFuncSetAttribute(k_scaff_score<CPL, WIDE, WM>,
+                                  cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     configured[c->cfg.device & 63] = true;
   }
   k_scaff_score<CPL, WIDE, WM><<<grid, kThreads, smem, c->stream>>>(prm);
@@ -516,6 +520,89 @@ int launch_score_cpl(lxy_ctx* c, int cpl, const ScoreParams& prm, int grid) {
 
 static bool g_lut_loaded[64] = {};
 
+// The streaming kernels run with most of the SM's L1 carved out as shared memory; the small
+// kernels around them (layout, check, head, finish) use none.  Left to the default, the driver
+// switches the carve-out between consecutive launches and serialises them (measured: +20 us per
+// call around k_scaff_stream1).  Asking for the same carve-out everywhere removes the switch.
+static int prefer_max_carveout(lxy_ctx* c) {
+  static bool done[64] = {};
+  if (done[c->cfg.device & 63]) return LXY_OK;
+  const void* fns[] = {
+      (const void*)k_scaff_layout<false>, (const void*)k_scaff_layout<true>,
+      (const void*)k_scaff_check<false>,  (const void*)k_scaff_check<true>,
+      (const void*)k_scaff_head<W_UNIT>,  (const void*)k_scaff_head<W_INT32>, (const void*)k_scaff_head<W_F64>,
+      (const void*)k_scaff_finish<W_UNIT>, (const void*)k_scaff_finish<W_INT32>, (const void*)k_scaff_finish<W_F64>};
+  for (const void* f : fns)
+    LXY_CUDA(cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  done[c->cfg.device & 63] = true;
+  return LXY_OK;
+}
+
+// Streaming regime (scaff_stream1.cuh): head look-ups on the side stream, one pass over the records
+// with lane = record, the same fixed-order finish as the batch path.
+static int scaff_score_stream1(lxy_ctx* c, const int32_t* perm_dev, int32_t P, int nc, size_t smem,
+                               double* out_dev, int64_t* x100_dev) {
+  ScaffLinks& S = c->scaff;
+  cudaStream_t st = c->stream;
+  const int n = S.n;
+  LXY_TRY(c->d_flag.reserve(64));
+  LXY_TRY(c->d_corr.reserve(8 * (size_t)P));
+  LXY_TRY(prefer_max_carveout(c));
+  if (!g_lut_loaded[c->cfg.device & 63]) {
+    LXY_CUDA(cudaMemcpyToSymbolAsync(c_lut100, h_lut100, kLutLen, 0, cudaMemcpyHostToDevice, st));
+    g_lut_loaded[c->cfg.device & 63] = true;
+  }
+  LXY_CUDA(cudaMemsetAsync(c->d_flag.p, 0, 64, st));
+  LXY_CUDA(cudaEventRecord(c->ev[0], st));
+  {
+    cudaStream_t s2 = c->stream2;
+    LXY_CUDA(cudaStreamWaitEvent(s2, c->ev[0], 0));
+    const int hb = (P * 32 + 255) / 256;
+    const uint16_t* rec = S.rec.as<uint16_t>();
+    const int64_t* ts = S.tile_start.as<int64_t>();
+    if (S.wmode == W_UNIT) k_scaff_head<W_UNIT><<<hb, 256, 0, s2>>>(perm_dev, P, n, S.nblk, rec, S.w.p, ts, c->d_corr.p);
+    else if (S.wmode == W_INT32) k_scaff_head<W_INT32><<<hb, 256, 0, s2>>>(perm_dev, P, n, S.nblk, rec, S.w.p, ts, c->d_corr.p);
+    else k_scaff_head<W_F64><<<hb, 256, 0, s2>>>(perm_dev, P, n, S.nblk, rec, S.w.p, ts, c->d_corr.p);
+    LXY_CUDA(cudaGetLastError());
+    LXY_CUDA(cudaEventRecord(c->ev_join, s2));
+  }
+  LXY_CUDA(cudaEventRecord(c->ev[1], st));
+  // persistent CTAs: as many as fit per SM (<= 2 x 512 threads), each an equal share of the packets
+  const int per_sm = (2 * (smem + 1024) <= (size_t)c->max_smem_optin) ? 2 : 1;
+  const int64_t npk = (S.L + kPacket - 1) / kPacket;
+  int64_t grid = (int64_t)c->sm_count * per_sm;
+  if (grid * 64 > npk) grid = npk / 64 > 0 ? npk / 64 : 1;  // at least 512 records per CTA
+  LXY_TRY(c->d_partial.reserve(8 * (size_t)grid * nc));
+  Stream1Params prm;
+  prm.rec = S.rec.as<uint16_t>();
+  prm.w = S.w.p;
+  prm.tile_start = S.tile_start.as<int64_t>();
+  prm.perm = perm_dev;
+  prm.partial = c->d_partial.p;
+  prm.flag = c->d_flag.as<int>();
+  prm.L = S.L;
+  prm.n = n;
+  prm.nblk = S.nblk;
+  prm.P = P;
+  prm.validate = (c->cfg.flags & LXY_FLAG_NO_VALIDATE) ? 0 : 1;
+  LXY_TRY(S.wmode == W_UNIT ? launch_stream1_nc<W_UNIT>(c, nc, prm, (int)grid, smem)
+        : S.wmode == W_INT32 ? launch_stream1_nc<W_INT32>(c, nc, prm, (int)grid, smem)
+                             : launch_stream1_nc<W_F64>(c, nc, prm, (int)grid, smem));
+  LXY_CUDA(cudaEventRecord(c->ev[2], st));
+  LXY_CUDA(cudaStreamWaitEvent(st, c->ev_join, 0));
+  const int splits = (int)grid;
+  if (S.wmode == W_UNIT) k_scaff_finish<W_UNIT><<<(P + 7) / 8, 256, 0, st>>>(P, nc, splits, c->d_partial.p, c->d_corr.p, out_dev, x100_dev);
+  else if (S.wmode == W_INT32) k_scaff_finish<W_INT32><<<(P + 7) / 8, 256, 0, st>>>(P, nc, splits, c->d_partial.p, c->d_corr.p, out_dev, x100_dev);
+  else k_scaff_finish<W_F64><<<(P + 7) / 8, 256, 0, st>>>(P, nc, splits, c->d_partial.p, c->d_corr.p, out_dev, x100_dev);
+  LXY_CUDA(cudaGetLastError());
+  LXY_CUDA(cudaEventRecord(c->ev[3], st));
+  c->timing.launches = 3;
+  c->timing.grid = (int)grid;
+  c->timing.link_bytes = S.L * (2 + (S.wmode == W_INT32 ? 4 : S.wmode == W_F64 ? 8 : 0));
+  c->timing.table_bytes = (int64_t)grid * nc * n * 4;
+  return LXY_OK;
+}
+
 int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int32_t P,
                 double* out_dev, int64_t* x100_dev) {
   ScaffLinks& S = c->scaff;
@@ -525,6 +612,13 @@ int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int
   if (P <= 0) return LXY_OK;
   cudaStream_t st = c->stream;
   const int n = S.n;
+  // ---- streaming regime: up to 8 candidates (a lone Score() call is a batch of one) ----
+  if (P <= 8 && n <= 65536 && !(c->cfg.flags & LXY_FLAG_NO_STREAM1)) {
+    int nc = 1;
+    while (nc < P) nc *= 2;
+    const size_t smem = stream1_smem(nc, n);
+    if (smem <= (size_t)c->max_smem_optin) return scaff_score_stream1(c, perm_dev, P, nc, smem, out_dev, x100_dev);
+  }
   const bool wide = (n + kBias + 1 >= 0x8000);
   // candidates per lane: 4 (narrow) / 2 (wide) fill 128 KB of tables; small populations use less
   int cpl = wide ? 2 : 4;
@@ -537,6 +631,7 @@ int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int
   LXY_TRY(c->d_posB.reserve((size_t)Ppad * n * es));
   LXY_TRY(c->d_flag.reserve(64));
   LXY_TRY(c->d_corr.reserve(8 * (size_t)P));
+  LXY_TRY(prefer_max_carveout(c));
   if (!g_lut_loaded[c->cfg.device & 63]) {
     LXY_CUDA(cudaMemcpyToSymbolAsync(c_lut100, h_lut100, kLutLen, 0, cudaMemcpyHostToDevice, st));
     g_lut_loaded[c->cfg.device & 63] = true;

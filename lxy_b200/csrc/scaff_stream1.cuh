@@ -1,0 +1,321 @@
+// scaff_stream1.cuh — the streaming regime of the scaffolding scorer: 1..8 candidates per call.
+// (included by scaff_kernels.cu inside its anonymous namespace)
+//
+// This is the reference's literal boundary: Genome.Score() hands ONE ordering to score()
+// (/root/reference/src/lxy/scaff/genome.go:153-159 -> scaff.go:246-310).  With a single candidate
+// there is no cross-candidate reuse of a record, so the pass is bound by HBM: every 2-byte record
+// is read once and scored once.  The mapping is therefore turned around with respect to
+// k_scaff_score: lane = record (8 consecutive records per lane per 128-bit load, a warp reads 512
+// contiguous bytes), and the whole placement table pos[] of each candidate (u16, n <= 65536) sits in
+// shared memory for the lifetime of the CTA, built in the kernel from the ordering itself
+// (pos[perm[i]] = i: the exclusive prefix scan of unit lengths is the ordering index).
+//   per record:  d = |pos[a] - pos[b]|,  acc += 100*T[min(d, 21)]      (T of scaff.go:252-302)
+// The `i-k > 0` quirk (scaff.go:256) is applied by k_scaff_head / k_scaff_finish as in the batch
+// path (fitness = -(2S - H)/100), so both paths return identical integers.
+#pragma once
+
+constexpr int kS1Threads = 512;
+constexpr int kS1Warps = kS1Threads / 32;
+#ifndef LXY_S1_DEPTH
+#define LXY_S1_DEPTH 8
+#endif
+constexpr int kS1Depth = LXY_S1_DEPTH;     // 16-byte record copies in flight per lane
+constexpr int kS1Stage = kS1Threads * 16;  // bytes of one ring stage (one packet per thread)
+
+
+struct Stream1Params {
+  const uint16_t* rec;
+  const void* w;
+  const int64_t* tile_start;
+  const int32_t* perm;  // [P][n]
+  void* partial;        // [grid][NC] int64 / double
+  int* flag;
+  int64_t L;
+  int32_t n, nblk, P;
+  int32_t validate;
+};
+
+// Table entries are tab[x] = 32767 - pos[x] as int16 (pos in [0, 65535]), so that
+//   pos a - pos b = tab[b] - tab[a]   and   v = clamp(tab[b] + (21 - tab[a]), 0, 42)
+// is one VIADDMNMX.RELU per record; v indexes the 43-entry decay table c_lut100 (v = d + 21; the two
+// far entries 0 and 42 hold 0).  Every contig block of the table starts on a 512-byte boundary of
+// the shared window, so a record's row address is one LOP3: (2 * local id) | block base.
+__device__ __forceinline__ int32_t lds_s16(uint32_t addr) {
+  int32_t v;
+  asm("ld.shared.s16 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+
+__device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
+  uint4 r;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "r"(addr)
+               : "memory");
+  return r;
+}
+
+template <int WM>
+__device__ __forceinline__ void s1_acc(int32_t t, int32_t wi, double wd, int32_t& a32, int64_t& a64,
+                                       double& ad) {
+  if (WM == W_UNIT) a32 += t;
+  else if (WM == W_INT32) a64 += (int64_t)t * (int64_t)wi;
+  else ad += (double)t * wd;
+}
+
+// One record (general path: boundary packets, packets that span two a's).
+template <int NC, int WM>
+__device__ __forceinline__ void s1_eval(uint32_t baseA, uint32_t baseB, uint32_t cstride,
+                                        const uint8_t* lut, uint32_t r, int32_t wi, double wd,
+                                        int32_t (&a32)[NC], int64_t (&a64)[NC], double (&ad)[NC]) {
+  const uint32_t oa = (r >> 7) & 0x1FEu, ob = (r << 1) & 0x1FEu;
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    const int32_t ta = lds_s16((baseA + c * cstride) | oa), tb = lds_s16((baseB + c * cstride) | ob);
+    const int32_t v = __viaddmin_s32_relu(tb, (kBias + 1) - ta, kMiss + 1);
+    s1_acc<WM>(lut[v], wi, wd, a32[c], a64[c], ad[c]);
+  }
+}
+
+// Eight records of one packet, all inside the segment and all with the same a (the common case:
+// records are sorted by (a, b) inside a tile): tab[a] is fetched once.
+template <int NC, int WM>
+__device__ __forceinline__ void s1_packet_same_a(const uint4 v, uint32_t baseA, uint32_t baseB,
+                                                 uint32_t cstride, const uint8_t* lut,
+                                                 const int32_t (&wi)[kPacket], const double (&wd)[kPacket],
+                                                 int32_t (&a32)[NC], int64_t (&a64)[NC], double (&ad)[NC]) {
+  const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+  const uint32_t oa = (v.x >> 7) & 0x1FEu;
+  int32_t pterm[NC];
+#pragma unroll
+  for (int c = 0; c < NC; ++c) pterm[c] = (kBias + 1) - lds_s16((baseA + c * cstride) | oa);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const uint32_t o0 = (words[q] << 1) & 0x1FEu, o1 = (words[q] >> 15) & 0x1FEu;
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      const uint32_t bb = baseB + c * cstride;
+      const int32_t v0 = __viaddmin_s32_relu(lds_s16(bb | o0), pterm[c], kMiss + 1);
+      const int32_t v1 = __viaddmin_s32_relu(lds_s16(bb | o1), pterm[c], kMiss + 1);
+      s1_acc<WM>(lut[v0], wi[2 * q], wd[2 * q], a32[c], a64[c], ad[c]);
+      s1_acc<WM>(lut[v1], wi[2 * q + 1], wd[2 * q + 1], a32[c], a64[c], ad[c]);
+    }
+  }
+}
+
+struct S1Tile {  // a tile cursor: tile t = (I, J) holds records [.., end)
+  int64_t t, end;
+  int32_t I, J;
+  __device__ __forceinline__ void advance_to(int64_t r, const int64_t* __restrict__ tile_start, int32_t nblk) {
+    while (r >= end) {  // skips empty tiles too
+      ++t; ++J;
+      if (J == nblk) { ++I; J = I; }
+      end = tile_start[t + 1];
+    }
+  }
+};
+
+template <int NC, int WM>
+__global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params prm) {
+  typedef typename Acc<WM>::type acc_t;
+  extern __shared__ __align__(128) uint8_t smem_raw1[];
+  // contig blocks of the table must start on 512-byte boundaries of the shared window
+  uint8_t* smem = smem_raw1 + ((512u - (smem_u32(smem_raw1) & 511u)) & 511u);
+  const int32_t n = prm.n;
+  const int32_t nstride = (n + kBlk - 1) & ~(kBlk - 1);      // whole contig blocks: 512-byte aligned
+  int16_t* sPos = (int16_t*)smem;                            // [NC][nstride], 32767 - pos
+  uint8_t* s_lut = smem + (size_t)NC * nstride * 2;          // kLutLen bytes
+  acc_t* s_red = (acc_t*)(s_lut + 64);                       // [kS1Warps][NC]
+  int64_t* s_tile = (int64_t*)(s_red + kS1Warps * NC);
+  const uint32_t sbase = smem_u32(sPos), cstride = (uint32_t)nstride * 2;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+  // ---- this CTA's share of the record stream: an even split of the 8-record packets, walked in
+  // chunks of one packet per thread (8 KB; a warp owns 256 consecutive records of each chunk).
+  // Every lane keeps kS1Depth 16-byte cp.async copies (LDGSTS, L1 bypass) in flight into its own
+  // slots of a shared-memory ring: the depth is set by cp.async.wait_group, not by register
+  // scoreboards (prefetching loads all land on one scoreboard, so waiting for the oldest also waits
+  // for the newest — measured: no gain from any depth).  The first kS1Depth chunks are requested
+  // right away; their latency hides behind the table build. ----
+  const int64_t npk_all = (prm.L + kPacket - 1) / kPacket;
+  const int64_t lo = (npk_all * blockIdx.x / gridDim.x) * kPacket;
+  const int64_t hi = min((npk_all * (blockIdx.x + 1) / gridDim.x) * kPacket, prm.L);
+  constexpr int64_t kSlice = 32 * kPacket;                          // records per warp per chunk
+  constexpr int64_t kChunk = (int64_t)kS1Threads * kPacket;         // records per CTA per chunk
+  const int32_t nchunks = (int32_t)((hi - lo + kChunk - 1) / kChunk);
+  const uint32_t my_slot = smem_u32(s_tile + 2) + (uint32_t)tid * 16;  // ring: [kS1Depth][threads] x 16 B
+  int64_t r0 = lo + (int64_t)tid * kPacket;                         // this thread's packet of chunk 0
+#pragma unroll
+  for (int q = 0; q < kS1Depth; ++q) {
+    if (r0 + q * kChunk < hi) cp_async16(my_slot + q * kS1Stage, prm.rec + r0 + q * kChunk);
+    cp_async_commit();
+  }
+  // the tile holding record `lo` (the only t with tile_start[t] <= lo < tile_start[t+1])
+  if (lo < hi) {
+    const int64_t ntiles = (int64_t)prm.nblk * (prm.nblk + 1) / 2;
+    for (int64_t t = tid; t < ntiles; t += kS1Threads)
+      if (prm.tile_start[t] <= lo && lo < prm.tile_start[t + 1]) s_tile[0] = t;
+  }
+  // ---- placement tables: pos[perm[i]] = i (pad candidates: identity, discarded) ----
+  if (tid < kLutLen) s_lut[tid] = c_lut100[tid];
+  int bad = 0;
+#pragma unroll 1
+  for (int c = 0; c < NC; ++c) {
+    const int32_t* row = prm.perm + (size_t)c * n;
+    for (int i = tid; i < n; i += kS1Threads) {
+      const int32_t cid = (c < prm.P) ? row[i] : i;
+      if ((uint32_t)cid >= (uint32_t)n) bad |= 1;
+      else sPos[c * nstride + cid] = (int16_t)(32767 - i);
+    }
+  }
+  __syncthreads();
+  if (prm.validate) {  // pos[perm[i]] == i for all i <=> the row is a permutation; CTA k checks slice k
+    const int32_t i0 = (int32_t)((int64_t)n * blockIdx.x / gridDim.x), i1 = (int32_t)((int64_t)n * (blockIdx.x + 1) / gridDim.x);
+    for (int c = 0; c < prm.P && c < NC; ++c) {
+      const int32_t* row = prm.perm + (size_t)c * n;
+      for (int i = i0 + tid; i < i1; i += kS1Threads) {
+        const int32_t cid = row[i];
+        if ((uint32_t)cid < (uint32_t)n && sPos[c * nstride + cid] != (int16_t)(32767 - i)) bad |= 2;
+      }
+    }
+  }
+  if (bad) atomicOr(prm.flag, bad);
+
+  int32_t a32[NC];
+  int64_t a64[NC];
+  double ad[NC];
+#pragma unroll
+  for (int c = 0; c < NC; ++c) { a32[c] = 0; a64[c] = 0; ad[c] = 0.0; }
+
+  if (lo < hi) {
+    // warp-uniform tile cursor: the tile of the first record of this warp's slice
+    S1Tile cur;
+    cur.t = s_tile[0];
+    {
+      int32_t a = 0, b = prm.nblk;
+      while (b - a > 1) {
+        const int32_t m = (a + b) >> 1;
+        if (tile_row_start(m, prm.nblk) <= cur.t) a = m; else b = m;
+      }
+      cur.I = a;
+    }
+    cur.J = cur.I + (int32_t)(cur.t - tile_row_start(cur.I, prm.nblk));
+    cur.end = prm.tile_start[cur.t + 1];
+    // 32-bit offsets relative to `lo` from here on (a share is far below 2^31 records)
+    const int32_t hi_rel = (int32_t)(hi - lo);
+    int32_t w_rel = warp * (int32_t)kSlice;                   // first record of the warp's slice
+    int32_t r_rel = tid * kPacket;                            // this lane's packet
+    int32_t lim_rel = 0;                                      // end of (share ∩ current tile); 0 forces the set-up
+    uint32_t baseA = sbase, baseB = sbase;
+    const uint16_t* pre = prm.rec + lo + r_rel + (int64_t)kS1Depth * kChunk;  // next packet to request
+#pragma unroll 1
+    for (int32_t c = 0; c < nchunks; ++c) {
+      cp_async_wait<kS1Depth - 1>();
+      const uint4 v = lds_v4(my_slot + (uint32_t)(c & (kS1Depth - 1)) * kS1Stage);
+      bool whole = (w_rel + (int32_t)kSlice <= lim_rel);      // warp-uniform
+      if (!whole && w_rel < hi_rel) {                         // next tile (or the first one)
+        cur.advance_to(lo + w_rel, prm.tile_start, prm.nblk);
+        lim_rel = (int32_t)(min(hi, cur.end) - lo);
+        baseA = sbase + (uint32_t)cur.I * (kBlk * 2);
+        baseB = sbase + (uint32_t)cur.J * (kBlk * 2);
+        whole = (w_rel + (int32_t)kSlice <= lim_rel);
+      }
+      // one a for the whole packet (sorted by (a, b): first a == last a)
+      const bool one_a = __all_sync(0xffffffffu, ((v.x ^ (v.w >> 16)) & 0xFF00u) == 0u);
+      // v is in registers (the vote consumed it): the slot can be refilled
+      if (r_rel + kS1Depth * (int32_t)kChunk < hi_rel) cp_async16(my_slot + (uint32_t)(c & (kS1Depth - 1)) * kS1Stage, pre);
+      cp_async_commit();
+      int32_t wi[kPacket];
+      double wd[kPacket];
+      if (WM != W_UNIT && r_rel < hi_rel) load_weights<WM>(prm.w, lo + r_rel, wi, wd);
+      if (whole && one_a) {
+        s1_packet_same_a<NC, WM>(v, baseA, baseB, cstride, s_lut, wi, wd, a32, a64, ad);
+      } else if (whole) {
+        const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int k = 0; k < kPacket; ++k) {
+          const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
+          s1_eval<NC, WM>(baseA, baseB, cstride, s_lut, r, WM == W_INT32 ? wi[k] : 0,
+                          WM == W_F64 ? wd[k] : 0.0, a32, a64, ad);
+        }
+      } else if (r_rel < hi_rel) {
+        // the slice crosses a tile boundary or the end of the share: per-lane tile cursor
+        S1Tile mine = cur;
+        const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int k = 0; k < kPacket; ++k) {  // unrolled: words[] stays in registers
+          if (r_rel + k < hi_rel) {
+            mine.advance_to(lo + r_rel + k, prm.tile_start, prm.nblk);
+            const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
+            s1_eval<NC, WM>(sbase + (uint32_t)mine.I * (kBlk * 2), sbase + (uint32_t)mine.J * (kBlk * 2),
+                            cstride, s_lut, r, WM == W_INT32 ? wi[k] : 0, WM == W_F64 ? wd[k] : 0.0,
+                            a32, a64, ad);
+          }
+        }
+      }
+      w_rel += (int32_t)kChunk;
+      r_rel += (int32_t)kChunk;
+      pre += kChunk;
+    }
+  }
+  cp_async_wait<0>();
+
+  // ---- warp shuffle tree, then a fixed-order sum over the warps ----
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    acc_t v;
+    if (WM == W_F64) v = (acc_t)ad[c];
+    else if (WM == W_UNIT) v = (acc_t)a32[c];
+    else v = (acc_t)a64[c];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      if (WM == W_F64) v += (acc_t)__shfl_xor_sync(0xffffffffu, (double)v, o);
+      else v += (acc_t)__shfl_xor_sync(0xffffffffu, (long long)v, o);
+    }
+    if (lane == 0) s_red[warp * NC + c] = v;
+  }
+  __syncthreads();
+  if (tid < NC) {
+    acc_t sum = 0;
+    for (int wq = 0; wq < kS1Warps; ++wq) sum += s_red[wq * NC + tid];
+    ((acc_t*)prm.partial)[(size_t)blockIdx.x * NC + tid] = sum;
+  }
+}
+
+template <int NC, int WM>
+int launch_stream1(lxy_ctx* c, const Stream1Params& prm, int grid, size_t smem) {
+  static size_t configured[64] = {};
+  if (configured[c->cfg.device & 63] < smem) {
+    LXY_CUDA(cudaFuncSetAttribute(k_scaff_stream1<NC, WM>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)smem));
+    LXY_CUDA(cudaFuncSetAttribute(k_scaff_stream1<NC, WM>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                  cudaSharedmemCarveoutMaxShared));
+    configured[c->cfg.device & 63] = smem;
+  }
+  k_scaff_stream1<NC, WM><<<grid, kS1Threads, smem, c->stream>>>(prm);
+  LXY_CUDA(cudaGetLastError());
+  return LXY_OK;
+}
+
+template <int WM>
+int launch_stream1_nc(lxy_ctx* c, int nc, const Stream1Params& prm, int grid, size_t smem) {
+  switch (nc) {
+    case 1: return launch_stream1<1, WM>(c, prm, grid, smem);
+    case 2: return launch_stream1<2, WM>(c, prm, grid, smem);
+    case 4: return launch_stream1<4, WM>(c, prm, grid, smem);
+    default: return launch_stream1<8, WM>(c, prm, grid, smem);
+  }
+}
+
+inline size_t stream1_smem(int nc, int n) {
+  return (size_t)nc * ((n + kBlk - 1) & ~(kBlk - 1)) * 2 + 64 + (size_t)kS1Warps * nc * 8 + 16 + 512 +
+         (size_t)kS1Depth * kS1Stage;  // (alignment slack) table | lut | warp sums | start tile | record ring
+}

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Small fixed workloads for ncu: `python tools/prof_workload.py {r|g|pairs|phase} [steps]`.
+"""Small fixed workloads for ncu: `python tools/prof_workload.py {r|g|pairs|phase|s1} [steps]`.
 cfg2-sized (500 contigs, 5 M records, population 128); phase: 100k blocks, population 256."""
 import os
 import sys
@@ -21,6 +21,19 @@ if mode == "phase":
         ctx.set_phase_links(pn, a, b, w)
         for _ in range(steps):
             ctx.phase_score_batch(genes)
+        print(ctx.timing())
+    sys.exit(0)
+if mode == "s1":      # streaming regime at config-3 size: one ordering against 200 M records
+    import torch
+    import bench
+    n, L = 5000, 200_000_000
+    ta, tb, order = bench.gen_links(n, L, 3, torch.device("cuda", 0))
+    perm = torch.from_numpy(np.random.default_rng(5).permutation(n).astype(np.int32)).cuda()
+    out = torch.zeros(8, dtype=torch.float64, device="cuda")
+    with N.Context(0) as ctx:
+        ctx.set_links_dev(n, L, ta.data_ptr(), tb.data_ptr(), None)
+        for _ in range(steps):
+            ctx.scaff_score_batch_dev(perm.data_ptr(), 1, out.data_ptr(), None)
         print(ctx.timing())
     sys.exit(0)
 a, b, w = S.scaff_links(n, L, 2)
