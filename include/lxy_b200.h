@@ -152,6 +152,67 @@ int lxy_phase_score_batch_dev(lxy_ctx* ctx, const uint8_t* genes_dev, int32_t P,
 /* ---- rank / elite (go-galib sorts by Score(); lower is better, ties keep population order) --- */
 int lxy_rank(const double* scores, int32_t P, int32_t* order);
 
+/* ---- device-resident GA generation loop --------------------------------------------------------
+ * Replaces the loop `gao.Optimize(1); best := gao.Best()` of Scaffold / Phase (scaff.go:105-126,
+ * phase.go:74-95) and the genome operators it drives (scaff/genome.go:47-91,93-97,125-138,161-209;
+ * phase/genome.go:37-72,95-131): selection, PMX / two-point crossover, the shift / switch / invert
+ * mutators, scoring of the new individuals, sort and truncation all run on the device; per
+ * generation only the child count (4 bytes) crosses PCIe.  Every random decision is a pure
+ * function of (seed, generation, slot, draw) — include/lxy_ga_plan.h — so runs are reproducible and
+ * comparable with the CPU oracle.  The context must have its links set (lxy_ctx_set_links for
+ * LXY_GA_SCAFF, lxy_ctx_set_phase_links for LXY_GA_PHASE) and outlive the engine. */
+#define LXY_GA_SCAFF 0 /* GAOrderedIntGenome: permutations of 0..n-1, scored by scaff.score */
+#define LXY_GA_PHASE 1 /* GAFixedBitstringGenome: n bits, scored by phase.score           */
+
+typedef struct lxy_ga_params {
+  int32_t kind;      /* LXY_GA_*                                                               */
+  int32_t popsize;   /* gao.Init(40, genome) scaff.go:94; Init(10, ...) phase.go:63            */
+  double p_breed;    /* GAParameter.PBreed  (.2 scaff.go:85, .7 phase.go:53)                   */
+  double p_mutate;   /* GAParameter.PMutate (.6 scaff.go:84, .7 phase.go:52)                   */
+  double tour_p;     /* NewGATournamentSelector(0.7, 5) scaff.go:82, phase.go:50               */
+  int32_t tour_k;    /* contestants, <= 16                                                     */
+  uint32_t mutators; /* LXY_MUT_* mask (lxy_ga_plan.h); scaff.go:72-78 registers all three,    \
+                        phase.go:42-46 invert + switch                                        */
+  uint64_t seed;
+} lxy_ga_params;
+
+typedef struct lxy_ga_stats {
+  int64_t generations;     /* generations run so far                                           */
+  int64_t scored;          /* individuals scored so far (the reference's `scores` counter)     */
+  int32_t last_children;   /* children appended by the most recent generation                  */
+  float ms_last;           /* device time of the most recent generation                        */
+  float ms_operators;      /*   plan + children (selection, crossover, mutation)               */
+  float ms_score;          /*   scoring of the children                                        */
+  float ms_select;         /*   sort + truncation + gather                                     */
+} lxy_ga_stats;
+
+typedef struct lxy_ga lxy_ga;
+
+int lxy_ga_create(lxy_ctx* ctx, const lxy_ga_params* prm, lxy_ga** out);
+void lxy_ga_destroy(lxy_ga* ga);
+/* GARandomInitializer (scaff.go:81): every individual is a copy of `first` (nullable: 0..n-1 /
+ * all false) followed by Randomize() (n random transpositions, scaff/genome.go:130-138; n random
+ * bits, phase/genome.go:61-72) unless randomize == 0.  first: int32[n] (scaff) / uint8[n] (phase).
+ * The population is scored and sorted before the call returns. */
+int lxy_ga_init(lxy_ga* ga, const void* first, int32_t randomize);
+/* Population from the caller (popsize rows, host memory); scored and sorted. */
+int lxy_ga_set_population(lxy_ga* ga, const void* genes);
+int lxy_ga_optimize(lxy_ga* ga, int32_t generations);
+/* One generation in two halves, for callers that score the children themselves (e.g. sharded
+ * over several GPUs): begin makes the children on the device, the caller fills the score arrays
+ * (fitness, lower is better; x100 optional, unused by the engine), end sorts and truncates. */
+int lxy_ga_step_begin(lxy_ga* ga, int32_t* n_children, void** children_dev, double** scores_dev,
+                      int64_t** x100_dev);
+int lxy_ga_step_end(lxy_ga* ga);
+int lxy_ga_score_children(lxy_ga* ga, int32_t first, int32_t count); /* the local scorer on [first, first+count) */
+/* Best() (scaff.go:109): gene (int32[n] / uint8[n], nullable) and fitness of the first individual. */
+int lxy_ga_best(lxy_ga* ga, void* gene, double* score);
+/* The sorted population: genes[popsize][n] (nullable), scores[popsize] (nullable). */
+int lxy_ga_population(lxy_ga* ga, void* genes, double* scores);
+/* Test hooks: the children of the generation begun last (host copies), their plan entries. */
+int lxy_ga_children(lxy_ga* ga, void* genes, void* plan /* lxy_ga_child[n_children], nullable */);
+int lxy_ga_get_stats(lxy_ga* ga, lxy_ga_stats* out);
+
 #ifdef __cplusplus
 }
 #endif

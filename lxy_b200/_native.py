@@ -26,6 +26,9 @@ SYMBOLS = [
     "lxy_scaffg_score_batch_dev",
     "lxy_scaffg_layout", "lxy_scaffg_link_distances", "lxy_ctx_set_phase_links",
     "lxy_phase_score_batch", "lxy_phase_score_batch_dev", "lxy_rank",
+    "lxy_ga_create", "lxy_ga_destroy", "lxy_ga_init", "lxy_ga_set_population", "lxy_ga_optimize",
+    "lxy_ga_step_begin", "lxy_ga_step_end", "lxy_ga_score_children", "lxy_ga_best",
+    "lxy_ga_population", "lxy_ga_children", "lxy_ga_get_stats",
 ]
 
 ACC_AUTO, ACC_F64, ACC_INT = 0, 1, 2
@@ -53,6 +56,34 @@ class Timing(C.Structure):
 
     def asdict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class GaParams(C.Structure):
+    """lxy_ga_params (include/lxy_b200.h); defaults = the reference's Scaffold (scaff.go:72-94)."""
+    _fields_ = [("kind", C.c_int32), ("popsize", C.c_int32), ("p_breed", C.c_double),
+                ("p_mutate", C.c_double), ("tour_p", C.c_double), ("tour_k", C.c_int32),
+                ("mutators", C.c_uint32), ("seed", C.c_uint64)]
+
+
+class GaChild(C.Structure):
+    """lxy_ga_child (include/lxy_ga_plan.h)."""
+    _fields_ = [("kind", C.c_int32), ("pa", C.c_int32), ("pb", C.c_int32), ("p1", C.c_int32),
+                ("p2", C.c_int32), ("slot", C.c_int32)]
+
+
+class GaStats(C.Structure):
+    _fields_ = [("generations", C.c_int64), ("scored", C.c_int64), ("last_children", C.c_int32),
+                ("ms_last", C.c_float), ("ms_operators", C.c_float), ("ms_score", C.c_float),
+                ("ms_select", C.c_float)]
+
+    def asdict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+GA_SCAFF, GA_PHASE = 0, 1
+MUT_SHIFT, MUT_SWITCH, MUT_INVERT = 1, 2, 4
+CHILD_DTYPE = np.dtype([("kind", "<i4"), ("pa", "<i4"), ("pb", "<i4"), ("p1", "<i4"), ("p2", "<i4"),
+                        ("slot", "<i4")])
 
 
 def build(verbose=False):
@@ -101,6 +132,18 @@ def lib():
         "lxy_phase_score_batch": (i32, [vp, vp, i32, vp, vp]),
         "lxy_phase_score_batch_dev": (i32, [vp, vp, i32, vp, vp]),
         "lxy_rank": (i32, [vp, i32, vp]),
+        "lxy_ga_create": (i32, [vp, C.POINTER(GaParams), C.POINTER(vp)]),
+        "lxy_ga_destroy": (None, [vp]),
+        "lxy_ga_init": (i32, [vp, vp, i32]),
+        "lxy_ga_set_population": (i32, [vp, vp]),
+        "lxy_ga_optimize": (i32, [vp, i32]),
+        "lxy_ga_step_begin": (i32, [vp, C.POINTER(i32), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
+        "lxy_ga_step_end": (i32, [vp]),
+        "lxy_ga_score_children": (i32, [vp, i32, i32]),
+        "lxy_ga_best": (i32, [vp, vp, C.POINTER(f64)]),
+        "lxy_ga_population": (i32, [vp, vp, vp]),
+        "lxy_ga_children": (i32, [vp, vp, vp]),
+        "lxy_ga_get_stats": (i32, [vp, C.POINTER(GaStats)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -289,3 +332,80 @@ class Context:
         _check(lib().lxy_phase_score_batch_dev(self._h, C.c_void_p(genes_ptr), P,
                                                C.c_void_p(out_i64_ptr) if out_i64_ptr else None,
                                                C.c_void_p(out_f64_ptr) if out_f64_ptr else None))
+
+
+class GA:
+    """lxy_ga: the device-resident generation loop (go-galib's GAParallel as the reference uses it,
+    scaff.go:80-126 / phase.go:48-95).  Defaults are Scaffold's: population 40, PBreed .2,
+    PMutate .6, tournament(0.7, 5), shift + switch + invert mutators."""
+
+    def __init__(self, ctx, kind=GA_SCAFF, popsize=40, p_breed=0.2, p_mutate=0.6, tour_p=0.7, tour_k=5,
+                 mutators=MUT_SHIFT | MUT_SWITCH | MUT_INVERT, seed=1):
+        self.ctx = ctx
+        self.kind = kind
+        self.params = GaParams(kind, popsize, p_breed, p_mutate, tour_p, tour_k, mutators, seed)
+        self.popsize = popsize
+        self.n = ctx.phase_n if kind == GA_PHASE else ctx.n
+        self.dtype = np.uint8 if kind == GA_PHASE else np.int32
+        self._h = C.c_void_p()
+        _check(lib().lxy_ga_create(ctx._h, C.byref(self.params), C.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib().lxy_ga_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def init(self, first=None, randomize=True):
+        first = _c(first, self.dtype)
+        _check(lib().lxy_ga_init(self._h, _p(first), 1 if randomize else 0))
+
+    def set_population(self, genes):
+        genes = _c(genes, self.dtype)
+        if genes.shape != (self.popsize, self.n):
+            raise ValueError(f"genes must be [{self.popsize}][{self.n}]")
+        _check(lib().lxy_ga_set_population(self._h, _p(genes)))
+
+    def optimize(self, generations=1):
+        _check(lib().lxy_ga_optimize(self._h, generations))
+
+    def step_begin(self):
+        """-> (n_children, children device address, scores device address, x100 device address)"""
+        n = C.c_int32(0)
+        ch, sc, xx = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        _check(lib().lxy_ga_step_begin(self._h, C.byref(n), C.byref(ch), C.byref(sc), C.byref(xx)))
+        return n.value, ch.value or 0, sc.value or 0, xx.value or 0
+
+    def score_children(self, first, count):
+        _check(lib().lxy_ga_score_children(self._h, first, count))
+
+    def step_end(self):
+        _check(lib().lxy_ga_step_end(self._h))
+
+    def children(self, n_children):
+        genes = np.zeros((n_children, self.n), self.dtype)
+        plan = np.zeros(n_children, CHILD_DTYPE)
+        _check(lib().lxy_ga_children(self._h, _p(genes), _p(plan)))
+        return genes, plan
+
+    def best(self):
+        gene = np.zeros(self.n, self.dtype)
+        s = C.c_double(0)
+        _check(lib().lxy_ga_best(self._h, _p(gene), C.byref(s)))
+        return gene, s.value
+
+    def population(self):
+        genes = np.zeros((self.popsize, self.n), self.dtype)
+        scores = np.zeros(self.popsize, np.float64)
+        _check(lib().lxy_ga_population(self._h, _p(genes), _p(scores)))
+        return genes, scores
+
+    def stats(self):
+        st = GaStats()
+        _check(lib().lxy_ga_get_stats(self._h, C.byref(st)))
+        return st.asdict()
