@@ -148,6 +148,73 @@ class ClockSampler:
                 "samples": len(self.samples)}
 
 
+class _DevArray:
+    """A device allocation owned by liblxyb200, exposed to torch through __cuda_array_interface__."""
+
+    def __init__(self, ptr, count, typestr):
+        self.__cuda_array_interface__ = {"shape": (count,), "typestr": typestr, "data": (ptr, False),
+                                         "version": 2}
+
+
+def measure_ga(ctx, N, torch, dist, dev, P, n, L_eval, rank, world, generations):
+    """GA generations/sec (BASELINE.json's third metric): the device-resident loop of lxy_ga_* with
+    the reference's Scaffold parameters (PBreed .2, PMutate .6, tournament(0.7, 5), shift + switch +
+    invert; scaff.go:72-94) at the workload's population size.  N > 1: every rank runs the same
+    deterministic plan and makes the same children; rank r scores its slice of them and the fitness
+    vector is all-gathered (the only per-generation traffic between GPUs)."""
+    ga = N.GA(ctx, N.GA_SCAFF, popsize=P, seed=1234)
+    ga.init()
+    stream = torch.cuda.ExternalStream(ctx.stream(), device=dev)
+
+    def generation():
+        if world == 1:
+            ga.optimize(1)
+            return
+        C, _, sc_ptr, _ = ga.step_begin()
+        q = (C + world - 1) // world
+        lo, hi = min(rank * q, C), min((rank + 1) * q, C)
+        ga.score_children(lo, hi - lo)
+        ctx.sync()
+        sc = torch.as_tensor(_DevArray(sc_ptr, world * q, "<f8"), device=dev)   # capacity 3P >= world*q
+        mine = sc[rank * q:(rank + 1) * q].clone()
+        dist.all_gather_into_tensor(sc, mine)
+        torch.cuda.current_stream().synchronize()
+        ga.step_end()
+
+    for _ in range(3):
+        generation()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    first = ga.best()[1]
+    t0 = time.perf_counter()
+    children = 0
+    parts = {"ms_operators": 0.0, "ms_score": 0.0, "ms_select": 0.0}
+    for _ in range(generations):
+        generation()
+        st = ga.stats()
+        children += st["last_children"]
+        for k in parts:
+            parts[k] += st[k]
+    ctx.sync()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    if dist is not None:
+        tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt[0])
+    best = ga.best()[1]
+    ga.close()
+    return {"what": "device-resident GA loop (selection, PMX, mutators, scoring of the children, sort/"
+                    "truncate on the GPU; only the child count crosses PCIe per generation); wall clock "
+                    "around the generation calls, max over ranks",
+            "generations_per_sec": generations / dt, "ms_per_generation": 1e3 * dt / generations,
+            "population": P, "children_per_generation": children / generations,
+            "link_evals_per_sec": children * float(L_eval) / dt,
+            "device_ms_per_generation": {k: v / generations for k, v in parts.items()},
+            "best_fitness_before_after": [first, best]}
+
+
 def measured_peak_hbm():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -215,6 +282,17 @@ def run_reference(args, name, n, L, P):
     dt = time.perf_counter() - t0
     cand_per_s = Ps * args.steps / dt
     value = cand_per_s * L
+    # one GA generation the reference's way: its own O(n^2) PMX / mutators for ~P new individuals
+    # (oracle/ga_oracle.cpp, one thread per go-galib's breeding loop) + scoring them on all cores
+    import _ga_oracle as G
+    t0 = time.perf_counter()
+    ch = G.children(1234, 0, perms, 0.2, 0.6, 0.7, 5, 7)
+    t_ops = time.perf_counter() - t0
+    ga_ref = {"generations_per_sec": 1.0 / (t_ops + len(ch) / cand_per_s),
+              "operators_s": t_ops, "children": int(len(ch)),
+              "what": "reference-style generation on the host: genome operators as restated from "
+                      "scaff/genome.go (PMX O(n^2)) on one thread + scaff.score of the children on "
+                      f"{cores} threads"}
     sample = (f"{Ps} of {P} candidates per step against the full aggregated table "
               f"({len(ua)} pairs from {L} records), {cores} host threads; "
               f"value = candidates/s x L (the reference's cost is 12N-90 look-ups per candidate, "
@@ -223,7 +301,7 @@ def run_reference(args, name, n, L, P):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic", "candidates_per_sec": cand_per_s,
+        "data": "synthetic", "candidates_per_sec": cand_per_s, "ga": ga_ref,
         "config": {"workload": f"{name}: {n} contigs / {L} links / population {P}"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": sample},
@@ -417,6 +495,7 @@ def main():
                                                                 x100_dev.data_ptr()),
                        lambda: pctx.scaff_score_batch(perms), args.steps)
         same = bool((x100_dev == stream_x100).all().item())
+        ga_pairs = measure_ga(pctx, N, torch, dist, dev, P, n, L, rank, world, max(args.steps, 5))
         pctx.close()
         extras["pair_table_path"] = {
             "what": "LXY_PATH_PAIRS: records aggregated per pair at set_links (Links.Add), 6n table "
@@ -429,7 +508,7 @@ def main():
                     "ms_per_step": pr["ms_e2e"] / args.steps},
             "kernel_ms": pr["kernel_ms"], "table_bytes": 4 * n * n, "table_build_s": round(t_pbuild, 3),
             "gather_sector_GBps": 6.0 * P_loc * n * 32 / (pr["kernel_ms"]["ms_score"] * 1e-3) / 1e9,
-            "identical_x100_to_streaming_path": same}
+            "identical_x100_to_streaming_path": same, "ga": ga_pairs}
 
         # ---- G-profile (north_star's generalisation): lengths, orientations, in-contig offsets ----
         g = torch.Generator(device=dev)
@@ -497,10 +576,13 @@ def main():
                         "h2d_bytes_per_step": int(genes.nbytes), "d2h_bytes_per_step": 16 * pP},
                 "kernel_ms": {"k_phase_score": pt["ms_score"], "k_phase_bits": pt["ms_layout"]}}
             del genes_dev
+    if not args.no_extras and not link_mode:
+        extras["ga"] = measure_ga(ctx, N, torch, dist, dev, P, n, L, rank, world, max(args.steps, 5))
     del a, b
     torch.cuda.empty_cache()
 
-    evals_per_step = float(P) * float(L_loc * world)
+    L_total = L_loc * world if link_mode else L      # records scored per candidate, whole job
+    evals_per_step = float(P) * float(L_total)
     value = evals_per_step * args.steps / (ms_dev * 1e-3)
     e2e_value = evals_per_step * args.steps / (ms_e2e * 1e-3)
 
@@ -525,7 +607,7 @@ def main():
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "int64 (exact integer accumulation of 100*T*w; fitness = -x/100 in f64)",
             "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {n} contigs / {L_loc * world} link records / "
+            "config": {"workload": f"{args.workload}: {n} contigs / {L_total} link records / "
                                    f"population {P}"
                                    + (f" (BASELINE.json configs[{cfg_index}])" if cfg_index else ""),
                        "parallelism": (f"link-sharded x{world} (NCCL all-reduce of exact int64 partials), "

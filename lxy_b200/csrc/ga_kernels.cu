@@ -404,8 +404,8 @@ int lxy_ga_create(lxy_ctx* ctx, const lxy_ga_params* prm, lxy_ga** out) {
     if (rc == LXY_OK) rc = g->x100[b].reserve(8 * P);
   }
   if (rc == LXY_OK) rc = g->child.reserve(3 * P * row + 16);
-  if (rc == LXY_OK) rc = g->child_score.reserve(8 * 3 * P);
-  if (rc == LXY_OK) rc = g->child_x100.reserve(8 * 3 * P);
+  if (rc == LXY_OK) rc = g->child_score.reserve(8 * (3 * P + 64));
+  if (rc == LXY_OK) rc = g->child_x100.reserve(8 * (3 * P + 64));
   if (rc == LXY_OK) rc = g->plan.reserve(sizeof(lxy_ga_child) * 3 * P);
   if (rc == LXY_OK) rc = g->count.reserve(64);
   if (rc == LXY_OK) rc = g->order.reserve(4 * P);
