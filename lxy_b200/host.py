@@ -372,3 +372,88 @@ class PhaseScorer:
 def Rank(genomes):
     """Ascending fitness (lower is better, scaff.go:308), ties keep population order."""
     return [genomes[i] for i in N.rank(np.asarray([g.Score() for g in genomes], np.float64))]
+
+
+# ---------------------------------------------------------------------------------------------
+# workflows: the generation loops of scaff.Scaffold / phase.Phase on the device-resident GA
+# ---------------------------------------------------------------------------------------------
+class Intermediate:
+    """scaff.go:59-63."""
+
+    def __init__(self, iteration, score, order):
+        self.iteration, self.score, self.order = iteration, score, order
+
+
+def WriteScaffolding(scaffolding, path):              # scaff.go:24-39: one contig name per line
+    with open(path, "w") as f:
+        for v in scaffolding:
+            f.write(v + "\n")
+
+
+def ReadScaffolding(path):                            # scaff.go:41-57
+    with open(path) as f:
+        return [line.rstrip("\n") for line in f]
+
+
+def Scaffold(links, outPath, iterations, optReportFreq, device=0, seed=None, popsize=40):
+    """scaff.Scaffold (scaff.go:68-141) with the same arguments and return values: the generation
+    loop `gao.Optimize(1); best := gao.Best()` runs on the GPU (lxy_ga_*), with the reference's
+    parameters (population 40, PMutate .6, PBreed .2, tournament(0.7, 5), shift + switch + invert
+    mutators; scaff.go:72-94).  The reference seeds from the clock (scaff.go:70); `seed` makes a run
+    reproducible.  Returns (scaffolding, intermediateSolutions)."""
+    import math
+    import time
+    n = links.Size()
+    a, b, w = links.records()
+    if seed is None:
+        seed = time.time_ns() & 0xFFFFFFFFFFFF
+    with N.Context(device) as ctx:
+        ctx.set_links(n, a, b, w)
+        with N.GA(ctx, N.GA_SCAFF, popsize=popsize, p_breed=0.2, p_mutate=0.6, tour_p=0.7, tour_k=5,
+                  mutators=N.MUT_SHIFT | N.MUT_SWITCH | N.MUT_INVERT, seed=seed) as ga:
+            ga.init(np.asarray(links.IntIDs(), np.int32), randomize=True)     # GARandomInitializer
+            reportEvery = int(math.floor(iterations * optReportFreq) + 1.0)   # scaff.go:96
+            intermediates, ct, intermed = [], 0, 0
+            while True:                                                       # scaff.go:105-126
+                ct += 1
+                ga.optimize(1)
+                if ct >= iterations:
+                    break
+                if intermed > reportEvery:
+                    gene, sc = ga.best()
+                    intermediates.append(Intermediate(ct, sc, links.Decode(gene)))
+                    intermed = 0
+                intermed += 1
+            gene, _ = ga.best()
+            scores = ga.stats()["scored"]                                     # `Calls to score`
+    scaffolding = links.Decode(gene)
+    WriteScaffolding(scaffolding, outPath)
+    Scaffold.scores = scores
+    return scaffolding, intermediates
+
+
+def writePhasing(phasing, path):                      # phase.go:151-167: `name\tA|B`
+    with open(path, "w") as f:
+        for k, v in phasing.items():
+            f.write(f"{k}\t{'A' if v else 'B'}\n")
+
+
+def Phase(links, outPath, iterations, optReportFreq=0.01, device=0, seed=None, popsize=10):
+    """phase.Phase (phase.go:34-111): all-false start genome of links.Size() bits, population 10,
+    PMutate .7, PBreed .7, tournament(0.7, 5), invert + switch mutators (phase.go:42-63), the
+    generation loop on the GPU.  Returns the phasing as {name: bool} (DecodePhasing)."""
+    import time
+    n = links.Size()
+    a, b, w = links.records()
+    if seed is None:
+        seed = time.time_ns() & 0xFFFFFFFFFFFF
+    with N.Context(device) as ctx:
+        ctx.set_phase_links(n, a, b, w)
+        with N.GA(ctx, N.GA_PHASE, popsize=popsize, p_breed=0.7, p_mutate=0.7, tour_p=0.7, tour_k=5,
+                  mutators=N.MUT_INVERT | N.MUT_SWITCH, seed=seed) as ga:
+            ga.init(np.zeros(n, np.uint8), randomize=True)
+            ga.optimize(iterations)
+            gene, _ = ga.best()
+    phasing = links.DecodePhasing(gene)
+    writePhasing(phasing, outPath)
+    return phasing

@@ -59,3 +59,35 @@ def test_phasing_fixture_through_the_reference_interface(golden_files):
     for c in pop:
         assert c.Score() == ref.phase_score([int(b) for b in c.Gene])
     sc.close()
+
+
+def test_scaffold_workflow_on_the_reference_fixture(golden_files, tmp_path):
+    """scaff.Scaffold end to end (the reference's own e2e idea, scaff_test.go:10-30) on its fixture
+    test.ctg.links: 11 contigs chr2_0..chr2_10 with Toeplitz weights — the GA must find an ordering at
+    least as good as the true one, and the output file holds one contig name per line."""
+    import lxy_b200.host as H
+    links = H.LoadLinks(golden_files["test_ctg"])
+    out = tmp_path / "x.scaff.txt"
+    scaffolding, inter = H.Scaffold(links, str(out), 400, 0.01, seed=3)
+    assert sorted(scaffolding) == sorted(links.StringIDs())
+    assert H.ReadScaffolding(str(out)) == scaffolding
+    scorer = H.ScaffScorer(links)
+    true = H.NewOrderedIntGenome(list(range(11)), scorer.score)
+    found = H.NewOrderedIntGenome([links.idKey[x] for x in scaffolding], scorer.score)
+    assert found.Score() <= true.Score() + 1e-9
+    assert all(i.score >= found.Score() - 1e-9 for i in inter)      # best-so-far never gets worse
+    scorer.close()
+    assert H.Scaffold.scores > 400                                   # children were scored
+
+
+def test_phase_workflow_on_the_reference_fixture(golden_files, tmp_path):
+    """phase.Phase on test.var.links (11 variants, true phase A A B A A A A A A B A in its header):
+    the optimum (-679, brute-forced in SURVEY.md §4) is the key phasing or its complement."""
+    import lxy_b200.host as H
+    links = H.LoadLinks(golden_files["test_var"])
+    out = tmp_path / "x.phase.txt"
+    phasing = H.Phase(links, str(out), 300, seed=4)
+    bits = [phasing[links.idKeyRev[i]] for i in range(11)]
+    key = [c == "A" for c in "AABAAAAAABA"]
+    assert bits == key or bits == [not x for x in key]
+    assert len(out.read_text().splitlines()) == 11
