@@ -601,6 +601,14 @@ def main():
         cfg_index = {"cfg2": 1, "cfg3": 2, "cfg4": 3}.get(args.workload)
         k_ms = float(np.mean(ms_score))
         achieved = alg_bytes / (k_ms * 1e-3) / 1e9
+        traffic = None
+        try:                                          # ncu-measured DRAM bytes of the same launch shape
+            with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+                ent = json.load(f).get(args.workload)
+            if ent and ent["population_per_gpu"] == P_loc and not link_mode:
+                traffic = ent["bytes"]
+        except Exception:
+            pass
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps,
@@ -624,7 +632,7 @@ def main():
             "kernel_ms": {"k_scaff_score": k_ms, "layout+check": float(np.mean(ms_layout)),
                           "head+finish": float(np.mean(ms_finish))},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "kernel": "k_scaff_score", "algorithmic_bytes_per_launch": alg_bytes,
                          "smem_wavefront": {
                              "what": "the roof that binds: per record-warp (128 evaluations; 64 with "

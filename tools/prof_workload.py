@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Small fixed workloads for ncu: `python tools/prof_workload.py {r|g|pairs|phase|s1} [steps]`.
+"""Small fixed workloads for ncu: `python tools/prof_workload.py {r|g|pairs|phase|s1|r3} [steps]`.
 cfg2-sized (500 contigs, 5 M records, population 128); phase: 100k blocks, population 256."""
 import os
 import sys
@@ -21,6 +21,19 @@ if mode == "phase":
         ctx.set_phase_links(pn, a, b, w)
         for _ in range(steps):
             ctx.phase_score_batch(genes)
+        print(ctx.timing())
+    sys.exit(0)
+if mode == "r3":      # the bench default: config 3, population 1024, batch kernel
+    import torch
+    import bench
+    n, L, P = 5000, 200_000_000, 1024
+    ta, tb, order = bench.gen_links(n, L, 3, torch.device("cuda", 0))
+    perms = torch.from_numpy(bench.gen_population(n, P, 103, order.cpu().numpy())).cuda()
+    out = torch.zeros(P, dtype=torch.float64, device="cuda")
+    with N.Context(0) as ctx:
+        ctx.set_links_dev(n, L, ta.data_ptr(), tb.data_ptr(), None)
+        for _ in range(steps):
+            ctx.scaff_score_batch_dev(perms.data_ptr(), P, out.data_ptr(), None)
         print(ctx.timing())
     sys.exit(0)
 if mode == "s1":      # streaming regime at config-3 size: one ordering against 200 M records
