@@ -152,6 +152,30 @@ int lxy_phase_score_batch_dev(lxy_ctx* ctx, const uint8_t* genes_dev, int32_t P,
 /* ---- rank / elite (go-galib sorts by Score(); lower is better, ties keep population order) --- */
 int lxy_rank(const double* scores, int32_t P, int32_t* order);
 
+/* ---- host-side link table: sequtil.Links as the fitness path needs it --------------------------
+ * LoadLinks (links.go:427-491): lines starting with '#' skipped, fields split at every single space,
+ * ids by first appearance, a malformed value reads as 0, Set semantics (the last row of a pair wins,
+ * (a,b) == (b,a)), LXY_ERR_STATE when nothing was loaded; LXY_ERR_ARG where the Go code would panic
+ * (empty line, fewer than three fields).  lxy_links_id(.., create != 0) is Links.ID (links.go:100-110);
+ * lxy_links_name is Decode for one id (links.go:276-286, NULL for an unknown id); lxy_links_value is
+ * Links.Get (links.go:190-221: absent pair 0; unknown id -> -1 and LXY_ERR_ARG); lxy_links_set / _add
+ * are Set / Add (links.go:113-177); lxy_links_write is Write (links.go:242-264). */
+typedef struct lxy_links lxy_links;
+int lxy_links_new(lxy_links** out);
+int lxy_links_load(const char* path, lxy_links** out);
+void lxy_links_free(lxy_links* l);
+int lxy_links_write(const lxy_links* l, const char* path);
+int32_t lxy_links_size(const lxy_links* l);
+int64_t lxy_links_npairs(const lxy_links* l);
+int32_t lxy_links_id(lxy_links* l, const char* name, int32_t create);
+const char* lxy_links_name(const lxy_links* l, int32_t id);
+int lxy_links_set(lxy_links* l, int32_t id1, int32_t id2, double v);
+int lxy_links_add(lxy_links* l, int32_t id1, int32_t id2, double v);
+int lxy_links_value(const lxy_links* l, int32_t id1, int32_t id2, double* out);
+int lxy_links_records(const lxy_links* l, uint32_t* a, uint32_t* b, double* w); /* npairs entries, a <= b */
+/* kind 0: the table becomes the scaffolding link store (lxy_ctx_set_links); 1: the phasing store. */
+int lxy_ctx_set_links_from(lxy_ctx* ctx, const lxy_links* l, int32_t kind);
+
 /* ---- device-resident GA generation loop --------------------------------------------------------
  * Replaces the loop `gao.Optimize(1); best := gao.Best()` of Scaffold / Phase (scaff.go:105-126,
  * phase.go:74-95) and the genome operators it drives (scaff/genome.go:47-91,93-97,125-138,161-209;
@@ -212,6 +236,19 @@ int lxy_ga_population(lxy_ga* ga, void* genes, double* scores);
 /* Test hooks: the children of the generation begun last (host copies), their plan entries. */
 int lxy_ga_children(lxy_ga* ga, void* genes, void* plan /* lxy_ga_child[n_children], nullable */);
 int lxy_ga_get_stats(lxy_ga* ga, lxy_ga_stats* out);
+
+
+/* ---- the two workflows, file to file -----------------------------------------------------------
+ * lxy_scaffold_file = Scaffold (scaff.go:68-141) as `lxy scaff infer` calls it (scaff/cmd.go:135-202,
+ * without the quality metrics and plots): LoadLinks, the GA with the reference's parameters when
+ * prm is NULL (population 40, PBreed .2, PMutate .6, tournament(0.7, 5), shift + switch + invert),
+ * Decode, WriteScaffolding (one contig name per line).  lxy_phase_file = Phase (phase.go:34-111):
+ * population 10, PBreed .7, PMutate .7, invert + switch; output `name<TAB>A|B` (phase.go:151-167).
+ * best_score (nullable) receives Best().Score(). */
+int lxy_scaffold_file(const char* links_path, const char* out_path, int32_t iterations,
+                      const lxy_ga_params* prm, int32_t device, double* best_score);
+int lxy_phase_file(const char* links_path, const char* out_path, int32_t iterations,
+                   const lxy_ga_params* prm, int32_t device, double* best_score);
 
 #ifdef __cplusplus
 }

@@ -29,6 +29,10 @@ SYMBOLS = [
     "lxy_ga_create", "lxy_ga_destroy", "lxy_ga_init", "lxy_ga_set_population", "lxy_ga_optimize",
     "lxy_ga_step_begin", "lxy_ga_step_end", "lxy_ga_score_children", "lxy_ga_best",
     "lxy_ga_population", "lxy_ga_children", "lxy_ga_get_stats",
+    "lxy_links_new", "lxy_links_load", "lxy_links_free", "lxy_links_write", "lxy_links_size",
+    "lxy_links_npairs", "lxy_links_id", "lxy_links_name", "lxy_links_set", "lxy_links_add",
+    "lxy_links_value", "lxy_links_records", "lxy_ctx_set_links_from",
+    "lxy_scaffold_file", "lxy_phase_file",
 ]
 
 ACC_AUTO, ACC_F64, ACC_INT = 0, 1, 2
@@ -144,6 +148,21 @@ def lib():
         "lxy_ga_population": (i32, [vp, vp, vp]),
         "lxy_ga_children": (i32, [vp, vp, vp]),
         "lxy_ga_get_stats": (i32, [vp, C.POINTER(GaStats)]),
+        "lxy_links_new": (i32, [C.POINTER(vp)]),
+        "lxy_links_load": (i32, [C.c_char_p, C.POINTER(vp)]),
+        "lxy_links_free": (None, [vp]),
+        "lxy_links_write": (i32, [vp, C.c_char_p]),
+        "lxy_links_size": (i32, [vp]),
+        "lxy_links_npairs": (i64, [vp]),
+        "lxy_links_id": (i32, [vp, C.c_char_p, i32]),
+        "lxy_links_name": (C.c_char_p, [vp, i32]),
+        "lxy_links_set": (i32, [vp, i32, i32, f64]),
+        "lxy_links_add": (i32, [vp, i32, i32, f64]),
+        "lxy_links_value": (i32, [vp, i32, i32, C.POINTER(f64)]),
+        "lxy_links_records": (i32, [vp, vp, vp, vp]),
+        "lxy_ctx_set_links_from": (i32, [vp, vp, i32]),
+        "lxy_scaffold_file": (i32, [C.c_char_p, C.c_char_p, i32, C.POINTER(GaParams), i32, C.POINTER(f64)]),
+        "lxy_phase_file": (i32, [C.c_char_p, C.c_char_p, i32, C.POINTER(GaParams), i32, C.POINTER(f64)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -409,3 +428,86 @@ class GA:
         st = GaStats()
         _check(lib().lxy_ga_get_stats(self._h, C.byref(st)))
         return st.asdict()
+
+
+class NativeLinks:
+    """lxy_links: the library's own sequtil.Links (links.go:14-28) for the fitness path."""
+
+    def __init__(self, path=None):
+        self._h = C.c_void_p()
+        if path is None:
+            _check(lib().lxy_links_new(C.byref(self._h)))
+        else:
+            _check(lib().lxy_links_load(os.fsencode(path), C.byref(self._h)))     # LoadLinks
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib().lxy_links_free(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def Size(self):
+        return lib().lxy_links_size(self._h)
+
+    def npairs(self):
+        return lib().lxy_links_npairs(self._h)
+
+    def ID(self, name, create=True):
+        return lib().lxy_links_id(self._h, name.encode(), 1 if create else 0)
+
+    def Decode(self, ids):
+        out = []
+        for i in ids:
+            s = lib().lxy_links_name(self._h, int(i))
+            if s is None:
+                raise LxyError(-1, lib().lxy_last_error().decode(errors="replace"))
+            out.append(s.decode())
+        return out
+
+    def Set(self, id1, id2, v):
+        _check(lib().lxy_links_set(self._h, id1, id2, float(v)))
+
+    def Add(self, id1, id2, v):
+        _check(lib().lxy_links_add(self._h, id1, id2, float(v)))
+
+    def Get(self, id1, id2):
+        """(value, error-or-None) like Links.Get: (-1, error) for an unknown id."""
+        v = C.c_double(0)
+        rc = lib().lxy_links_value(self._h, id1, id2, C.byref(v))
+        return v.value, (None if rc == 0 else LxyError(rc, lib().lxy_last_error().decode(errors="replace")))
+
+    def Write(self, path):
+        _check(lib().lxy_links_write(self._h, os.fsencode(path)))
+
+    def records(self):
+        m = self.npairs()
+        a, b, w = np.zeros(m, np.uint32), np.zeros(m, np.uint32), np.zeros(m, np.float64)
+        _check(lib().lxy_links_records(self._h, _p(a), _p(b), _p(w)))
+        return a, b, w
+
+    def attach(self, ctx, phase=False):
+        _check(lib().lxy_ctx_set_links_from(ctx._h, self._h, 1 if phase else 0))
+        if phase:
+            ctx.phase_n = self.Size()
+        else:
+            ctx.n = self.Size()
+
+
+def scaffold_file(links_path, out_path, iterations, params=None, device=0):
+    """lxy_scaffold_file: `lxy scaff infer` core inside the library; returns Best().Score()."""
+    s = C.c_double(0)
+    _check(lib().lxy_scaffold_file(os.fsencode(links_path), os.fsencode(out_path), iterations,
+                                   C.byref(params) if params is not None else None, device, C.byref(s)))
+    return s.value
+
+
+def phase_file(links_path, out_path, iterations, params=None, device=0):
+    s = C.c_double(0)
+    _check(lib().lxy_phase_file(os.fsencode(links_path), os.fsencode(out_path), iterations,
+                                C.byref(params) if params is not None else None, device, C.byref(s)))
+    return s.value

@@ -91,3 +91,27 @@ def test_phase_workflow_on_the_reference_fixture(golden_files, tmp_path):
     key = [c == "A" for c in "AABAAAAAABA"]
     assert bits == key or bits == [not x for x in key]
     assert len(out.read_text().splitlines()) == 11
+
+
+def test_native_links_attach_and_file_workflows(golden, golden_files, tmp_path):
+    """The library's own LoadLinks -> resident store -> scores (golden values of the reference
+    fixtures), and the file-to-file workflows lxy_scaffold_file / lxy_phase_file."""
+    import lxy_b200._native as N
+    nl = N.NativeLinks(golden_files["test_ctg"])
+    with N.Context(0) as ctx:
+        nl.attach(ctx)
+        genes = np.array([c["gene"] for c in golden["test_ctg"]["cases"]], np.int32)
+        want = np.array([c["score"] for c in golden["test_ctg"]["cases"]])
+        np.testing.assert_allclose(ctx.scaff_score_batch(genes), want, rtol=1e-9, atol=0)
+        ident = ctx.scaff_score_batch(np.arange(11, dtype=np.int32)[None, :])[0]
+    out = tmp_path / "s.txt"
+    best = N.scaffold_file(golden_files["test_ctg"], str(out), 300)
+    names = out.read_text().splitlines()
+    assert sorted(names) == sorted(nl.Decode(range(11))) and best <= ident + 1e-9
+    pout = tmp_path / "p.txt"
+    pbest = N.phase_file(golden_files["test_var"], str(pout), 300)
+    assert pbest == -679.0                                           # SURVEY.md §4: the global optimum
+    rows = [r.split("\t") for r in pout.read_text().splitlines()]
+    assert len(rows) == 11 and {r[1] for r in rows} <= {"A", "B"}
+    with pytest.raises(N.LxyError):
+        N.scaffold_file(str(tmp_path / "nope.links"), str(out), 10)
