@@ -238,6 +238,19 @@ int lxy_ga_children(lxy_ga* ga, void* genes, void* plan /* lxy_ga_child[n_childr
 int lxy_ga_get_stats(lxy_ga* ga, lxy_ga_stats* out);
 
 
+/* ---- solution-quality metrics for whole populations ---------------------------------------------
+ * lxy_eval_scaffolding = EvalScaffolding (scaff.go:329-384) for P orderings against one key:
+ * key_rank[c] = index of contig c in the key order (the reference's keyOrder map), out[P][2] =
+ * (fraction of index triples i<j<k in key order — or in reversed key order, whichever is larger —,
+ * the same over adjacent triples).  O(n^2) per ordering instead of the reference's O(n^3), same
+ * numbers.  n <= 65536.
+ * lxy_eval_phasing = EvalPhasing (phase.go:211-263): out[P][4] = (score, firstScore, secondScore,
+ * thirdScore), including the reference's neighbour-counter quirk (phase.go:225-235). */
+int lxy_eval_scaffolding(lxy_ctx* ctx, const int32_t* perm, const int32_t* key_rank, int32_t n,
+                         int32_t P, double* out);
+int lxy_eval_phasing(lxy_ctx* ctx, const uint8_t* genes, const uint8_t* key, int32_t n, int32_t P,
+                     double* out);
+
 /* ---- the two workflows, file to file -----------------------------------------------------------
  * lxy_scaffold_file = Scaffold (scaff.go:68-141) as `lxy scaff infer` calls it (scaff/cmd.go:135-202,
  * without the quality metrics and plots): LoadLinks, the GA with the reference's parameters when

@@ -32,7 +32,7 @@ SYMBOLS = [
     "lxy_links_new", "lxy_links_load", "lxy_links_free", "lxy_links_write", "lxy_links_size",
     "lxy_links_npairs", "lxy_links_id", "lxy_links_name", "lxy_links_set", "lxy_links_add",
     "lxy_links_value", "lxy_links_records", "lxy_ctx_set_links_from",
-    "lxy_scaffold_file", "lxy_phase_file",
+    "lxy_scaffold_file", "lxy_phase_file", "lxy_eval_scaffolding", "lxy_eval_phasing",
 ]
 
 ACC_AUTO, ACC_F64, ACC_INT = 0, 1, 2
@@ -163,6 +163,8 @@ def lib():
         "lxy_ctx_set_links_from": (i32, [vp, vp, i32]),
         "lxy_scaffold_file": (i32, [C.c_char_p, C.c_char_p, i32, C.POINTER(GaParams), i32, C.POINTER(f64)]),
         "lxy_phase_file": (i32, [C.c_char_p, C.c_char_p, i32, C.POINTER(GaParams), i32, C.POINTER(f64)]),
+        "lxy_eval_scaffolding": (i32, [vp, vp, vp, i32, i32, vp]),
+        "lxy_eval_phasing": (i32, [vp, vp, vp, i32, i32, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -511,3 +513,24 @@ def phase_file(links_path, out_path, iterations, params=None, device=0):
     _check(lib().lxy_phase_file(os.fsencode(links_path), os.fsencode(out_path), iterations,
                                 C.byref(params) if params is not None else None, device, C.byref(s)))
     return s.value
+
+
+def eval_scaffolding(ctx, perms, key_order):
+    """EvalScaffolding (scaff.go:329-384) for every row of perms against key_order (contig ids in the
+    true order): -> [P][2] (qscore, neighbour score)."""
+    perms = _c(perms, np.int32)
+    key_order = _c(key_order, np.int32)
+    n = perms.shape[1]
+    rank = np.empty(n, np.int32)
+    rank[key_order] = np.arange(n, dtype=np.int32)
+    out = np.zeros((perms.shape[0], 2))
+    _check(lib().lxy_eval_scaffolding(ctx._h, _p(perms), _p(rank), n, perms.shape[0], _p(out)))
+    return out
+
+
+def eval_phasing(ctx, genes, key):
+    """EvalPhasing (phase.go:211-263): -> [P][4]."""
+    genes, key = _c(genes, np.uint8), _c(key, np.uint8)
+    out = np.zeros((genes.shape[0], 4))
+    _check(lib().lxy_eval_phasing(ctx._h, _p(genes), _p(key), genes.shape[1], genes.shape[0], _p(out)))
+    return out

@@ -158,4 +158,59 @@ void lxyo_ga_select(int popsize, int nchildren, const int64_t* keys_i64, const d
   std::copy(idx.begin(), idx.begin() + popsize, order_out);
 }
 
+
+// ---- solution-quality metrics, the reference's loops as written ------------------------------------
+// EvalScaffolding (src/lxy/scaff/scaff.go:329-384): O(n^3) walk over index triples.  scaff[i] and
+// key[i] are contig ids here (the reference uses names; keyOrder maps a name to its index in key).
+void lxyo_eval_scaffolding(const int32_t* scaff, const int32_t* key, int n, double* out2) {
+  std::vector<int> keyOrder(n), keyOrderReverse(n);
+  for (int i = 0; i < n; ++i) { keyOrder[key[i]] = i; keyOrderReverse[key[i]] = n - i; }
+  double comparisons = 0, correct = 0, correctReverse = 0, neighbors = 0, neighborsCorrect = 0,
+         neighborsCorrectReverse = 0;
+  for (int i = 0; i < n; ++i)
+    for (int j = 0; j < n; ++j)
+      for (int k = 0; k < n; ++k) {
+        if (i < j && k > j) {
+          const int v1 = scaff[i], v2 = scaff[j], v3 = scaff[k];
+          comparisons += 1;
+          if (keyOrder[v1] < keyOrder[v2] && keyOrder[v2] < keyOrder[v3]) correct += 1;
+          if (keyOrderReverse[v1] < keyOrderReverse[v2] && keyOrderReverse[v2] < keyOrderReverse[v3]) correctReverse += 1;
+          if (j == i + 1 && k == j + 1) {
+            neighbors += 1;
+            if (keyOrder[v1] < keyOrder[v2] && keyOrder[v2] < keyOrder[v3]) neighborsCorrect += 1;
+            if (keyOrderReverse[v1] < keyOrderReverse[v2] && keyOrderReverse[v2] < keyOrderReverse[v3]) neighborsCorrectReverse += 1;
+          }
+        }
+      }
+  const double qscoreF = correct / comparisons, qscoreR = correctReverse / comparisons;
+  if (qscoreF > qscoreR) { out2[0] = qscoreF; out2[1] = neighborsCorrect / neighbors; }
+  else { out2[0] = qscoreR; out2[1] = neighborsCorrectReverse / neighbors; }
+}
+
+// EvalPhasing (src/lxy/phase/phase.go:211-263), including its counter quirk (:225-235).
+void lxyo_eval_phasing(const uint8_t* phasing, const uint8_t* key, int n, double* out4) {
+  double matches = 0, comparisons = 0, neighbor_matches = 0, neighbor_comparisons = 0;
+  double second_neighbor_matches = 0, second_neighbor_comparisons = 0, third_neighbor_matches = 0,
+         third_neighbor_comparisons = 0;
+  for (int i = 0; i < n; ++i)
+    for (int j = 0; j < n; ++j) {
+      comparisons += 1;
+      if (i - j == 1 || j - i == 1) neighbor_comparisons += 1;
+      if (i - j == 2 || j - i == 2) neighbor_comparisons += 1;
+      if (i - j == 3 || j - i == 3) neighbor_comparisons += 1;
+      const bool pmatch = (phasing[i] != 0) == (phasing[j] != 0), kmatch = (key[i] != 0) == (key[j] != 0);
+      if ((pmatch && kmatch) || (!pmatch && !kmatch)) {
+        matches += 1;
+        if (i - j == 1 || j - i == 1) neighbor_matches += 1;
+        if (i - j == 2 || j - i == 2) second_neighbor_matches += 1;
+        if (i - j == 3 || j - i == 3) third_neighbor_matches += 1;
+      }
+    }
+  out4[0] = matches / comparisons;
+  out4[1] = neighbor_matches / neighbor_comparisons;
+  out4[2] = (neighbor_matches + second_neighbor_matches) / (neighbor_comparisons + second_neighbor_comparisons);
+  out4[3] = (neighbor_matches + second_neighbor_matches + third_neighbor_matches) /
+            (neighbor_comparisons + second_neighbor_comparisons + third_neighbor_comparisons);
+}
+
 }  // extern "C"

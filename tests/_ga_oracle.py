@@ -27,6 +27,8 @@ def _load():
     lib.lxyo_ga_children.argtypes = [u64, u64, i32, i32, f64, f64, f64, i32, u32, i32, vp, vp]
     lib.lxyo_ga_children.restype = i32
     lib.lxyo_ga_select.argtypes = [i32, i32, vp, vp, vp]
+    lib.lxyo_eval_scaffolding.argtypes = [vp, vp, i32, vp]
+    lib.lxyo_eval_phasing.argtypes = [vp, vp, i32, vp]
     return lib
 
 
@@ -72,3 +74,19 @@ def select(pop_scores, child_scores):
     order = np.zeros(len(pop_scores), np.int32)
     _lib.lxyo_ga_select(len(pop_scores), len(child_scores), None, _p(keys), _p(order))
     return order
+
+
+def eval_scaffolding(scaff, key):
+    """EvalScaffolding (scaff.go:329-384), the reference's O(n^3) loop; ids instead of names."""
+    scaff, key = np.ascontiguousarray(scaff, np.int32), np.ascontiguousarray(key, np.int32)
+    out = np.zeros(2)
+    _lib.lxyo_eval_scaffolding(_p(scaff), _p(key), len(scaff), _p(out))
+    return out
+
+
+def eval_phasing(phasing, key):
+    """EvalPhasing (phase.go:211-263)."""
+    phasing, key = np.ascontiguousarray(phasing, np.uint8), np.ascontiguousarray(key, np.uint8)
+    out = np.zeros(4)
+    _lib.lxyo_eval_phasing(_p(phasing), _p(key), len(phasing), _p(out))
+    return out

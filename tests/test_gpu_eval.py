@@ -1,0 +1,56 @@
+"""GPU parity of the quality metrics (lxy_eval_scaffolding / lxy_eval_phasing) against the
+reference's own loops restated in the oracle (scaff.go:329-384 O(n^3), phase.go:211-263 O(n^2)).
+The counts are integers, the results quotients of exactly representable doubles: compared exactly."""
+import numpy as np
+import pytest
+
+import _ga_oracle as G
+import lxy_b200._native as N
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("n,P,seed", [(3, 4, 1), (4, 6, 2), (11, 40, 3), (64, 16, 4), (150, 8, 5)])
+def test_eval_scaffolding_matches_reference_loop(n, P, seed):
+    rng = np.random.default_rng(seed)
+    key = rng.permutation(n).astype(np.int32)
+    perms = np.stack([rng.permutation(n) for _ in range(P)]).astype(np.int32)
+    perms[0] = key                                   # perfect: (1, 1)
+    perms[1] = key[::-1]                             # reversed key is as good (scaff.go:378-382)
+    if P > 2:
+        perms[2] = key
+        perms[2, :2] = perms[2, 1::-1]               # one adjacent swap
+    with N.Context(0) as ctx:
+        got = N.eval_scaffolding(ctx, perms, key)
+    want = np.stack([G.eval_scaffolding(p, key) for p in perms])
+    assert got.tolist() == want.tolist()
+    assert got[0].tolist() == [1.0, 1.0] and got[1].tolist() == [1.0, 1.0]
+
+
+def test_eval_scaffolding_degenerate_and_errors():
+    with N.Context(0) as ctx:
+        two = N.eval_scaffolding(ctx, np.array([[0, 1]], np.int32), np.array([0, 1], np.int32))
+        assert np.isnan(two).all()                   # 0/0 in the reference as well (no triple)
+        assert np.isnan(G.eval_scaffolding([0, 1], [0, 1])).all()
+        with pytest.raises(N.LxyError):              # an ordering that is no permutation
+            N.eval_scaffolding(ctx, np.array([[0, 0, 5]], np.int32), np.array([0, 1, 2], np.int32))
+        big = np.arange(5000, dtype=np.int32)
+        rng = np.random.default_rng(7)
+        perms = np.stack([big, big[::-1], rng.permutation(5000).astype(np.int32)])
+        q = N.eval_scaffolding(ctx, perms, big)      # config-3 size: infeasible for the O(n^3) loop
+        assert q[0].tolist() == [1.0, 1.0] and q[1].tolist() == [1.0, 1.0]
+        assert 0.15 < q[2, 0] < 0.19                 # a random order: about 1/6 of the triples
+
+
+@pytest.mark.parametrize("n,P,seed", [(1, 2, 1), (2, 3, 2), (4, 5, 3), (11, 10, 4), (300, 16, 5)])
+def test_eval_phasing_matches_reference_loop(n, P, seed):
+    rng = np.random.default_rng(seed)
+    key = rng.integers(0, 2, n).astype(np.uint8)
+    genes = rng.integers(0, 2, (P, n)).astype(np.uint8)
+    genes[0] = key
+    genes[1] = 1 - key                               # the complement phases identically
+    with N.Context(0) as ctx:
+        got = N.eval_phasing(ctx, genes, key)
+    want = np.stack([G.eval_phasing(g, key) for g in genes])
+    assert np.array_equal(got, want, equal_nan=True)
+    assert got[0, 0] == 1.0 and got[1, 0] == 1.0
