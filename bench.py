@@ -590,7 +590,7 @@ def main():
         peak, peak_src = measured_peak_hbm()
         # algorithmic bytes of one k_scaff_score launch: every record once (2 B),
         # both placement tables of every local candidate once, the per-CTA partial sums once
-        wide = n + 21 >= 0x8000                       # 32-bit placement tables (scaff_kernels.cu)
+        wide = n > 65536                              # 32-bit placement tables (scaff_kernels.cu)
         cmax = 64 if wide else 128
         cand = cmax if P_loc > cmax // 2 else (cmax // 2 if P_loc > cmax // 4 else cmax // 4)
         groups = (P_loc + cand - 1) // cand

@@ -36,7 +36,7 @@ const uint8_t h_lut100[kLutLen] = {
 // the rows of one contig block are one contiguous TMA bulk copy.  tabA holds pos + kBias + 1 and
 // tabB holds -pos (16-bit two's complement when n + kBias < 2^15, else 32-bit): the kernel's
 // VIADDMNMX then yields clamp(pos a - pos b + kBias + 1, 0, kMiss + 1) per candidate.
-template <bool WIDE>
+template <int WIDE>
 __global__ void k_scaff_layout(const int32_t* __restrict__ perm, int32_t P, int32_t Ppad, int32_t n,
                                int32_t cand, void* __restrict__ tabA, void* __restrict__ tabB,
                                int* __restrict__ flag) {
@@ -52,9 +52,12 @@ __global__ void k_scaff_layout(const int32_t* __restrict__ perm, int32_t P, int3
     }
     int32_t g = p / cand, pc = p - g * cand;
     size_t at = ((size_t)g * n + cid) * cand + pc;
-    if (WIDE) {
+    if (WIDE == 1) {
       ((uint32_t*)tabA)[at] = (uint32_t)(i + kBias + 1);
       ((uint32_t*)tabB)[at] = (uint32_t)(-i);
+    } else if (WIDE == 2) {  // centred int16, one format for both sides: pos a - pos b = tab b - tab a
+      ((uint16_t*)tabA)[at] = (uint16_t)(32767 - i);
+      ((uint16_t*)tabB)[at] = (uint16_t)(32767 - i);
     } else {
       ((uint16_t*)tabA)[at] = (uint16_t)(i + kBias + 1);
       ((uint16_t*)tabB)[at] = (uint16_t)(-i);
@@ -63,7 +66,7 @@ __global__ void k_scaff_layout(const int32_t* __restrict__ perm, int32_t P, int3
 }
 
 // pos[perm[i]] == i for every i  <=>  the row is a permutation (given the range check above).
-template <bool WIDE>
+template <int WIDE>
 __global__ void k_scaff_check(const int32_t* __restrict__ perm, int32_t P, int32_t n, int32_t cand,
                               const void* __restrict__ tabB, int* __restrict__ flag) {
   int64_t total = (int64_t)P * n;
@@ -75,8 +78,8 @@ __global__ void k_scaff_check(const int32_t* __restrict__ perm, int32_t P, int32
     if ((uint32_t)cid >= (uint32_t)n) continue;
     int32_t g = p / cand, pc = p - g * cand;
     size_t at = ((size_t)g * n + cid) * cand + pc;
-    const uint32_t got = WIDE ? ((const uint32_t*)tabB)[at] : ((const uint16_t*)tabB)[at];
-    const uint32_t want = WIDE ? (uint32_t)(-i) : (uint32_t)(uint16_t)(-i);
+    const uint32_t got = WIDE == 1 ? ((const uint32_t*)tabB)[at] : ((const uint16_t*)tabB)[at];
+    const uint32_t want = WIDE == 1 ? (uint32_t)(-i) : (uint32_t)(uint16_t)(WIDE == 2 ? 32767 - i : -i);
     if (got != want) atomicOr(flag, 2);
   }
 }
@@ -113,9 +116,9 @@ struct Lane {
 };
 
 // This lane's slice of one table row (CPL candidates) as up to four 32-bit words.
-template <int CPL, bool WIDE>
+template <int CPL, int WIDE>
 __device__ __forceinline__ void load_row(const uint8_t* row, uint32_t (&X)[4]) {
-  constexpr int BYTES = CPL * (WIDE ? 4 : 2);
+  constexpr int BYTES = CPL * (WIDE == 1 ? 4 : 2);
   if (BYTES == 16) {
     const uint4 a = *(const uint4*)row;
     X[0] = a.x; X[1] = a.y; X[2] = a.z; X[3] = a.w;
@@ -129,21 +132,49 @@ __device__ __forceinline__ void load_row(const uint8_t* row, uint32_t (&X)[4]) {
   }
 }
 
+// Sign-extended half of a 32-bit word (__byte_perm ignores the sign-replicate bit of its selector).
+__device__ __forceinline__ int sext16(uint32_t word, int high) {
+  return high ? ((int)word >> 16) : (int)(int16_t)(uint16_t)word;
+}
+
+// Row A of a record / packet.  Centred 16-bit tables (WIDE == 2): unpack to the per-candidate
+// 32-bit term 21 - tab a that eval_record adds to tab b.
+template <int CPL, int WIDE>
+__device__ __forceinline__ void load_row_a(const uint8_t* row, uint32_t (&A)[4]) {
+  if (WIDE == 2) {
+    uint32_t raw[4] = {0, 0, 0, 0};
+    load_row<CPL, WIDE>(row, raw);
+#pragma unroll
+    for (int j = 0; j < CPL; ++j)
+      A[j] = (uint32_t)((kBias + 1) - sext16(raw[j >> 1], j & 1));
+  } else {
+    load_row<CPL, WIDE>(row, A);
+  }
+}
+
 // One record against the CPL candidates of this lane, row A already in registers.
 //   narrow tables (u16): A = pos + kBias + 1, B = -pos; VIADDMNMX.S16x2.RELU gives, per half-word,
 //   v = clamp(pos a - pos b + kBias + 1, 0, kMiss + 1): one instruction for two candidates.
 //   wide tables (u32): the same with VIADDMNMX.RELU on full words.
 // v indexes the decay table: v in [1, 41] <=> |d| <= 20; 0 and 42 are the two "far" entries.
-template <int CPL, bool WIDE, int WM>
+template <int CPL, int WIDE, int WM>
 __device__ __forceinline__ void eval_record(const uint32_t (&A)[4], const uint8_t* rowB,
                                             const uint8_t* lut, const double* lutd, int32_t wi,
                                             double wd, Lane<CPL, WM>& L) {
   constexpr uint32_t kHi = kMiss + 1;  // 42
   uint32_t idx[CPL], B[4];
   load_row<CPL, WIDE>(rowB, B);
-  if (WIDE) {
+  if (WIDE == 1) {
 #pragma unroll
     for (int j = 0; j < CPL; ++j) idx[j] = (uint32_t)__viaddmin_s32_relu((int)A[j], (int)B[j], (int)kHi);
+  } else if (WIDE == 2) {
+    // 32768 <= n + 21, n <= 65536: 16-bit table entries (tab = 32767 - pos), 32-bit arithmetic.  A[]
+    // already holds 21 - tab a per candidate (eval_packet); tab b is sign-extended by one instruction.
+#pragma unroll
+    for (int j = 0; j < CPL; ++j) {
+      const int tb = sext16(B[j >> 1], j & 1);
+      idx[j] = (uint32_t)__viaddmin_s32_relu(tb, (int)A[j], (int)kHi);
+    }
   } else {
 #pragma unroll
     for (int q = 0; q < (CPL + 1) / 2; ++q) {
@@ -163,17 +194,17 @@ __device__ __forceinline__ void eval_record(const uint32_t (&A)[4], const uint8_
 // Records k in [k0, k1) of one 8-record packet (k0 = 0, k1 = 8 compiles to straight-line code).
 // SAME_A: every record of the packet has the same a (records are sorted by (a, b) inside a tile,
 // so this is the common case): row A is gathered once for the whole packet.
-template <int CPL, bool WIDE, int WM, bool SAME_A>
+template <int CPL, int WIDE, int WM, bool SAME_A>
 __device__ __forceinline__ void eval_packet(const uint4 v, const uint8_t* laneA, const uint8_t* laneB,
                                             uint32_t lane_off, const uint8_t* lut, const double* lutd,
                                             const int32_t* wi, const double* wd, int k0, int k1,
                                             Lane<CPL, WM>& L) {
-  constexpr int ROWB = 32 * CPL * (WIDE ? 4 : 2);
+  constexpr int ROWB = 32 * CPL * (WIDE == 1 ? 4 : 2);
   const uint32_t words[4] = {v.x, v.y, v.z, v.w};
   uint32_t A[4] = {0, 0, 0, 0};
   if (SAME_A) {
-    if (ROWB == 256) load_row<CPL, WIDE>(laneA - lane_off + __byte_perm(v.x, lane_off, 0x7614), A);
-    else load_row<CPL, WIDE>(laneA + ((v.x >> 8) & 0xFFu) * ROWB, A);
+    if (ROWB == 256) load_row_a<CPL, WIDE>(laneA - lane_off + __byte_perm(v.x, lane_off, 0x7614), A);
+    else load_row_a<CPL, WIDE>(laneA + ((v.x >> 8) & 0xFFu) * ROWB, A);
   }
 #pragma unroll
   for (int k = 0; k < kPacket; ++k) {
@@ -191,7 +222,7 @@ __device__ __forceinline__ void eval_packet(const uint4 v, const uint8_t* laneA,
       rowA = laneA + (r >> 8) * ROWB;
       rowB = laneB + (r & 0xFFu) * ROWB;
     }
-    if (!SAME_A) load_row<CPL, WIDE>(rowA, A);
+    if (!SAME_A) load_row_a<CPL, WIDE>(rowA, A);
     eval_record<CPL, WIDE, WM>(A, rowB, lut, lutd, WM == W_INT32 ? wi[k] : 0,
                                WM == W_F64 ? wd[k] : 0.0, L);
   }
@@ -212,10 +243,10 @@ __device__ __forceinline__ void load_weights(const void* w, int64_t base, int32_
   }
 }
 
-template <int CPL, bool WIDE, int WM>
+template <int CPL, int WIDE, int WM>
 __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
   constexpr int CAND = 32 * CPL;
-  constexpr int ES = WIDE ? 4 : 2;
+  constexpr int ES = WIDE == 1 ? 4 : 2;
   constexpr int ROWB = CAND * ES;           // bytes per contig row
   constexpr int TABB = kBlk * ROWB;         // bytes per table
   typedef typename Acc<WM>::type acc_t;
@@ -489,9 +520,9 @@ __global__ void k_link_dist(int64_t L, const uint32_t* __restrict__ a, const uin
   }
 }
 
-template <int CPL, bool WIDE, int WM>
+template <int CPL, int WIDE, int WM>
 int launch_score(lxy_ctx* c, const ScoreParams& prm, int grid) {
-  constexpr int smem = 2 * kBlk * 32 * CPL * (WIDE ? 4 : 2) + 64 + 8 * kLutLen + 16;
+  constexpr int smem = 2 * kBlk * 32 * CPL * (WIDE == 1 ? 4 : 2) + 64 + 8 * kLutLen + 16;
   static bool configured[64] = {};
   if (!configured[c->cfg.device & 63]) {
     LXY_CUDA(cudaFuncSetAttribute(k_scaff_score<CPL, WIDE, WM>,
@@ -505,13 +536,13 @@ int launch_score(lxy_ctx* c, const ScoreParams& prm, int grid) {
   return LXY_OK;
 }
 
-template <bool WIDE, int WM>
+template <int WIDE, int WM>
 int launch_score_cpl(lxy_ctx* c, int cpl, const ScoreParams& prm, int grid) {
   switch (cpl) {
     case 1: return launch_score<1, WIDE, WM>(c, prm, grid);
     case 2: return launch_score<2, WIDE, WM>(c, prm, grid);
     default:
-      if constexpr (WIDE) return launch_score<2, WIDE, WM>(c, prm, grid);
+      if constexpr (WIDE == 1) return launch_score<2, WIDE, WM>(c, prm, grid);
       else return launch_score<4, WIDE, WM>(c, prm, grid);
   }
 }
@@ -528,8 +559,8 @@ static int prefer_max_carveout(lxy_ctx* c) {
   static bool done[64] = {};
   if (done[c->cfg.device & 63]) return LXY_OK;
   const void* fns[] = {
-      (const void*)k_scaff_layout<false>, (const void*)k_scaff_layout<true>,
-      (const void*)k_scaff_check<false>,  (const void*)k_scaff_check<true>,
+      (const void*)k_scaff_layout<0>, (const void*)k_scaff_layout<1>, (const void*)k_scaff_layout<2>,
+      (const void*)k_scaff_check<0>,  (const void*)k_scaff_check<1>,  (const void*)k_scaff_check<2>,
       (const void*)k_scaff_head<W_UNIT>,  (const void*)k_scaff_head<W_INT32>, (const void*)k_scaff_head<W_F64>,
       (const void*)k_scaff_finish<W_UNIT>, (const void*)k_scaff_finish<W_INT32>, (const void*)k_scaff_finish<W_F64>};
   for (const void* f : fns)
@@ -619,8 +650,11 @@ int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int
     const size_t smem = stream1_smem(nc, n);
     if (smem <= (size_t)c->max_smem_optin) return scaff_score_stream1(c, perm_dev, P, nc, smem, out_dev, x100_dev);
   }
-  const bool wide = (n + kBias + 1 >= 0x8000);
-  // candidates per lane: 4 (narrow) / 2 (wide) fill 128 KB of tables; small populations use less
+  // table mode: 0 = packed s16 (pos + 21 | -pos; n + 21 < 2^15), 2 = centred s16 (32767 - pos; n <= 65536),
+  // 1 = 32-bit.  Modes 0 and 2 hold 128 candidates in the 128 KB of tables, mode 1 holds 64.
+  const int tm = (n + kBias + 1 < 0x8000) ? 0 : (n <= 65536 ? 2 : 1);
+  const bool wide = (tm == 1);
+  // candidates per lane: 4 (16-bit tables) / 2 (32-bit) fill 128 KB of tables; small populations use less
   int cpl = wide ? 2 : 4;
   while (cpl > 1 && P <= 32 * (cpl / 2)) cpl /= 2;
   const int cand = 32 * cpl;
@@ -655,12 +689,14 @@ int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int
     LXY_CUDA(cudaEventRecord(c->ev_join, s2));
   }
   const int lg = grid_for((int64_t)Ppad * n, 256, c->sm_count);
-  if (wide) k_scaff_layout<true><<<lg, 256, 0, st>>>(perm_dev, P, Ppad, n, cand, c->d_posA.p, c->d_posB.p, c->d_flag.as<int>());
-  else k_scaff_layout<false><<<lg, 256, 0, st>>>(perm_dev, P, Ppad, n, cand, c->d_posA.p, c->d_posB.p, c->d_flag.as<int>());
+  if (tm == 1) k_scaff_layout<1><<<lg, 256, 0, st>>>(perm_dev, P, Ppad, n, cand, c->d_posA.p, c->d_posB.p, c->d_flag.as<int>());
+  else if (tm == 2) k_scaff_layout<2><<<lg, 256, 0, st>>>(perm_dev, P, Ppad, n, cand, c->d_posA.p, c->d_posB.p, c->d_flag.as<int>());
+  else k_scaff_layout<0><<<lg, 256, 0, st>>>(perm_dev, P, Ppad, n, cand, c->d_posA.p, c->d_posB.p, c->d_flag.as<int>());
   ++launches;
   if (!(c->cfg.flags & LXY_FLAG_NO_VALIDATE)) {
-    if (wide) k_scaff_check<true><<<lg, 256, 0, st>>>(perm_dev, P, n, cand, c->d_posB.p, c->d_flag.as<int>());
-    else k_scaff_check<false><<<lg, 256, 0, st>>>(perm_dev, P, n, cand, c->d_posB.p, c->d_flag.as<int>());
+    if (tm == 1) k_scaff_check<1><<<lg, 256, 0, st>>>(perm_dev, P, n, cand, c->d_posB.p, c->d_flag.as<int>());
+    else if (tm == 2) k_scaff_check<2><<<lg, 256, 0, st>>>(perm_dev, P, n, cand, c->d_posB.p, c->d_flag.as<int>());
+    else k_scaff_check<0><<<lg, 256, 0, st>>>(perm_dev, P, n, cand, c->d_posB.p, c->d_flag.as<int>());
     ++launches;
   }
   LXY_CUDA(cudaGetLastError());
@@ -688,14 +724,18 @@ int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int
   prm.groups = groups;
   prm.splits = splits;
   int rc;
-  if (wide) {
-    rc = S.wmode == W_UNIT ? launch_score_cpl<true, W_UNIT>(c, cpl, prm, grid)
-       : S.wmode == W_INT32 ? launch_score_cpl<true, W_INT32>(c, cpl, prm, grid)
-                            : launch_score_cpl<true, W_F64>(c, cpl, prm, grid);
+  if (tm == 1) {
+    rc = S.wmode == W_UNIT ? launch_score_cpl<1, W_UNIT>(c, cpl, prm, grid)
+       : S.wmode == W_INT32 ? launch_score_cpl<1, W_INT32>(c, cpl, prm, grid)
+                            : launch_score_cpl<1, W_F64>(c, cpl, prm, grid);
+  } else if (tm == 2) {
+    rc = S.wmode == W_UNIT ? launch_score_cpl<2, W_UNIT>(c, cpl, prm, grid)
+       : S.wmode == W_INT32 ? launch_score_cpl<2, W_INT32>(c, cpl, prm, grid)
+                            : launch_score_cpl<2, W_F64>(c, cpl, prm, grid);
   } else {
-    rc = S.wmode == W_UNIT ? launch_score_cpl<false, W_UNIT>(c, cpl, prm, grid)
-       : S.wmode == W_INT32 ? launch_score_cpl<false, W_INT32>(c, cpl, prm, grid)
-                            : launch_score_cpl<false, W_F64>(c, cpl, prm, grid);
+    rc = S.wmode == W_UNIT ? launch_score_cpl<0, W_UNIT>(c, cpl, prm, grid)
+       : S.wmode == W_INT32 ? launch_score_cpl<0, W_INT32>(c, cpl, prm, grid)
+                            : launch_score_cpl<0, W_F64>(c, cpl, prm, grid);
   }
   LXY_TRY(rc);
   ++launches;

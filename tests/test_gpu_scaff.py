@@ -145,8 +145,37 @@ def test_links_get_matches_table(ctx):
     assert val == -1.0 and rc != 0
 
 
+@pytest.mark.parametrize("n,P,wts", [
+    (32746, 40, "unit"),     # last n of the packed s16 tables (pos + 21 < 2^15)
+    (32747, 40, "unit"),     # first n of the centred s16 tables (tab = 32767 - pos)
+    (40000, 130, "unit"), (50000, 40, "int"), (65536, 33, "real"),   # centred s16, all weight modes
+    (65537, 40, "unit"), (70000, 70, "int"),                         # 32-bit tables
+])
+def test_table_modes_by_n(ctx, n, P, wts):
+    """The three placement-table formats of k_scaff_score (scaff_kernels.cu) against the oracle's
+    exact integers / reference-order fitness.  Populations include the identity and its reverse,
+    where |pos a - pos b| reaches n - 1 (the 17-bit differences the centred format must survive)."""
+    L = 300000
+    a, b, _ = S.scaff_links(n, L, 61)
+    rng = np.random.default_rng(n)
+    a[:64] = 0                                       # links between the two ends of the id range
+    b[:64] = n - 1 - rng.integers(0, 30, 64).astype(np.uint32)
+    w = {"unit": np.ones(L), "int": rng.integers(-9, 300, L).astype(np.float64),
+         "real": rng.gamma(2.0, 1.5, L)}[wts]
+    perms = S.scaff_population(n, P, 161)
+    perms[0] = np.arange(n)
+    perms[1] = np.arange(n)[::-1]
+    perms[2] = np.roll(np.arange(n), 7)              # a and b end up 65529 apart: aliases to -7 in 16 bits
+    lin, ox100 = O.scaff_score_links_batch(n, a, b, w, perms, nthreads=4)
+    ctx.set_links(n, a, b, None if wts == "unit" else w)
+    got, x100 = ctx.scaff_score_batch(perms, want_x100=True)
+    if wts != "real":
+        assert x100.tolist() == ox100.tolist()
+    np.testing.assert_allclose(got, lin, rtol=REL, atol=1e-9 if wts == "int" else 0)
+
+
 def test_wide_positions_large_n(ctx):
-    n, L, P = 40000, 400000, 40                     # n > 32747 -> 32-bit placement tables
+    n, L, P = 40000, 400000, 40                     # n > 32746 -> centred 16-bit placement tables
     a, b, w = S.scaff_links(n, L, 61)
     perms = S.scaff_population(n, P, 161)
     lin, ox100 = O.scaff_score_links_batch(n, a, b, w, perms, nthreads=4)
@@ -213,7 +242,7 @@ def test_full_size_config2_properties(ctx):
 
 
 def test_link_sharding_identity_with_32bit_tables(ctx):
-    """BASELINE config 4's shape in small: n = 50,000 (32-bit placement tables), records split in
+    """BASELINE config 4's shape in small: n = 50,000 (centred 16-bit placement tables), records split in
     two shards; the exact integer partials add up to the unsharded result (what the NCCL
     all-reduce relies on), and agree with the oracle."""
     n, L, P = 50_000, 3_000_000, 70
