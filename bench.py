@@ -162,6 +162,7 @@ def measure_ga(ctx, N, torch, dist, dev, P, n, L_eval, rank, world, generations)
     invert; scaff.go:72-94) at the workload's population size.  N > 1: every rank runs the same
     deterministic plan and makes the same children; rank r scores its slice of them and the fitness
     vector is all-gathered (the only per-generation traffic between GPUs)."""
+    from lxy_b200 import sharding as SH
     ga = N.GA(ctx, N.GA_SCAFF, popsize=P, seed=1234)
     ga.init()
     stream = torch.cuda.ExternalStream(ctx.stream(), device=dev)
@@ -171,13 +172,11 @@ def measure_ga(ctx, N, torch, dist, dev, P, n, L_eval, rank, world, generations)
             ga.optimize(1)
             return
         C, _, sc_ptr, _ = ga.step_begin()
-        q = (C + world - 1) // world
-        lo, hi = min(rank * q, C), min((rank + 1) * q, C)
-        ga.score_children(lo, hi - lo)
+        lo, cnt, q = SH.ga_child_slice(C, world, rank)
+        ga.score_children(lo, cnt)
         ctx.sync()
-        sc = torch.as_tensor(_DevArray(sc_ptr, world * q, "<f8"), device=dev)   # capacity 3P >= world*q
-        mine = sc[rank * q:(rank + 1) * q].clone()
-        dist.all_gather_into_tensor(sc, mine)
+        sc = torch.as_tensor(_DevArray(sc_ptr, world * q, "<f8"), device=dev)   # capacity 3P + 64 >= world*q
+        SH.ga_gather_child_scores(sc, C)
         torch.cuda.current_stream().synchronize()
         ga.step_end()
 

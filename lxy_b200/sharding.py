@@ -66,3 +66,28 @@ def broadcast_elite(elite, src=0, group=None):
     """Elite individuals travel by broadcast (north_star): `elite` is an int32 [E][n] tensor."""
     dist.broadcast(elite, src=src, group=group)
     return elite
+
+
+# ---- GA generation with sharded scoring ---------------------------------------------------------
+# Every rank runs the same deterministic plan (include/lxy_ga_plan.h) and therefore holds the same
+# children; rank r scores the slice ga_child_slice(C, world, r) and the fitness vector is
+# all-gathered in place into the engine's score array (capacity >= world * width).
+def ga_child_slice(n_children, world, rank):
+    """(first, count, width): equal-width slices of ceil(C / world) children, the last ones short."""
+    width = (int(n_children) + world - 1) // world
+    lo = min(rank * width, n_children)
+    hi = min((rank + 1) * width, n_children)
+    return lo, hi - lo, width
+
+
+def ga_gather_child_scores(scores, n_children, group=None):
+    """`scores`: this rank's view of the children's score array (length >= world * width) with its own
+    slice filled in; afterwards entries [0, C) hold every rank's scores."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    _, _, width = ga_child_slice(n_children, world, rank)
+    if width == 0:
+        return scores
+    mine = scores[rank * width:(rank + 1) * width].clone()
+    dist.all_gather_into_tensor(scores[:world * width], mine, group=group)
+    return scores

@@ -50,6 +50,27 @@ def _worker(rank, world, port, q):
         totr = SH.combine_link_partials_f64(torch.from_numpy(pr))
         np.testing.assert_allclose(totr.numpy(), fullr, rtol=1e-12)
 
+        # GA generation with sharded scoring: same plan and children on every rank (oracle operators),
+        # each rank scores its slice, all-gather of the fitness vector, identical survivors everywhere
+        import _ga_oracle as G
+        Pg = 24
+        pop = perms[:Pg]
+        s_pop, _ = O.scaff_score_links_batch(n, a, b, w, pop)
+        order0 = np.argsort(s_pop, kind="stable")
+        pop, s_pop = pop[order0], s_pop[order0]
+        ch = G.children(9, 0, pop, 0.4, 0.6, 0.7, 5, 7)
+        C = len(ch)
+        lo, cnt, width = SH.ga_child_slice(C, world, rank)
+        assert sum(SH.ga_child_slice(C, world, r)[1] for r in range(world)) == C
+        buf = torch.full((world * width + 3,), float("nan"), dtype=torch.float64)
+        if cnt:
+            buf[lo:lo + cnt] = torch.from_numpy(O.scaff_score_links_batch(n, a, b, w, ch[lo:lo + cnt])[0])
+        SH.ga_gather_child_scores(buf, C)
+        s_ch, _ = O.scaff_score_links_batch(n, a, b, w, ch)
+        assert buf[:C].numpy().tolist() == s_ch.tolist()
+        survivors = G.select(s_pop, buf[:C].numpy())
+        assert survivors.tolist() == G.select(s_pop, s_ch).tolist()
+
         # elite broadcast
         elite = torch.from_numpy(perms[:3].copy()) if rank == 0 else torch.zeros(3, n, dtype=torch.int32)
         SH.broadcast_elite(elite, src=0)
