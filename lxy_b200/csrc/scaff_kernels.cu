@@ -103,9 +103,22 @@ struct Lane {
   int32_t a32[CPL];   // W_UNIT: 100*T summed per record (flushed into a64 before it can overflow)
   int64_t a64[CPL];
   double ad[CPL];
+  uint32_t p32[(CPL + 1) / 2];  // pair look-ups (W_UNIT): two 16-bit sums per word, flushed every <= 655 records
   __device__ __forceinline__ void clear() {
 #pragma unroll
     for (int j = 0; j < CPL; ++j) { a32[j] = 0; a64[j] = 0; ad[j] = 0.0; }
+#pragma unroll
+    for (int q = 0; q < (CPL + 1) / 2; ++q) p32[q] = 0;
+  }
+  __device__ __forceinline__ void flush16() {
+    if (WM == W_UNIT) {
+#pragma unroll
+      for (int q = 0; q < CPL / 2; ++q) {
+        a32[2 * q] += (int32_t)(p32[q] & 0xFFFFu);
+        a32[2 * q + 1] += (int32_t)(p32[q] >> 16);
+        p32[q] = 0;
+      }
+    }
   }
   __device__ __forceinline__ void flush() {
     if (WM == W_UNIT) {
@@ -152,6 +165,22 @@ __device__ __forceinline__ void load_row_a(const uint8_t* row, uint32_t (&A)[4])
   }
 }
 
+// Pair decay table (narrow tables, integer modes, even CPL): VIADDMNMX.S16x2 leaves the indices of
+// two candidates in one register, v0 | v1 << 16; one IDP.2A turns that into the shared address of
+// lut2[v1][v0] = lut[v0] | lut[v1] << 16 (rows of kLut2Stride words: the four far/far combinations
+// fall into different banks), so ONE 32-bit look-up serves two candidates and the two 16-bit halves
+// are summed in one IADD.  6.25 -> 4.25 shared-memory wavefronts per record-warp.
+constexpr int kLut2Stride = 44;
+constexpr int kLut2Words = kLutLen * kLut2Stride;
+template <int CPL, int WIDE, int WM>
+struct PairLut { static constexpr bool on = (WIDE == 0) && (WM != W_F64) && (CPL % 2 == 0); };
+
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+  uint32_t v;
+  asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+
 // One record against the CPL candidates of this lane, row A already in registers.
 //   narrow tables (u16): A = pos + kBias + 1, B = -pos; VIADDMNMX.S16x2.RELU gives, per half-word,
 //   v = clamp(pos a - pos b + kBias + 1, 0, kMiss + 1): one instruction for two candidates.
@@ -159,11 +188,25 @@ __device__ __forceinline__ void load_row_a(const uint8_t* row, uint32_t (&A)[4])
 // v indexes the decay table: v in [1, 41] <=> |d| <= 20; 0 and 42 are the two "far" entries.
 template <int CPL, int WIDE, int WM>
 __device__ __forceinline__ void eval_record(const uint32_t (&A)[4], const uint8_t* rowB,
-                                            const uint8_t* lut, const double* lutd, int32_t wi,
-                                            double wd, Lane<CPL, WM>& L) {
+                                            const uint8_t* lut, const double* lutd, uint32_t lut2,
+                                            int32_t wi, double wd, Lane<CPL, WM>& L) {
   constexpr uint32_t kHi = kMiss + 1;  // 42
   uint32_t idx[CPL], B[4];
   load_row<CPL, WIDE>(rowB, B);
+  if (PairLut<CPL, WIDE, WM>::on) {
+#pragma unroll
+    for (int q = 0; q < CPL / 2; ++q) {
+      const uint32_t m = __viaddmin_s16x2_relu(A[q], B[q], kHi | (kHi << 16));
+      const uint32_t e = lds_u32(__dp2a_lo(m, 4u | ((4u * kLut2Stride) << 8), lut2));
+      if (WM == W_UNIT) {
+        L.p32[q] += e;
+      } else {
+        L.a64[2 * q] += (int64_t)(int32_t)(e & 0xFFFFu) * (int64_t)wi;
+        L.a64[2 * q + 1] += (int64_t)(int32_t)(e >> 16) * (int64_t)wi;
+      }
+    }
+    return;
+  }
   if (WIDE == 1) {
 #pragma unroll
     for (int j = 0; j < CPL; ++j) idx[j] = (uint32_t)__viaddmin_s32_relu((int)A[j], (int)B[j], (int)kHi);
@@ -197,7 +240,7 @@ __device__ __forceinline__ void eval_record(const uint32_t (&A)[4], const uint8_
 template <int CPL, int WIDE, int WM, bool SAME_A>
 __device__ __forceinline__ void eval_packet(const uint4 v, const uint8_t* laneA, const uint8_t* laneB,
                                             uint32_t lane_off, const uint8_t* lut, const double* lutd,
-                                            const int32_t* wi, const double* wd, int k0, int k1,
+                                            uint32_t lut2, const int32_t* wi, const double* wd, int k0, int k1,
                                             Lane<CPL, WM>& L) {
   constexpr int ROWB = 32 * CPL * (WIDE == 1 ? 4 : 2);
   const uint32_t words[4] = {v.x, v.y, v.z, v.w};
@@ -223,7 +266,7 @@ __device__ __forceinline__ void eval_packet(const uint4 v, const uint8_t* laneA,
       rowB = laneB + (r & 0xFFu) * ROWB;
     }
     if (!SAME_A) load_row_a<CPL, WIDE>(rowA, A);
-    eval_record<CPL, WIDE, WM>(A, rowB, lut, lutd, WM == W_INT32 ? wi[k] : 0,
+    eval_record<CPL, WIDE, WM>(A, rowB, lut, lutd, lut2, WM == W_INT32 ? wi[k] : 0,
                                WM == W_F64 ? wd[k] : 0.0, L);
   }
 }
@@ -257,6 +300,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
   uint8_t* s_lut = smem + 2 * TABB;                       // kLutLen bytes
   double* s_lutd = (double*)(smem + 2 * TABB + 64);       // kLutLen doubles
   uint64_t* bar = (uint64_t*)(smem + 2 * TABB + 64 + 8 * kLutLen);
+  uint32_t* s_lut2 = (uint32_t*)(smem + 2 * TABB + 64 + 8 * kLutLen + 16);  // [kLutLen][kLut2Stride]
+  const uint32_t lut2 = smem_u32(s_lut2);
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid < kLutLen) {
@@ -268,6 +313,13 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
+  if (PairLut<CPL, WIDE, WM>::on) {
+    for (int i = tid; i < kLut2Words; i += kThreads) {
+      const int v1 = i / kLut2Stride, v0 = i - v1 * kLut2Stride;
+      s_lut2[i] = (v0 < kLutLen ? (uint32_t)s_lut[v0] : 0u) | ((uint32_t)s_lut[v1] << 16);
+    }
+    __syncthreads();
+  }
   uint32_t parity = 0;
   const uint32_t lane_off = lane * (CPL * ES);
   const uint8_t* laneA = sA + lane_off;
@@ -340,7 +392,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
           const int k0 = (int)(cur - base), k1 = (int)min((int64_t)kPacket, seg_end - base);
 #pragma unroll 1
           for (int k = k0; k < k1; ++k)
-            eval_packet<CPL, WIDE, WM, false>(v, laneA, laneB, lane_off, s_lut, s_lutd, wi, wd, k, k + 1, acc);
+            eval_packet<CPL, WIDE, WM, false>(v, laneA, laneB, lane_off, s_lut, s_lutd, lut2, wi, wd, k, k + 1, acc);
+          acc.flush16();
         }
         if (tail_partial && warp == 1 && !(head_partial && p_last == p_first)) {
           const int64_t base = p_last * kPacket;
@@ -349,7 +402,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
           const int k1 = (int)(seg_end - base);
 #pragma unroll 1
           for (int k = 0; k < k1; ++k)
-            eval_packet<CPL, WIDE, WM, false>(v, laneA, laneB, lane_off, s_lut, s_lutd, wi, wd, k, k + 1, acc);
+            eval_packet<CPL, WIDE, WM, false>(v, laneA, laneB, lane_off, s_lut, s_lutd, lut2, wi, wd, k, k + 1, acc);
+          acc.flush16();
         }
         // full packets: straight-line code, next packet's load in flight while this one is scored
         const int64_t f0 = p_first + (head_partial ? 1 : 0);
@@ -365,17 +419,20 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
             int32_t it = warp;
             uint4 vn = make_uint4(0, 0, 0, 0);
             if (it < cnt) vn = ldg_stream_v4(rp + (size_t)it * kPacket);
+            int32_t since = 0;  // packets since the 16-bit pair sums were unpacked: 64 * 8 * 100 < 2^16
 #pragma unroll 1
             for (; it < cnt; it += kWarps) {
+              if (PairLut<CPL, WIDE, WM>::on && WM == W_UNIT && ++since == 64) { acc.flush16(); since = 0; }
               const uint4 v = vn;
               if (it + kWarps < cnt) vn = ldg_stream_v4(rp + (size_t)(it + kWarps) * kPacket);
               load_weights<WM>(prm.w, wbase + (c0 + it) * kPacket, wi, wd);
               // sorted by (a, b): first a == last a  <=>  one a for the whole packet (warp-uniform)
               if (((v.x >> 8) & 0xFFu) == (v.w >> 24))
-                eval_packet<CPL, WIDE, WM, true>(v, laneA, laneB, lane_off, s_lut, s_lutd, wi, wd, 0, kPacket, acc);
+                eval_packet<CPL, WIDE, WM, true>(v, laneA, laneB, lane_off, s_lut, s_lutd, lut2, wi, wd, 0, kPacket, acc);
               else
-                eval_packet<CPL, WIDE, WM, false>(v, laneA, laneB, lane_off, s_lut, s_lutd, wi, wd, 0, kPacket, acc);
+                eval_packet<CPL, WIDE, WM, false>(v, laneA, laneB, lane_off, s_lut, s_lutd, lut2, wi, wd, 0, kPacket, acc);
             }
+            acc.flush16();
             acc.flush();
           }
         }
@@ -522,7 +579,7 @@ __global__ void k_link_dist(int64_t L, const uint32_t* __restrict__ a, const uin
 
 template <int CPL, int WIDE, int WM>
 int launch_score(lxy_ctx* c, const ScoreParams& prm, int grid) {
-  constexpr int smem = 2 * kBlk * 32 * CPL * (WIDE == 1 ? 4 : 2) + 64 + 8 * kLutLen + 16;
+  constexpr int smem = 2 * kBlk * 32 * CPL * (WIDE == 1 ? 4 : 2) + 64 + 8 * kLutLen + 16 + 4 * kLut2Words;
   static bool configured[64] = {};
   if (!configured[c->cfg.device & 63]) {
     LXY_CUDA(cudaFuncSetAttribute(k_scaff_score<CPL, WIDE, WM>,

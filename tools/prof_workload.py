@@ -39,7 +39,8 @@ if mode == "r3":      # the bench default: config 3, population 1024, batch kern
 if mode == "s1":      # streaming regime at config-3 size: one ordering against 200 M records
     import torch
     import bench
-    n, L = 5000, 200_000_000
+    import os
+    n, L = 5000, int(float(os.environ.get("S1_L", "2e8")))
     ta, tb, order = bench.gen_links(n, L, 3, torch.device("cuda", 0))
     perm = torch.from_numpy(np.random.default_rng(5).permutation(n).astype(np.int32)).cuda()
     out = torch.zeros(8, dtype=torch.float64, device="cuda")

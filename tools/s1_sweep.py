@@ -18,7 +18,8 @@ ta, tb, order = bench.gen_links(n, Lmax, 3, dev)
 perm = torch.from_numpy(np.random.default_rng(5).permutation(n).astype(np.int32)).cuda()
 out = torch.zeros(8, dtype=torch.float64, device="cuda")
 with N.Context(0) as ctx:
-    for L in (1_000_000, 10_000_000, 50_000_000, 100_000_000, 200_000_000, 400_000_000):
+    Ls = [int(float(x)) for x in os.environ.get("S1_LS", "1e6,1e7,5e7,1e8,2e8,4e8").split(",")]
+    for L in Ls:
         ctx.set_links_dev(n, L, ta.data_ptr(), tb.data_ptr(), None)
         ts = []
         for _ in range(8):
