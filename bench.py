@@ -37,8 +37,9 @@ WORKLOADS = {
     # link-sharded (BASELINE.json configs[3]): records split across ranks, NCCL all-reduce of partials
     "cfg4": (50_000, 2_000_000_000, 1024, 4, 104),
     "cfg4s": (50_000, 64_000_000, 256, 4, 104),
+    "cfg4m": (50_000, 500_000_000, 1024, 4, 104),
 }
-LINK_SHARDED = {"cfg4", "cfg4s"}
+LINK_SHARDED = {"cfg4", "cfg4s", "cfg4m"}
 METRIC = "ga_fitness_link_evals_per_sec"
 UNIT = "link-evals/s"
 
@@ -596,7 +597,7 @@ def main():
         es = 4 if wide else 2
         alg_bytes = 2.0 * L_loc + es * 2.0 * groups * cand * n + 8.0 * timing["grid"] * 2 * cand
         # shared-memory wavefronts per record-warp: row B + decay look-ups + row A / 8 (per packet)
-        evals_per_cycle = (64 / 4.25) if wide else (128 / 6.25)
+        evals_per_cycle = (64 / 3.375) if wide else (128 / 4.375)
         cfg_index = {"cfg2": 1, "cfg3": 2, "cfg4": 3}.get(args.workload)
         k_ms = float(np.mean(ms_score))
         achieved = alg_bytes / (k_ms * 1e-3) / 1e9
@@ -635,9 +636,11 @@ def main():
                          "kernel": "k_scaff_score", "algorithmic_bytes_per_launch": alg_bytes,
                          "smem_wavefront": {
                              "what": "the roof that binds: per record-warp (128 evaluations; 64 with "
-                                     "32-bit tables) 2 wavefronts for row B + 4 (2) decay-table "
-                                     "look-ups + 2/8 for row A (gathered once per 8-record packet) "
-                                     "= 6.25 (4.25) shared-memory wavefronts, one wavefront/cycle/SM",
+                                     "32-bit tables) 2 wavefronts for row B + 2 (1) decay-table look-ups "
+                                     "(pair table: one 32-bit look-up per two candidates) + 2/8 for "
+                                     "row A (gathered once per 8-record packet) + 1/8 for the packet's "
+                                     "own 16-byte load = 4.375 (3.375) wavefronts of the L1/shared data pipe, "
+                                     "one wavefront/cycle/SM",
                              "evals_per_cycle_per_sm": evals_per_cycle,
                              "peak_evals_per_s": evals_per_cycle * 148 * (clocks["sm_mhz"] or 1965.0) * 1e6,
                              "achieved_evals_per_s": float(P_loc) * L_loc / (k_ms * 1e-3),

@@ -18,7 +18,10 @@
 namespace lxy {
 namespace {
 
-constexpr int kThreads = 512;
+#ifndef LXY_SCORE_THREADS
+#define LXY_SCORE_THREADS 768
+#endif
+constexpr int kThreads = LXY_SCORE_THREADS;
 constexpr int kWarps = kThreads / 32;
 constexpr int kPacket = 8;  // records per 128-bit load
 
@@ -55,10 +58,7 @@ __global__ void k_scaff_layout(const int32_t* __restrict__ perm, int32_t P, int3
     if (WIDE == 1) {
       ((uint32_t*)tabA)[at] = (uint32_t)(i + kBias + 1);
       ((uint32_t*)tabB)[at] = (uint32_t)(-i);
-    } else if (WIDE == 2) {  // centred int16, one format for both sides: pos a - pos b = tab b - tab a
-      ((uint16_t*)tabA)[at] = (uint16_t)(32767 - i);
-      ((uint16_t*)tabB)[at] = (uint16_t)(32767 - i);
-    } else {
+    } else {  // WIDE 0 and 2 share the 16-bit format (2: read modulo 2^16)
       ((uint16_t*)tabA)[at] = (uint16_t)(i + kBias + 1);
       ((uint16_t*)tabB)[at] = (uint16_t)(-i);
     }
@@ -79,7 +79,7 @@ __global__ void k_scaff_check(const int32_t* __restrict__ perm, int32_t P, int32
     int32_t g = p / cand, pc = p - g * cand;
     size_t at = ((size_t)g * n + cid) * cand + pc;
     const uint32_t got = WIDE == 1 ? ((const uint32_t*)tabB)[at] : ((const uint16_t*)tabB)[at];
-    const uint32_t want = WIDE == 1 ? (uint32_t)(-i) : (uint32_t)(uint16_t)(WIDE == 2 ? 32767 - i : -i);
+    const uint32_t want = WIDE == 1 ? (uint32_t)(-i) : (uint32_t)(uint16_t)(-i);
     if (got != want) atomicOr(flag, 2);
   }
 }
@@ -150,30 +150,24 @@ __device__ __forceinline__ int sext16(uint32_t word, int high) {
   return high ? ((int)word >> 16) : (int)(int16_t)(uint16_t)word;
 }
 
-// Row A of a record / packet.  Centred 16-bit tables (WIDE == 2): unpack to the per-candidate
-// 32-bit term 21 - tab a that eval_record adds to tab b.
+// Row A of a record / packet.
 template <int CPL, int WIDE>
 __device__ __forceinline__ void load_row_a(const uint8_t* row, uint32_t (&A)[4]) {
-  if (WIDE == 2) {
-    uint32_t raw[4] = {0, 0, 0, 0};
-    load_row<CPL, WIDE>(row, raw);
-#pragma unroll
-    for (int j = 0; j < CPL; ++j)
-      A[j] = (uint32_t)((kBias + 1) - sext16(raw[j >> 1], j & 1));
-  } else {
-    load_row<CPL, WIDE>(row, A);
-  }
+  load_row<CPL, WIDE>(row, A);
 }
 
-// Pair decay table (narrow tables, integer modes, even CPL): VIADDMNMX.S16x2 leaves the indices of
+// Pair decay table (integer modes, even CPL).  Narrow tables: VIADDMNMX.S16x2 leaves the indices of
 // two candidates in one register, v0 | v1 << 16; one IDP.2A turns that into the shared address of
 // lut2[v1][v0] = lut[v0] | lut[v1] << 16 (rows of kLut2Stride words: the four far/far combinations
 // fall into different banks), so ONE 32-bit look-up serves two candidates and the two 16-bit halves
 // are summed in one IADD.  6.25 -> 4.25 shared-memory wavefronts per record-warp.
 constexpr int kLut2Stride = 44;
 constexpr int kLut2Words = kLutLen * kLut2Stride;
+#ifndef LXY_PAIRLUT_MASK
+#define LXY_PAIRLUT_MASK 7  /* bit WIDE: table formats that use the pair table */
+#endif
 template <int CPL, int WIDE, int WM>
-struct PairLut { static constexpr bool on = (WIDE == 0) && (WM != W_F64) && (CPL % 2 == 0); };
+struct PairLut { static constexpr bool on = (WM != W_F64) && (CPL % 2 == 0) && ((LXY_PAIRLUT_MASK >> WIDE) & 1); };
 
 __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
   uint32_t v;
@@ -196,8 +190,19 @@ __device__ __forceinline__ void eval_record(const uint32_t (&A)[4], const uint8_
   if (PairLut<CPL, WIDE, WM>::on) {
 #pragma unroll
     for (int q = 0; q < CPL / 2; ++q) {
-      const uint32_t m = __viaddmin_s16x2_relu(A[q], B[q], kHi | (kHi << 16));
-      const uint32_t e = lds_u32(__dp2a_lo(m, 4u | ((4u * kLut2Stride) << 8), lut2));
+      uint32_t addr;
+      if (WIDE == 1) {  // 32-bit tables: one word per candidate, two IMADs for the address
+        const uint32_t v0 = (uint32_t)__viaddmin_s32_relu((int)A[2 * q], (int)B[2 * q], (int)kHi);
+        const uint32_t v1 = (uint32_t)__viaddmin_s32_relu((int)A[2 * q + 1], (int)B[2 * q + 1], (int)kHi);
+        addr = v1 * (4u * kLut2Stride) + (v0 * 4u + lut2);
+      } else if (WIDE == 2) {  // 16-bit tables read modulo 2^16: every miss is index 43
+        const uint32_t m = __viaddmin_u16x2(A[q], B[q], (kHi + 1) | ((kHi + 1) << 16));
+        addr = __dp2a_lo(m, 4u | ((4u * kLut2Stride) << 8), lut2);
+      } else {
+        const uint32_t m = __viaddmin_s16x2_relu(A[q], B[q], kHi | (kHi << 16));
+        addr = __dp2a_lo(m, 4u | ((4u * kLut2Stride) << 8), lut2);
+      }
+      const uint32_t e = lds_u32(addr);
       if (WM == W_UNIT) {
         L.p32[q] += e;
       } else {
@@ -211,12 +216,11 @@ __device__ __forceinline__ void eval_record(const uint32_t (&A)[4], const uint8_
 #pragma unroll
     for (int j = 0; j < CPL; ++j) idx[j] = (uint32_t)__viaddmin_s32_relu((int)A[j], (int)B[j], (int)kHi);
   } else if (WIDE == 2) {
-    // 32768 <= n + 21, n <= 65536: 16-bit table entries (tab = 32767 - pos), 32-bit arithmetic.  A[]
-    // already holds 21 - tab a per candidate (eval_packet); tab b is sign-extended by one instruction.
 #pragma unroll
-    for (int j = 0; j < CPL; ++j) {
-      const int tb = sext16(B[j >> 1], j & 1);
-      idx[j] = (uint32_t)__viaddmin_s32_relu(tb, (int)A[j], (int)kHi);
+    for (int q = 0; q < (CPL + 1) / 2; ++q) {
+      const uint32_t m = __viaddmin_u16x2(A[q], B[q], (kHi + 1) | ((kHi + 1) << 16));
+      idx[2 * q] = m & 0xFFFFu;
+      if (2 * q + 1 < CPL) idx[2 * q + 1] = m >> 16;
     }
   } else {
 #pragma unroll
@@ -707,9 +711,14 @@ int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int
     const size_t smem = stream1_smem(nc, n);
     if (smem <= (size_t)c->max_smem_optin) return scaff_score_stream1(c, perm_dev, P, nc, smem, out_dev, x100_dev);
   }
-  // table mode: 0 = packed s16 (pos + 21 | -pos; n + 21 < 2^15), 2 = centred s16 (32767 - pos; n <= 65536),
-  // 1 = 32-bit.  Modes 0 and 2 hold 128 candidates in the 128 KB of tables, mode 1 holds 64.
-  const int tm = (n + kBias + 1 < 0x8000) ? 0 : (n <= 65536 ? 2 : 1);
+  // table mode: 0 = 16-bit entries (pos + 21 | -pos) added as signed halves (n + 21 < 2^15); 2 = the same
+  // entries added modulo 2^16 and clamped by an unsigned min (every miss is index 43; exact while
+  // n <= 65515: |d| <= n - 1 keeps d + 21 mod 2^16 out of [0, 42] unless |d| <= 21); 1 = 32-bit.
+  // Modes 0 and 2 hold 128 candidates in the 128 KB of tables, mode 1 holds 64.
+  static const int force_tm = getenv("LXY_TABLE_MODE") ? atoi(getenv("LXY_TABLE_MODE")) : -1;  // experiments
+  int tm = (n + kBias + 1 < 0x8000) ? 0 : (n <= 65536 - (kBias + 1) ? 2 : 1);
+  if (force_tm == 2 && n <= 65536 - (kBias + 1)) tm = 2;
+  if (force_tm == 1) tm = 1;
   const bool wide = (tm == 1);
   // candidates per lane: 4 (16-bit tables) / 2 (32-bit) fill 128 KB of tables; small populations use less
   int cpl = wide ? 2 : 4;

@@ -146,15 +146,16 @@ def test_links_get_matches_table(ctx):
 
 
 @pytest.mark.parametrize("n,P,wts", [
-    (32746, 40, "unit"),     # last n of the packed s16 tables (pos + 21 < 2^15)
-    (32747, 40, "unit"),     # first n of the centred s16 tables (tab = 32767 - pos)
-    (40000, 130, "unit"), (50000, 40, "int"), (65536, 33, "real"),   # centred s16, all weight modes
-    (65537, 40, "unit"), (70000, 70, "int"),                         # 32-bit tables
+    (32746, 40, "unit"),     # last n of the signed 16-bit sums (pos + 21 < 2^15)
+    (32747, 40, "unit"),     # first n of the sums modulo 2^16 (misses clamp to index 43)
+    (40000, 130, "unit"), (50000, 40, "int"), (65000, 33, "real"),   # modulo 2^16, all weight modes
+    (65515, 40, "unit"),     # last n for which d + 21 mod 2^16 cannot alias into the window
+    (65516, 34, "int"), (65536, 33, "real"), (65537, 40, "unit"), (70000, 70, "int"),   # 32-bit tables
 ])
 def test_table_modes_by_n(ctx, n, P, wts):
     """The three placement-table formats of k_scaff_score (scaff_kernels.cu) against the oracle's
     exact integers / reference-order fitness.  Populations include the identity and its reverse,
-    where |pos a - pos b| reaches n - 1 (the 17-bit differences the centred format must survive)."""
+    where |pos a - pos b| reaches n - 1 (17-bit differences: the modulo-2^16 format must not alias them)."""
     L = 300000
     a, b, _ = S.scaff_links(n, L, 61)
     rng = np.random.default_rng(n)
