@@ -215,6 +215,13 @@ def measure_ga(ctx, N, torch, dist, dev, P, n, L_eval, rank, world, generations)
             "best_fitness_before_after": [first, best]}
 
 
+def pinned(arr):
+    """A page-locked copy of a host array (the e2e legs copy their inputs from pinned host memory:
+    the library hands page-locked caller memory straight to the copy engine)."""
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(arr)).pin_memory().numpy()
+
+
 def measured_peak_hbm():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -353,6 +360,7 @@ def main():
         a, b, order = gen_links(n, L, seed, dev)
         perms_all = gen_population(n, P, pseed, order.cpu().numpy())
         perms = np.ascontiguousarray(perms_all[rank * P_loc:(rank + 1) * P_loc])
+    perms = pinned(perms)
     torch.cuda.synchronize()
     ctx = N.Context(local)
     t0 = time.perf_counter()
@@ -442,6 +450,15 @@ def main():
     ms_score, ms_layout, ms_finish = ([main["kernel_ms"]["ms_score"]], [main["kernel_ms"]["ms_layout"]],
                                       [main["kernel_ms"]["ms_finish"]])
     stream_x100 = x100_dev.clone()
+    # the same host-buffer call with PAGEABLE caller memory (what a cgo caller passes): the library
+    # stages it through its pinned buffer with a few host threads
+    perms_pageable = np.array(perms, copy=True)
+    ctx.scaff_score_batch(perms_pageable, want_x100=link_mode)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ctx.scaff_score_batch(perms_pageable, want_x100=link_mode)
+    ms_e2e_pageable = 1e3 * (time.perf_counter() - t0) / args.steps
+    del perms_pageable
 
     extras = {}
     if not args.no_extras and not link_mode and world == 1:
@@ -517,7 +534,7 @@ def main():
                            + float(np.log(min(1_000_000, 1_600_000_000 // n)))).clamp_(1000).long()
         xa = (torch.rand(L, generator=g, device=dev, dtype=torch.float64) * lens_t[a.long()]).int()
         xb = (torch.rand(L, generator=g, device=dev, dtype=torch.float64) * lens_t[b.long()]).int()
-        ori_host = (np.random.default_rng(pseed + 31).random((P_loc, n)) < 0.5).astype(np.uint8)
+        ori_host = pinned((np.random.default_rng(pseed + 31).random((P_loc, n)) < 0.5).astype(np.uint8))
         ori_dev = torch.from_numpy(ori_host).to(dev)
         unit = int(lens_t.double().median().item())
         gctx = N.Context(local)
@@ -544,7 +561,7 @@ def main():
             from lxy_b200 import synth as SY
             pn, pP = 300_000, 1024
             pa, pb, pw, truth = SY.phase_links(pn, 5)
-            genes = SY.phase_population(pn, pP, 105, truth)
+            genes = pinned(SY.phase_population(pn, pP, 105, truth))
             hctx = N.Context(local)
             hctx.set_phase_links(pn, pa, pb, pw)
             genes_dev = torch.from_numpy(genes).to(dev)
@@ -563,17 +580,26 @@ def main():
             torch.cuda.synchronize()
             pms = e0.elapsed_time(e1) / args.steps
             pt = hctx.timing()
+            hctx.phase_score_batch(genes)               # warm-up: sizes the library's pinned staging buffer
             t0 = time.perf_counter()
             for _ in range(args.steps):
                 hctx.phase_score_batch(genes)
             pms_h = 1e3 * (time.perf_counter() - t0) / args.steps
+            genes_pageable = np.array(genes, copy=True)
+            hctx.phase_score_batch(genes_pageable)
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                hctx.phase_score_batch(genes_pageable)
+            pms_hp = 1e3 * (time.perf_counter() - t0) / args.steps
+            del genes_pageable
             hctx.close()
             extras["phasing"] = {
                 "what": f"phase.score over {pn} simulated variant blocks, {len(pa)} block-pair records, "
                         f"population {pP}; int64 exact",
                 "value": float(pP) * len(pa) / (pms * 1e-3), "unit": UNIT, "ms_per_step": pms,
                 "e2e": {"value": float(pP) * len(pa) / (pms_h * 1e-3), "unit": UNIT, "ms_per_step": pms_h,
-                        "h2d_bytes_per_step": int(genes.nbytes), "d2h_bytes_per_step": 16 * pP},
+                        "h2d_bytes_per_step": int(genes.nbytes), "d2h_bytes_per_step": 16 * pP,
+                        "host_memory": "pinned", "pageable_ms_per_step": pms_hp},
                 "kernel_ms": {"k_phase_score": pt["ms_score"], "k_phase_bits": pt["ms_layout"]}}
             del genes_dev
     if not args.no_extras and not link_mode:
@@ -590,7 +616,7 @@ def main():
         peak, peak_src = measured_peak_hbm()
         # algorithmic bytes of one k_scaff_score launch: every record once (2 B),
         # both placement tables of every local candidate once, the per-CTA partial sums once
-        wide = n > 65536                              # 32-bit placement tables (scaff_kernels.cu)
+        wide = n > 65515                              # 32-bit placement tables (scaff_kernels.cu)
         cmax = 64 if wide else 128
         cand = cmax if P_loc > cmax // 2 else (cmax // 2 if P_loc > cmax // 4 else cmax // 4)
         groups = (P_loc + cand - 1) // cand
@@ -627,7 +653,9 @@ def main():
                        "link_store_build_s": round(t_build, 3)},
             "candidates_per_sec": P * args.steps / (ms_dev * 1e-3),
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
-                    "h2d_bytes_per_step": int(perms.nbytes), "d2h_bytes_per_step": int(16 * P_loc)},
+                    "h2d_bytes_per_step": int(perms.nbytes), "d2h_bytes_per_step": int(16 * P_loc),
+                    "host_memory": "pinned (page-locked caller buffers go straight to the copy engine)",
+                    "pageable_ms_per_step": ms_e2e_pageable},
             "gpu_launches": int(launches),
             "kernel_ms": {"k_scaff_score": k_ms, "layout+check": float(np.mean(ms_layout)),
                           "head+finish": float(np.mean(ms_finish))},

@@ -1,6 +1,8 @@
 // api.cu — the extern "C" boundary of liblxyb200.so (declared in include/lxy_b200.h).
 #include <algorithm>
+#include <atomic>
 #include <cstring>
+#include <thread>
 #include <numeric>
 #include <vector>
 
@@ -27,6 +29,42 @@ int pin_reserve(lxy_ctx* c, size_t bytes) {
   size_t want = bytes + (bytes >> 2) + 4096;
   LXY_CUDA(cudaMallocHost(&c->h_pin, want));
   c->h_pin_cap = want;
+  return LXY_OK;
+}
+
+// Host -> device copy of one call's inputs.  Caller memory that is already page-locked
+// (cudaHostAlloc / cudaHostRegister, e.g. a pinned torch tensor) is handed to the copy engine as it
+// is; pageable memory (Go slices through cgo) goes through the context's pinned staging buffer at
+// offset pin_off, in 2 MB chunks copied by up to four host threads, each chunk's DMA queued as soon as
+// it is staged so the copy engine overlaps the remaining memcpys.  The caller's memory is not retained
+// past the return of the entry point in either case (the entry points synchronise before returning).
+int stage_h2d(lxy_ctx* c, void* dst_dev, const void* src, size_t bytes, size_t pin_off) {
+  if (bytes == 0) return LXY_OK;
+  cudaPointerAttributes attr;
+  if (cudaPointerGetAttributes(&attr, src) == cudaSuccess && attr.type == cudaMemoryTypeHost) {
+    LXY_CUDA(cudaMemcpyAsync(dst_dev, src, bytes, cudaMemcpyHostToDevice, c->stream));
+    return LXY_OK;
+  }
+  (void)cudaGetLastError();  // unregistered host memory reports an error on older drivers
+  char* pin = (char*)c->h_pin + pin_off;
+  constexpr size_t kChunk = (size_t)2 << 20;
+  const size_t nchunks = (bytes + kChunk - 1) / kChunk;
+  unsigned hw = std::thread::hardware_concurrency();
+  const size_t nthreads = std::min<size_t>(std::min<size_t>(4, hw ? hw : 1), nchunks);
+  std::atomic<int> err(0);
+  auto work = [&](size_t t) {
+    if (t != 0 && cudaSetDevice(c->cfg.device) != cudaSuccess) { err = 1; return; }
+    for (size_t i = t; i < nchunks; i += nthreads) {
+      const size_t off = i * kChunk, len = std::min(kChunk, bytes - off);
+      std::memcpy(pin + off, (const char*)src + off, len);
+      if (cudaMemcpyAsync((char*)dst_dev + off, pin + off, len, cudaMemcpyHostToDevice, c->stream) != cudaSuccess) err = 1;
+    }
+  };
+  std::vector<std::thread> pool;
+  for (size_t t = 1; t < nthreads; ++t) pool.emplace_back(work, t);
+  work(0);
+  for (auto& th : pool) th.join();
+  if (err) { set_error("host -> device staging copy failed: %s", cudaGetErrorString(cudaGetLastError())); return LXY_ERR_CUDA; }
   return LXY_OK;
 }
 
@@ -231,9 +269,8 @@ int lxy_scaff_score_batch(lxy_ctx* c, const int32_t* perm, int32_t P, double* ou
   LXY_TRY(c->d_x100.reserve(8 * (size_t)P));
   // pinned staging: the copy below is then a true async DMA (and the caller's memory is not
   // retained — cgo rule)
-  std::memcpy(c->h_pin, perm, pbytes);
   LXY_CUDA(cudaEventRecord(c->ev[4], c->stream));
-  LXY_CUDA(cudaMemcpyAsync(c->d_perm.p, c->h_pin, pbytes, cudaMemcpyHostToDevice, c->stream));
+  LXY_TRY(stage_h2d(c, c->d_perm.p, perm, pbytes, 0));
   LXY_TRY(scaff_dispatch(c, c->d_perm.as<int32_t>(), P, c->d_out.as<double>(), c->d_x100.as<int64_t>()));
   char* hout = (char*)c->h_pin + pbytes;
   LXY_CUDA(cudaMemcpyAsync(hout, c->d_out.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, c->stream));
@@ -323,11 +360,9 @@ int lxy_scaffg_score_batch(lxy_ctx* c, const int32_t* perm, const uint8_t* ori, 
   LXY_TRY(c->d_ori.reserve(obytes + 16));
   LXY_TRY(c->d_out.reserve(8 * (size_t)P));
   LXY_TRY(c->d_x100.reserve(8 * (size_t)P));
-  std::memcpy(c->h_pin, perm, pbytes);
-  if (ori) std::memcpy((char*)c->h_pin + pbytes, ori, obytes);
   LXY_CUDA(cudaEventRecord(c->ev[4], c->stream));
-  LXY_CUDA(cudaMemcpyAsync(c->d_perm.p, c->h_pin, pbytes, cudaMemcpyHostToDevice, c->stream));
-  if (ori) LXY_CUDA(cudaMemcpyAsync(c->d_ori.p, (char*)c->h_pin + pbytes, obytes, cudaMemcpyHostToDevice, c->stream));
+  LXY_TRY(stage_h2d(c, c->d_perm.p, perm, pbytes, 0));
+  if (ori) LXY_TRY(stage_h2d(c, c->d_ori.p, ori, obytes, pbytes));
   LXY_TRY(scaffg_score(c, c->d_perm.as<int32_t>(), ori ? c->d_ori.as<uint8_t>() : nullptr, P,
                        c->d_out.as<double>(), c->d_x100.as<int64_t>()));
   char* hout = (char*)c->h_pin + ooff;
@@ -429,9 +464,8 @@ int lxy_phase_score_batch(lxy_ctx* c, const uint8_t* genes, int32_t P, int64_t* 
   LXY_TRY(c->d_genes.reserve(gbytes));
   LXY_TRY(c->d_out.reserve(8 * (size_t)P));
   LXY_TRY(c->d_x100.reserve(8 * (size_t)P));
-  std::memcpy(c->h_pin, genes, gbytes);
   LXY_CUDA(cudaEventRecord(c->ev[4], c->stream));
-  LXY_CUDA(cudaMemcpyAsync(c->d_genes.p, c->h_pin, gbytes, cudaMemcpyHostToDevice, c->stream));
+  LXY_TRY(stage_h2d(c, c->d_genes.p, genes, gbytes, 0));
   LXY_TRY(phase_score(c, c->d_genes.as<uint8_t>(), P, c->d_x100.as<int64_t>(), c->d_out.as<double>()));
   char* hout = (char*)c->h_pin + gbytes;
   LXY_CUDA(cudaMemcpyAsync(hout, c->d_out.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, c->stream));

@@ -37,8 +37,8 @@ const uint8_t h_lut100[kLutLen] = {
 // ---- k_scaff_layout -----------------------------------------------------------------------------
 // Tables are stored group-major: tab[g][contig][cand] with kCand = 32*CPL candidates per group, so
 // the rows of one contig block are one contiguous TMA bulk copy.  tabA holds pos + kBias + 1 and
-// tabB holds -pos (16-bit two's complement when n + kBias < 2^15, else 32-bit): the kernel's
-// VIADDMNMX then yields clamp(pos a - pos b + kBias + 1, 0, kMiss + 1) per candidate.
+// tabB holds -pos (16-bit, read modulo 2^16, while n <= 65515, else 32-bit): one VIADDMNMX per
+// candidate (pair) turns a row of each into decay-table indices (eval_record).
 template <int WIDE>
 __global__ void k_scaff_layout(const int32_t* __restrict__ perm, int32_t P, int32_t Ppad, int32_t n,
                                int32_t cand, void* __restrict__ tabA, void* __restrict__ tabB,
@@ -58,7 +58,7 @@ __global__ void k_scaff_layout(const int32_t* __restrict__ perm, int32_t P, int3
     if (WIDE == 1) {
       ((uint32_t*)tabA)[at] = (uint32_t)(i + kBias + 1);
       ((uint32_t*)tabB)[at] = (uint32_t)(-i);
-    } else {  // WIDE 0 and 2 share the 16-bit format (2: read modulo 2^16)
+    } else {
       ((uint16_t*)tabA)[at] = (uint16_t)(i + kBias + 1);
       ((uint16_t*)tabB)[at] = (uint16_t)(-i);
     }
@@ -145,11 +145,6 @@ __device__ __forceinline__ void load_row(const uint8_t* row, uint32_t (&X)[4]) {
   }
 }
 
-// Sign-extended half of a 32-bit word (__byte_perm ignores the sign-replicate bit of its selector).
-__device__ __forceinline__ int sext16(uint32_t word, int high) {
-  return high ? ((int)word >> 16) : (int)(int16_t)(uint16_t)word;
-}
-
 // Row A of a record / packet.
 template <int CPL, int WIDE>
 __device__ __forceinline__ void load_row_a(const uint8_t* row, uint32_t (&A)[4]) {
@@ -163,11 +158,8 @@ __device__ __forceinline__ void load_row_a(const uint8_t* row, uint32_t (&A)[4])
 // are summed in one IADD.  6.25 -> 4.25 shared-memory wavefronts per record-warp.
 constexpr int kLut2Stride = 44;
 constexpr int kLut2Words = kLutLen * kLut2Stride;
-#ifndef LXY_PAIRLUT_MASK
-#define LXY_PAIRLUT_MASK 7  /* bit WIDE: table formats that use the pair table */
-#endif
 template <int CPL, int WIDE, int WM>
-struct PairLut { static constexpr bool on = (WM != W_F64) && (CPL % 2 == 0) && ((LXY_PAIRLUT_MASK >> WIDE) & 1); };
+struct PairLut { static constexpr bool on = (WM != W_F64) && (CPL % 2 == 0); };
 
 __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
   uint32_t v;
@@ -176,10 +168,12 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
 }
 
 // One record against the CPL candidates of this lane, row A already in registers.
-//   narrow tables (u16): A = pos + kBias + 1, B = -pos; VIADDMNMX.S16x2.RELU gives, per half-word,
-//   v = clamp(pos a - pos b + kBias + 1, 0, kMiss + 1): one instruction for two candidates.
-//   wide tables (u32): the same with VIADDMNMX.RELU on full words.
-// v indexes the decay table: v in [1, 41] <=> |d| <= 20; 0 and 42 are the two "far" entries.
+//   16-bit tables: A = pos + kBias + 1, B = -pos (mod 2^16); VIADDMNMX.U16x2 gives, per half-word,
+//   v = min((pos a - pos b + kBias + 1) mod 2^16, kMiss + 2): one instruction for two candidates.
+//   v in [1, 41] <=> |d| <= 20; 0 and 42 are d = -21 / +21, every other difference lands on 43
+//   (exact while n <= 65515: |d| <= n - 1 cannot alias into [0, 42] modulo 2^16).
+//   32-bit tables: VIADDMNMX.RELU on full words, v = clamp(d + 21, 0, 42); 0 and 42 are "far".
+// v indexes the decay table (zero outside the six weighted steps).
 template <int CPL, int WIDE, int WM>
 __device__ __forceinline__ void eval_record(const uint32_t (&A)[4], const uint8_t* rowB,
                                             const uint8_t* lut, const double* lutd, uint32_t lut2,
@@ -195,11 +189,8 @@ __device__ __forceinline__ void eval_record(const uint32_t (&A)[4], const uint8_
         const uint32_t v0 = (uint32_t)__viaddmin_s32_relu((int)A[2 * q], (int)B[2 * q], (int)kHi);
         const uint32_t v1 = (uint32_t)__viaddmin_s32_relu((int)A[2 * q + 1], (int)B[2 * q + 1], (int)kHi);
         addr = v1 * (4u * kLut2Stride) + (v0 * 4u + lut2);
-      } else if (WIDE == 2) {  // 16-bit tables read modulo 2^16: every miss is index 43
+      } else {  // 16-bit tables, sums modulo 2^16: every miss is index 43
         const uint32_t m = __viaddmin_u16x2(A[q], B[q], (kHi + 1) | ((kHi + 1) << 16));
-        addr = __dp2a_lo(m, 4u | ((4u * kLut2Stride) << 8), lut2);
-      } else {
-        const uint32_t m = __viaddmin_s16x2_relu(A[q], B[q], kHi | (kHi << 16));
         addr = __dp2a_lo(m, 4u | ((4u * kLut2Stride) << 8), lut2);
       }
       const uint32_t e = lds_u32(addr);
@@ -215,17 +206,10 @@ __device__ __forceinline__ void eval_record(const uint32_t (&A)[4], const uint8_
   if (WIDE == 1) {
 #pragma unroll
     for (int j = 0; j < CPL; ++j) idx[j] = (uint32_t)__viaddmin_s32_relu((int)A[j], (int)B[j], (int)kHi);
-  } else if (WIDE == 2) {
-#pragma unroll
-    for (int q = 0; q < (CPL + 1) / 2; ++q) {
-      const uint32_t m = __viaddmin_u16x2(A[q], B[q], (kHi + 1) | ((kHi + 1) << 16));
-      idx[2 * q] = m & 0xFFFFu;
-      if (2 * q + 1 < CPL) idx[2 * q + 1] = m >> 16;
-    }
   } else {
 #pragma unroll
     for (int q = 0; q < (CPL + 1) / 2; ++q) {
-      const uint32_t m = __viaddmin_s16x2_relu(A[q], B[q], kHi | (kHi << 16));
+      const uint32_t m = __viaddmin_u16x2(A[q], B[q], (kHi + 1) | ((kHi + 1) << 16));
       idx[2 * q] = m & 0xFFFFu;
       if (2 * q + 1 < CPL) idx[2 * q + 1] = m >> 16;
     }
@@ -620,8 +604,8 @@ static int prefer_max_carveout(lxy_ctx* c) {
   static bool done[64] = {};
   if (done[c->cfg.device & 63]) return LXY_OK;
   const void* fns[] = {
-      (const void*)k_scaff_layout<0>, (const void*)k_scaff_layout<1>, (const void*)k_scaff_layout<2>,
-      (const void*)k_scaff_check<0>,  (const void*)k_scaff_check<1>,  (const void*)k_scaff_check<2>,
+      (const void*)k_scaff_layout<0>, (const void*)k_scaff_layout<1>,
+      (const void*)k_scaff_check<0>,  (const void*)k_scaff_check<1>,
       (const void*)k_scaff_head<W_UNIT>,  (const void*)k_scaff_head<W_INT32>, (const void*)k_scaff_head<W_F64>,
       (const void*)k_scaff_finish<W_UNIT>, (const void*)k_scaff_finish<W_INT32>, (const void*)k_scaff_finish<W_F64>};
   for (const void* f : fns)
@@ -711,14 +695,10 @@ int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int
     const size_t smem = stream1_smem(nc, n);
     if (smem <= (size_t)c->max_smem_optin) return scaff_score_stream1(c, perm_dev, P, nc, smem, out_dev, x100_dev);
   }
-  // table mode: 0 = 16-bit entries (pos + 21 | -pos) added as signed halves (n + 21 < 2^15); 2 = the same
-  // entries added modulo 2^16 and clamped by an unsigned min (every miss is index 43; exact while
-  // n <= 65515: |d| <= n - 1 keeps d + 21 mod 2^16 out of [0, 42] unless |d| <= 21); 1 = 32-bit.
-  // Modes 0 and 2 hold 128 candidates in the 128 KB of tables, mode 1 holds 64.
+  // table mode: 0 = 16-bit entries (pos + 21 | -pos) summed modulo 2^16 (n <= 65515, see eval_record),
+  // 128 candidates in the 128 KB of tables; 1 = 32-bit entries, 64 candidates.
   static const int force_tm = getenv("LXY_TABLE_MODE") ? atoi(getenv("LXY_TABLE_MODE")) : -1;  // experiments
-  int tm = (n + kBias + 1 < 0x8000) ? 0 : (n <= 65536 - (kBias + 1) ? 2 : 1);
-  if (force_tm == 2 && n <= 65536 - (kBias + 1)) tm = 2;
-  if (force_tm == 1) tm = 1;
+  const int tm = (n <= 65536 - (kBias + 1) && force_tm != 1) ? 0 : 1;
   const bool wide = (tm == 1);
   // candidates per lane: 4 (16-bit tables) / 2 (32-bit) fill 128 KB of tables; small populations use less
   int cpl = wide ? 2 : 4;
@@ -756,12 +736,10 @@ int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int
   }
   const int lg = grid_for((int64_t)Ppad * n, 256, c->sm_count);
   if (tm == 1) k_scaff_layout<1><<<lg, 256, 0, st>>>(perm_dev, P, Ppad, n, cand, c->d_posA.p, c->d_posB.p, c->d_flag.as<int>());
-  else if (tm == 2) k_scaff_layout<2><<<lg, 256, 0, st>>>(perm_dev, P, Ppad, n, cand, c->d_posA.p, c->d_posB.p, c->d_flag.as<int>());
   else k_scaff_layout<0><<<lg, 256, 0, st>>>(perm_dev, P, Ppad, n, cand, c->d_posA.p, c->d_posB.p, c->d_flag.as<int>());
   ++launches;
   if (!(c->cfg.flags & LXY_FLAG_NO_VALIDATE)) {
     if (tm == 1) k_scaff_check<1><<<lg, 256, 0, st>>>(perm_dev, P, n, cand, c->d_posB.p, c->d_flag.as<int>());
-    else if (tm == 2) k_scaff_check<2><<<lg, 256, 0, st>>>(perm_dev, P, n, cand, c->d_posB.p, c->d_flag.as<int>());
     else k_scaff_check<0><<<lg, 256, 0, st>>>(perm_dev, P, n, cand, c->d_posB.p, c->d_flag.as<int>());
     ++launches;
   }
@@ -794,10 +772,6 @@ int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int
     rc = S.wmode == W_UNIT ? launch_score_cpl<1, W_UNIT>(c, cpl, prm, grid)
        : S.wmode == W_INT32 ? launch_score_cpl<1, W_INT32>(c, cpl, prm, grid)
                             : launch_score_cpl<1, W_F64>(c, cpl, prm, grid);
-  } else if (tm == 2) {
-    rc = S.wmode == W_UNIT ? launch_score_cpl<2, W_UNIT>(c, cpl, prm, grid)
-       : S.wmode == W_INT32 ? launch_score_cpl<2, W_INT32>(c, cpl, prm, grid)
-                            : launch_score_cpl<2, W_F64>(c, cpl, prm, grid);
   } else {
     rc = S.wmode == W_UNIT ? launch_score_cpl<0, W_UNIT>(c, cpl, prm, grid)
        : S.wmode == W_INT32 ? launch_score_cpl<0, W_INT32>(c, cpl, prm, grid)
