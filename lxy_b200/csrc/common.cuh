@@ -80,9 +80,10 @@ struct PhaseLinks {
   int32_t n = 0;
   int64_t L = 0;            // records kept (valid step only)
   int64_t L_in = 0;
-  DevBuf rec;               // uint32 (lo << 5 | stepcode) sorted by lo, see phase_kernels.cu
+  DevBuf rec;               // uint2 (lo, hi) sorted by lo, see phase_kernels.cu
   DevBuf w;                 // int32 w * m
   int64_t sum_w = 0;        // sum of w * m over kept records
+  bool narrow = true;       // max |w * m| * chunk < 2^31: 32-bit chunk sums
 };
 
 }  // namespace lxy

@@ -8,8 +8,8 @@
 // Everything is integer; int64 accumulation is exact.
 //
 //   k_phase_bits    genes[P][n] bytes -> bit-sliced words bits[g][i] (bit c = candidate 32g + c)
-//   k_phase_score   one warp per (32-candidate group, link chunk); lane = candidate; the two gene
-//                   words of a record are warp-uniform loads from a window that stays in L1
+//   k_phase_score   one warp per (block of up to four 32-candidate groups, link chunk); lane = candidate
+//                   of each group; records and gene words are warp-uniform loads (L1-resident window)
 //   k_phase_finish  out = -(sumW - 2 D)
 #include <algorithm>
 #include <cmath>
@@ -22,8 +22,11 @@ namespace {
 
 constexpr int kChunk = 2048;  // records per warp work item
 
+// bits[q][i][G]: word (q, i, s) holds the gene bits of group g = q * G + s (bit c = candidate 32g + c),
+// so the G words a warp needs for variant i are one aligned G * 4-byte load.  Groups past the
+// population read as zero.
 __global__ void k_phase_bits(const uint8_t* __restrict__ genes, int32_t P, int32_t n, int32_t groups,
-                             uint32_t* __restrict__ bits) {
+                             int32_t G, uint32_t* __restrict__ bits) {
   // one warp per (group, 32 consecutive variants); lane = variant
   const int64_t warp_id = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
@@ -38,39 +41,104 @@ __global__ void k_phase_bits(const uint8_t* __restrict__ genes, int32_t P, int32
       const int p = g * 32 + cnd;
       if (p < P && genes[(size_t)p * n + i] != 0) word |= (1u << cnd);
     }
-    bits[(size_t)g * n + i] = word;
+    bits[((size_t)(g / G) * n + i) * G + (g % G)] = word;
   }
 }
 
-__global__ void __launch_bounds__(256) k_phase_score(const uint32_t* __restrict__ rec,
+// Same, four variants per lane (n % 4 == 0 and a 4-byte aligned population): a warp reads 128
+// consecutive gene bytes of each of its 32 candidates with one coalesced 32-bit load per lane, 32
+// independent loads in flight per lane.
+__global__ void k_phase_bits4(const uint8_t* __restrict__ genes, int32_t P, int32_t n, int32_t groups,
+                              int32_t G, uint32_t* __restrict__ bits) {
+  const int64_t warp_id = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  const int64_t vchunks = (n + 127) / 128;
+  if (warp_id >= vchunks * groups) return;
+  const int g = (int)(warp_id / vchunks);
+  const int32_t i0 = (int32_t)(warp_id - (int64_t)g * vchunks) * 128 + lane * 4;
+  if (i0 >= n) return;
+  uint32_t v[32];
+#pragma unroll
+  for (int cnd = 0; cnd < 32; ++cnd) {
+    const int p = g * 32 + cnd;
+    v[cnd] = p < P ? __ldg(reinterpret_cast<const uint32_t*>(genes + (size_t)p * n + i0)) : 0u;
+  }
+  uint32_t word[4] = {0, 0, 0, 0};
+#pragma unroll
+  for (int cnd = 0; cnd < 32; ++cnd) {
+#pragma unroll
+    for (int t = 0; t < 4; ++t) word[t] |= ((v[cnd] >> (8 * t)) & 0xFFu) ? (1u << cnd) : 0u;
+  }
+  uint32_t* out = bits + ((size_t)(g / G) * n + i0) * G + (g % G);
+#pragma unroll
+  for (int t = 0; t < 4; ++t) out[(size_t)t * G] = word[t];
+}
+
+template <int G> struct GeneWords;
+template <> struct GeneWords<1> { typedef uint32_t type; };
+template <> struct GeneWords<2> { typedef uint2 type; };
+template <> struct GeneWords<4> { typedef uint4 type; };
+__device__ __forceinline__ uint32_t gw_get(uint32_t v, int) { return v; }
+__device__ __forceinline__ uint32_t gw_get(const uint2& v, int s) { return s ? v.y : v.x; }
+__device__ __forceinline__ uint32_t gw_get(const uint4& v, int s) { return s == 0 ? v.x : s == 1 ? v.y : s == 2 ? v.z : v.w; }
+
+// One warp per (block of G 32-candidate groups, chunk of kChunk records); lane = candidate c of each of
+// its G groups.  Every load is warp-uniform, and what bounds the kernel is the L1 data pipe that
+// returns those loads to the 32 lanes (128 B per cycle per SM: a uniform 16-byte load costs 4
+// wavefronts): the record (i, j, w) is 12 bytes per lane whatever the number of candidates, so each
+// warp scores G = 4 groups per record (one 16-byte load for the gene words of j; the word of i is kept
+// across the run of records with the same i).  Per group the test is one LOP3 ((bits i ^ bits j) &
+// lane bit) + SEL + half an IADD3; addresses are IMAD.WIDE on the FMA pipe.
+// NARROW: |w| * kChunk < 2^31, so a chunk's sum fits 32 bits.
+template <int G, bool NARROW>
+__global__ void __launch_bounds__(256) k_phase_score(const uint2* __restrict__ rec,
                                                      const int32_t* __restrict__ w, int64_t L,
                                                      const uint32_t* __restrict__ bits, int32_t n,
-                                                     int32_t groups, int64_t chunks,
+                                                     int32_t qgroups, int64_t chunks, int32_t chunk,
                                                      unsigned long long* __restrict__ D) {
+  typedef typename GeneWords<G>::type words_t;
   const int lane = threadIdx.x & 31;
+  const uint32_t lanebit = 1u << lane;
   const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   int64_t unit = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
-  for (; unit < chunks * groups; unit += warps) {
-    const int g = (int)(unit / chunks);
-    const int64_t ch = unit - (int64_t)g * chunks;
-    const int64_t lo = ch * kChunk, hi = min(L, lo + kChunk);
-    const uint32_t* gb = bits + (size_t)g * n;
-    long long acc = 0;
+  for (; unit < chunks * qgroups; unit += warps) {
+    const int q = (int)(unit / chunks);
+    const int64_t ch = unit - (int64_t)q * chunks;
+    const int64_t lo = ch * chunk, hi = min(L, lo + chunk);
+    const words_t* gb = reinterpret_cast<const words_t*>(bits) + (size_t)q * n;
+    asm volatile("" : "+l"(gb));   // keep the row base one 64-bit value: gb + i is then ONE IMAD.WIDE.U32
+    long long acc[G];
+    int32_t acc32[G];
+#pragma unroll
+    for (int s = 0; s < G; ++s) { acc[s] = 0; acc32[s] = 0; }
+    uint32_t prev_i = 0xFFFFFFFFu;   // records are sorted by i: its gene words are loaded once per run
+    words_t word_i = words_t();
+#pragma unroll 2
     for (int64_t base = lo; base < hi; base += 4) {
-      // 4 records per 128-bit load (the store is padded to a multiple of 4)
-      const uint4 r = *reinterpret_cast<const uint4*>(rec + base);
-      const int4 ww = *reinterpret_cast<const int4*>(w + base);
-      const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+      // 4 records per iteration (the store is padded to a multiple of 4 with i = j = 0, w = 0)
+      const uint4 r0 = __ldg(reinterpret_cast<const uint4*>(rec + base));
+      const uint4 r1 = __ldg(reinterpret_cast<const uint4*>(rec + base + 2));
+      const int4 ww = __ldg(reinterpret_cast<const int4*>(w + base));
+      const uint32_t ii[4] = {r0.x, r0.z, r1.x, r1.z}, jj[4] = {r0.y, r0.w, r1.y, r1.w};
       const int32_t wv[4] = {ww.x, ww.y, ww.z, ww.w};
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        const uint32_t i = rr[k] >> 5, j = i + (rr[k] & 31u);
-        const uint32_t x = (__ldg(gb + i) ^ __ldg(gb + j)) >> lane;
-        acc += (x & 1u) ? (long long)wv[k] : 0ll;   // pad records carry w = 0
+        if (ii[k] != prev_i) { word_i = __ldg(gb + ii[k]); prev_i = ii[k]; }   // warp-uniform
+        const words_t word_j = __ldg(gb + jj[k]);
+#pragma unroll
+        for (int s = 0; s < G; ++s) {
+          const uint32_t x = (gw_get(word_i, s) ^ gw_get(word_j, s)) & lanebit;
+          if (NARROW) acc32[s] += x ? wv[k] : 0;
+          else acc[s] += x ? (long long)wv[k] : 0ll;
+        }
       }
     }
-    const int p = g * 32 + lane;
-    if (acc != 0) atomicAdd(D + p, (unsigned long long)acc);
+#pragma unroll
+    for (int s = 0; s < G; ++s) {
+      if (NARROW) acc[s] = acc32[s];
+      const int p = (q * G + s) * 32 + lane;
+      if (acc[s] != 0) atomicAdd(D + p, (unsigned long long)acc[s]);
+    }
   }
 }
 
@@ -112,25 +180,28 @@ int build_phase_links(lxy_ctx* c, int32_t n, int64_t L, const uint32_t* a, const
   }
   for (int32_t i = 0; i < n; ++i) count[(size_t)i + 1] += count[(size_t)i];
   const int64_t padded = (kept + 3) / 4 * 4;
-  std::vector<uint32_t> rec((size_t)padded + 4, 0);
+  std::vector<uint32_t> rec(2 * ((size_t)padded + 4), 0);   // (i, j) per record
   std::vector<int32_t> ww((size_t)padded + 4, 0);
-  int64_t sum_w = 0;
+  int64_t sum_w = 0, max_abs = 0;
   for (int64_t l = 0; l < L; ++l) {
     const int64_t i = std::min(a[l], b[l]), j = std::max(a[l], b[l]);
     if (!phase_step(j - i)) continue;
     const int64_t at = count[(size_t)i]++;
     const int64_t wm = (int64_t)w[l] * (i > 0 ? 2 : 1);  // 1 + [min(i,j) > 0], phase.go:192
-    rec[(size_t)at] = ((uint32_t)i << 5) | (uint32_t)(j - i);
+    rec[2 * (size_t)at] = (uint32_t)i;
+    rec[2 * (size_t)at + 1] = (uint32_t)j;
     ww[(size_t)at] = (int32_t)wm;
     sum_w += wm;
+    max_abs = std::max<int64_t>(max_abs, wm < 0 ? -wm : wm);
   }
   S.n = n;
   S.L = padded;
   S.L_in = L;
   S.sum_w = sum_w;
-  LXY_TRY(S.rec.reserve(4 * (size_t)(padded + 4)));
-  LXY_TRY(S.w.reserve(4 * (size_t)(padded + 4)));
-  LXY_CUDA(cudaMemcpyAsync(S.rec.p, rec.data(), 4 * (size_t)(padded + 4), cudaMemcpyHostToDevice, c->stream));
+  S.narrow = max_abs * kChunk < ((int64_t)1 << 31);
+  LXY_TRY(S.rec.reserve(8 * (size_t)(padded + 4 + 128)));   // + the prefetch distance of k_phase_score
+  LXY_TRY(S.w.reserve(4 * (size_t)(padded + 4 + 128)));
+  LXY_CUDA(cudaMemcpyAsync(S.rec.p, rec.data(), 8 * (size_t)(padded + 4), cudaMemcpyHostToDevice, c->stream));
   LXY_CUDA(cudaMemcpyAsync(S.w.p, ww.data(), 4 * (size_t)(padded + 4), cudaMemcpyHostToDevice, c->stream));
   LXY_CUDA(cudaStreamSynchronize(c->stream));
   S.ready = true;
@@ -143,26 +214,50 @@ int phase_score(lxy_ctx* c, const uint8_t* genes_dev, int32_t P, int64_t* out_i6
   if (!S.ready) { set_error("phase score: links not set"); return LXY_ERR_STATE; }
   cudaStream_t st = c->stream;
   const int groups = (P + 31) / 32;
+  const int G = groups >= 4 ? 4 : groups >= 2 ? 2 : 1;   // groups scored per warp (k_phase_score)
+  const int qgroups = (groups + G - 1) / G;
   const int n = S.n;
-  LXY_TRY(c->d_gbits.reserve(4 * (size_t)groups * n));
-  LXY_TRY(c->d_corr.reserve(8 * (size_t)groups * 32));
+  const size_t bits_bytes = 4 * (size_t)qgroups * G * n;
+  LXY_TRY(c->d_gbits.reserve(bits_bytes));
+  LXY_TRY(c->d_corr.reserve(8 * (size_t)qgroups * G * 32));
   LXY_TRY(c->d_flag.reserve(64));
   LXY_CUDA(cudaMemsetAsync(c->d_flag.p, 0, 64, st));
   LXY_CUDA(cudaEventRecord(c->ev[0], st));
-  LXY_CUDA(cudaMemsetAsync(c->d_corr.p, 0, 8 * (size_t)groups * 32, st));
-  const int64_t bwarps = (int64_t)((n + 31) / 32) * groups;
-  k_phase_bits<<<(unsigned)((bwarps * 32 + 255) / 256), 256, 0, st>>>(genes_dev, P, n, groups, c->d_gbits.as<uint32_t>());
+  LXY_CUDA(cudaMemsetAsync(c->d_corr.p, 0, 8 * (size_t)qgroups * G * 32, st));
+  if (groups % G) LXY_CUDA(cudaMemsetAsync(c->d_gbits.p, 0, bits_bytes, st));   // words of the absent groups
+  if ((n & 3) == 0 && ((uintptr_t)genes_dev & 3) == 0) {
+    const int64_t bwarps = (int64_t)((n + 127) / 128) * groups;
+    k_phase_bits4<<<(unsigned)((bwarps * 32 + 255) / 256), 256, 0, st>>>(genes_dev, P, n, groups, G, c->d_gbits.as<uint32_t>());
+  } else {
+    const int64_t bwarps = (int64_t)((n + 31) / 32) * groups;
+    k_phase_bits<<<(unsigned)((bwarps * 32 + 255) / 256), 256, 0, st>>>(genes_dev, P, n, groups, G, c->d_gbits.as<uint32_t>());
+  }
   LXY_CUDA(cudaGetLastError());
   LXY_CUDA(cudaEventRecord(c->ev[1], st));
   int launches = 1, grid = 0;
   if (S.L > 0) {
-    const int64_t chunks = (S.L + kChunk - 1) / kChunk;
-    const int64_t units = chunks * groups;
+    // records per warp work item: kChunk, less when that would leave the SMs short of warps
+    int64_t chunk = S.L * qgroups / ((int64_t)c->sm_count * 64 * 2);
+    chunk = std::min<int64_t>(kChunk, std::max<int64_t>(128, chunk)) / 4 * 4;
+    const int64_t chunks = (S.L + chunk - 1) / chunk;
+    const int64_t units = chunks * qgroups;
     int64_t blocks = (units + 7) / 8;
     const int64_t cap = (int64_t)c->sm_count * 8;
     if (blocks > cap) blocks = cap;
     grid = (int)blocks;
-    k_phase_score<<<grid, 256, 0, st>>>(S.rec.as<uint32_t>(), S.w.as<int32_t>(), S.L, c->d_gbits.as<uint32_t>(), n, groups, chunks, c->d_corr.as<unsigned long long>());
+    const uint2* rec = S.rec.as<uint2>();
+    const int32_t* w = S.w.as<int32_t>();
+    const uint32_t* bits = c->d_gbits.as<uint32_t>();
+    unsigned long long* D = c->d_corr.as<unsigned long long>();
+#define LXY_PHASE_LAUNCH(GG)                                                                              \
+    do {                                                                                                   \
+      if (S.narrow) k_phase_score<GG, true><<<grid, 256, 0, st>>>(rec, w, S.L, bits, n, qgroups, chunks, (int32_t)chunk, D); \
+      else k_phase_score<GG, false><<<grid, 256, 0, st>>>(rec, w, S.L, bits, n, qgroups, chunks, (int32_t)chunk, D);        \
+    } while (0)
+    if (G == 4) LXY_PHASE_LAUNCH(4);
+    else if (G == 2) LXY_PHASE_LAUNCH(2);
+    else LXY_PHASE_LAUNCH(1);
+#undef LXY_PHASE_LAUNCH
     LXY_CUDA(cudaGetLastError());
     ++launches;
   }
@@ -173,7 +268,7 @@ int phase_score(lxy_ctx* c, const uint8_t* genes_dev, int32_t P, int64_t* out_i6
   LXY_CUDA(cudaEventRecord(c->ev[3], st));
   c->timing.launches = launches;
   c->timing.grid = grid;
-  c->timing.link_bytes = (int64_t)groups * S.L * 8;
+  c->timing.link_bytes = (int64_t)qgroups * S.L * 12;
   c->timing.table_bytes = 0;
   return LXY_OK;
 }

@@ -41,7 +41,9 @@ def test_all_bitstrings_of_the_reference_fixture(ctx, golden_files):
 
 
 @pytest.mark.parametrize("n,P,seed,far", [(50, 10, 1, 0), (1000, 128, 2, 500), (4097, 33, 3, 100),
-                                          (25000, 64, 5, 5000)])
+                                          (25000, 64, 5, 5000),
+                                          (4100, 130, 7, 300),    # 5 groups: a block of 4 + a block with 3 absent
+                                          (2048, 200, 8, 0), (1001, 97, 9, 50)])
 def test_synthetic_blocks_bit_exact(ctx, n, P, seed, far):
     a, b, w, truth = S.phase_links(n, seed, far_pairs=far)
     genes = S.phase_population(n, P, seed + 100, truth)
@@ -57,6 +59,21 @@ def test_synthetic_blocks_bit_exact(ctx, n, P, seed, far):
     order = N.rank(of)
     assert order[0] in (0, 1)                        # the truth and its complement tie for best
     assert of[0] == of[1]
+
+
+def test_large_weights_take_the_64_bit_chunk_sums(ctx):
+    """|w| up to 2^30 - 1 (the setter's limit): a chunk of 2048 records no longer fits 32 bits, the
+    kernel's wide variant sums it in 64; small weights take the 32-bit variant.  Both exact."""
+    n, P = 3000, 70
+    a, b, w, truth = S.phase_links(n, 11, far_pairs=50)
+    genes = S.phase_population(n, P, 111, truth)
+    rng = np.random.default_rng(11)
+    for scale in (1, (1 << 19) - 1, (1 << 30) - 1):
+        ws = np.sign(w) * rng.integers(scale // 2 + 1, scale + 1, len(w)).astype(np.float64)
+        _, exact = O.phase_score_links_batch(n, a, b, ws, genes, nthreads=4)
+        ctx.set_phase_links(n, a, b, ws)
+        oi, of = ctx.phase_score_batch(genes)
+        assert oi.tolist() == exact.tolist()
 
 
 def test_edge_cases(ctx):

@@ -14,7 +14,7 @@ mode = sys.argv[1] if len(sys.argv) > 1 else "r"
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
 n, L, P = 500, 5_000_000, 128
 if mode == "phase":
-    pn, pP = 100_000, 256
+    pn, pP = 300_000, 1024       # the bench's phasing shape (BASELINE config 5)
     a, b, w, truth = S.phase_links(pn, 5)
     genes = S.phase_population(pn, pP, 105, truth)
     with N.Context(0) as ctx:
