@@ -151,12 +151,13 @@ __device__ __forceinline__ void load_row_a(const uint8_t* row, uint32_t (&A)[4])
   load_row<CPL, WIDE>(row, A);
 }
 
-// Pair decay table (integer modes, even CPL).  Narrow tables: VIADDMNMX.S16x2 leaves the indices of
-// two candidates in one register, v0 | v1 << 16; one IDP.2A turns that into the shared address of
-// lut2[v1][v0] = lut[v0] | lut[v1] << 16 (rows of kLut2Stride words: the four far/far combinations
-// fall into different banks), so ONE 32-bit look-up serves two candidates and the two 16-bit halves
-// are summed in one IADD.  6.25 -> 4.25 shared-memory wavefronts per record-warp.
-constexpr int kLut2Stride = 44;
+// Pair decay table (integer modes, even CPL).  VIADDMNMX.U16x2 leaves the indices of two candidates in
+// one register, v0 | v1 << 16; one IDP.2A turns that into the shared address of
+// lut2[v1][v0] = lut[v0] | lut[v1] << 16, so ONE 32-bit look-up serves two candidates and the two
+// 16-bit halves are summed in one IADD: 6.25 -> 4.25 shared-memory wavefronts per record-warp.  Rows
+// are kLut2Stride words, an odd number, so that the entries a warp touches at once (mostly (43, 43),
+// some (v, 43) and (43, v)) spread over all 32 banks.
+constexpr int kLut2Stride = 45;
 constexpr int kLut2Words = kLutLen * kLut2Stride;
 template <int CPL, int WIDE, int WM>
 struct PairLut { static constexpr bool on = (WM != W_F64) && (CPL % 2 == 0); };
