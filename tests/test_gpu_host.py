@@ -115,3 +115,44 @@ def test_native_links_attach_and_file_workflows(golden, golden_files, tmp_path):
     assert len(rows) == 11 and {r[1] for r in rows} <= {"A", "B"}
     with pytest.raises(N.LxyError):
         N.scaffold_file(str(tmp_path / "nope.links"), str(out), 10)
+
+
+def test_concurrent_score_calls_from_seven_threads():
+    """go-galib's GAParallel enters Score() from 7 goroutines at once (scaff.go:88): the C ABI takes
+    the context mutex per call, so concurrent single-genome calls (and batch calls mixed in) from 7
+    OS threads must return exactly what the same calls return one after the other."""
+    import threading
+
+    import _synth as S
+    import lxy_b200._native as N
+    n, L = 700, 150000
+    a, b, w = S.scaff_links(n, L, 77)
+    perms = S.scaff_population(n, 7 * 12, 177)
+    with N.Context(0) as ctx:
+        ctx.set_links(n, a, b, None)
+        want, want_x = ctx.scaff_score_batch(perms, want_x100=True)
+        got = np.zeros(len(perms))
+        gotx = np.zeros(len(perms), np.int64)
+        errors = []
+
+        def worker(t):
+            try:
+                for k in range(12):
+                    p = t * 12 + k
+                    if k % 4 == 3:                       # a small batch now and then
+                        s, x = ctx.scaff_score_batch(perms[p - 1:p + 1], want_x100=True)
+                        got[p], gotx[p] = s[1], x[1]
+                    else:                                # the reference's literal call: one genome
+                        s, x = ctx.scaff_score_batch(perms[p:p + 1], want_x100=True)
+                        got[p], gotx[p] = s[0], x[0]
+            except Exception as e:                       # noqa: BLE001
+                errors.append(e)
+
+        threads = [threading.Thread(target=worker, args=(t,)) for t in range(7)]
+        for th in threads:
+            th.start()
+        for th in threads:
+            th.join()
+        assert not errors
+        assert gotx.tolist() == want_x.tolist()
+        assert got.tolist() == want.tolist()
