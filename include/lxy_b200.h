@@ -46,6 +46,8 @@ typedef enum lxy_status {
 #define LXY_FLAG_NO_STREAM1 2u  /* score batches of <= 8 orderings with the batch kernel too    \
                                    (default: the lane = record streaming kernel, HBM-bound)     */
 
+#define LXY_FLAG_NO_GRAPH 8u    /* never replay a repeated scoring call from a captured CUDA graph */
+
 /* which kernel scores the R-profile (lxy_scaff_score_batch*) */
 #define LXY_PATH_STREAM 0 /* stream every record for every candidate (north_star design; default)  */
 #define LXY_PATH_PAIRS 1  /* aggregate the records into a dense pair table at set_links and score a  \

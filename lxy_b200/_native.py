@@ -39,6 +39,7 @@ ACC_AUTO, ACC_F64, ACC_INT = 0, 1, 2
 PATH_STREAM, PATH_PAIRS = 0, 1
 FLAG_NO_VALIDATE = 1
 FLAG_NO_STREAM1 = 2
+FLAG_NO_GRAPH = 8
 
 
 class LxyError(RuntimeError):

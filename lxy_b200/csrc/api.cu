@@ -21,6 +21,13 @@ void set_error(const char* fmt, ...) {
   g_err = buf;
 }
 
+void drop_score_graphs(lxy_ctx* c) {
+  for (auto& g : c->graphs) {
+    if (g.exec) cudaGraphExecDestroy(g.exec);
+    g = ScoreGraph();
+  }
+}
+
 int pin_reserve(lxy_ctx* c, size_t bytes) {
   if (bytes <= c->h_pin_cap) return LXY_OK;
   if (c->h_pin) cudaFreeHost(c->h_pin);
@@ -153,7 +160,8 @@ int lxy_ctx_create(const lxy_cfg* cfg, lxy_ctx** out) {
     return LXY_ERR_CUDA;
   }
   if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess ||
-      cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+      cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess) {
     set_error("cudaStreamCreate failed");
     lxy_ctx_destroy(c);
     return LXY_ERR_CUDA;
@@ -177,7 +185,9 @@ void lxy_ctx_destroy(lxy_ctx* c) {
   for (DevBuf* b : bufs) b->release();
   if (c->h_pin) cudaFreeHost(c->h_pin);
   for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
+  lxy::drop_score_graphs(c);
   if (c->ev_join) cudaEventDestroy(c->ev_join);
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   if (c->stream2) cudaStreamDestroy(c->stream2);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;

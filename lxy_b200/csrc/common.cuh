@@ -73,6 +73,25 @@ struct ScaffLinks {
   // pair-table path (cfg.path == LXY_PATH_PAIRS): dense symmetric n x n table, int32 or double
   DevBuf dense;
   bool dense_ready = false;
+  uint64_t version = 0;     // bumped by every build: cached launch graphs of older stores are dropped
+};
+
+// A scoring call captured as a CUDA graph: a GA loop (or a host that scores single orderings) calls
+// with the same buffers over and over, and for small problems the 15 or so runtime calls of one
+// scoring pass cost more host time than the kernels take on the device.
+struct ScoreGraph {
+  const void* perm = nullptr;
+  void* out = nullptr;
+  void* x100 = nullptr;
+  int32_t P = 0;
+  uint64_t version = 0;
+  int seen = 0;                    // identical calls so far (captured on the second)
+  bool failed = false;             // capture was refused once: stay on the direct path
+  cudaGraphExec_t exec = nullptr;
+  lxy_timing timing{};
+  uint64_t stamp = 0;              // last use (eviction)
+  const void* scratch[5] = {};     // the context's scratch buffers the graph writes to: a later, larger
+                                   // call may have reallocated them
 };
 
 struct PhaseLinks {
@@ -94,7 +113,11 @@ struct lxy_ctx {
   cudaStream_t stream = nullptr;
   cudaStream_t stream2 = nullptr;   // side stream (head-of-ordering look-ups)
   cudaEvent_t ev_join = nullptr;
+  cudaEvent_t ev_fork = nullptr;
   cudaEvent_t ev[8]{};
+  bool capturing = false;           // the scoring pass is being captured into a graph
+  lxy::ScoreGraph graphs[4];
+  uint64_t graph_clock = 0;
   int sm_count = 0;
   int max_smem_optin = 0;
   lxy_timing timing{};
@@ -110,6 +133,12 @@ struct lxy_ctx {
 
 namespace lxy {
 int pin_reserve(lxy_ctx* c, size_t bytes);
+void drop_score_graphs(lxy_ctx* c);
+// timing event k of the context on its main stream; inside a capture the record must be an
+// "external" one to become a node whose time stamp can be read after the graph ran
+inline cudaError_t record_timing_event(lxy_ctx* c, int k) {
+  return cudaEventRecordWithFlags(c->ev[k], c->stream, c->capturing ? cudaEventRecordExternal : cudaEventRecordDefault);
+}
 
 // link_store.cu
 struct LinkInput {

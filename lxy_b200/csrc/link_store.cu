@@ -241,6 +241,8 @@ int build_scaff_links(lxy_ctx* c, const LinkInput& in) {
     B_CUDA(cudaStreamSynchronize(st));
     cleanup();
     S.ready = true;
+    ++S.version;
+    drop_score_graphs(c);
     return LXY_OK;
   }
 
@@ -302,6 +304,8 @@ int build_scaff_links(lxy_ctx* c, const LinkInput& in) {
     return LXY_ERR_ARG;
   }
   S.ready = true;
+  ++S.version;
+  drop_score_graphs(c);
   return LXY_OK;
 }
 

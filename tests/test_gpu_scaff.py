@@ -289,3 +289,53 @@ def test_full_size_config3_properties():
     _, ox = O.scaff_score_links_batch(n, ah, bh, np.ones(L), perms[:2], nthreads=2)
     assert xf[:2].tolist() == ox.tolist()
     assert N.rank(full)[0] in (0, 1)
+
+
+def test_repeated_calls_replay_a_graph_with_identical_results():
+    """A scoring call repeated with the same buffers is replayed from a captured CUDA graph from the
+    third call on; results, error reporting and timings must be those of the direct path, also after
+    the populations on the device changed, after a larger call reallocated the scratch buffers, and
+    after the link store was replaced."""
+    torch = pytest.importorskip("torch")
+    n, L = 900, 200000
+    a, b, _ = S.scaff_links(n, L, 91)
+    a2, b2, _ = S.scaff_links(n, L, 92)
+    pops = [S.scaff_population(n, 96, 190 + k) for k in range(4)]
+    big = S.scaff_population(n, 400, 199)
+    with N.Context(0) as cg, N.Context(0, flags=N.FLAG_NO_GRAPH) as cd:
+        for ctx in (cg, cd):
+            ctx.set_links(n, a, b, None)
+        dev = torch.device("cuda", 0)
+        for P in (96, 1):                                   # batch kernel and streaming-regime kernel
+            perm = torch.zeros((P, n), dtype=torch.int32, device=dev)
+            out = torch.zeros(P, dtype=torch.float64, device=dev)
+            x100 = torch.zeros(P, dtype=torch.int64, device=dev)
+            for k in range(6):
+                perm.copy_(torch.from_numpy(pops[k % 4][:P]))
+                torch.cuda.synchronize()
+                cg.scaff_score_batch_dev(perm.data_ptr(), P, out.data_ptr(), x100.data_ptr())
+                cg.sync()
+                t = cg.timing()
+                assert t["ms_score"] > 0 and t["ms_total"] >= t["ms_score"]
+                want, wx = cd.scaff_score_batch(pops[k % 4][:P], want_x100=True)
+                assert x100.cpu().numpy().tolist() == wx.tolist()
+                assert out.cpu().numpy().tolist() == want.tolist()
+                if k == 3:                                  # a larger call moves the scratch buffers
+                    gb, _ = cg.scaff_score_batch(big, want_x100=True)
+                    assert gb.tolist() == cd.scaff_score_batch(big).tolist()
+            bad = pops[0][:P].copy()                        # the replayed pass still validates
+            bad[0, 5] = bad[0, 6]
+            perm.copy_(torch.from_numpy(bad))
+            torch.cuda.synchronize()
+            with pytest.raises(N.LxyError):
+                cg.scaff_score_batch_dev(perm.data_ptr(), P, out.data_ptr(), x100.data_ptr())
+            perm.copy_(torch.from_numpy(pops[1][:P]))       # new links: old graphs are dropped
+            torch.cuda.synchronize()
+            for ctx in (cg, cd):
+                ctx.set_links(n, a2, b2, None)
+            for _ in range(3):
+                cg.scaff_score_batch_dev(perm.data_ptr(), P, out.data_ptr(), x100.data_ptr())
+                cg.sync()
+                assert out.cpu().numpy().tolist() == cd.scaff_score_batch(pops[1][:P]).tolist()
+            for ctx in (cg, cd):
+                ctx.set_links(n, a, b, None)
