@@ -236,6 +236,7 @@ __device__ __forceinline__ void eval_packet(const uint4 v, const uint8_t* laneA,
   constexpr int ROWB = 32 * CPL * (WIDE == 1 ? 4 : 2);
   const uint32_t words[4] = {v.x, v.y, v.z, v.w};
   uint32_t A[4] = {0, 0, 0, 0};
+  uint32_t a_prev = 0xFFFFFFFFu;
   if (SAME_A) {
     if (ROWB == 256) load_row_a<CPL, WIDE>(laneA - lane_off + __byte_perm(v.x, lane_off, 0x7614), A);
     else load_row_a<CPL, WIDE>(laneA + ((v.x >> 8) & 0xFFu) * ROWB, A);
@@ -256,7 +257,11 @@ __device__ __forceinline__ void eval_packet(const uint4 v, const uint8_t* laneA,
       rowA = laneA + (r >> 8) * ROWB;
       rowB = laneB + (r & 0xFFu) * ROWB;
     }
-    if (!SAME_A) load_row_a<CPL, WIDE>(rowA, A);
+    if (!SAME_A) {  // a packet that crosses from one a to the next: row A again only where a changes
+      const uint32_t a_k = (k & 1) ? (wv >> 24) : ((wv >> 8) & 0xFFu);   // warp-uniform
+      if (a_k != a_prev) load_row_a<CPL, WIDE>(rowA, A);
+      a_prev = a_k;
+    }
     eval_record<CPL, WIDE, WM>(A, rowB, lut, lutd, lut2, WM == W_INT32 ? wi[k] : 0,
                                WM == W_F64 ? wd[k] : 0.0, L);
   }
@@ -326,6 +331,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
     const int64_t hi = min((npk_all * (s + 1) / prm.splits) * kPacket, prm.L);
     Lane<CPL, WM> acc;
     acc.clear();
+    int32_t loadedI = -1;   // block of table A in shared memory (none: the reduction below reuses the area)
 
     if (lo < hi) {
       // tile containing record `lo`: largest t with tile_start[t] <= lo
@@ -358,14 +364,17 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
         // ---- stage the two contig-block tables of tile (I, J) for group g (TMA bulk copies) ----
         __syncthreads();  // everyone is done with the previous tables
         if (tid == 0) {
-          const int rowsA = min(kBlk, prm.n - I * kBlk), rowsB = min(kBlk, prm.n - J * kBlk);
+          // tiles are walked row by row: block I of table A stays while J moves along the row
+          const bool needA = (I != loadedI);
+          const int rowsA = needA ? min(kBlk, prm.n - I * kBlk) : 0, rowsB = min(kBlk, prm.n - J * kBlk);
           const uint8_t* gA = (const uint8_t*)prm.tabA + ((size_t)g * prm.n + (size_t)I * kBlk) * ROWB;
           const uint8_t* gB = (const uint8_t*)prm.tabB + ((size_t)g * prm.n + (size_t)J * kBlk) * ROWB;
           fence_proxy_async();
           mbar_expect_tx(bar, (uint32_t)(rowsA + rowsB) * ROWB);
-          tma_bulk_g2s(sA, gA, (uint32_t)rowsA * ROWB, bar);
+          if (needA) tma_bulk_g2s(sA, gA, (uint32_t)rowsA * ROWB, bar);
           tma_bulk_g2s(sB, gB, (uint32_t)rowsB * ROWB, bar);
         }
+        loadedI = I;
         mbar_wait(bar, parity);
         parity ^= 1;
 
