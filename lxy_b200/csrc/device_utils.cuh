@@ -52,6 +52,23 @@ __device__ __forceinline__ uint4 ldg_stream_v4(const void* p) {
   return r;
 }
 
+// One 16-byte packet for the whole warp through the uniform datapath: lanes 0..3 load one word each
+// (one 16-byte request; a warp-uniform 128-bit load hands 512 bytes to the register file, four
+// wavefronts of the L1 data pipe), four REDUX.OR spread the words (results live in uniform registers).
+__device__ __forceinline__ uint32_t ldg_stream_word(const void* p, int lane) {
+  uint32_t r = 0;
+  if (lane < 4) asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"((const uint32_t*)p + lane));
+  return r;
+}
+__device__ __forceinline__ uint4 warp_packet(uint32_t mine, int lane) {
+  uint4 v;
+  v.x = __reduce_or_sync(0xffffffffu, lane == 0 ? mine : 0u);
+  v.y = __reduce_or_sync(0xffffffffu, lane == 1 ? mine : 0u);
+  v.z = __reduce_or_sync(0xffffffffu, lane == 2 ? mine : 0u);
+  v.w = __reduce_or_sync(0xffffffffu, lane == 3 ? mine : 0u);
+  return v;
+}
+
 __host__ __device__ inline int64_t tile_row_start(int64_t I, int64_t nblk) {
   return I * nblk - I * (I - 1) / 2;
 }

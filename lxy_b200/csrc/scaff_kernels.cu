@@ -417,14 +417,14 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
             const int32_t cnt = (int32_t)min((int64_t)kWarps << 16, nfull - c0);
             const uint16_t* rp = recp + c0 * kPacket;
             int32_t it = warp;
-            uint4 vn = make_uint4(0, 0, 0, 0);
-            if (it < cnt) vn = ldg_stream_v4(rp + (size_t)it * kPacket);
+            uint32_t mine_n = 0;
+            if (it < cnt) mine_n = ldg_stream_word(rp + (size_t)it * kPacket, lane);
             int32_t since = 0;  // packets since the 16-bit pair sums were unpacked: 64 * 8 * 100 < 2^16
 #pragma unroll 1
             for (; it < cnt; it += kWarps) {
               if (PairLut<CPL, WIDE, WM>::on && WM == W_UNIT && ++since == 64) { acc.flush16(); since = 0; }
-              const uint4 v = vn;
-              if (it + kWarps < cnt) vn = ldg_stream_v4(rp + (size_t)(it + kWarps) * kPacket);
+              const uint4 v = warp_packet(mine_n, lane);
+              if (it + kWarps < cnt) mine_n = ldg_stream_word(rp + (size_t)(it + kWarps) * kPacket, lane);
               load_weights<WM>(prm.w, wbase + (c0 + it) * kPacket, wi, wd);
               // sorted by (a, b): first a == last a  <=>  one a for the whole packet (warp-uniform)
               if (((v.x >> 8) & 0xFFu) == (v.w >> 24))
