@@ -667,7 +667,8 @@ def main():
                                      "32-bit tables) 2 wavefronts for row B + 2 (1) decay-table look-ups "
                                      "(pair table: one 32-bit look-up per two candidates) + 2/8 for "
                                      "row A (gathered once per 8-record packet) + 1/8 for the packet's "
-                                     "own 16-byte load = 4.375 (3.375) wavefronts of the L1/shared data pipe, "
+                                     "own 16 bytes (four lanes load a word each, REDUX.OR spreads them "
+                                     "through uniform registers) = 4.375 (3.375) wavefronts of the L1/shared data pipe, "
                                      "one wavefront/cycle/SM",
                              "evals_per_cycle_per_sm": evals_per_cycle,
                              "peak_evals_per_s": evals_per_cycle * 148 * (clocks["sm_mhz"] or 1965.0) * 1e6,
