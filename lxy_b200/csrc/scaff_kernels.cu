@@ -97,6 +97,7 @@ struct ScoreParams {
   int64_t L;
   int32_t n, nblk;
   int32_t groups, splits;     // units = groups * splits
+  int32_t prefetch;           // ask the record stream into L2 ahead of the warps (few groups share it)
 };
 
 // Per-lane state of the streaming loop: CPL candidates, their running sums.
@@ -419,12 +420,23 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
             int32_t it = warp;
             uint32_t mine_n = 0;
             if (it < cnt) mine_n = ldg_stream_word(rp + (size_t)it * kPacket, lane);
+            // A warp takes a packet every ~0.5 us and asks for it one round ahead, which does not cover a
+            // DRAM miss.  With 8 candidate groups the four groups that walk a stretch of the stream at the
+            // same time hide each other's misses in L2 (measured: a prefetch then only costs); with fewer
+            // groups the 128-byte line kPfAhead rounds further on is asked into L2.  Consecutive packets go
+            // to consecutive warps and kWarps is a multiple of 8, so warps 0, 8 and 16 between them see every
+            // line exactly once.  (A deeper register pipeline is slower: the loads share one scoreboard.)
+            static_assert(kWarps % 8 == 0, "a packet's line index must be fixed per warp");
+            constexpr int kPfAhead = 6;
+            const bool pf_warp = prm.prefetch && (warp & 7) == 0;
             int32_t since = 0;  // packets since the 16-bit pair sums were unpacked: 64 * 8 * 100 < 2^16
 #pragma unroll 1
             for (; it < cnt; it += kWarps) {
               if (PairLut<CPL, WIDE, WM>::on && WM == W_UNIT && ++since == 64) { acc.flush16(); since = 0; }
               const uint4 v = warp_packet(mine_n, lane);
               if (it + kWarps < cnt) mine_n = ldg_stream_word(rp + (size_t)(it + kWarps) * kPacket, lane);
+              if (pf_warp && it + kPfAhead * kWarps < cnt)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + (size_t)(it + kPfAhead * kWarps) * kPacket));
               load_weights<WM>(prm.w, wbase + (c0 + it) * kPacket, wi, wd);
               // sorted by (a, b): first a == last a  <=>  one a for the whole packet (warp-uniform)
               if (((v.x >> 8) & 0xFFu) == (v.w >> 24))
@@ -847,6 +859,7 @@ static int scaff_score_enqueue(lxy_ctx* c, const int32_t* perm_dev, int32_t P, d
   prm.nblk = S.nblk;
   prm.groups = groups;
   prm.splits = splits;
+  prm.prefetch = (groups <= 4 && 2 * S.L > ((int64_t)96 << 20)) ? 1 : 0;   // a stream that stays in L2 needs none
   int rc;
   if (tm == 1) {
     rc = S.wmode == W_UNIT ? launch_score_cpl<1, W_UNIT>(c, cpl, prm, grid)
