@@ -178,6 +178,33 @@ int lxy_links_records(const lxy_links* l, uint32_t* a, uint32_t* b, double* w); 
 /* kind 0: the table becomes the scaffolding link store (lxy_ctx_set_links); 1: the phasing store. */
 int lxy_ctx_set_links_from(lxy_ctx* ctx, const lxy_links* l, int32_t kind);
 
+/* ---- LoadLinks on the device (lxy_b200/csrc/links_parse.cu) -----------------------------------------
+ * The same table as lxy_links_load (names -> ids by first appearance; one record per pair, in order
+ * of the pair's first row, holding the value of its LAST row; the same error returns), built by
+ * kernels: the text crosses PCIe once, lines, fields, name hashing, decimal -> double conversion,
+ * id assignment and the last-row-wins reduction all run on the GPU.  Values outside the exactly
+ * rounded fast path (inf / nan / hex / 20+ digits / malformed) are resolved by the host loader's own
+ * conversion, so the two loaders agree on every bit.  lxy_links_load_gpu returns the table as a
+ * host object; lxy_ctx_load_links also makes it the context's link store (kind 0: scaffolding, the
+ * record arrays never leave the device; kind 1: phasing) - `out` and `stats` are nullable. */
+typedef struct lxy_load_stats {
+  int64_t bytes;       /* file size                                                          */
+  int64_t lines;       /* lines incl. comments                                               */
+  int64_t records;     /* data lines                                                         */
+  int64_t pairs;       /* distinct pairs = records of the table                              */
+  int32_t names;       /* distinct names = Size()                                            */
+  int32_t slow_values; /* value tokens resolved on the host                                  */
+  int32_t attempts;    /* 1 unless a 64-bit name-hash collision was detected and re-seeded   */
+  int32_t reserved;
+  float ms_read;       /* file -> host memory                                                */
+  float ms_h2d;        /* text host -> device                                                */
+  float ms_device;     /* all kernels, from text resident to records resident                */
+  float ms_total;      /* wall clock of the call's parsing part                              */
+} lxy_load_stats;
+int lxy_links_load_gpu(const char* path, int32_t device, lxy_links** out, lxy_load_stats* stats);
+int lxy_ctx_load_links(lxy_ctx* ctx, const char* path, int32_t kind, lxy_links** out,
+                       lxy_load_stats* stats);
+
 /* ---- device-resident GA generation loop --------------------------------------------------------
  * Replaces the loop `gao.Optimize(1); best := gao.Best()` of Scaffold / Phase (scaff.go:105-126,
  * phase.go:74-95) and the genome operators it drives (scaff/genome.go:47-91,93-97,125-138,161-209;

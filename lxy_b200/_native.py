@@ -32,6 +32,7 @@ SYMBOLS = [
     "lxy_links_new", "lxy_links_load", "lxy_links_free", "lxy_links_write", "lxy_links_size",
     "lxy_links_npairs", "lxy_links_id", "lxy_links_name", "lxy_links_set", "lxy_links_add",
     "lxy_links_value", "lxy_links_records", "lxy_ctx_set_links_from",
+    "lxy_links_load_gpu", "lxy_ctx_load_links",
     "lxy_scaffold_file", "lxy_phase_file", "lxy_eval_scaffolding", "lxy_eval_phasing",
 ]
 
@@ -61,6 +62,17 @@ class Timing(C.Structure):
 
     def asdict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class LoadStats(C.Structure):
+    """lxy_load_stats (include/lxy_b200.h): what the device loader read and where its time went."""
+    _fields_ = [("bytes", C.c_int64), ("lines", C.c_int64), ("records", C.c_int64), ("pairs", C.c_int64),
+                ("names", C.c_int32), ("slow_values", C.c_int32), ("attempts", C.c_int32),
+                ("reserved", C.c_int32), ("ms_read", C.c_float), ("ms_h2d", C.c_float),
+                ("ms_device", C.c_float), ("ms_total", C.c_float)]
+
+    def asdict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
 
 
 class GaParams(C.Structure):
@@ -162,6 +174,8 @@ def lib():
         "lxy_links_value": (i32, [vp, i32, i32, C.POINTER(f64)]),
         "lxy_links_records": (i32, [vp, vp, vp, vp]),
         "lxy_ctx_set_links_from": (i32, [vp, vp, i32]),
+        "lxy_links_load_gpu": (i32, [C.c_char_p, i32, C.POINTER(vp), C.POINTER(LoadStats)]),
+        "lxy_ctx_load_links": (i32, [vp, C.c_char_p, i32, C.POINTER(vp), C.POINTER(LoadStats)]),
         "lxy_scaffold_file": (i32, [C.c_char_p, C.c_char_p, i32, C.POINTER(GaParams), i32, C.POINTER(f64)]),
         "lxy_phase_file": (i32, [C.c_char_p, C.c_char_p, i32, C.POINTER(GaParams), i32, C.POINTER(f64)]),
         "lxy_eval_scaffolding": (i32, [vp, vp, vp, i32, i32, vp]),
@@ -436,10 +450,27 @@ class GA:
 class NativeLinks:
     """lxy_links: the library's own sequtil.Links (links.go:14-28) for the fitness path."""
 
-    def __init__(self, path=None):
+    def __init__(self, path=None, device=None, ctx=None, phase=False):
+        """path None: an empty table; path: LoadLinks on the host (lxy_links_load); with device=d the
+        text is parsed by the GPU loader (lxy_links_load_gpu); with ctx=... the parsed table also
+        becomes that context's link store without leaving the device (lxy_ctx_load_links)."""
         self._h = C.c_void_p()
+        self.load_stats = None
         if path is None:
             _check(lib().lxy_links_new(C.byref(self._h)))
+        elif ctx is not None:
+            st = LoadStats()
+            _check(lib().lxy_ctx_load_links(ctx._h, os.fsencode(path), 1 if phase else 0, C.byref(self._h),
+                                            C.byref(st)))
+            self.load_stats = st.asdict()
+            if phase:
+                ctx.phase_n = self.Size()
+            else:
+                ctx.n = self.Size()
+        elif device is not None:
+            st = LoadStats()
+            _check(lib().lxy_links_load_gpu(os.fsencode(path), int(device), C.byref(self._h), C.byref(st)))
+            self.load_stats = st.asdict()
         else:
             _check(lib().lxy_links_load(os.fsencode(path), C.byref(self._h)))     # LoadLinks
 

@@ -23,14 +23,7 @@
 
 #include "../../include/lxy_ga_plan.h"
 #include "common.cuh"
-
-struct lxy_links {
-  std::unordered_map<std::string, int32_t> id_of;  // idKey
-  std::vector<std::string> name_of;                // idKeyRev (dense: id == index)
-  std::unordered_map<uint64_t, size_t> slot;       // (lo << 32 | hi) -> index into a/b/w
-  std::vector<uint32_t> a, b;                      // a <= b
-  std::vector<double> w;
-};
+#include "links_table.h"
 
 using namespace lxy;
 
@@ -56,6 +49,7 @@ int put(lxy_links* l, int32_t id1, int32_t id2, double v, bool accumulate) {
   }
   const uint32_t lo = (uint32_t)(id1 < id2 ? id1 : id2), hi = (uint32_t)(id1 < id2 ? id2 : id1);
   const uint64_t key = ((uint64_t)lo << 32) | hi;
+  l->ensure_slots();
   auto it = l->slot.find(key);
   if (it == l->slot.end()) {
     l->slot.emplace(key, l->a.size());
@@ -70,6 +64,9 @@ int put(lxy_links* l, int32_t id1, int32_t id2, double v, bool accumulate) {
   return LXY_OK;
 }
 
+}  // namespace
+
+namespace lxy {
 // strconv.ParseFloat(tok, 64) with the error ignored (links.go:473): on a syntax error the Go
 // function returns 0; on a range error it returns +-Inf, which is what strtod gives as well.
 double parse_float_or_zero(const char* s, size_t len) {
@@ -84,7 +81,7 @@ double parse_float_or_zero(const char* s, size_t len) {
   return v;
 }
 
-}  // namespace
+}  // namespace lxy
 
 extern "C" {
 
@@ -199,6 +196,7 @@ int lxy_links_value(const lxy_links* l, int32_t id1, int32_t id2, double* out) {
     return LXY_ERR_ARG;
   }
   const uint32_t lo = (uint32_t)(id1 < id2 ? id1 : id2), hi = (uint32_t)(id1 < id2 ? id2 : id1);
+  l->ensure_slots();
   auto it = l->slot.find(((uint64_t)lo << 32) | hi);
   *out = it == l->slot.end() ? 0.0 : l->w[it->second];
   return LXY_OK;
@@ -238,17 +236,17 @@ namespace {
 int run_ga_file(const char* links_path, const char* out_path, int32_t iterations, const lxy_ga_params* prm_in,
                 int32_t device, int32_t kind, double* best_score) {
   if (!links_path || !out_path || iterations < 0) { set_error("infer: bad argument"); return LXY_ERR_ARG; }
-  lxy_links* l = nullptr;
-  LXY_TRY(lxy_links_load(links_path, &l));
   lxy_cfg cfg{};
   cfg.device = device;
   lxy_ctx* ctx = nullptr;
-  int rc = lxy_ctx_create(&cfg, &ctx);
+  LXY_TRY(lxy_ctx_create(&cfg, &ctx));
+  lxy_links* l = nullptr;  // LoadLinks on the device; the records go straight into the link store
+  int rc = lxy_ctx_load_links(ctx, links_path, kind, &l, nullptr);
+  if (rc != LXY_OK) { lxy_ctx_destroy(ctx); return rc; }
   lxy_ga* ga = nullptr;
   const int32_t n = lxy_links_size(l);
   std::vector<int32_t> gene32;
   std::vector<uint8_t> gene8;
-  if (rc == LXY_OK) rc = lxy_ctx_set_links_from(ctx, l, kind);
   if (rc == LXY_OK) {
     lxy_ga_params prm{};
     if (prm_in) {
