@@ -32,6 +32,12 @@
 // The record arrays stay on the device for lxy_ctx_load_links (they feed the link store directly).
 #include <cub/device/device_radix_sort.cuh>
 
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <algorithm>
 #include <cerrno>
 #include <chrono>
 #include <cstdio>
@@ -301,7 +307,8 @@ __global__ void __launch_bounds__(kThreads) k_parse_lines(const ParseArgs A) {
   A.tl[2 * i] = len0;
   A.tl[2 * i + 1] = len1;
   A.val[i] = v;
-  atomicAdd(A.ndata, 1ull);
+  const unsigned peers = __activemask();  // one counter update per warp, not per line
+  if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(A.ndata, (unsigned long long)__popc(peers));
 }
 
 __global__ void k_scatter_vals(const uint32_t* __restrict__ line, const double* __restrict__ v, uint32_t n,
@@ -348,9 +355,10 @@ __global__ void __launch_bounds__(kThreads) k_names_insert(const uint64_t* __res
 __global__ void __launch_bounds__(kThreads) k_names_verify(const uint8_t* __restrict__ text, const int64_t* __restrict__ nl_pos,
                                                            const uint32_t* __restrict__ tl, uint32_t ntok,
                                                            const uint32_t* __restrict__ first,
-                                                           const uint32_t* __restrict__ tok_slot, int* collision) {
+                                                           const uint32_t* __restrict__ tok_slot, const int* overflow,
+                                                           int* collision) {
   const uint32_t t = blockIdx.x * kThreads + threadIdx.x;
-  if (t >= ntok || tl[t] == kInvalid) return;
+  if (t >= ntok || tl[t] == kInvalid || *overflow) return;  // after an overflow tok_slot is incomplete
   const uint32_t ft = first[tok_slot[t]];
   if (ft == t) return;
   const uint32_t len = tl[t];
@@ -426,16 +434,43 @@ __global__ void __launch_bounds__(kThreads) k_pairs_emit(const uint32_t* __restr
   w[i] = val[last[s]];
 }
 
-struct Scratch {  // every device buffer of one load, freed on every exit path
-  DevBuf text, counts, chunk_base, nl_pos, h, tl, val, tok_slot, flags, slow_off, slow_len, slow_line, slow_val,
-      nkeys, nfirst, lf, ls, lf2, ls2, slot_id, name_off, name_len, pkeys, pfirst, plast, sort_tmp;
+// Device memory of one load: one cudaMalloc per stage instead of one per array (26 cudaMalloc /
+// cudaFree pairs cost several times what all the kernels take); everything is freed on every exit path.
+struct Arena {
+  std::vector<void*> slabs;
+  char* cur = nullptr;
+  size_t left = 0;
+  int open(size_t bytes) {
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) {
+      (void)cudaGetLastError();
+      set_error("links_load: cudaMalloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+      return LXY_ERR_NOMEM;
+    }
+    slabs.push_back(p);
+    cur = (char*)p;
+    left = bytes;
+    return LXY_OK;
+  }
+  template <class T> T* take(size_t count) {
+    const size_t b = (count * sizeof(T) + 255) & ~(size_t)255;
+    if (b > left) return nullptr;  // sizing bug; callers check through ok()
+    T* r = reinterpret_cast<T*>(cur);
+    cur += b;
+    left -= b;
+    return r;
+  }
+  ~Arena() {
+    for (void* p : slabs) cudaFree(p);
+  }
+};
+inline size_t r256(size_t b) { return (b + 255) & ~(size_t)255; }
+
+struct Handles {
   cudaStream_t st = nullptr;
   cudaEvent_t ev[3] = {};
-  ~Scratch() {
-    DevBuf* all[] = {&text, &counts, &chunk_base, &nl_pos, &h, &tl, &val, &tok_slot, &flags, &slow_off, &slow_len,
-                     &slow_line, &slow_val, &nkeys, &nfirst, &lf, &ls, &lf2, &ls2, &slot_id, &name_off, &name_len,
-                     &pkeys, &pfirst, &plast, &sort_tmp};
-    for (DevBuf* b : all) b->release();
+  ~Handles() {
     for (auto& e : ev)
       if (e) cudaEventDestroy(e);
     if (st) cudaStreamDestroy(st);
@@ -445,10 +480,50 @@ struct Scratch {  // every device buffer of one load, freed on every exit path
 struct Parsed {
   int32_t n = 0;
   int64_t m = 0;
-  DevBuf a, b, w;  // device records, order of first appearance (released by the caller)
+  void* slab = nullptr;  // device records a | b | w, order of first appearance
+  uint32_t *a = nullptr, *b = nullptr;
+  double* w = nullptr;
   std::vector<std::string> names;
-  ~Parsed() { a.release(); b.release(); w.release(); }
+  ~Parsed() { if (slab) cudaFree(slab); }
 };
+
+// The file as one read-only byte range: mapped (the page cache is the buffer; nothing is copied on the
+// host before the DMA staging) or, for things that cannot be mapped, read into memory.
+struct FileText {
+  const char* p = nullptr;
+  size_t n = 0;
+  bool mapped = false;
+  std::vector<char> buf;
+  ~FileText() { if (mapped) munmap(const_cast<char*>(p), n); }
+};
+
+int read_file(const char* path, FileText& ft) {
+  const int fd = ::open(path, O_RDONLY);
+  if (fd < 0) { set_error("links_load: cannot open %s: %s", path, std::strerror(errno)); return LXY_ERR_ARG; }
+  struct stat sb;
+  if (fstat(fd, &sb) == 0 && S_ISREG(sb.st_mode) && sb.st_size > 0) {
+    void* m = mmap(nullptr, (size_t)sb.st_size, PROT_READ, MAP_PRIVATE | MAP_POPULATE, fd, 0);
+    if (m != MAP_FAILED) {
+      ft.p = (const char*)m;
+      ft.n = (size_t)sb.st_size;
+      ft.mapped = true;
+      ::close(fd);
+      return LXY_OK;
+    }
+  }
+  char chunk[1 << 16];
+  for (;;) {
+    const ssize_t r = ::read(fd, chunk, sizeof(chunk));
+    if (r < 0 && errno == EINTR) continue;
+    if (r < 0) { set_error("links_load: cannot read %s: %s", path, std::strerror(errno)); ::close(fd); return LXY_ERR_ARG; }
+    if (r == 0) break;
+    ft.buf.insert(ft.buf.end(), chunk, chunk + r);
+  }
+  ::close(fd);
+  ft.p = ft.buf.data();
+  ft.n = ft.buf.size();
+  return LXY_OK;
+}
 
 uint32_t pow2_at_least(uint64_t x) {
   uint64_t c = 1024;
@@ -456,16 +531,32 @@ uint32_t pow2_at_least(uint64_t x) {
   return (uint32_t)c;
 }
 
-// (first, slot) pairs sorted by first; results in lf2 / ls2
-int sort_by_first(Scratch& S, uint32_t n) {
-  LXY_TRY(S.lf2.reserve((size_t)n * 4 + 4));
-  LXY_TRY(S.ls2.reserve((size_t)n * 4 + 4));
+// (first, slot) pairs -> sorted by first
+struct SortBufs {
+  uint32_t *lf = nullptr, *ls = nullptr, *lf2 = nullptr, *ls2 = nullptr;
+  void* tmp = nullptr;
+  size_t tmp_bytes = 0;
+};
+size_t sort_tmp_bytes(uint32_t n) {
   size_t tmp = 0;
-  P_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp, S.lf.as<uint32_t>(), S.lf2.as<uint32_t>(), S.ls.as<uint32_t>(),
-                                         S.ls2.as<uint32_t>(), (int64_t)n, 0, 32, S.st));
-  LXY_TRY(S.sort_tmp.reserve(tmp + 16));
-  P_CUDA(cub::DeviceRadixSort::SortPairs(S.sort_tmp.p, tmp, S.lf.as<uint32_t>(), S.lf2.as<uint32_t>(), S.ls.as<uint32_t>(),
-                                         S.ls2.as<uint32_t>(), (int64_t)n, 0, 32, S.st));
+  cub::DeviceRadixSort::SortPairs(nullptr, tmp, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const uint32_t*)nullptr,
+                                  (uint32_t*)nullptr, (int64_t)n, 0, 32, (cudaStream_t) nullptr);
+  return tmp + 256;
+}
+size_t sort_bytes(uint32_t n) { return 4 * r256((size_t)n * 4 + 4) + r256(sort_tmp_bytes(n)); }
+bool sort_take(Arena& A, uint32_t n, SortBufs& B) {
+  B.lf = A.take<uint32_t>((size_t)n + 1);
+  B.ls = A.take<uint32_t>((size_t)n + 1);
+  B.lf2 = A.take<uint32_t>((size_t)n + 1);
+  B.ls2 = A.take<uint32_t>((size_t)n + 1);
+  B.tmp_bytes = sort_tmp_bytes(n);
+  B.tmp = A.take<char>(B.tmp_bytes);
+  return B.lf && B.ls && B.lf2 && B.ls2 && B.tmp;
+}
+int sort_by_first(const SortBufs& B, uint32_t n, cudaStream_t st) {
+  size_t tmp = B.tmp_bytes;
+  P_CUDA(cub::DeviceRadixSort::SortPairs(B.tmp, tmp, (const uint32_t*)B.lf, B.lf2, (const uint32_t*)B.ls, B.ls2,
+                                         (int64_t)n, 0, 32, st));
   return LXY_OK;
 }
 
@@ -482,73 +573,91 @@ struct Flags {
   int overflow, collision, pad;
 };
 
+struct NameTable {  // arrays whose size follows the table capacity
+  unsigned long long* keys = nullptr;
+  uint32_t *first = nullptr, *slot_id = nullptr, *name_len = nullptr;
+  int64_t* name_off = nullptr;
+  SortBufs sort;
+};
+size_t name_table_bytes(uint32_t cap) {
+  return r256((size_t)cap * 8) + 2 * r256((size_t)cap * 4) + r256((size_t)cap / 2 * 4) + r256((size_t)cap / 2 * 8) +
+         sort_bytes(cap / 2);
+}
+bool name_table_take(Arena& A, uint32_t cap, NameTable& N) {
+  N.keys = A.take<unsigned long long>(cap);
+  N.first = A.take<uint32_t>(cap);
+  N.slot_id = A.take<uint32_t>(cap);
+  N.name_len = A.take<uint32_t>(cap / 2);
+  N.name_off = A.take<int64_t>(cap / 2);
+  return N.keys && N.first && N.slot_id && N.name_len && N.name_off && sort_take(A, cap / 2, N.sort);
+}
+
+#define P_SIZED(ok) do { if (!(ok)) { set_error("links_load: arena sizing (internal)"); return LXY_ERR_STATE; } } while (0)
+
 int parse_links_on_device(const char* path, int device, Parsed& out, lxy_load_stats* stats) {
   const auto t_start = std::chrono::steady_clock::now();
   lxy_load_stats stt{};
-  FILE* f = std::fopen(path, "rb");
-  if (!f) { set_error("links_load: cannot open %s: %s", path, std::strerror(errno)); return LXY_ERR_ARG; }
-  std::vector<char> text;
-  {
-    std::fseek(f, 0, SEEK_END);
-    const long sz = std::ftell(f);
-    std::fseek(f, 0, SEEK_SET);
-    if (sz > 0) text.resize((size_t)sz);
-    size_t got = 0;
-    while (got < text.size()) {
-      const size_t r = std::fread(text.data() + got, 1, text.size() - got, f);
-      if (r == 0) break;
-      got += r;
-    }
-    text.resize(got);
-    char buf[1 << 12];  // a file that grew, or a stream without a size
-    size_t r;
-    while ((r = std::fread(buf, 1, sizeof(buf), f)) > 0) text.insert(text.end(), buf, buf + r);
-  }
-  std::fclose(f);
+  FileText ft;
+  LXY_TRY(read_file(path, ft));
+  const char* text = ft.p;
   stt.ms_read = (float)ms_since(t_start);
-  const int64_t T = (int64_t)text.size();
+  const int64_t T = (int64_t)ft.n;
   stt.bytes = T;
   if (T == 0) { set_error("links_load: Loaded empty links object..."); return LXY_ERR_STATE; }
 
   P_CUDA(cudaSetDevice(device));
-  Scratch S;
-  P_CUDA(cudaStreamCreateWithFlags(&S.st, cudaStreamNonBlocking));
-  for (auto& e : S.ev) P_CUDA(cudaEventCreate(&e));
-  LXY_TRY(S.text.reserve((size_t)T + 48));
-  LXY_TRY(S.flags.reserve(sizeof(Flags)));
-  Flags* dF = S.flags.as<Flags>();
-  P_CUDA(cudaEventRecord(S.ev[0], S.st));
-  P_CUDA(cudaMemsetAsync(S.text.as<uint8_t>() + T, 0, 48, S.st));
-  P_CUDA(cudaMemcpyAsync(S.text.p, text.data(), (size_t)T, cudaMemcpyHostToDevice, S.st));
-  P_CUDA(cudaEventRecord(S.ev[1], S.st));
-  const uint8_t* d_text = S.text.as<uint8_t>();
+  Handles H;
+  Arena A;
+  P_CUDA(cudaStreamCreateWithFlags(&H.st, cudaStreamNonBlocking));
+  for (auto& e : H.ev) P_CUDA(cudaEventCreate(&e));
+  cudaStream_t st = H.st;
+
+  // stage A: the text and the per-chunk newline counts
+  const int64_t nchunks = (T + kChunk - 1) / kChunk;
+  LXY_TRY(A.open(r256((size_t)T + 48) + r256((size_t)nchunks * 4) + r256((size_t)nchunks * 8) + r256(sizeof(Flags))));
+  uint8_t* d_text_w = A.take<uint8_t>((size_t)T + 48);
+  uint32_t* d_counts = A.take<uint32_t>((size_t)nchunks);
+  int64_t* d_chunk_base = A.take<int64_t>((size_t)nchunks);
+  Flags* dF = A.take<Flags>(1);
+  P_SIZED(d_text_w && d_counts && d_chunk_base && dF);
+  const uint8_t* d_text = d_text_w;
+  P_CUDA(cudaEventRecord(H.ev[0], st));
+  P_CUDA(cudaMemsetAsync(d_text_w + T, 0, 48, st));
+  P_CUDA(cudaMemcpyAsync(d_text_w, text, (size_t)T, cudaMemcpyHostToDevice, st));
+  P_CUDA(cudaEventRecord(H.ev[1], st));
 
   // 1. newline positions
-  const int64_t nchunks = (T + kChunk - 1) / kChunk;
-  LXY_TRY(S.counts.reserve((size_t)nchunks * 4));
-  LXY_TRY(S.chunk_base.reserve((size_t)nchunks * 8));
-  P_CUDA(cudaMemsetAsync(dF, 0, sizeof(Flags), S.st));
-  k_newline_count<<<(unsigned)nchunks, kThreads, 0, S.st>>>(d_text, T, S.counts.as<uint32_t>());
-  k_scan_counts<<<1, 1024, 0, S.st>>>(S.counts.as<uint32_t>(), nchunks, S.chunk_base.as<int64_t>(), &dF->nl_total);
+  P_CUDA(cudaMemsetAsync(dF, 0, sizeof(Flags), st));
+  k_newline_count<<<(unsigned)nchunks, kThreads, 0, st>>>(d_text, T, d_counts);
+  k_scan_counts<<<1, 1024, 0, st>>>(d_counts, nchunks, d_chunk_base, &dF->nl_total);
   int64_t NL = 0;
-  P_CUDA(cudaMemcpyAsync(&NL, &dF->nl_total, 8, cudaMemcpyDeviceToHost, S.st));
-  P_CUDA(cudaStreamSynchronize(S.st));
+  P_CUDA(cudaMemcpyAsync(&NL, &dF->nl_total, 8, cudaMemcpyDeviceToHost, st));
+  P_CUDA(cudaStreamSynchronize(st));
   const int64_t lines = NL + (text[(size_t)T - 1] != '\n' ? 1 : 0);
   if (lines >= (1ll << 31)) { set_error("links_load: %lld lines exceed the device loader's 2^31", (long long)lines); return LXY_ERR_RANGE; }
   stt.lines = lines;
-  LXY_TRY(S.nl_pos.reserve((size_t)(NL + 1) * 8));
-  k_newline_pos<<<(unsigned)nchunks, kThreads, 0, S.st>>>(d_text, T, S.chunk_base.as<int64_t>(), S.nl_pos.as<int64_t>());
+
+  // stage B: everything sized by the line count, and the first name table
+  const uint32_t ntok = (uint32_t)(2 * lines);
+  uint32_t cap = pow2_at_least(1u << 16);
+  LXY_TRY(A.open(r256((size_t)(NL + 1) * 8) + r256((size_t)ntok * 8) + 2 * r256((size_t)ntok * 4) +
+                 3 * r256((size_t)lines * 8) + 2 * r256((size_t)lines * 4) + name_table_bytes(cap)));
+  int64_t* d_nl = A.take<int64_t>((size_t)NL + 1);
+  uint64_t* d_h = A.take<uint64_t>(ntok);
+  uint32_t* d_tl = A.take<uint32_t>(ntok);
+  uint32_t* d_tok_slot = A.take<uint32_t>(ntok);
+  double* d_val = A.take<double>((size_t)lines);
+  int64_t* d_slow_off = A.take<int64_t>((size_t)lines);
+  double* d_slow_val = A.take<double>((size_t)lines);
+  uint32_t* d_slow_len = A.take<uint32_t>((size_t)lines);
+  uint32_t* d_slow_line = A.take<uint32_t>((size_t)lines);
+  NameTable NT;
+  P_SIZED(d_nl && d_h && d_tl && d_tok_slot && d_val && d_slow_off && d_slow_val && d_slow_len && d_slow_line &&
+          name_table_take(A, cap, NT));
+  k_newline_pos<<<(unsigned)nchunks, kThreads, 0, st>>>(d_text, T, d_chunk_base, d_nl);
   P_CUDA(cudaGetLastError());
 
   // 2..3: parse + name table; a detected hash collision re-runs both with another seed
-  const uint32_t ntok = (uint32_t)(2 * lines);
-  LXY_TRY(S.h.reserve((size_t)ntok * 8));
-  LXY_TRY(S.tl.reserve((size_t)ntok * 4));
-  LXY_TRY(S.val.reserve((size_t)lines * 8));
-  LXY_TRY(S.tok_slot.reserve((size_t)ntok * 4));
-  LXY_TRY(S.slow_off.reserve((size_t)lines * 8));
-  LXY_TRY(S.slow_len.reserve((size_t)lines * 4));
-  LXY_TRY(S.slow_line.reserve((size_t)lines * 4));
   const unsigned line_grid = (unsigned)((lines + kThreads - 1) / kThreads);
   const unsigned tok_grid = (unsigned)(((int64_t)ntok + kThreads - 1) / kThreads);
   uint64_t hmask0 = ~0ull;  // test hook: a narrow first hash forces the collision path
@@ -556,135 +665,125 @@ int parse_links_on_device(const char* path, int device, Parsed& out, lxy_load_st
     const int bits = std::atoi(hb);
     if (bits > 0 && bits < 64) hmask0 = (1ull << bits) - 1;
   }
-  uint32_t cap = pow2_at_least(1u << 16);
   uint32_t N = 0;
   Flags hF{};
   for (int attempt = 0;; ++attempt) {
     if (attempt == 4) { set_error("links_load: name hash collisions persisted over 4 seeds"); return LXY_ERR_STATE; }
     stt.attempts = attempt + 1;
-    P_CUDA(cudaMemsetAsync(dF, 0, sizeof(Flags), S.st));
-    P_CUDA(cudaMemsetAsync(&dF->err, 0xFF, 8, S.st));
-    ParseArgs A{d_text, T, S.nl_pos.as<int64_t>(), (int64_t)NL, lines, 0x9e3779b97f4a7c15ull * (uint64_t)attempt,
-                attempt == 0 ? hmask0 : ~0ull, S.h.as<uint64_t>(), S.tl.as<uint32_t>(), S.val.as<double>(),
-                &dF->err, &dF->slow_cnt, S.slow_off.as<int64_t>(), S.slow_len.as<uint32_t>(),
-                S.slow_line.as<uint32_t>(), &dF->ndata};
-    k_parse_lines<<<line_grid, kThreads, 0, S.st>>>(A);
-    P_CUDA(cudaMemcpyAsync(&hF, dF, sizeof(Flags), cudaMemcpyDeviceToHost, S.st));
-    P_CUDA(cudaStreamSynchronize(S.st));
-    if (hF.err != ~0ull) {
-      const unsigned long long ln = (hF.err >> 2) + 1;
-      const int kind = (int)(hF.err & 3);
-      if (kind == 1) set_error("links_load: %s:%llu: empty line (the reference panics here)", path, ln);
-      else if (kind == 2) set_error("links_load: %s:%llu: fewer than three fields (the reference panics here)", path, ln);
-      else set_error("links_load: %s:%llu: line longer than 2 GiB", path, ln);
-      return LXY_ERR_ARG;
+    P_CUDA(cudaMemsetAsync(dF, 0, sizeof(Flags), st));
+    P_CUDA(cudaMemsetAsync(&dF->err, 0xFF, 8, st));
+    ParseArgs PA{d_text, T, d_nl, NL, lines, 0x9e3779b97f4a7c15ull * (uint64_t)attempt,
+                 attempt == 0 ? hmask0 : ~0ull, d_h, d_tl, d_val, &dF->err, &dF->slow_cnt, d_slow_off, d_slow_len,
+                 d_slow_line, &dF->ndata};
+    k_parse_lines<<<line_grid, kThreads, 0, st>>>(PA);
+    // the name table is filled on the assumption that the file is well formed (checked right after)
+    bool first_pass = true;
+    for (;;) {
+      P_CUDA(cudaMemsetAsync(NT.keys, 0, (size_t)cap * 8, st));
+      P_CUDA(cudaMemsetAsync(NT.first, 0xFF, (size_t)cap * 4, st));
+      P_CUDA(cudaMemsetAsync(&dF->used, 0, 4, st));
+      P_CUDA(cudaMemsetAsync(&dF->overflow, 0, 8, st));  // overflow + collision
+      k_names_insert<<<tok_grid, kThreads, 0, st>>>(d_h, d_tl, ntok, NT.keys, NT.first, cap - 1, d_tok_slot, &dF->used,
+                                                    cap / 2, &dF->overflow);
+      k_names_verify<<<tok_grid, kThreads, 0, st>>>(d_text, d_nl, d_tl, ntok, NT.first, d_tok_slot, &dF->overflow,
+                                                    &dF->collision);
+      P_CUDA(cudaMemcpyAsync(&hF, dF, sizeof(Flags), cudaMemcpyDeviceToHost, st));
+      P_CUDA(cudaStreamSynchronize(st));
+      if (first_pass) {
+        first_pass = false;
+        if (hF.err != ~0ull) {
+          const unsigned long long ln = (hF.err >> 2) + 1;
+          const int kind = (int)(hF.err & 3);
+          if (kind == 1) set_error("links_load: %s:%llu: empty line (the reference panics here)", path, ln);
+          else if (kind == 2) set_error("links_load: %s:%llu: fewer than three fields (the reference panics here)", path, ln);
+          else set_error("links_load: %s:%llu: line longer than 2 GiB", path, ln);
+          return LXY_ERR_ARG;
+        }
+        stt.records = (int64_t)hF.ndata;
+        if (hF.ndata == 0) { set_error("links_load: Loaded empty links object..."); return LXY_ERR_STATE; }
+        stt.slow_values = (int32_t)hF.slow_cnt;
+      }
+      if (!hF.overflow) break;
+      if (cap >= (1u << 31)) { set_error("links_load: more than 2^30 distinct names"); return LXY_ERR_RANGE; }
+      cap = cap >= (1u << 28) ? cap * 2 : cap * 8;  // grown until the names fill at most half of it
+      LXY_TRY(A.open(name_table_bytes(cap)));
+      P_SIZED(name_table_take(A, cap, NT));
     }
-    stt.records = (int64_t)hF.ndata;
-    if (hF.ndata == 0) { set_error("links_load: Loaded empty links object..."); return LXY_ERR_STATE; }
-    stt.slow_values = (int32_t)hF.slow_cnt;
     if (hF.slow_cnt) {  // tokens outside the exact fast path: the host loader's own function decides
       const uint32_t k = hF.slow_cnt;
       std::vector<int64_t> off(k);
       std::vector<uint32_t> len(k);
       std::vector<double> v(k);
-      P_CUDA(cudaMemcpyAsync(off.data(), S.slow_off.p, (size_t)k * 8, cudaMemcpyDeviceToHost, S.st));
-      P_CUDA(cudaMemcpyAsync(len.data(), S.slow_len.p, (size_t)k * 4, cudaMemcpyDeviceToHost, S.st));
-      P_CUDA(cudaStreamSynchronize(S.st));
-      for (uint32_t q = 0; q < k; ++q) v[q] = parse_float_or_zero(text.data() + off[q], len[q]);
-      LXY_TRY(S.slow_val.reserve((size_t)k * 8));
-      P_CUDA(cudaMemcpyAsync(S.slow_val.p, v.data(), (size_t)k * 8, cudaMemcpyHostToDevice, S.st));
-      k_scatter_vals<<<(k + 255) / 256, 256, 0, S.st>>>(S.slow_line.as<uint32_t>(), S.slow_val.as<double>(), k,
-                                                         S.val.as<double>());
-      P_CUDA(cudaStreamSynchronize(S.st));  // v must outlive the copy
+      P_CUDA(cudaMemcpyAsync(off.data(), d_slow_off, (size_t)k * 8, cudaMemcpyDeviceToHost, st));
+      P_CUDA(cudaMemcpyAsync(len.data(), d_slow_len, (size_t)k * 4, cudaMemcpyDeviceToHost, st));
+      P_CUDA(cudaStreamSynchronize(st));
+      for (uint32_t q = 0; q < k; ++q) v[q] = parse_float_or_zero(text + off[q], len[q]);
+      P_CUDA(cudaMemcpyAsync(d_slow_val, v.data(), (size_t)k * 8, cudaMemcpyHostToDevice, st));
+      k_scatter_vals<<<(k + 255) / 256, 256, 0, st>>>(d_slow_line, d_slow_val, k, d_val);
+      P_CUDA(cudaStreamSynchronize(st));  // v must outlive the copy
     }
-    // name table, grown until the distinct names fill at most half of it
-    bool collided = false;
-    for (;;) {
-      LXY_TRY(S.nkeys.reserve((size_t)cap * 8));
-      LXY_TRY(S.nfirst.reserve((size_t)cap * 4));
-      P_CUDA(cudaMemsetAsync(S.nkeys.p, 0, (size_t)cap * 8, S.st));
-      P_CUDA(cudaMemsetAsync(S.nfirst.p, 0xFF, (size_t)cap * 4, S.st));
-      P_CUDA(cudaMemsetAsync(&dF->used, 0, 4, S.st));
-      P_CUDA(cudaMemsetAsync(&dF->overflow, 0, 8, S.st));  // overflow + collision
-      k_names_insert<<<tok_grid, kThreads, 0, S.st>>>(S.h.as<uint64_t>(), S.tl.as<uint32_t>(), ntok,
-                                                      S.nkeys.as<unsigned long long>(), S.nfirst.as<uint32_t>(), cap - 1,
-                                                      S.tok_slot.as<uint32_t>(), &dF->used, cap / 2, &dF->overflow);
-      P_CUDA(cudaMemcpyAsync(&hF, dF, sizeof(Flags), cudaMemcpyDeviceToHost, S.st));
-      P_CUDA(cudaStreamSynchronize(S.st));
-      if (!hF.overflow) break;
-      if (cap >= (1u << 31)) { set_error("links_load: more than 2^30 distinct names"); return LXY_ERR_RANGE; }
-      cap = cap >= (1u << 28) ? cap * 2 : cap * 8;
-    }
-    k_names_verify<<<tok_grid, kThreads, 0, S.st>>>(d_text, S.nl_pos.as<int64_t>(), S.tl.as<uint32_t>(), ntok,
-                                                    S.nfirst.as<uint32_t>(), S.tok_slot.as<uint32_t>(), &dF->collision);
-    P_CUDA(cudaMemcpyAsync(&hF, dF, sizeof(Flags), cudaMemcpyDeviceToHost, S.st));
-    P_CUDA(cudaStreamSynchronize(S.st));
-    collided = hF.collision != 0;
-    if (!collided) { N = hF.used; break; }
+    if (!hF.collision) { N = hF.used; break; }
   }
 
   // 4. ids = rank of a name's first token
-  LXY_TRY(S.lf.reserve((size_t)N * 4 + 4));
-  LXY_TRY(S.ls.reserve((size_t)N * 4 + 4));
-  LXY_TRY(S.slot_id.reserve((size_t)cap * 4));
-  LXY_TRY(S.name_off.reserve((size_t)N * 8));
-  LXY_TRY(S.name_len.reserve((size_t)N * 4));
-  P_CUDA(cudaMemsetAsync(&dF->cnt, 0, 4, S.st));
-  k_collect_slots<<<(cap + kThreads - 1) / kThreads, kThreads, 0, S.st>>>(S.nkeys.as<unsigned long long>(),
-                                                                         S.nfirst.as<uint32_t>(), cap, S.lf.as<uint32_t>(),
-                                                                         S.ls.as<uint32_t>(), &dF->cnt);
-  LXY_TRY(sort_by_first(S, N));
-  k_assign_ids<<<(N + kThreads - 1) / kThreads, kThreads, 0, S.st>>>(S.lf2.as<uint32_t>(), S.ls2.as<uint32_t>(), N,
-                                                                    S.nl_pos.as<int64_t>(), S.tl.as<uint32_t>(),
-                                                                    S.slot_id.as<uint32_t>(), S.name_off.as<int64_t>(),
-                                                                    S.name_len.as<uint32_t>());
+  P_CUDA(cudaMemsetAsync(&dF->cnt, 0, 4, st));
+  k_collect_slots<<<(cap + kThreads - 1) / kThreads, kThreads, 0, st>>>(NT.keys, NT.first, cap, NT.sort.lf, NT.sort.ls, &dF->cnt);
+  LXY_TRY(sort_by_first(NT.sort, N, st));
+  k_assign_ids<<<(N + kThreads - 1) / kThreads, kThreads, 0, st>>>(NT.sort.lf2, NT.sort.ls2, N, d_nl, d_tl, NT.slot_id,
+                                                                  NT.name_off, NT.name_len);
   std::vector<int64_t> noff(N);
   std::vector<uint32_t> nlen(N);
-  P_CUDA(cudaMemcpyAsync(noff.data(), S.name_off.p, (size_t)N * 8, cudaMemcpyDeviceToHost, S.st));
-  P_CUDA(cudaMemcpyAsync(nlen.data(), S.name_len.p, (size_t)N * 4, cudaMemcpyDeviceToHost, S.st));
+  P_CUDA(cudaMemcpyAsync(noff.data(), NT.name_off, (size_t)N * 8, cudaMemcpyDeviceToHost, st));
+  P_CUDA(cudaMemcpyAsync(nlen.data(), NT.name_len, (size_t)N * 4, cudaMemcpyDeviceToHost, st));
 
-  // 5. pairs: first / last data line of every (lo, hi)
+  // stage C / 5. pairs: first / last data line of every (lo, hi)
   const uint64_t max_pairs = std::min<uint64_t>((uint64_t)stt.records, (uint64_t)N * ((uint64_t)N + 1) / 2);
   const uint32_t pcap = pow2_at_least(2 * max_pairs);
-  LXY_TRY(S.pkeys.reserve((size_t)pcap * 8));
-  LXY_TRY(S.pfirst.reserve((size_t)pcap * 4));
-  LXY_TRY(S.plast.reserve((size_t)pcap * 4));
-  P_CUDA(cudaMemsetAsync(S.pkeys.p, 0, (size_t)pcap * 8, S.st));
-  P_CUDA(cudaMemsetAsync(S.pfirst.p, 0xFF, (size_t)pcap * 4, S.st));
-  P_CUDA(cudaMemsetAsync(S.plast.p, 0, (size_t)pcap * 4, S.st));
-  P_CUDA(cudaMemsetAsync(&dF->cnt, 0, 4, S.st));
-  P_CUDA(cudaMemsetAsync(&dF->overflow, 0, 4, S.st));
-  k_pairs_insert<<<line_grid, kThreads, 0, S.st>>>(S.tl.as<uint32_t>(), S.tok_slot.as<uint32_t>(), S.slot_id.as<uint32_t>(),
-                                                   (uint32_t)lines, S.pkeys.as<unsigned long long>(),
-                                                   S.pfirst.as<uint32_t>(), S.plast.as<uint32_t>(), pcap - 1, &dF->overflow);
-  LXY_TRY(S.lf.reserve((size_t)max_pairs * 4 + 4));
-  LXY_TRY(S.ls.reserve((size_t)max_pairs * 4 + 4));
-  k_collect_slots<<<(pcap + kThreads - 1) / kThreads, kThreads, 0, S.st>>>(S.pkeys.as<unsigned long long>(),
-                                                                          S.pfirst.as<uint32_t>(), pcap, S.lf.as<uint32_t>(),
-                                                                          S.ls.as<uint32_t>(), &dF->cnt);
-  P_CUDA(cudaMemcpyAsync(&hF, dF, sizeof(Flags), cudaMemcpyDeviceToHost, S.st));
-  P_CUDA(cudaStreamSynchronize(S.st));
+  LXY_TRY(A.open(r256((size_t)pcap * 8) + 2 * r256((size_t)pcap * 4) + sort_bytes((uint32_t)max_pairs)));
+  unsigned long long* d_pkeys = A.take<unsigned long long>(pcap);
+  uint32_t* d_pfirst = A.take<uint32_t>(pcap);
+  uint32_t* d_plast = A.take<uint32_t>(pcap);
+  SortBufs PS;
+  P_SIZED(d_pkeys && d_pfirst && d_plast && sort_take(A, (uint32_t)max_pairs, PS));
+  P_CUDA(cudaMemsetAsync(d_pkeys, 0, (size_t)pcap * 8, st));
+  P_CUDA(cudaMemsetAsync(d_pfirst, 0xFF, (size_t)pcap * 4, st));
+  P_CUDA(cudaMemsetAsync(d_plast, 0, (size_t)pcap * 4, st));
+  P_CUDA(cudaMemsetAsync(&dF->cnt, 0, 4, st));
+  P_CUDA(cudaMemsetAsync(&dF->overflow, 0, 4, st));
+  k_pairs_insert<<<line_grid, kThreads, 0, st>>>(d_tl, d_tok_slot, NT.slot_id, (uint32_t)lines, d_pkeys, d_pfirst, d_plast,
+                                                 pcap - 1, &dF->overflow);
+  k_collect_slots<<<(pcap + kThreads - 1) / kThreads, kThreads, 0, st>>>(d_pkeys, d_pfirst, pcap, PS.lf, PS.ls, &dF->cnt);
+  P_CUDA(cudaMemcpyAsync(&hF, dF, sizeof(Flags), cudaMemcpyDeviceToHost, st));
+  P_CUDA(cudaStreamSynchronize(st));
   if (hF.overflow) { set_error("links_load: pair table overflow (internal)"); return LXY_ERR_STATE; }
   const uint32_t M = hF.cnt;
-  LXY_TRY(sort_by_first(S, M));
-  LXY_TRY(out.a.reserve((size_t)M * 4 + 4));
-  LXY_TRY(out.b.reserve((size_t)M * 4 + 4));
-  LXY_TRY(out.w.reserve((size_t)M * 8 + 8));
-  k_pairs_emit<<<(M + kThreads - 1) / kThreads, kThreads, 0, S.st>>>(S.ls2.as<uint32_t>(), M, S.pkeys.as<unsigned long long>(),
-                                                                    S.plast.as<uint32_t>(), S.val.as<double>(),
-                                                                    out.a.as<uint32_t>(), out.b.as<uint32_t>(), out.w.as<double>());
-  P_CUDA(cudaEventRecord(S.ev[2], S.st));
-  P_CUDA(cudaStreamSynchronize(S.st));
+  LXY_TRY(sort_by_first(PS, M, st));
+  {
+    const size_t ab = r256((size_t)M * 4 + 4);
+    cudaError_t e = cudaMalloc(&out.slab, 2 * ab + (size_t)M * 8 + 8);
+    if (e != cudaSuccess) {
+      (void)cudaGetLastError();
+      out.slab = nullptr;
+      set_error("links_load: cudaMalloc of the records failed: %s", cudaGetErrorString(e));
+      return LXY_ERR_NOMEM;
+    }
+    out.a = reinterpret_cast<uint32_t*>(out.slab);
+    out.b = reinterpret_cast<uint32_t*>((char*)out.slab + ab);
+    out.w = reinterpret_cast<double*>((char*)out.slab + 2 * ab);
+  }
+  k_pairs_emit<<<(M + kThreads - 1) / kThreads, kThreads, 0, st>>>(PS.ls2, M, d_pkeys, d_plast, d_val, out.a, out.b, out.w);
+  P_CUDA(cudaEventRecord(H.ev[2], st));
+  P_CUDA(cudaStreamSynchronize(st));
   P_CUDA(cudaGetLastError());
 
   out.n = (int32_t)N;
   out.m = (int64_t)M;
   out.names.resize(N);
-  for (uint32_t i = 0; i < N; ++i) out.names[i].assign(text.data() + noff[i], nlen[i]);
+  for (uint32_t i = 0; i < N; ++i) out.names[i].assign(text + noff[i], nlen[i]);
   stt.names = (int32_t)N;
   stt.pairs = (int64_t)M;
-  cudaEventElapsedTime(&stt.ms_h2d, S.ev[0], S.ev[1]);
-  cudaEventElapsedTime(&stt.ms_device, S.ev[1], S.ev[2]);
+  cudaEventElapsedTime(&stt.ms_h2d, H.ev[0], H.ev[1]);
+  cudaEventElapsedTime(&stt.ms_device, H.ev[1], H.ev[2]);
   stt.ms_total = (float)ms_since(t_start);
   if (stats) *stats = stt;
   return LXY_OK;
@@ -701,9 +800,9 @@ int to_host_table(const Parsed& P, bool with_records, lxy_links** out) {
     l->a.resize((size_t)P.m);
     l->b.resize((size_t)P.m);
     l->w.resize((size_t)P.m);
-    cudaError_t e = cudaMemcpy(l->a.data(), P.a.p, (size_t)P.m * 4, cudaMemcpyDeviceToHost);
-    if (e == cudaSuccess) e = cudaMemcpy(l->b.data(), P.b.p, (size_t)P.m * 4, cudaMemcpyDeviceToHost);
-    if (e == cudaSuccess) e = cudaMemcpy(l->w.data(), P.w.p, (size_t)P.m * 8, cudaMemcpyDeviceToHost);
+    cudaError_t e = cudaMemcpy(l->a.data(), P.a, (size_t)P.m * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(l->b.data(), P.b, (size_t)P.m * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(l->w.data(), P.w, (size_t)P.m * 8, cudaMemcpyDeviceToHost);
     if (e != cudaSuccess) {
       set_error("links_load: device -> host copy failed: %s", cudaGetErrorString(e));
       delete l;
@@ -737,7 +836,7 @@ int lxy_ctx_load_links(lxy_ctx* c, const char* path, int32_t kind, lxy_links** o
   if (out || kind == 1) LXY_TRY(to_host_table(P, true, &l));
   int rc;
   if (kind == 0) {  // the device records feed the link store as they are
-    rc = lxy_ctx_set_links_dev(c, P.n, P.m, P.a.as<uint32_t>(), P.b.as<uint32_t>(), P.w.as<double>());
+    rc = lxy_ctx_set_links_dev(c, P.n, P.m, P.a, P.b, P.w);
   } else {          // the phasing store is built from host arrays (deduplicated pairs: small)
     rc = lxy_ctx_set_phase_links(c, P.n, P.m, l->a.data(), l->b.data(), l->w.data());
   }
