@@ -279,6 +279,14 @@ int lxy_eval_scaffolding(lxy_ctx* ctx, const int32_t* perm, const int32_t* key_r
                          int32_t P, double* out);
 int lxy_eval_phasing(lxy_ctx* ctx, const uint8_t* genes, const uint8_t* key, int32_t n, int32_t P,
                      double* out);
+/* lxy_eval_phasing_dev = EvalPhasingDev (phase.go:266-325), the metric `lxy phase infer` logs
+ * (phase/cmd.go:152): index[i] is the integer after '_' in the name of block i (Atoi of
+ * Split(name, "_")[1], :279-280; 0 when it does not parse), the n blocks are those present in both
+ * the phasing and the key (the others are skipped, :289-299).  out[P][3] = matches / comparisons over
+ * all ordered pairs, over the pairs whose indices differ by <= 2, and by <= 9 (i == j included).
+ * O(n log n + P n) instead of the reference's O(P n^2), same numbers.  n <= 2^26. */
+int lxy_eval_phasing_dev(lxy_ctx* ctx, const uint8_t* genes, const uint8_t* key, const int32_t* index,
+                         int32_t n, int32_t P, double* out);
 
 /* ---- the two workflows, file to file -----------------------------------------------------------
  * lxy_scaffold_file = Scaffold (scaff.go:68-141) as `lxy scaff infer` calls it (scaff/cmd.go:135-202,

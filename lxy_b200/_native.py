@@ -34,6 +34,7 @@ SYMBOLS = [
     "lxy_links_value", "lxy_links_records", "lxy_ctx_set_links_from",
     "lxy_links_load_gpu", "lxy_ctx_load_links",
     "lxy_scaffold_file", "lxy_phase_file", "lxy_eval_scaffolding", "lxy_eval_phasing",
+    "lxy_eval_phasing_dev",
 ]
 
 ACC_AUTO, ACC_F64, ACC_INT = 0, 1, 2
@@ -180,6 +181,7 @@ def lib():
         "lxy_phase_file": (i32, [C.c_char_p, C.c_char_p, i32, C.POINTER(GaParams), i32, C.POINTER(f64)]),
         "lxy_eval_scaffolding": (i32, [vp, vp, vp, i32, i32, vp]),
         "lxy_eval_phasing": (i32, [vp, vp, vp, i32, i32, vp]),
+        "lxy_eval_phasing_dev": (i32, [vp, vp, vp, vp, i32, i32, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -565,4 +567,14 @@ def eval_phasing(ctx, genes, key):
     genes, key = _c(genes, np.uint8), _c(key, np.uint8)
     out = np.zeros((genes.shape[0], 4))
     _check(lib().lxy_eval_phasing(ctx._h, _p(genes), _p(key), genes.shape[1], genes.shape[0], _p(out)))
+    return out
+
+
+def eval_phasing_dev(ctx, genes, key, index):
+    """EvalPhasingDev (phase.go:266-325): -> [P][3] (all pairs, index distance <= 2, <= 9)."""
+    genes, key, index = _c(genes, np.uint8), _c(key, np.uint8), _c(index, np.int32)
+    if genes.ndim != 2 or genes.shape[1] != len(key) or len(index) != len(key):
+        raise ValueError("genes must be [P][n]; key and index [n]")
+    out = np.zeros((genes.shape[0], 3))
+    _check(lib().lxy_eval_phasing_dev(ctx._h, _p(genes), _p(key), _p(index), genes.shape[1], genes.shape[0], _p(out)))
     return out

@@ -16,6 +16,19 @@
 //                    are 2 * #{i : x_i == x_(i+d)}.  The reference adds the comparisons at distance
 //                    1, 2 AND 3 to one counter and leaves the other two at zero (phase.go:225-235);
 //                    that is reproduced, since these are the numbers its callers log.
+//   EvalPhasingDev   /root/reference/src/lxy/phase/phase.go:266-325, the metric `lxy phase infer`
+//                    logs (phase/cmd.go:152).  As above over all ordered pairs, plus the pairs whose
+//                    name indices (the integer after '_' in a block name, :279-280) differ by at most
+//                    2 and at most 9.  With the blocks sorted by index, the partners of block s are
+//                    one contiguous range [lo, hi) per window (two binary searches, done once per
+//                    call), and with S = prefix count of x along that order
+//                       matches_w = sum_s (x_s ? S[hi]-S[lo] : (hi-lo) - (S[hi]-S[lo]))
+//                    so a candidate costs O(n), the whole call O(n log n + P n), in exact integers
+//                    (duplicate or unparsable indices - Atoi errors read as 0 - included).
+#include <cub/device/device_radix_sort.cuh>
+
+#include <algorithm>
+
 #include "common.cuh"
 #include "device_utils.cuh"
 
@@ -110,6 +123,94 @@ __global__ void __launch_bounds__(256) k_eval_phase(const uint8_t* __restrict__ 
   }
 }
 
+__global__ void k_evdev_iota(uint32_t* __restrict__ out, int32_t n) {
+  const int32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (uint32_t)i;
+}
+
+// EvalPhasingDev, step 1: partner ranges of every sorted position for the two windows; the comparison
+// counts (candidate independent) are summed into cmp[0] (<= 2) and cmp[1] (<= 9).
+__global__ void __launch_bounds__(256) k_evdev_ranges(const int32_t* __restrict__ si, int32_t n, uint32_t* __restrict__ lo2,
+                                                      uint32_t* __restrict__ hi2, uint32_t* __restrict__ lo9,
+                                                      uint32_t* __restrict__ hi9, unsigned long long* __restrict__ cmp) {
+  __shared__ unsigned long long s_red[8];
+  const int32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned long long c2 = 0, c9 = 0;
+  if (s < n) {
+    const long long v = si[s];
+    auto lower = [&](long long x) {  // first position with si >= x
+      int32_t a = 0, b = n;
+      while (a < b) { const int32_t m = (a + b) >> 1; if ((long long)si[m] < x) a = m + 1; else b = m; }
+      return (uint32_t)a;
+    };
+    const uint32_t l2 = lower(v - 2), h2 = lower(v + 3), l9 = lower(v - 9), h9 = lower(v + 10);
+    lo2[s] = l2; hi2[s] = h2; lo9[s] = l9; hi9[s] = h9;
+    c2 = h2 - l2;
+    c9 = h9 - l9;
+  }
+  c2 = block_sum(c2, s_red);
+  c9 = block_sum(c9, s_red);
+  if (threadIdx.x == 0) { atomicAdd(cmp, c2); atomicAdd(cmp + 1, c9); }
+}
+
+// step 2: one CTA per phasing; S (n + 1 prefix counts, this CTA's slice of scratch) is written and then
+// read back by the same CTA.
+__global__ void __launch_bounds__(512) k_evdev_score(const uint8_t* __restrict__ genes, const uint8_t* __restrict__ key,
+                                                     const uint32_t* __restrict__ order, int32_t n,
+                                                     const uint32_t* __restrict__ lo2, const uint32_t* __restrict__ hi2,
+                                                     const uint32_t* __restrict__ lo9, const uint32_t* __restrict__ hi9,
+                                                     const unsigned long long* __restrict__ cmp, uint32_t* __restrict__ scratch,
+                                                     double* __restrict__ out) {
+  __shared__ unsigned long long s_red[16];
+  __shared__ uint32_t s_w[16];
+  __shared__ uint32_t s_carry;
+  const uint8_t* g = genes + (size_t)blockIdx.x * n;
+  uint32_t* S = scratch + (size_t)blockIdx.x * ((size_t)n + 1);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) s_carry = 0;
+  __syncthreads();
+  for (int32_t base = 0; base < n; base += 512) {
+    const int32_t s = base + threadIdx.x;
+    uint32_t x = 0;
+    if (s < n) { const uint32_t i = order[s]; x = (g[i] != 0) != (key[i] != 0); }
+    uint32_t incl = x;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t up = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += up;
+    }
+    if (lane == 31) s_w[warp] = incl;
+    __syncthreads();
+    uint32_t wb = 0, all = 0;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) { const uint32_t t = s_w[k]; if (k < warp) wb += t; all += t; }
+    const uint32_t carry = s_carry;
+    if (s < n) S[s] = carry + wb + incl - x;
+    __syncthreads();
+    if (threadIdx.x == 0) s_carry = carry + all;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) S[n] = s_carry;
+  __syncthreads();
+  unsigned long long m2 = 0, m9 = 0;
+  for (int32_t s = threadIdx.x; s < n; s += 512) {
+    const uint32_t x = S[s + 1] - S[s];
+    const uint32_t l2 = lo2[s], h2 = hi2[s], l9 = lo9[s], h9 = hi9[s];
+    const uint32_t o2 = S[h2] - S[l2], o9 = S[h9] - S[l9];
+    m2 += x ? o2 : (h2 - l2) - o2;
+    m9 += x ? o9 : (h9 - l9) - o9;
+  }
+  m2 = block_sum(m2, s_red);
+  m9 = block_sum(m9, s_red);
+  if (threadIdx.x == 0) {
+    const double N = (double)n, c1 = (double)S[n], c0 = N - c1;
+    double* o = out + 3 * (size_t)blockIdx.x;
+    o[0] = (c0 * c0 + c1 * c1) / (N * N);
+    o[1] = (double)m2 / (double)cmp[0];
+    o[2] = (double)m9 / (double)cmp[1];
+  }
+}
+
 __global__ void k_check_perm(const int32_t* __restrict__ key_rank, int32_t n, int32_t* __restrict__ seen,
                              int* __restrict__ flag) {
   const int32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -178,6 +279,54 @@ int lxy_eval_phasing(lxy_ctx* c, const uint8_t* genes, const uint8_t* key, int32
   LXY_CUDA(cudaGetLastError());
   LXY_CUDA(cudaMemcpyAsync(out, c->d_out.p, 32 * (size_t)P, cudaMemcpyDeviceToHost, st));
   LXY_CUDA(cudaStreamSynchronize(st));
+  return LXY_OK;
+}
+
+int lxy_eval_phasing_dev(lxy_ctx* c, const uint8_t* genes, const uint8_t* key, const int32_t* index, int32_t n,
+                         int32_t P, double* out) {
+  if (!c) { set_error("null context"); return LXY_ERR_ARG; }
+  std::lock_guard<std::mutex> lk(c->mu);
+  LXY_CUDA(cudaSetDevice(c->cfg.device));
+  if (n <= 0 || P < 0 || (P > 0 && (!genes || !key || !index || !out))) { set_error("eval_phasing_dev: bad argument"); return LXY_ERR_ARG; }
+  if (n > (1 << 26)) { set_error("eval_phasing_dev: n > 2^26 (the pair counts would leave the exact range of a double)"); return LXY_ERR_RANGE; }
+  if (P == 0) return LXY_OK;
+  cudaStream_t st = c->stream;
+  const size_t N = (size_t)n;
+  // index -> sorted index + original position
+  LXY_TRY(c->d_tmp0.reserve(4 * N * 4));      // index in, index sorted, iota in, order out
+  LXY_TRY(c->d_tmp1.reserve(4 * N * 4));      // lo2, hi2, lo9, hi9
+  LXY_TRY(c->d_tmp2.reserve(N));              // key
+  LXY_TRY(c->d_flag.reserve(64));
+  int32_t* d_idx = c->d_tmp0.as<int32_t>();
+  int32_t* d_si = d_idx + N;
+  uint32_t* d_iota = reinterpret_cast<uint32_t*>(d_idx + 2 * N);
+  uint32_t* d_order = d_iota + N;
+  uint32_t* d_lo2 = c->d_tmp1.as<uint32_t>();
+  unsigned long long* d_cmp = c->d_flag.as<unsigned long long>();
+  LXY_CUDA(cudaMemsetAsync(d_cmp, 0, 16, st));
+  LXY_CUDA(cudaMemcpyAsync(d_idx, index, 4 * N, cudaMemcpyHostToDevice, st));
+  LXY_CUDA(cudaMemcpyAsync(c->d_tmp2.p, key, N, cudaMemcpyHostToDevice, st));
+  k_evdev_iota<<<(n + 255) / 256, 256, 0, st>>>(d_iota, n);
+  size_t tmp = 0;
+  LXY_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp, (const int32_t*)d_idx, d_si, (const uint32_t*)d_iota, d_order, n, 0, 32, st));
+  LXY_TRY(c->d_tmp3.reserve(tmp + 16));
+  LXY_CUDA(cub::DeviceRadixSort::SortPairs(c->d_tmp3.p, tmp, (const int32_t*)d_idx, d_si, (const uint32_t*)d_iota, d_order, n, 0, 32, st));
+  k_evdev_ranges<<<(n + 255) / 256, 256, 0, st>>>(d_si, n, d_lo2, d_lo2 + N, d_lo2 + 2 * N, d_lo2 + 3 * N, d_cmp);
+  LXY_CUDA(cudaGetLastError());
+  // candidates in batches bounded by the prefix-count scratch (256 MB)
+  const int32_t batch = (int32_t)std::max<size_t>(1, std::min<size_t>((size_t)P, ((size_t)64 << 20) / (N + 1)));
+  LXY_TRY(c->d_genes.reserve(N * (size_t)batch));
+  LXY_TRY(c->d_partial.reserve(4 * (N + 1) * (size_t)batch));
+  LXY_TRY(c->d_out.reserve(24 * (size_t)batch));
+  for (int32_t p0 = 0; p0 < P; p0 += batch) {
+    const int32_t pb = std::min(batch, P - p0);
+    LXY_CUDA(cudaMemcpyAsync(c->d_genes.p, genes + (size_t)p0 * N, N * (size_t)pb, cudaMemcpyHostToDevice, st));
+    k_evdev_score<<<pb, 512, 0, st>>>(c->d_genes.as<uint8_t>(), c->d_tmp2.as<uint8_t>(), d_order, n, d_lo2, d_lo2 + N,
+                                      d_lo2 + 2 * N, d_lo2 + 3 * N, d_cmp, c->d_partial.as<uint32_t>(), c->d_out.as<double>());
+    LXY_CUDA(cudaGetLastError());
+    LXY_CUDA(cudaMemcpyAsync(out + 3 * (size_t)p0, c->d_out.p, 24 * (size_t)pb, cudaMemcpyDeviceToHost, st));
+    LXY_CUDA(cudaStreamSynchronize(st));
+  }
   return LXY_OK;
 }
 

@@ -457,3 +457,32 @@ def Phase(links, outPath, iterations, optReportFreq=0.01, device=0, seed=None, p
     phasing = links.DecodePhasing(gene)
     writePhasing(phasing, outPath)
     return phasing
+
+
+# ---- solution-quality metrics with the reference's signatures (maps / lists of names) ----------------
+def _atoi_or_zero(tok):                               # strconv.Atoi with the error ignored (phase.go:279-280)
+    body = tok[1:] if tok[:1] in ("+", "-") else tok
+    if not body or not all("0" <= ch <= "9" for ch in body):
+        return 0
+    return max(-2**31, min(2**31 - 1, int(tok)))
+
+
+def EvalPhasingDev(phasing, key, device=0):
+    """EvalPhasingDev(phasing, key map[string]bool) (phase.go:266-325) on the device: (score over all
+    ordered pairs, over pairs whose name indices differ by <= 2, by <= 9).  Names missing from `key`
+    are skipped as in the reference (:289-299); a name without '_' makes the reference panic (:279) and
+    raises here."""
+    names = [nm for nm in phasing if nm in key]
+    if not names:
+        return float("nan"), float("nan"), float("nan")                  # 0/0 in the reference
+    index = []
+    for nm in names:
+        parts = nm.split("_")
+        if len(parts) < 2:
+            raise IndexError(f"variant block name {nm!r} has no '_' (the reference panics here)")
+        index.append(_atoi_or_zero(parts[1]))
+    genes = np.array([[1 if phasing[nm] else 0 for nm in names]], np.uint8)
+    keyb = np.array([1 if key[nm] else 0 for nm in names], np.uint8)
+    with N.Context(device) as ctx:
+        out = N.eval_phasing_dev(ctx, genes, keyb, np.array(index, np.int32))
+    return float(out[0, 0]), float(out[0, 1]), float(out[0, 2])

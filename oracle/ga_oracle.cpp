@@ -213,4 +213,31 @@ void lxyo_eval_phasing(const uint8_t* phasing, const uint8_t* key, int n, double
             (neighbor_comparisons + second_neighbor_comparisons + third_neighbor_comparisons);
 }
 
+// EvalPhasingDev (src/lxy/phase/phase.go:266-325), the metric `lxy phase infer` logs (phase/cmd.go:152).
+// The reference ranges over two maps keyed by variant-block name; `index[i]` stands for
+// Atoi(Split(name_i, "_")[1]) (:279-280) and the n entries are the names present in BOTH maps (the
+// others are skipped at :289-299 before anything is counted).  out3 = (all ordered pairs, pairs whose
+// indices differ by <= 2, by <= 9), each matches / comparisons, i == j included.
+void lxyo_eval_phasing_dev(const uint8_t* phasing, const uint8_t* key, const int32_t* index, int n, double* out3) {
+  double matches = 0, comparisons = 0, matches300k = 0, matches1mbp = 0, comparisons300k = 0, comparisons1mbp = 0;
+  for (int i = 0; i < n; ++i)
+    for (int j = 0; j < n; ++j) {
+      long long inddiff = (long long)index[i] - (long long)index[j];
+      if (inddiff < 0) inddiff = inddiff * -1;
+      const bool is3k = inddiff <= 2, is1mbp = inddiff <= 9;
+      const bool pmatch = (phasing[i] != 0) == (phasing[j] != 0), kmatch = (key[i] != 0) == (key[j] != 0);
+      comparisons += 1;
+      if (is3k) comparisons300k += 1;
+      if (is1mbp) comparisons1mbp += 1;
+      if ((pmatch && kmatch) || (!pmatch && !kmatch)) {
+        matches += 1;
+        if (is3k) matches300k += 1;
+        if (is1mbp) matches1mbp += 1;
+      }
+    }
+  out3[0] = matches / comparisons;
+  out3[1] = matches300k / comparisons300k;
+  out3[2] = matches1mbp / comparisons1mbp;
+}
+
 }  // extern "C"

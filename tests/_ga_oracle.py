@@ -29,6 +29,7 @@ def _load():
     lib.lxyo_ga_select.argtypes = [i32, i32, vp, vp, vp]
     lib.lxyo_eval_scaffolding.argtypes = [vp, vp, i32, vp]
     lib.lxyo_eval_phasing.argtypes = [vp, vp, i32, vp]
+    lib.lxyo_eval_phasing_dev.argtypes = [vp, vp, vp, i32, vp]
     return lib
 
 
@@ -89,4 +90,13 @@ def eval_phasing(phasing, key):
     phasing, key = np.ascontiguousarray(phasing, np.uint8), np.ascontiguousarray(key, np.uint8)
     out = np.zeros(4)
     _lib.lxyo_eval_phasing(_p(phasing), _p(key), len(phasing), _p(out))
+    return out
+
+
+def eval_phasing_dev(phasing, key, index):
+    """EvalPhasingDev (phase.go:266-325); index[i] = the integer after '_' in the i-th block name."""
+    phasing, key = np.ascontiguousarray(phasing, np.uint8), np.ascontiguousarray(key, np.uint8)
+    index = np.ascontiguousarray(index, np.int32)
+    out = np.zeros(3)
+    _lib.lxyo_eval_phasing_dev(_p(phasing), _p(key), _p(index), len(phasing), _p(out))
     return out

@@ -54,3 +54,55 @@ def test_eval_phasing_matches_reference_loop(n, P, seed):
     want = np.stack([G.eval_phasing(g, key) for g in genes])
     assert np.array_equal(got, want, equal_nan=True)
     assert got[0, 0] == 1.0 and got[1, 0] == 1.0
+
+
+@pytest.mark.parametrize("n,P,seed,kind", [(1, 2, 1, "seq"), (2, 3, 2, "seq"), (7, 5, 3, "gaps"), (40, 10, 4, "seq"),
+                                           (300, 16, 5, "gaps"), (300, 4, 6, "dups"), (64, 3, 7, "zero"),
+                                           (257, 6, 8, "shuffled")])
+def test_eval_phasing_dev_matches_reference_loop(n, P, seed, kind):   # phase.go:266-325
+    rng = np.random.default_rng(seed)
+    key = rng.integers(0, 2, n).astype(np.uint8)
+    genes = rng.integers(0, 2, (P, n)).astype(np.uint8)
+    genes[0] = key
+    genes[1] = 1 - key
+    if kind == "seq":
+        index = np.arange(n)
+    elif kind == "gaps":                             # blocks missing from the key leave holes
+        index = np.cumsum(rng.integers(1, 6, n))
+    elif kind == "dups":                             # repeated indices (several chromosomes numbered alike)
+        index = rng.integers(0, 40, n)
+    elif kind == "zero":                             # names whose suffix does not parse: Atoi -> 0 for all
+        index = np.zeros(n, np.int64)
+    else:                                            # map iteration order is arbitrary in the reference
+        index = rng.permutation(n) - 100
+    index = index.astype(np.int32)
+    with N.Context(0) as ctx:
+        got = N.eval_phasing_dev(ctx, genes, key, index)
+    want = np.stack([G.eval_phasing_dev(g, key, index) for g in genes])
+    assert got.tolist() == want.tolist()
+    assert got[0].tolist() == [1.0, 1.0, 1.0] and got[1].tolist() == [1.0, 1.0, 1.0]
+
+
+def test_eval_phasing_dev_large_and_host_signature():
+    from lxy_b200 import host as H
+    n = 300_000                                      # config-5 size: 9e10 pairs in the reference's loop
+    rng = np.random.default_rng(9)
+    key = rng.integers(0, 2, n).astype(np.uint8)
+    flip = (rng.random(n) < 0.25).astype(np.uint8)
+    genes = np.stack([key, 1 - key, key ^ flip])
+    with N.Context(0) as ctx:
+        q = N.eval_phasing_dev(ctx, genes, key, np.arange(n, dtype=np.int32))
+    assert q[0].tolist() == [1.0, 1.0, 1.0] and q[1].tolist() == [1.0, 1.0, 1.0]
+    c1 = int(flip.sum())
+    assert q[2, 0] == (float(c1) ** 2 + float(n - c1) ** 2) / float(n) ** 2
+    assert 0.6 < q[2, 1] < 0.66 and 0.6 < q[2, 2] < 0.66          # 0.75^2 + 0.25^2 = 0.625 plus the i == j pairs
+    # the reference's map signature (names `chr_<index>`), blocks absent from the key skipped
+    names = [f"blk_{i}" for i in range(50)]
+    phasing = {nm: bool(rng.integers(0, 2)) for nm in names}
+    keym = {nm: bool(rng.integers(0, 2)) for nm in names[:45]}
+    keym["other_999"] = True
+    got = H.EvalPhasingDev(phasing, keym)
+    common = [nm for nm in phasing if nm in keym]
+    want = G.eval_phasing_dev([phasing[nm] for nm in common], [keym[nm] for nm in common],
+                              [int(nm.split("_")[1]) for nm in common])
+    assert list(got) == want.tolist()

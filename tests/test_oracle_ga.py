@@ -106,3 +106,28 @@ def test_children_and_select():
     order = G.select(s_pop, s_ch)
     allk = np.concatenate([s_pop, s_ch])
     assert order.tolist() == np.argsort(allk, kind="stable")[:P].tolist()
+
+
+def test_eval_phasing_dev_oracle_against_a_second_restatement():
+    """EvalPhasingDev (phase.go:266-325): the C++ oracle against an independent restatement over the
+    reference's own data shape (maps keyed by `name_<index>`, names missing from the key skipped)."""
+    import numpy as np
+    import _ga_oracle as G
+    rng = np.random.default_rng(21)
+    for n, extra in ((1, 0), (5, 2), (37, 5)):
+        phasing = {f"b_{3 * i}": bool(rng.integers(0, 2)) for i in range(n + extra)}
+        key = {nm: bool(rng.integers(0, 2)) for nm in list(phasing)[:n]}
+        m = c = m3 = c3 = m1 = c1 = 0.0
+        for i in phasing:                                           # :277-278
+            for j in phasing:
+                d = abs(int(i.split("_")[1]) - int(j.split("_")[1]))   # :279-285
+                if i not in key or j not in key:                    # :289-293
+                    continue
+                agree = (phasing[i] == phasing[j]) == (key[i] == key[j])   # :301-314
+                c += 1; c3 += d <= 2; c1 += d <= 9
+                if agree:
+                    m += 1; m3 += d <= 2; m1 += d <= 9
+        common = [nm for nm in phasing if nm in key]
+        got = G.eval_phasing_dev([phasing[nm] for nm in common], [key[nm] for nm in common],
+                                 [int(nm.split("_")[1]) for nm in common])
+        assert got.tolist() == [m / c, m3 / c3, m1 / c1]
