@@ -134,6 +134,24 @@ def LoadLinks(path):
     return l
 
 
+def LoadLinksDevice(path, device=0):
+    """LoadLinks with the text parsed on the GPU (lxy_links_load_gpu, lxy_b200/csrc/links_parse.cu):
+    the same Links object as LoadLinks(path) - ids by first appearance, the last row of a pair wins -
+    for files whose size makes the line-by-line host loop the longest step of a run."""
+    try:
+        t = N.NativeLinks(path, device=device)
+    except N.LxyError as e:
+        raise LinksError(str(e))
+    l = Links()
+    for name in t.Decode(range(t.Size())):
+        l.addKey(name)
+    a, b, w = t.records()
+    for x, y, v in zip(a.tolist(), b.tolist(), w.tolist()):
+        l.data.setdefault(x, {})[y] = v
+    t.close()
+    return l
+
+
 # ---------------------------------------------------------------------------------------------
 # genomes
 # ---------------------------------------------------------------------------------------------
@@ -486,3 +504,72 @@ def EvalPhasingDev(phasing, key, device=0):
     with N.Context(device) as ctx:
         out = N.eval_phasing_dev(ctx, genes, keyb, np.array(index, np.int32))
     return float(out[0, 0]), float(out[0, 1]), float(out[0, 2])
+
+
+def EvalScaffolding(scaff, key, device=0):
+    """EvalScaffolding(scaff, key []string) (scaff.go:329-384) on the device: (score, neighbour score).
+    The device metric is defined for a scaffolding that is a permutation of the key (what Scaffold
+    returns for the key's link set); anything else raises."""
+    rank = {nm: i for i, nm in enumerate(key)}
+    if len(rank) != len(key) or len(scaff) != len(key) or any(nm not in rank for nm in scaff):
+        raise ValueError("EvalScaffolding: the scaffolding must be a permutation of the key")
+    ids = np.array([[rank[nm] for nm in scaff]], np.int32)      # contig id := its index in the key
+    with N.Context(device) as ctx:
+        out = N.eval_scaffolding(ctx, ids, np.arange(len(key), dtype=np.int32))
+    return float(out[0, 0]), float(out[0, 1])
+
+
+def EvalPhasing(phasing, key, device=0):
+    """EvalPhasing(phasing, key []bool) (phase.go:211-263): (score, firstScore, secondScore, thirdScore)."""
+    with N.Context(device) as ctx:
+        out = N.eval_phasing(ctx, np.array([[1 if v else 0 for v in phasing]], np.uint8),
+                             np.array([1 if v else 0 for v in key], np.uint8))
+    return tuple(float(v) for v in out[0])
+
+
+def readPhasing(path):                                # phase.go:119-149: `name 0|1` per line
+    phasing = {}
+    with open(path) as f:
+        for line in f.read().splitlines():
+            arr = line.split(" ")
+            if len(arr) != 2 or arr[1] not in ("0", "1"):
+                raise ValueError("Tried to read phasing file with more than two haplotypes, not currently supported.")
+            phasing[arr[0]] = arr[1] == "1"
+    return phasing
+
+
+def ScaffoldInfer(linksPath, outputPrefix, keyPath, iterations=1000, optReportFreq=0.01, device=0, seed=None):
+    """`lxy scaff infer` (scaff/cmd.go:135-202) without the plots: LoadLinks (text parsed on the device),
+    Scaffold -> <prefix>.scaff.txt, EvalScaffolding -> <prefix>.qscore.txt (`score=%f;score_neighbor=%f`),
+    the intermediates' scores -> <prefix>.opt.txt (`iteration fitness qscore` per line).  Returns
+    (scaffolding, score, neighbour score)."""
+    links = LoadLinksDevice(linksPath, device=device)
+    key = ReadScaffolding(keyPath)
+    scaffolding, intermediates = Scaffold(links, outputPrefix + ".scaff.txt", iterations, optReportFreq,
+                                          device=device, seed=seed)
+    score, nscore = EvalScaffolding(scaffolding, key, device=device)
+    with open(outputPrefix + ".qscore.txt", "w") as f:
+        f.write("score=%f;score_neighbor=%f\n" % (score, nscore))
+    with open(outputPrefix + ".opt.txt", "w") as f:
+        if intermediates:                                           # one device call for all of them
+            rank = {nm: i for i, nm in enumerate(key)}
+            ids = np.array([[rank[nm] for nm in im.order] for im in intermediates], np.int32)
+            with N.Context(device) as ctx:
+                q = N.eval_scaffolding(ctx, ids, np.arange(len(key), dtype=np.int32))
+            for im, row in zip(intermediates, q):
+                f.write("%d %f %f\n" % (im.iteration, im.score, row[0]))
+    return scaffolding, score, nscore
+
+
+def PhaseInfer(linksPath, outpath, keyPath, iterations=1000, subruntag="", optReportFreq=0.01, device=0, seed=None):
+    """`lxy phase infer` (phase/cmd.go:114-165): LoadLinks, Phase -> <outpath>.<tag>.phasing.txt,
+    EvalPhasingDev against the key -> <outpath>.<tag>.qscore.txt
+    (`score=%f;300kbp_score=%f;1mbp_score=%f`).  Returns (phasing, (score, score3k, score1mbp))."""
+    links = LoadLinksDevice(linksPath, device=device)
+    phasing = Phase(links, outpath + "." + subruntag + ".phasing.txt", iterations, optReportFreq,
+                    device=device, seed=seed)
+    key = readPhasing(keyPath)
+    scores = EvalPhasingDev(phasing, key, device=device)
+    with open(outpath + "." + subruntag + ".qscore.txt", "w") as f:
+        f.write("score=%f;300kbp_score=%f;1mbp_score=%f\n" % scores)
+    return phasing, scores

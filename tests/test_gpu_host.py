@@ -6,6 +6,7 @@ import random
 import numpy as np
 import pytest
 
+import _ga_oracle as G
 import _oracle as O
 from lxy_b200 import host as H
 
@@ -156,3 +157,51 @@ def test_concurrent_score_calls_from_seven_threads():
         assert not errors
         assert gotx.tolist() == want_x.tolist()
         assert got.tolist() == want.tolist()
+
+
+def test_infer_workflows_file_to_file(tmp_path, golden_files):
+    """`lxy scaff infer` / `lxy phase infer` (scaff/cmd.go:135-202, phase/cmd.go:114-165) without the
+    plots: links parsed on the device, GA, quality metrics, the reference's output files."""
+    import numpy as np
+    from lxy_b200 import host as H
+    # a chain of 12 contigs: adjacent pairs strongly linked, so the GA recovers the order (or its reverse)
+    names = [f"ctg{i}" for i in range(12)]
+    lp = tmp_path / "chain.links"
+    with open(lp, "w") as f:
+        for i in range(12):
+            for j in range(i + 1, 12):
+                f.write(f"{names[i]} {names[j]} {1000 // (j - i) ** 2}\n")
+    kp = tmp_path / "key.txt"
+    kp.write_text("".join(nm + "\n" for nm in names))
+    dev = H.LoadLinksDevice(str(lp))
+    ref = H.LoadLinks(str(lp))
+    assert dev.idKey == ref.idKey and dev.data == ref.data
+    prefix = str(tmp_path / "run")
+    scaffolding, score, nscore = H.ScaffoldInfer(str(lp), prefix, str(kp), iterations=300, optReportFreq=0.05, seed=3)
+    assert sorted(scaffolding) == sorted(names)
+    assert H.ReadScaffolding(prefix + ".scaff.txt") == scaffolding
+    assert open(prefix + ".qscore.txt").read() == "score=%f;score_neighbor=%f\n" % (score, nscore)
+    want = G.eval_scaffolding([names.index(nm) for nm in scaffolding], list(range(12)))
+    assert [score, nscore] == want.tolist()
+    assert score > 0.9
+    rows = [r.split(" ") for r in open(prefix + ".opt.txt").read().splitlines()]
+    assert len(rows) >= 3 and all(len(r) == 3 for r in rows)
+    assert [int(r[0]) for r in rows] == sorted(int(r[0]) for r in rows)
+    assert float(rows[-1][1]) <= float(rows[0][1])                    # the best fitness never gets worse
+    # phasing: the reference fixture, key = the known phasing of SURVEY.md §4 in readPhasing's format
+    links = H.LoadLinks(golden_files["test_var"])
+    truth = "AABAAAAAABA"
+    pk = tmp_path / "phase.key"
+    pk.write_text("".join(f"{links.idKeyRev[i]} {1 if c == 'A' else 0}\n" for i, c in enumerate(truth)))
+    if all("_" in nm for nm in links.idKey):
+        phasing, scores = H.PhaseInfer(golden_files["test_var"], str(tmp_path / "ph"), str(pk), iterations=300,
+                                       subruntag="t", seed=4)
+        assert set(phasing) == set(links.idKey)
+        text = open(str(tmp_path / "ph") + ".t.qscore.txt").read()
+        assert text == "score=%f;300kbp_score=%f;1mbp_score=%f\n" % scores
+        key = H.readPhasing(str(pk))
+        common = [nm for nm in phasing if nm in key]
+        want = G.eval_phasing_dev([phasing[nm] for nm in common], [key[nm] for nm in common],
+                                  [H._atoi_or_zero(nm.split("_")[1]) for nm in common])
+        assert list(scores) == want.tolist()
+        assert scores[0] == 1.0                                        # 11 blocks: the GA finds the phasing
