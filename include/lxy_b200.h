@@ -205,6 +205,27 @@ int lxy_links_load_gpu(const char* path, int32_t device, lxy_links** out, lxy_lo
 int lxy_ctx_load_links(lxy_ctx* ctx, const char* path, int32_t kind, lxy_links** out,
                        lxy_load_stats* stats);
 
+/* ---- ScaffoldLinksFromSam (src/sequtil/alignment.go:624-676): SAM text -> contig link table --------
+ * The step before LoadLinks in a scaffolding run (`lxy scaff links`, scaff/cmd.go:225).  Semantics of
+ * the reference loop, quirks included: lines starting with '@' are skipped; every other line is split
+ * at tabs; consecutive lines with the same field 0 (read id) form a group; when the NEXT read id
+ * arrives, a group of exactly two hits adds 1 to the pair (ID(field 2 of hit 1), ID(field 2 of hit
+ * 2)) - names receive their ids at that moment, in that order, same-contig pairs included; the group
+ * open at end of file is never added (the loop has no final flush).  LXY_ERR_ARG where the Go code
+ * would panic (empty line: line[0] at :648; fewer than three fields: arr[2] at :668).  An empty
+ * result is not an error (the reference writes the empty table).
+ *   lxy_links_from_sam           the host loop (lxy_b200/csrc/links_io.cu)
+ *   lxy_links_from_sam_gpu       the same table built by kernels (links_parse.cu): tab split, group
+ *                                detection, name ids and pair counts on the device
+ *   lxy_scaffold_links_from_sam  ScaffoldLinksFromSam(samPath, outPath): device table + Write
+ *   lxy_ctx_load_sam             SAM -> the context's scaffolding link store, the records never leave
+ *                                the device; `out` (nullable) receives the table (names for Decode). */
+int lxy_links_from_sam(const char* sam_path, lxy_links** out);
+int lxy_links_from_sam_gpu(const char* sam_path, int32_t device, lxy_links** out, lxy_load_stats* stats);
+int lxy_scaffold_links_from_sam(const char* sam_path, const char* out_path, int32_t device,
+                                lxy_load_stats* stats);
+int lxy_ctx_load_sam(lxy_ctx* ctx, const char* sam_path, lxy_links** out, lxy_load_stats* stats);
+
 /* ---- device-resident GA generation loop --------------------------------------------------------
  * Replaces the loop `gao.Optimize(1); best := gao.Best()` of Scaffold / Phase (scaff.go:105-126,
  * phase.go:74-95) and the genome operators it drives (scaff/genome.go:47-91,93-97,125-138,161-209;

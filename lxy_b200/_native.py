@@ -33,6 +33,7 @@ SYMBOLS = [
     "lxy_links_npairs", "lxy_links_id", "lxy_links_name", "lxy_links_set", "lxy_links_add",
     "lxy_links_value", "lxy_links_records", "lxy_ctx_set_links_from",
     "lxy_links_load_gpu", "lxy_ctx_load_links",
+    "lxy_links_from_sam", "lxy_links_from_sam_gpu", "lxy_scaffold_links_from_sam", "lxy_ctx_load_sam",
     "lxy_scaffold_file", "lxy_phase_file", "lxy_eval_scaffolding", "lxy_eval_phasing",
     "lxy_eval_phasing_dev",
 ]
@@ -177,6 +178,10 @@ def lib():
         "lxy_ctx_set_links_from": (i32, [vp, vp, i32]),
         "lxy_links_load_gpu": (i32, [C.c_char_p, i32, C.POINTER(vp), C.POINTER(LoadStats)]),
         "lxy_ctx_load_links": (i32, [vp, C.c_char_p, i32, C.POINTER(vp), C.POINTER(LoadStats)]),
+        "lxy_links_from_sam": (i32, [C.c_char_p, C.POINTER(vp)]),
+        "lxy_links_from_sam_gpu": (i32, [C.c_char_p, i32, C.POINTER(vp), C.POINTER(LoadStats)]),
+        "lxy_scaffold_links_from_sam": (i32, [C.c_char_p, C.c_char_p, i32, C.POINTER(LoadStats)]),
+        "lxy_ctx_load_sam": (i32, [vp, C.c_char_p, C.POINTER(vp), C.POINTER(LoadStats)]),
         "lxy_scaffold_file": (i32, [C.c_char_p, C.c_char_p, i32, C.POINTER(GaParams), i32, C.POINTER(f64)]),
         "lxy_phase_file": (i32, [C.c_char_p, C.c_char_p, i32, C.POINTER(GaParams), i32, C.POINTER(f64)]),
         "lxy_eval_scaffolding": (i32, [vp, vp, vp, i32, i32, vp]),
@@ -476,6 +481,27 @@ class NativeLinks:
         else:
             _check(lib().lxy_links_load(os.fsencode(path), C.byref(self._h)))     # LoadLinks
 
+    @classmethod
+    def from_sam(cls, sam_path, device=None, ctx=None):
+        """ScaffoldLinksFromSam's table (alignment.go:624-672): the host loop (lxy_links_from_sam), the
+        device pipeline with device=d (lxy_links_from_sam_gpu), or with ctx=... the device pipeline
+        feeding that context's link store directly (lxy_ctx_load_sam)."""
+        self = cls.__new__(cls)
+        self._h = C.c_void_p()
+        self.load_stats = None
+        if ctx is not None:
+            st = LoadStats()
+            _check(lib().lxy_ctx_load_sam(ctx._h, os.fsencode(sam_path), C.byref(self._h), C.byref(st)))
+            self.load_stats = st.asdict()
+            ctx.n = self.Size()
+        elif device is not None:
+            st = LoadStats()
+            _check(lib().lxy_links_from_sam_gpu(os.fsencode(sam_path), int(device), C.byref(self._h), C.byref(st)))
+            self.load_stats = st.asdict()
+        else:
+            _check(lib().lxy_links_from_sam(os.fsencode(sam_path), C.byref(self._h)))
+        return self
+
     def close(self):
         if getattr(self, "_h", None) and self._h.value:
             lib().lxy_links_free(self._h)
@@ -532,6 +558,14 @@ class NativeLinks:
             ctx.phase_n = self.Size()
         else:
             ctx.n = self.Size()
+
+
+def scaffold_links_from_sam(sam_path, out_path, device=0):
+    """lxy_scaffold_links_from_sam: ScaffoldLinksFromSam(samPath, outPath) (alignment.go:624-676) with
+    the table built on the device; returns the load statistics."""
+    st = LoadStats()
+    _check(lib().lxy_scaffold_links_from_sam(os.fsencode(sam_path), os.fsencode(out_path), int(device), C.byref(st)))
+    return st.asdict()
 
 
 def scaffold_file(links_path, out_path, iterations, params=None, device=0):

@@ -13,6 +13,8 @@
 //                                                  of a pair wins and (a,b) == (b,a); error when empty)
 // Where the Go code would panic (empty line: line[0] at :450; fewer than three fields: arr[2] at
 // :473) the loader returns LXY_ERR_ARG.
+//   ScaffoldLinksFromSam  src/sequtil/alignment.go:624-676  (lxy_links_from_sam: the table the
+//                                                  function builds before links.Write; see there)
 #include <cerrno>
 #include <cstdio>
 #include <cstdlib>
@@ -143,6 +145,77 @@ int lxy_links_load(const char* path, lxy_links** out) {
     set_error("links_load: Loaded empty links object...");
     delete l;
     return LXY_ERR_STATE;
+  }
+  *out = l;
+  return LXY_OK;
+}
+
+// ScaffoldLinksFromSam (alignment.go:624-676) up to links.Write: '@' lines skipped (:648; an empty
+// line panics on line[0]), strings.Split(line, "\t") (:650), consecutive lines sharing arr[0] form a
+// group, and when the NEXT read id arrives a group of exactly two hits does
+// Add(ID(arr[2] of hit 1), ID(arr[2] of hit 2), 1) (:652-660) — names get their ids there, in that
+// order.  The group open at end of file is never added (:672-674 has no flush).  arr[2] on a line
+// with fewer than three fields panics (:668) -> LXY_ERR_ARG.  An empty result is not an error (the
+// Go function writes the empty table).
+int lxy_links_from_sam(const char* path, lxy_links** out) {
+  if (!path || !out) { set_error("links_from_sam: null argument"); return LXY_ERR_ARG; }
+  *out = nullptr;
+  FILE* f = std::fopen(path, "rb");
+  if (!f) { set_error("links_from_sam: cannot open %s: %s", path, std::strerror(errno)); return LXY_ERR_ARG; }
+  std::string text;
+  {
+    char buf[1 << 16];
+    size_t got;
+    while ((got = std::fread(buf, 1, sizeof(buf), f)) > 0) text.append(buf, got);
+  }
+  std::fclose(f);
+  lxy_links* l = new (std::nothrow) lxy_links();
+  if (!l) { set_error("out of memory"); return LXY_ERR_NOMEM; }
+  size_t pos = 0, lineno = 0;
+  const char* cur = "";   // currentID
+  size_t cur_len = 0;
+  const char* hit[2] = {nullptr, nullptr};  // chrHits[0..1]; further hits only count
+  size_t hit_len[2] = {0, 0};
+  size_t nhits = 0;
+  while (pos < text.size()) {
+    size_t eol = text.find('\n', pos);
+    if (eol == std::string::npos) eol = text.size();
+    size_t len = eol - pos;
+    if (len > 0 && text[pos + len - 1] == '\r') --len;
+    const char* line = text.data() + pos;
+    pos = eol + 1;
+    ++lineno;
+    if (len == 0) {
+      set_error("links_from_sam: %s:%zu: empty line (the reference panics here)", path, lineno);
+      delete l;
+      return LXY_ERR_ARG;
+    }
+    if (line[0] == '@') continue;
+    const char* e = line + len;
+    const char* t1 = (const char*)std::memchr(line, '\t', len);
+    const size_t qlen = t1 ? (size_t)(t1 - line) : len;
+    if (qlen != cur_len || std::memcmp(line, cur, qlen) != 0) {
+      if (nhits == 2) {
+        const int32_t ida = id_create(l, std::string(hit[0], hit_len[0]));
+        const int32_t idb = id_create(l, std::string(hit[1], hit_len[1]));
+        put(l, ida, idb, 1.0, true);
+      }
+      cur = line;
+      cur_len = qlen;
+      nhits = 0;
+    }
+    const char* t2 = t1 ? (const char*)std::memchr(t1 + 1, '\t', (size_t)(e - t1 - 1)) : nullptr;
+    if (!t2) {
+      set_error("links_from_sam: %s:%zu: fewer than three fields (the reference panics here)", path, lineno);
+      delete l;
+      return LXY_ERR_ARG;
+    }
+    const char* t3 = (const char*)std::memchr(t2 + 1, '\t', (size_t)(e - t2 - 1));
+    if (nhits < 2) {
+      hit[nhits] = t2 + 1;
+      hit_len[nhits] = (size_t)((t3 ? t3 : e) - (t2 + 1));
+    }
+    ++nhits;
   }
   *out = l;
   return LXY_OK;

@@ -30,7 +30,18 @@
 //                         first and last data line of every pair.  Sorted by first line -> records in
 //                         the host loader's order, each with the value of its last line.
 // The record arrays stay on the device for lxy_ctx_load_links (they feed the link store directly).
+//
+// ScaffoldLinksFromSam (/root/reference/src/sequtil/alignment.go:624-676) runs through the same
+// pipeline with another front end (mode kSam): k_sam_fields splits every line at tabs (read id,
+// contig name), the data lines are compacted (cub select), k_sam_starts marks the lines whose read
+// id differs from the data line before (exact byte compare), and k_sam_emit turns every group of
+// exactly two hits that is FOLLOWED by another group into one record (contig of hit 1, contig of
+// hit 2) — the reference adds a group only when the next read id arrives and never flushes the last
+// one.  Names then get their ids by first appearance over the records, and a pair's value is the
+// number of its records (Links.Add(.., 1) per read pair, alignment.go:656-660).
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_select.cuh>
+#include <thrust/iterator/counting_iterator.h>
 
 #include <fcntl.h>
 #include <sys/mman.h>
@@ -311,14 +322,119 @@ __global__ void __launch_bounds__(kThreads) k_parse_lines(const ParseArgs A) {
   if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(A.ndata, (unsigned long long)__popc(peers));
 }
 
+// ---- SAM front end (ScaffoldLinksFromSam, alignment.go:624-676) -----------------------------------
+struct SamArgs {
+  const uint8_t* text;
+  int64_t T;
+  const int64_t* nl_pos;
+  int64_t NL, lines;
+  uint64_t seed, hmask;
+  uint32_t* tl;        // [2 * lines] reset to kInvalid here; k_sam_emit fills the record lines
+  uint8_t* is_data;    // [lines] 1 on lines that do not start with '@'
+  uint32_t* qlen;      // [lines] length of arr[0] (the read id starts the line)
+  int64_t* r_off;      // [lines] arr[2]
+  uint32_t* r_len;
+  uint64_t* r_h;
+  unsigned long long* err;  // min over (line << 2 | kind)
+};
+
+// one thread per line: strings.Split(line, "\t") as far as arr[0] and arr[2] (alignment.go:650)
+__global__ void __launch_bounds__(kThreads) k_sam_fields(const SamArgs A) {
+  const int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+  if (i >= A.lines) return;
+  const uint8_t* __restrict__ p = A.text;
+  int64_t s = i ? A.nl_pos[i - 1] + 1 : 0;
+  int64_t e = i < A.NL ? A.nl_pos[i] : A.T;
+  A.tl[2 * i] = kInvalid;
+  A.tl[2 * i + 1] = kInvalid;
+  A.is_data[i] = 0;
+  if (e > s && p[e - 1] == '\r') --e;
+  if (e == s) { atomicMin(A.err, ((unsigned long long)i << 2) | 1ull); return; }   // line[0] panics (:648)
+  if (e - s >= 0x7fffffffll) { atomicMin(A.err, ((unsigned long long)i << 2) | 3ull); return; }
+  if (p[s] == '@') return;
+  int64_t j = s;
+  for (; j < e; ++j)
+    if (p[j] == '\t') break;
+  A.qlen[i] = (uint32_t)(j - s);
+  if (j < e) {
+    for (++j; j < e; ++j)
+      if (p[j] == '\t') break;
+  }
+  if (j >= e) { atomicMin(A.err, ((unsigned long long)i << 2) | 2ull); return; }   // arr[2] panics (:668)
+  const int64_t f2 = ++j;
+  uint64_t h = 0xcbf29ce484222325ull ^ A.seed;
+  for (; j < e; ++j) {
+    const uint8_t c = p[j];
+    if (c == '\t') break;
+    h = (h ^ c) * kFnvPrime;
+  }
+  const uint32_t len = (uint32_t)(j - f2);
+  h = fmix64(h ^ len) & A.hmask;
+  A.r_off[i] = f2;
+  A.r_len[i] = len;
+  A.r_h[i] = h ? h : 1;
+  A.is_data[i] = 1;  // only complete lines reach the later stages (a bad line ends the load anyway)
+}
+
+// start[d] = the d-th data line opens a group: its read id differs from the data line before
+// (alignment.go:652; currentID always equals the previous data line's arr[0]).  start[0] = 1: the
+// first group begins there whether or not its id equals the initial "".
+__global__ void __launch_bounds__(kThreads) k_sam_starts(const uint8_t* __restrict__ text, const int64_t* __restrict__ nl_pos,
+                                                         const uint32_t* __restrict__ data_idx,
+                                                         const uint32_t* __restrict__ ndata_lines,
+                                                         const uint32_t* __restrict__ qlen, uint8_t* __restrict__ start) {
+  const uint32_t d = blockIdx.x * kThreads + threadIdx.x;
+  const uint32_t D = *ndata_lines;
+  if (d >= D) return;
+  uint8_t st = 1;
+  if (d > 0) {
+    const uint32_t l1 = data_idx[d], l0 = data_idx[d - 1];
+    const uint32_t n = qlen[l1];
+    if (qlen[l0] == n) {
+      const uint8_t* x = text + (l1 ? nl_pos[l1 - 1] + 1 : 0);
+      const uint8_t* y = text + (l0 ? nl_pos[l0 - 1] + 1 : 0);
+      uint32_t k = 0;
+      while (k < n && x[k] == y[k]) ++k;
+      st = k < n;
+    }
+  }
+  start[d] = st;
+}
+
+// a group of exactly two hits that is followed by another group -> one record on its first line:
+// tokens (arr[2] of hit 1, arr[2] of hit 2), in the order ID() sees them (alignment.go:654-658)
+__global__ void __launch_bounds__(kThreads) k_sam_emit(const uint32_t* __restrict__ data_idx,
+                                                       const uint32_t* __restrict__ ndata_lines,
+                                                       const uint8_t* __restrict__ start, const int64_t* __restrict__ r_off,
+                                                       const uint32_t* __restrict__ r_len, const uint64_t* __restrict__ r_h,
+                                                       uint64_t* __restrict__ h, uint32_t* __restrict__ tl,
+                                                       int64_t* __restrict__ tok_off, double* __restrict__ val,
+                                                       unsigned long long* nrec) {
+  const uint32_t d = blockIdx.x * kThreads + threadIdx.x;
+  const uint32_t D = *ndata_lines;
+  if (d >= D || (uint64_t)d + 2 >= D) return;
+  if (!(start[d] && !start[d + 1] && start[d + 2])) return;
+  const uint32_t l0 = data_idx[d], l1 = data_idx[d + 1];
+  h[2 * (size_t)l0] = r_h[l0];
+  h[2 * (size_t)l0 + 1] = r_h[l1];
+  tl[2 * (size_t)l0] = r_len[l0];
+  tl[2 * (size_t)l0 + 1] = r_len[l1];
+  tok_off[2 * (size_t)l0] = r_off[l0];
+  tok_off[2 * (size_t)l0 + 1] = r_off[l1];
+  val[l0] = 1.0;
+  atomicAdd(nrec, 1ull);
+}
+
 __global__ void k_scatter_vals(const uint32_t* __restrict__ line, const double* __restrict__ v, uint32_t n,
                                double* __restrict__ val) {
   const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k < n) val[line[k]] = v[k];
 }
 
+// tok_off (SAM mode) holds the offsets explicitly; in a .links file they follow from the line start
 __device__ __forceinline__ int64_t token_offset(const int64_t* __restrict__ nl_pos, const uint32_t* __restrict__ tl,
-                                                uint32_t t) {
+                                                const int64_t* __restrict__ tok_off, uint32_t t) {
+  if (tok_off) return tok_off[t];
   const uint32_t line = t >> 1;
   const int64_t s = line ? nl_pos[line - 1] + 1 : 0;
   return (t & 1) ? s + tl[t - 1] + 1 : s;
@@ -353,7 +469,8 @@ __global__ void __launch_bounds__(kThreads) k_names_insert(const uint64_t* __res
 }
 
 __global__ void __launch_bounds__(kThreads) k_names_verify(const uint8_t* __restrict__ text, const int64_t* __restrict__ nl_pos,
-                                                           const uint32_t* __restrict__ tl, uint32_t ntok,
+                                                           const uint32_t* __restrict__ tl,
+                                                           const int64_t* __restrict__ tok_off, uint32_t ntok,
                                                            const uint32_t* __restrict__ first,
                                                            const uint32_t* __restrict__ tok_slot, const int* overflow,
                                                            int* collision) {
@@ -363,8 +480,8 @@ __global__ void __launch_bounds__(kThreads) k_names_verify(const uint8_t* __rest
   if (ft == t) return;
   const uint32_t len = tl[t];
   if (tl[ft] != len) { *collision = 1; return; }
-  const uint8_t* x = text + token_offset(nl_pos, tl, t);
-  const uint8_t* y = text + token_offset(nl_pos, tl, ft);
+  const uint8_t* x = text + token_offset(nl_pos, tl, tok_off, t);
+  const uint8_t* y = text + token_offset(nl_pos, tl, tok_off, ft);
   for (uint32_t k = 0; k < len; ++k)
     if (x[k] != y[k]) { *collision = 1; return; }
 }
@@ -384,13 +501,14 @@ __global__ void __launch_bounds__(kThreads) k_collect_slots(const unsigned long 
 __global__ void __launch_bounds__(kThreads) k_assign_ids(const uint32_t* __restrict__ first_sorted,
                                                          const uint32_t* __restrict__ slot_sorted, uint32_t n,
                                                          const int64_t* __restrict__ nl_pos, const uint32_t* __restrict__ tl,
+                                                         const int64_t* __restrict__ tok_off,
                                                          uint32_t* __restrict__ slot_id, int64_t* __restrict__ name_off,
                                                          uint32_t* __restrict__ name_len) {
   const uint32_t i = blockIdx.x * kThreads + threadIdx.x;
   if (i >= n) return;
   const uint32_t t = first_sorted[i];
   slot_id[slot_sorted[i]] = i;
-  name_off[i] = token_offset(nl_pos, tl, t);
+  name_off[i] = token_offset(nl_pos, tl, tok_off, t);
   name_len[i] = tl[t];
 }
 
@@ -398,7 +516,7 @@ __global__ void __launch_bounds__(kThreads) k_assign_ids(const uint32_t* __restr
 __global__ void __launch_bounds__(kThreads) k_pairs_insert(const uint32_t* __restrict__ tl, const uint32_t* __restrict__ tok_slot,
                                                            const uint32_t* __restrict__ slot_id, uint32_t lines,
                                                            unsigned long long* keys, uint32_t* first, uint32_t* last,
-                                                           uint32_t mask, int* overflow) {
+                                                           uint32_t* count, uint32_t mask, int* overflow) {
   const uint32_t l = blockIdx.x * kThreads + threadIdx.x;
   if (l >= lines || tl[2 * l] == kInvalid) return;
   const uint32_t ia = slot_id[tok_slot[2 * l]], ib = slot_id[tok_slot[2 * l + 1]];
@@ -414,6 +532,7 @@ __global__ void __launch_bounds__(kThreads) k_pairs_insert(const uint32_t* __res
     if (k == key) {
       if (*(volatile uint32_t*)(first + s) > l) atomicMin(first + s, l);
       if (*(volatile uint32_t*)(last + s) < l) atomicMax(last + s, l);
+      if (count) atomicAdd(count + s, 1u);  // Links.Add(.., 1) per record (SAM mode)
       return;
     }
     s = (s + 1) & mask;
@@ -424,14 +543,14 @@ __global__ void __launch_bounds__(kThreads) k_pairs_insert(const uint32_t* __res
 __global__ void __launch_bounds__(kThreads) k_pairs_emit(const uint32_t* __restrict__ slot_sorted, uint32_t m,
                                                          const unsigned long long* __restrict__ keys,
                                                          const uint32_t* __restrict__ last, const double* __restrict__ val,
-                                                         uint32_t* __restrict__ a, uint32_t* __restrict__ b, double* __restrict__ w) {
+                                                         const uint32_t* __restrict__ count, uint32_t* __restrict__ a, uint32_t* __restrict__ b, double* __restrict__ w) {
   const uint32_t i = blockIdx.x * kThreads + threadIdx.x;
   if (i >= m) return;
   const uint32_t s = slot_sorted[i];
   const unsigned long long key = keys[s] - 1ull;
   a[i] = (uint32_t)(key >> 32);
   b[i] = (uint32_t)key;
-  w[i] = val[last[s]];
+  w[i] = count ? (double)count[s] : val[last[s]];
 }
 
 // Device memory of one load: one cudaMalloc per stage instead of one per array (26 cudaMalloc /
@@ -594,7 +713,17 @@ bool name_table_take(Arena& A, uint32_t cap, NameTable& N) {
 
 #define P_SIZED(ok) do { if (!(ok)) { set_error("links_load: arena sizing (internal)"); return LXY_ERR_STATE; } } while (0)
 
-int parse_links_on_device(const char* path, int device, Parsed& out, lxy_load_stats* stats) {
+enum Mode { kLinks = 0, kSam = 1 };  // LoadLinks (links.go:427-491) / ScaffoldLinksFromSam (alignment.go:624-676)
+
+size_t select_tmp_bytes(int64_t lines) {
+  size_t tmp = 0;
+  cub::DeviceSelect::Flagged(nullptr, tmp, thrust::counting_iterator<uint32_t>(0), (const uint8_t*)nullptr,
+                             (uint32_t*)nullptr, (uint32_t*)nullptr, lines, (cudaStream_t) nullptr);
+  return tmp + 256;
+}
+
+int parse_links_on_device(const char* path, int device, Mode mode, Parsed& out, lxy_load_stats* stats) {
+  const char* who = mode == kSam ? "links_from_sam" : "links_load";
   const auto t_start = std::chrono::steady_clock::now();
   lxy_load_stats stt{};
   FileText ft;
@@ -603,7 +732,15 @@ int parse_links_on_device(const char* path, int device, Parsed& out, lxy_load_st
   stt.ms_read = (float)ms_since(t_start);
   const int64_t T = (int64_t)ft.n;
   stt.bytes = T;
-  if (T == 0) { set_error("links_load: Loaded empty links object..."); return LXY_ERR_STATE; }
+  if (T == 0) {
+    if (mode == kSam) {  // no read pairs: the reference writes the empty table
+      stt.ms_total = (float)ms_since(t_start);
+      if (stats) *stats = stt;
+      return LXY_OK;
+    }
+    set_error("links_load: Loaded empty links object...");
+    return LXY_ERR_STATE;
+  }
 
   P_CUDA(cudaSetDevice(device));
   Handles H;
@@ -634,14 +771,18 @@ int parse_links_on_device(const char* path, int device, Parsed& out, lxy_load_st
   P_CUDA(cudaMemcpyAsync(&NL, &dF->nl_total, 8, cudaMemcpyDeviceToHost, st));
   P_CUDA(cudaStreamSynchronize(st));
   const int64_t lines = NL + (text[(size_t)T - 1] != '\n' ? 1 : 0);
-  if (lines >= (1ll << 31)) { set_error("links_load: %lld lines exceed the device loader's 2^31", (long long)lines); return LXY_ERR_RANGE; }
+  if (lines >= (1ll << 31)) { set_error("%s: %lld lines exceed the device loader's 2^31", who, (long long)lines); return LXY_ERR_RANGE; }
   stt.lines = lines;
 
   // stage B: everything sized by the line count, and the first name table
   const uint32_t ntok = (uint32_t)(2 * lines);
   uint32_t cap = pow2_at_least(1u << 16);
+  const size_t sel_bytes = mode == kSam ? select_tmp_bytes(lines) : 0;
+  const size_t sam_bytes = mode == kSam ? 2 * r256((size_t)lines + 2) + 3 * r256((size_t)lines * 4) +
+                                              2 * r256((size_t)lines * 8) + r256((size_t)ntok * 8) + r256(sel_bytes)
+                                        : 0;
   LXY_TRY(A.open(r256((size_t)(NL + 1) * 8) + r256((size_t)ntok * 8) + 2 * r256((size_t)ntok * 4) +
-                 3 * r256((size_t)lines * 8) + 2 * r256((size_t)lines * 4) + name_table_bytes(cap)));
+                 3 * r256((size_t)lines * 8) + 2 * r256((size_t)lines * 4) + sam_bytes + name_table_bytes(cap)));
   int64_t* d_nl = A.take<int64_t>((size_t)NL + 1);
   uint64_t* d_h = A.take<uint64_t>(ntok);
   uint32_t* d_tl = A.take<uint32_t>(ntok);
@@ -651,6 +792,23 @@ int parse_links_on_device(const char* path, int device, Parsed& out, lxy_load_st
   double* d_slow_val = A.take<double>((size_t)lines);
   uint32_t* d_slow_len = A.take<uint32_t>((size_t)lines);
   uint32_t* d_slow_line = A.take<uint32_t>((size_t)lines);
+  uint8_t *d_is_data = nullptr, *d_start = nullptr;
+  uint32_t *d_data_idx = nullptr, *d_qlen = nullptr, *d_rlen = nullptr;
+  int64_t *d_roff = nullptr, *d_tok_off = nullptr;
+  uint64_t* d_rh = nullptr;
+  void* d_sel_tmp = nullptr;
+  if (mode == kSam) {
+    d_is_data = A.take<uint8_t>((size_t)lines + 2);
+    d_start = A.take<uint8_t>((size_t)lines + 2);
+    d_data_idx = A.take<uint32_t>((size_t)lines);
+    d_qlen = A.take<uint32_t>((size_t)lines);
+    d_rlen = A.take<uint32_t>((size_t)lines);
+    d_roff = A.take<int64_t>((size_t)lines);
+    d_rh = A.take<uint64_t>((size_t)lines);
+    d_tok_off = A.take<int64_t>(ntok);
+    d_sel_tmp = A.take<char>(sel_bytes);
+    P_SIZED(d_is_data && d_start && d_data_idx && d_qlen && d_rlen && d_roff && d_rh && d_tok_off && d_sel_tmp);
+  }
   NameTable NT;
   P_SIZED(d_nl && d_h && d_tl && d_tok_slot && d_val && d_slow_off && d_slow_val && d_slow_len && d_slow_line &&
           name_table_take(A, cap, NT));
@@ -668,14 +826,25 @@ int parse_links_on_device(const char* path, int device, Parsed& out, lxy_load_st
   uint32_t N = 0;
   Flags hF{};
   for (int attempt = 0;; ++attempt) {
-    if (attempt == 4) { set_error("links_load: name hash collisions persisted over 4 seeds"); return LXY_ERR_STATE; }
+    if (attempt == 4) { set_error("%s: name hash collisions persisted over 4 seeds", who); return LXY_ERR_STATE; }
     stt.attempts = attempt + 1;
     P_CUDA(cudaMemsetAsync(dF, 0, sizeof(Flags), st));
     P_CUDA(cudaMemsetAsync(&dF->err, 0xFF, 8, st));
-    ParseArgs PA{d_text, T, d_nl, NL, lines, 0x9e3779b97f4a7c15ull * (uint64_t)attempt,
-                 attempt == 0 ? hmask0 : ~0ull, d_h, d_tl, d_val, &dF->err, &dF->slow_cnt, d_slow_off, d_slow_len,
-                 d_slow_line, &dF->ndata};
-    k_parse_lines<<<line_grid, kThreads, 0, st>>>(PA);
+    const uint64_t seed = 0x9e3779b97f4a7c15ull * (uint64_t)attempt, hmask = attempt == 0 ? hmask0 : ~0ull;
+    if (mode == kLinks) {
+      ParseArgs PA{d_text, T, d_nl, NL, lines, seed, hmask, d_h, d_tl, d_val, &dF->err, &dF->slow_cnt, d_slow_off,
+                   d_slow_len, d_slow_line, &dF->ndata};
+      k_parse_lines<<<line_grid, kThreads, 0, st>>>(PA);
+    } else {
+      SamArgs SA{d_text, T, d_nl, NL, lines, seed, hmask, d_tl, d_is_data, d_qlen, d_roff, d_rlen, d_rh, &dF->err};
+      k_sam_fields<<<line_grid, kThreads, 0, st>>>(SA);
+      size_t tmp = sel_bytes;  // data lines in file order; their count stays on the device (dF->cnt)
+      P_CUDA(cub::DeviceSelect::Flagged(d_sel_tmp, tmp, thrust::counting_iterator<uint32_t>(0), (const uint8_t*)d_is_data,
+                                        d_data_idx, &dF->cnt, lines, st));
+      k_sam_starts<<<line_grid, kThreads, 0, st>>>(d_text, d_nl, d_data_idx, &dF->cnt, d_qlen, d_start);
+      k_sam_emit<<<line_grid, kThreads, 0, st>>>(d_data_idx, &dF->cnt, d_start, d_roff, d_rlen, d_rh, d_h, d_tl, d_tok_off,
+                                                 d_val, &dF->ndata);
+    }
     // the name table is filled on the assumption that the file is well formed (checked right after)
     bool first_pass = true;
     for (;;) {
@@ -685,8 +854,8 @@ int parse_links_on_device(const char* path, int device, Parsed& out, lxy_load_st
       P_CUDA(cudaMemsetAsync(&dF->overflow, 0, 8, st));  // overflow + collision
       k_names_insert<<<tok_grid, kThreads, 0, st>>>(d_h, d_tl, ntok, NT.keys, NT.first, cap - 1, d_tok_slot, &dF->used,
                                                     cap / 2, &dF->overflow);
-      k_names_verify<<<tok_grid, kThreads, 0, st>>>(d_text, d_nl, d_tl, ntok, NT.first, d_tok_slot, &dF->overflow,
-                                                    &dF->collision);
+      k_names_verify<<<tok_grid, kThreads, 0, st>>>(d_text, d_nl, d_tl, d_tok_off, ntok, NT.first, d_tok_slot,
+                                                    &dF->overflow, &dF->collision);
       P_CUDA(cudaMemcpyAsync(&hF, dF, sizeof(Flags), cudaMemcpyDeviceToHost, st));
       P_CUDA(cudaStreamSynchronize(st));
       if (first_pass) {
@@ -694,17 +863,26 @@ int parse_links_on_device(const char* path, int device, Parsed& out, lxy_load_st
         if (hF.err != ~0ull) {
           const unsigned long long ln = (hF.err >> 2) + 1;
           const int kind = (int)(hF.err & 3);
-          if (kind == 1) set_error("links_load: %s:%llu: empty line (the reference panics here)", path, ln);
-          else if (kind == 2) set_error("links_load: %s:%llu: fewer than three fields (the reference panics here)", path, ln);
-          else set_error("links_load: %s:%llu: line longer than 2 GiB", path, ln);
+          if (kind == 1) set_error("%s: %s:%llu: empty line (the reference panics here)", who, path, ln);
+          else if (kind == 2) set_error("%s: %s:%llu: fewer than three fields (the reference panics here)", who, path, ln);
+          else set_error("%s: %s:%llu: line longer than 2 GiB", who, path, ln);
           return LXY_ERR_ARG;
         }
         stt.records = (int64_t)hF.ndata;
-        if (hF.ndata == 0) { set_error("links_load: Loaded empty links object..."); return LXY_ERR_STATE; }
+        if (hF.ndata == 0) {
+          if (mode == kSam) {  // no group of two was followed by another read id: the empty table
+            cudaEventElapsedTime(&stt.ms_h2d, H.ev[0], H.ev[1]);
+            stt.ms_total = (float)ms_since(t_start);
+            if (stats) *stats = stt;
+            return LXY_OK;
+          }
+          set_error("links_load: Loaded empty links object...");
+          return LXY_ERR_STATE;
+        }
         stt.slow_values = (int32_t)hF.slow_cnt;
       }
       if (!hF.overflow) break;
-      if (cap >= (1u << 31)) { set_error("links_load: more than 2^30 distinct names"); return LXY_ERR_RANGE; }
+      if (cap >= (1u << 31)) { set_error("%s: more than 2^30 distinct names", who); return LXY_ERR_RANGE; }
       cap = cap >= (1u << 28) ? cap * 2 : cap * 8;  // grown until the names fill at most half of it
       LXY_TRY(A.open(name_table_bytes(cap)));
       P_SIZED(name_table_take(A, cap, NT));
@@ -729,8 +907,8 @@ int parse_links_on_device(const char* path, int device, Parsed& out, lxy_load_st
   P_CUDA(cudaMemsetAsync(&dF->cnt, 0, 4, st));
   k_collect_slots<<<(cap + kThreads - 1) / kThreads, kThreads, 0, st>>>(NT.keys, NT.first, cap, NT.sort.lf, NT.sort.ls, &dF->cnt);
   LXY_TRY(sort_by_first(NT.sort, N, st));
-  k_assign_ids<<<(N + kThreads - 1) / kThreads, kThreads, 0, st>>>(NT.sort.lf2, NT.sort.ls2, N, d_nl, d_tl, NT.slot_id,
-                                                                  NT.name_off, NT.name_len);
+  k_assign_ids<<<(N + kThreads - 1) / kThreads, kThreads, 0, st>>>(NT.sort.lf2, NT.sort.ls2, N, d_nl, d_tl, d_tok_off,
+                                                                  NT.slot_id, NT.name_off, NT.name_len);
   std::vector<int64_t> noff(N);
   std::vector<uint32_t> nlen(N);
   P_CUDA(cudaMemcpyAsync(noff.data(), NT.name_off, (size_t)N * 8, cudaMemcpyDeviceToHost, st));
@@ -739,23 +917,25 @@ int parse_links_on_device(const char* path, int device, Parsed& out, lxy_load_st
   // stage C / 5. pairs: first / last data line of every (lo, hi)
   const uint64_t max_pairs = std::min<uint64_t>((uint64_t)stt.records, (uint64_t)N * ((uint64_t)N + 1) / 2);
   const uint32_t pcap = pow2_at_least(2 * max_pairs);
-  LXY_TRY(A.open(r256((size_t)pcap * 8) + 2 * r256((size_t)pcap * 4) + sort_bytes((uint32_t)max_pairs)));
+  LXY_TRY(A.open(r256((size_t)pcap * 8) + 3 * r256((size_t)pcap * 4) + sort_bytes((uint32_t)max_pairs)));
   unsigned long long* d_pkeys = A.take<unsigned long long>(pcap);
   uint32_t* d_pfirst = A.take<uint32_t>(pcap);
   uint32_t* d_plast = A.take<uint32_t>(pcap);
+  uint32_t* d_pcount = mode == kSam ? A.take<uint32_t>(pcap) : nullptr;  // records per pair = Add(.., 1) each
   SortBufs PS;
-  P_SIZED(d_pkeys && d_pfirst && d_plast && sort_take(A, (uint32_t)max_pairs, PS));
+  P_SIZED(d_pkeys && d_pfirst && d_plast && (mode != kSam || d_pcount) && sort_take(A, (uint32_t)max_pairs, PS));
+  if (d_pcount) P_CUDA(cudaMemsetAsync(d_pcount, 0, (size_t)pcap * 4, st));
   P_CUDA(cudaMemsetAsync(d_pkeys, 0, (size_t)pcap * 8, st));
   P_CUDA(cudaMemsetAsync(d_pfirst, 0xFF, (size_t)pcap * 4, st));
   P_CUDA(cudaMemsetAsync(d_plast, 0, (size_t)pcap * 4, st));
   P_CUDA(cudaMemsetAsync(&dF->cnt, 0, 4, st));
   P_CUDA(cudaMemsetAsync(&dF->overflow, 0, 4, st));
   k_pairs_insert<<<line_grid, kThreads, 0, st>>>(d_tl, d_tok_slot, NT.slot_id, (uint32_t)lines, d_pkeys, d_pfirst, d_plast,
-                                                 pcap - 1, &dF->overflow);
+                                                 d_pcount, pcap - 1, &dF->overflow);
   k_collect_slots<<<(pcap + kThreads - 1) / kThreads, kThreads, 0, st>>>(d_pkeys, d_pfirst, pcap, PS.lf, PS.ls, &dF->cnt);
   P_CUDA(cudaMemcpyAsync(&hF, dF, sizeof(Flags), cudaMemcpyDeviceToHost, st));
   P_CUDA(cudaStreamSynchronize(st));
-  if (hF.overflow) { set_error("links_load: pair table overflow (internal)"); return LXY_ERR_STATE; }
+  if (hF.overflow) { set_error("%s: pair table overflow (internal)", who); return LXY_ERR_STATE; }
   const uint32_t M = hF.cnt;
   LXY_TRY(sort_by_first(PS, M, st));
   {
@@ -764,14 +944,15 @@ int parse_links_on_device(const char* path, int device, Parsed& out, lxy_load_st
     if (e != cudaSuccess) {
       (void)cudaGetLastError();
       out.slab = nullptr;
-      set_error("links_load: cudaMalloc of the records failed: %s", cudaGetErrorString(e));
+      set_error("%s: cudaMalloc of the records failed: %s", who, cudaGetErrorString(e));
       return LXY_ERR_NOMEM;
     }
     out.a = reinterpret_cast<uint32_t*>(out.slab);
     out.b = reinterpret_cast<uint32_t*>((char*)out.slab + ab);
     out.w = reinterpret_cast<double*>((char*)out.slab + 2 * ab);
   }
-  k_pairs_emit<<<(M + kThreads - 1) / kThreads, kThreads, 0, st>>>(PS.ls2, M, d_pkeys, d_plast, d_val, out.a, out.b, out.w);
+  k_pairs_emit<<<(M + kThreads - 1) / kThreads, kThreads, 0, st>>>(PS.ls2, M, d_pkeys, d_plast, d_val, d_pcount, out.a, out.b,
+                                                                  out.w);
   P_CUDA(cudaEventRecord(H.ev[2], st));
   P_CUDA(cudaStreamSynchronize(st));
   P_CUDA(cudaGetLastError());
@@ -822,8 +1003,42 @@ int lxy_links_load_gpu(const char* path, int32_t device, lxy_links** out, lxy_lo
   if (!path || !out) { set_error("links_load_gpu: null argument"); return LXY_ERR_ARG; }
   *out = nullptr;
   Parsed P;
-  LXY_TRY(parse_links_on_device(path, device, P, stats));
+  LXY_TRY(parse_links_on_device(path, device, kLinks, P, stats));
   return to_host_table(P, true, out);
+}
+
+// ScaffoldLinksFromSam's table (alignment.go:624-672), built on the device
+int lxy_links_from_sam_gpu(const char* path, int32_t device, lxy_links** out, lxy_load_stats* stats) {
+  if (!path || !out) { set_error("links_from_sam_gpu: null argument"); return LXY_ERR_ARG; }
+  *out = nullptr;
+  Parsed P;
+  LXY_TRY(parse_links_on_device(path, device, kSam, P, stats));
+  return to_host_table(P, true, out);
+}
+
+// ScaffoldLinksFromSam(samPath, outPath) (alignment.go:624-676): the table, then links.Write
+int lxy_scaffold_links_from_sam(const char* sam_path, const char* out_path, int32_t device, lxy_load_stats* stats) {
+  if (!sam_path || !out_path) { set_error("scaffold_links_from_sam: null argument"); return LXY_ERR_ARG; }
+  lxy_links* l = nullptr;
+  LXY_TRY(lxy_links_from_sam_gpu(sam_path, device, &l, stats));
+  const int rc = lxy_links_write(l, out_path);
+  lxy_links_free(l);
+  return rc;
+}
+
+// SAM -> link store without the .links file in between: the records never leave the device
+int lxy_ctx_load_sam(lxy_ctx* c, const char* path, lxy_links** out, lxy_load_stats* stats) {
+  if (!c || !path) { set_error("ctx_load_sam: null argument"); return LXY_ERR_ARG; }
+  if (out) *out = nullptr;
+  Parsed P;
+  LXY_TRY(parse_links_on_device(path, c->cfg.device, kSam, P, stats));
+  if (P.n == 0) { set_error("ctx_load_sam: %s holds no read pair to add (empty link table)", path); return LXY_ERR_STATE; }
+  lxy_links* l = nullptr;
+  if (out) LXY_TRY(to_host_table(P, true, &l));
+  const int rc = lxy_ctx_set_links_dev(c, P.n, P.m, P.a, P.b, P.w);
+  if (rc != LXY_OK) delete l;
+  else if (out) *out = l;
+  return rc;
 }
 
 int lxy_ctx_load_links(lxy_ctx* c, const char* path, int32_t kind, lxy_links** out, lxy_load_stats* stats) {
@@ -831,7 +1046,7 @@ int lxy_ctx_load_links(lxy_ctx* c, const char* path, int32_t kind, lxy_links** o
   if (kind != 0 && kind != 1) { set_error("ctx_load_links: kind must be 0 (scaffolding) or 1 (phasing)"); return LXY_ERR_ARG; }
   if (out) *out = nullptr;
   Parsed P;
-  LXY_TRY(parse_links_on_device(path, c->cfg.device, P, stats));
+  LXY_TRY(parse_links_on_device(path, c->cfg.device, kLinks, P, stats));
   lxy_links* l = nullptr;
   if (out || kind == 1) LXY_TRY(to_host_table(P, true, &l));
   int rc;

@@ -152,6 +152,16 @@ def LoadLinksDevice(path, device=0):
     return l
 
 
+def ScaffoldLinksFromSam(samPath, outPath, device=0):
+    """sequtil.ScaffoldLinksFromSam (alignment.go:624-676) with the reference's signature: the SAM text
+    is grouped by read id and counted into contig pairs on the GPU (lxy_scaffold_links_from_sam), the
+    table is written in the `.links` format LoadLinks reads (links.go:242-264)."""
+    try:
+        return N.scaffold_links_from_sam(samPath, outPath, device=device)
+    except N.LxyError as e:
+        raise LinksError(str(e))
+
+
 # ---------------------------------------------------------------------------------------------
 # genomes
 # ---------------------------------------------------------------------------------------------

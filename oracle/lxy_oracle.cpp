@@ -141,6 +141,52 @@ int load_links(const char* path, Links& l) {
   return 0;
 }
 
+// strings.Split(line, "\t") (alignment.go:650): every single tab separates; empty fields are kept.
+std::vector<std::string> split_tab(const std::string& s) {
+  std::vector<std::string> out;
+  size_t start = 0;
+  for (;;) {
+    size_t p = s.find('\t', start);
+    if (p == std::string::npos) { out.push_back(s.substr(start)); break; }
+    out.push_back(s.substr(start, p - start));
+    start = p + 1;
+  }
+  return out;
+}
+
+// ScaffoldLinksFromSam's table (src/sequtil/alignment.go:624-676, everything before links.Write):
+// lines not starting with '@' are split at tabs; consecutive lines with the same arr[0] (read id)
+// form a group; when a NEW read id arrives and the group just ended holds exactly two hits, the pair
+// (ID(chr of hit 1), ID(chr of hit 2)) gets Add(.., 1) (:654-660) — ids are created at that moment,
+// in that order.  The group that is open when the file ends is never added (no flush after the loop,
+// :672-674).  Same-contig pairs are added like any other.  Returns 0 ok (an empty table is ok: the
+// Go function writes it out), -1 cannot open, -3 where the Go code would panic (empty line: line[0]
+// at :648; fewer than three fields: arr[2] at :668).
+int links_from_sam(const char* path, Links& l) {
+  std::ifstream f(path);
+  if (!f.good()) return -1;
+  std::string line, currentID;
+  std::vector<std::string> chrHits;
+  while (std::getline(f, line)) {       // bufio.Scanner strips the trailing "\n" (and "\r\n")
+    if (!line.empty() && line.back() == '\r') line.pop_back();
+    if (line.empty()) return -3;                         // alignment.go:648
+    if (line[0] == '@') continue;
+    std::vector<std::string> arr = split_tab(line);     // alignment.go:650
+    if (arr[0] != currentID) {                           // alignment.go:652
+      if (chrHits.size() == 2) {                         // alignment.go:654-658
+        int id1 = id_of(l, chrHits[0]);
+        int id2 = id_of(l, chrHits[1]);
+        add_val(l, id1, id2, 1.0);
+      }
+      currentID = arr[0];
+      chrHits.clear();
+    }
+    if (arr.size() < 3) return -3;                       // alignment.go:668
+    chrHits.push_back(arr[2]);
+  }
+  return 0;
+}
+
 inline int size_of(const Links& l) { return (int)l.idKey.size(); }  // links.go:267-269
 
 // The reference ignores Get's error and uses the returned value (-1 for unknown ids):
@@ -358,6 +404,15 @@ int lxyo_links_load(const char* path, lxyo_links** out) {
   if (rc == -1 || rc == -3) { delete h; *out = nullptr; return rc; }
   *out = h;
   return rc;
+}
+
+// ScaffoldLinksFromSam up to (not including) links.Write (alignment.go:624-672).
+int lxyo_links_from_sam(const char* path, lxyo_links** out) {
+  lxyo_links* h = new lxyo_links();
+  int rc = links_from_sam(path, h->l);
+  if (rc != 0) { delete h; *out = nullptr; return rc; }
+  *out = h;
+  return 0;
 }
 
 // Decode, one element (links.go:276-286): returns name length, or -1 for an unknown id.

@@ -36,6 +36,7 @@ def _load():
         "lxyo_links_size": (i32, [vp]),
         "lxyo_links_has_name": (i32, [vp, C.c_char_p]),
         "lxyo_links_load": (i32, [C.c_char_p, C.POINTER(vp)]),
+        "lxyo_links_from_sam": (i32, [C.c_char_p, C.POINTER(vp)]),
         "lxyo_links_name": (i32, [vp, i32, C.c_char_p, i32]),
         "lxyo_links_npairs": (i64, [vp]),
         "lxyo_links_export": (i64, [vp, vp, vp, vp, i64]),
@@ -96,6 +97,15 @@ class Links:
         if rc == -2:
             raise ValueError("empty links object")
         return obj
+
+    @classmethod
+    def from_sam(cls, path):
+        """ScaffoldLinksFromSam's table before Write (alignment.go:624-672)."""
+        out = C.c_void_p()
+        rc = lib.lxyo_links_from_sam(os.fsencode(path), C.byref(out))
+        if rc != 0:
+            raise OSError(f"ScaffoldLinksFromSam({path}) failed rc={rc}")
+        return cls(out.value)
 
     @classmethod
     def from_records(cls, n, a, b, w):
