@@ -748,6 +748,12 @@ int parse_links_on_device(const char* path, int device, Mode mode, Parsed& out, 
   P_CUDA(cudaStreamCreateWithFlags(&H.st, cudaStreamNonBlocking));
   for (auto& e : H.ev) P_CUDA(cudaEventCreate(&e));
   cudaStream_t st = H.st;
+  const bool trace = std::getenv("LXY_PARSE_TRACE") != nullptr;  // phase times on stderr (adds a sync per phase)
+  auto mark = [&](const char* what) {
+    if (!trace) return;
+    cudaStreamSynchronize(st);
+    std::fprintf(stderr, "[%s] %8.3f ms  %s\n", who, ms_since(t_start), what);
+  };
 
   // stage A: the text and the per-chunk newline counts
   const int64_t nchunks = (T + kChunk - 1) / kChunk;
@@ -770,6 +776,7 @@ int parse_links_on_device(const char* path, int device, Mode mode, Parsed& out, 
   int64_t NL = 0;
   P_CUDA(cudaMemcpyAsync(&NL, &dF->nl_total, 8, cudaMemcpyDeviceToHost, st));
   P_CUDA(cudaStreamSynchronize(st));
+  mark("text resident, newlines counted");
   const int64_t lines = NL + (text[(size_t)T - 1] != '\n' ? 1 : 0);
   if (lines >= (1ll << 31)) { set_error("%s: %lld lines exceed the device loader's 2^31", who, (long long)lines); return LXY_ERR_RANGE; }
   stt.lines = lines;
@@ -812,8 +819,10 @@ int parse_links_on_device(const char* path, int device, Mode mode, Parsed& out, 
   NameTable NT;
   P_SIZED(d_nl && d_h && d_tl && d_tok_slot && d_val && d_slow_off && d_slow_val && d_slow_len && d_slow_line &&
           name_table_take(A, cap, NT));
+  mark("stage B allocated");
   k_newline_pos<<<(unsigned)nchunks, kThreads, 0, st>>>(d_text, T, d_chunk_base, d_nl);
   P_CUDA(cudaGetLastError());
+  mark("newline positions");
 
   // 2..3: parse + name table; a detected hash collision re-runs both with another seed
   const unsigned line_grid = (unsigned)((lines + kThreads - 1) / kThreads);
@@ -845,6 +854,7 @@ int parse_links_on_device(const char* path, int device, Mode mode, Parsed& out, 
       k_sam_emit<<<line_grid, kThreads, 0, st>>>(d_data_idx, &dF->cnt, d_start, d_roff, d_rlen, d_rh, d_h, d_tl, d_tok_off,
                                                  d_val, &dF->ndata);
     }
+    mark("lines parsed");
     // the name table is filled on the assumption that the file is well formed (checked right after)
     bool first_pass = true;
     for (;;) {
@@ -903,6 +913,7 @@ int parse_links_on_device(const char* path, int device, Mode mode, Parsed& out, 
     if (!hF.collision) { N = hF.used; break; }
   }
 
+  mark("name table");
   // 4. ids = rank of a name's first token
   P_CUDA(cudaMemsetAsync(&dF->cnt, 0, 4, st));
   k_collect_slots<<<(cap + kThreads - 1) / kThreads, kThreads, 0, st>>>(NT.keys, NT.first, cap, NT.sort.lf, NT.sort.ls, &dF->cnt);
@@ -925,6 +936,7 @@ int parse_links_on_device(const char* path, int device, Mode mode, Parsed& out, 
   SortBufs PS;
   P_SIZED(d_pkeys && d_pfirst && d_plast && (mode != kSam || d_pcount) && sort_take(A, (uint32_t)max_pairs, PS));
   if (d_pcount) P_CUDA(cudaMemsetAsync(d_pcount, 0, (size_t)pcap * 4, st));
+  mark("ids assigned, stage C allocated");
   P_CUDA(cudaMemsetAsync(d_pkeys, 0, (size_t)pcap * 8, st));
   P_CUDA(cudaMemsetAsync(d_pfirst, 0xFF, (size_t)pcap * 4, st));
   P_CUDA(cudaMemsetAsync(d_plast, 0, (size_t)pcap * 4, st));
@@ -936,6 +948,7 @@ int parse_links_on_device(const char* path, int device, Mode mode, Parsed& out, 
   P_CUDA(cudaMemcpyAsync(&hF, dF, sizeof(Flags), cudaMemcpyDeviceToHost, st));
   P_CUDA(cudaStreamSynchronize(st));
   if (hF.overflow) { set_error("%s: pair table overflow (internal)", who); return LXY_ERR_STATE; }
+  mark("pair table");
   const uint32_t M = hF.cnt;
   LXY_TRY(sort_by_first(PS, M, st));
   {
@@ -957,6 +970,7 @@ int parse_links_on_device(const char* path, int device, Mode mode, Parsed& out, 
   P_CUDA(cudaStreamSynchronize(st));
   P_CUDA(cudaGetLastError());
 
+  mark("records emitted");
   out.n = (int32_t)N;
   out.m = (int64_t)M;
   out.names.resize(N);
