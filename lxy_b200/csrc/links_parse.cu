@@ -751,8 +751,9 @@ int parse_links_on_device(const char* path, int device, Mode mode, Parsed& out, 
   const bool trace = std::getenv("LXY_PARSE_TRACE") != nullptr;  // phase times on stderr (adds a sync per phase)
   auto mark = [&](const char* what) {
     if (!trace) return;
+    const double t_host = ms_since(t_start);
     cudaStreamSynchronize(st);
-    std::fprintf(stderr, "[%s] %8.3f ms  %s\n", who, ms_since(t_start), what);
+    std::fprintf(stderr, "[%s] host %8.3f ms, stream idle %8.3f ms  %s\n", who, t_host, ms_since(t_start), what);
   };
 
   // stage A: the text and the per-chunk newline counts
@@ -788,6 +789,7 @@ int parse_links_on_device(const char* path, int device, Mode mode, Parsed& out, 
   const size_t sam_bytes = mode == kSam ? 2 * r256((size_t)lines + 2) + 3 * r256((size_t)lines * 4) +
                                               2 * r256((size_t)lines * 8) + r256((size_t)ntok * 8) + r256(sel_bytes)
                                         : 0;
+  mark("before stage B allocation");
   LXY_TRY(A.open(r256((size_t)(NL + 1) * 8) + r256((size_t)ntok * 8) + 2 * r256((size_t)ntok * 4) +
                  3 * r256((size_t)lines * 8) + 2 * r256((size_t)lines * 4) + sam_bytes + name_table_bytes(cap)));
   int64_t* d_nl = A.take<int64_t>((size_t)NL + 1);
@@ -925,6 +927,7 @@ int parse_links_on_device(const char* path, int device, Mode mode, Parsed& out, 
   P_CUDA(cudaMemcpyAsync(noff.data(), NT.name_off, (size_t)N * 8, cudaMemcpyDeviceToHost, st));
   P_CUDA(cudaMemcpyAsync(nlen.data(), NT.name_len, (size_t)N * 4, cudaMemcpyDeviceToHost, st));
 
+  mark("ids assigned");
   // stage C / 5. pairs: first / last data line of every (lo, hi)
   const uint64_t max_pairs = std::min<uint64_t>((uint64_t)stt.records, (uint64_t)N * ((uint64_t)N + 1) / 2);
   const uint32_t pcap = pow2_at_least(2 * max_pairs);

@@ -21,6 +21,12 @@ constexpr int kS1Warps = kS1Threads / 32;
 #endif
 constexpr int kS1Depth = LXY_S1_DEPTH;     // 16-byte record copies in flight per lane
 constexpr int kS1Stage = kS1Threads * 16;  // bytes of one ring stage (one packet per thread)
+// Unit weights: the two records of a 32-bit word share ONE decay look-up, lut2[v0 * 43 + v1] =
+// 100*T[v0] + 100*T[v1] (<= 200: a byte).  Saves one of the two look-ups, one add and moves the index
+// arithmetic to an IMAD (the FMA pipe idles in this kernel): 25 -> 21 shared-pipe wavefronts per packet.
+constexpr int kS1LutSide = kMiss + 2;                  // 43 values of v
+constexpr int kS1Lut2Len = kS1LutSide * kS1LutSide;    // 1849
+constexpr int kS1Lut2Bytes = 1856;
 
 
 struct Stream1Params {
@@ -48,6 +54,10 @@ __device__ __forceinline__ int32_t lds_s16(uint32_t addr) {
 
 __device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void* src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
+}
+// Branch-free conditional copy: with src-size 0 nothing is read and the 16 bytes are zero-filled.
+__device__ __forceinline__ void cp_async16_zfill(uint32_t dst_smem, const void* src, bool pred) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst_smem), "l"(src), "r"(pred ? 16u : 0u) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
@@ -89,7 +99,7 @@ __device__ __forceinline__ void s1_eval(uint32_t baseA, uint32_t baseB, uint32_t
 // records are sorted by (a, b) inside a tile): tab[a] is fetched once.
 template <int NC, int WM>
 __device__ __forceinline__ void s1_packet_same_a(const uint4 v, uint32_t baseA, uint32_t baseB,
-                                                 uint32_t cstride, const uint8_t* lut,
+                                                 uint32_t cstride, const uint8_t* lut, const uint8_t* lut2,
                                                  const int32_t (&wi)[kPacket], const double (&wd)[kPacket],
                                                  int32_t (&a32)[NC], int64_t (&a64)[NC], double (&ad)[NC]) {
   const uint32_t words[4] = {v.x, v.y, v.z, v.w};
@@ -105,8 +115,12 @@ __device__ __forceinline__ void s1_packet_same_a(const uint4 v, uint32_t baseA, 
       const uint32_t bb = baseB + c * cstride;
       const int32_t v0 = __viaddmin_s32_relu(lds_s16(bb | o0), pterm[c], kMiss + 1);
       const int32_t v1 = __viaddmin_s32_relu(lds_s16(bb | o1), pterm[c], kMiss + 1);
-      s1_acc<WM>(lut[v0], wi[2 * q], wd[2 * q], a32[c], a64[c], ad[c]);
-      s1_acc<WM>(lut[v1], wi[2 * q + 1], wd[2 * q + 1], a32[c], a64[c], ad[c]);
+      if (WM == W_UNIT) {
+        a32[c] += lut2[v0 * kS1LutSide + v1];
+      } else {
+        s1_acc<WM>(lut[v0], wi[2 * q], wd[2 * q], a32[c], a64[c], ad[c]);
+        s1_acc<WM>(lut[v1], wi[2 * q + 1], wd[2 * q + 1], a32[c], a64[c], ad[c]);
+      }
     }
   }
 }
@@ -133,7 +147,8 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
   const int32_t nstride = (n + kBlk - 1) & ~(kBlk - 1);      // whole contig blocks: 512-byte aligned
   int16_t* sPos = (int16_t*)smem;                            // [NC][nstride], 32767 - pos
   uint8_t* s_lut = smem + (size_t)NC * nstride * 2;          // kLutLen bytes
-  acc_t* s_red = (acc_t*)(s_lut + 64);                       // [kS1Warps][NC]
+  uint8_t* s_lut2 = s_lut + 64;                              // kS1Lut2Bytes: pair sums (unit weights)
+  acc_t* s_red = (acc_t*)(s_lut2 + kS1Lut2Bytes);            // [kS1Warps][NC]
   int64_t* s_tile = (int64_t*)(s_red + kS1Warps * NC);
   const uint32_t sbase = smem_u32(sPos), cstride = (uint32_t)nstride * 2;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -166,6 +181,9 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
   }
   // ---- placement tables: pos[perm[i]] = i (pad candidates: identity, discarded) ----
   if (tid < kLutLen) s_lut[tid] = c_lut100[tid];
+  if (WM == W_UNIT)
+    for (int i = tid; i < kS1Lut2Len; i += kS1Threads)
+      s_lut2[i] = (uint8_t)(c_lut100[i / kS1LutSide] + c_lut100[i % kS1LutSide]);
   int bad = 0;
 #pragma unroll 1
   for (int c = 0; c < NC; ++c) {
@@ -216,54 +234,81 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
     int32_t lim_rel = 0;                                      // end of (share ∩ current tile); 0 forces the set-up
     uint32_t baseA = sbase, baseB = sbase;
     const uint16_t* pre = prm.rec + lo + r_rel + (int64_t)kS1Depth * kChunk;  // next packet to request
+    // Chunks are walked in RUNS: as long as the warp's slice lies inside (share ∩ current tile) nothing
+    // but the ring and the packet itself is touched (the hot loop below: no tile test, branch-free
+    // refill).  A slice that crosses a tile boundary or the end of the share takes the per-lane path,
+    // one chunk, and the next run starts behind it.
+    int32_t c = 0;
 #pragma unroll 1
-    for (int32_t c = 0; c < nchunks; ++c) {
-      cp_async_wait<kS1Depth - 1>();
-      const uint4 v = lds_v4(my_slot + (uint32_t)(c & (kS1Depth - 1)) * kS1Stage);
-      bool whole = (w_rel + (int32_t)kSlice <= lim_rel);      // warp-uniform
-      if (!whole && w_rel < hi_rel) {                         // next tile (or the first one)
+    while (c < nchunks) {
+      if (w_rel < hi_rel && w_rel + (int32_t)kSlice > lim_rel) {   // next tile (or the first one)
         cur.advance_to(lo + w_rel, prm.tile_start, prm.nblk);
         lim_rel = (int32_t)(min(hi, cur.end) - lo);
         baseA = sbase + (uint32_t)cur.I * (kBlk * 2);
         baseB = sbase + (uint32_t)cur.J * (kBlk * 2);
-        whole = (w_rel + (int32_t)kSlice <= lim_rel);
       }
-      // one a for the whole packet (sorted by (a, b): first a == last a)
-      const bool one_a = __all_sync(0xffffffffu, ((v.x ^ (v.w >> 16)) & 0xFF00u) == 0u);
-      // v is in registers (the vote consumed it): the slot can be refilled
-      if (r_rel + kS1Depth * (int32_t)kChunk < hi_rel) cp_async16(my_slot + (uint32_t)(c & (kS1Depth - 1)) * kS1Stage, pre);
-      cp_async_commit();
-      int32_t wi[kPacket];
-      double wd[kPacket];
-      if (WM != W_UNIT && r_rel < hi_rel) load_weights<WM>(prm.w, lo + r_rel, wi, wd);
-      if (whole && one_a) {
-        s1_packet_same_a<NC, WM>(v, baseA, baseB, cstride, s_lut, wi, wd, a32, a64, ad);
-      } else if (whole) {
-        const uint32_t words[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-        for (int k = 0; k < kPacket; ++k) {
-          const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
-          s1_eval<NC, WM>(baseA, baseB, cstride, s_lut, r, WM == W_INT32 ? wi[k] : 0,
-                          WM == W_F64 ? wd[k] : 0.0, a32, a64, ad);
-        }
-      } else if (r_rel < hi_rel) {
+      int32_t nrun = 0;                                            // warp-uniform
+      if (w_rel + (int32_t)kSlice <= lim_rel) nrun = min((lim_rel - (int32_t)kSlice - w_rel) / (int32_t)kChunk + 1, nchunks - c);
+      if (nrun == 0) {
         // the slice crosses a tile boundary or the end of the share: per-lane tile cursor
-        S1Tile mine = cur;
-        const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+        cp_async_wait<kS1Depth - 1>();
+        const uint32_t slot = my_slot + (uint32_t)(c & (kS1Depth - 1)) * kS1Stage;
+        const uint4 v = lds_v4(slot);
+        cp_async16_zfill(slot, pre, r_rel + kS1Depth * (int32_t)kChunk < hi_rel);
+        cp_async_commit();
+        if (r_rel < hi_rel) {
+          int32_t wi[kPacket];
+          double wd[kPacket];
+          if (WM != W_UNIT) load_weights<WM>(prm.w, lo + r_rel, wi, wd);
+          S1Tile mine = cur;
+          const uint32_t words[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-        for (int k = 0; k < kPacket; ++k) {  // unrolled: words[] stays in registers
-          if (r_rel + k < hi_rel) {
-            mine.advance_to(lo + r_rel + k, prm.tile_start, prm.nblk);
-            const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
-            s1_eval<NC, WM>(sbase + (uint32_t)mine.I * (kBlk * 2), sbase + (uint32_t)mine.J * (kBlk * 2),
-                            cstride, s_lut, r, WM == W_INT32 ? wi[k] : 0, WM == W_F64 ? wd[k] : 0.0,
-                            a32, a64, ad);
+          for (int k = 0; k < kPacket; ++k) {  // unrolled: words[] stays in registers
+            if (r_rel + k < hi_rel) {
+              mine.advance_to(lo + r_rel + k, prm.tile_start, prm.nblk);
+              const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
+              s1_eval<NC, WM>(sbase + (uint32_t)mine.I * (kBlk * 2), sbase + (uint32_t)mine.J * (kBlk * 2),
+                              cstride, s_lut, r, WM == W_INT32 ? wi[k] : 0, WM == W_F64 ? wd[k] : 0.0,
+                              a32, a64, ad);
+            }
           }
         }
+        ++c;
+        w_rel += (int32_t)kChunk;
+        r_rel += (int32_t)kChunk;
+        pre += kChunk;
+        continue;
       }
-      w_rel += (int32_t)kChunk;
-      r_rel += (int32_t)kChunk;
-      pre += kChunk;
+      const int32_t c_end = c + nrun;
+      const int32_t r_pf_end = hi_rel - kS1Depth * (int32_t)kChunk;   // refill while r_rel < r_pf_end
+#pragma unroll 1
+      for (; c < c_end; ++c) {
+        cp_async_wait<kS1Depth - 1>();
+        const uint32_t slot = my_slot + (uint32_t)(c & (kS1Depth - 1)) * kS1Stage;
+        const uint4 v = lds_v4(slot);
+        // one a for the whole packet (sorted by (a, b): first a == last a)
+        const bool one_a = __all_sync(0xffffffffu, ((v.x ^ (v.w >> 16)) & 0xFF00u) == 0u);
+        // v is in registers (the vote consumed it): the slot can be refilled
+        cp_async16_zfill(slot, pre, r_rel < r_pf_end);
+        cp_async_commit();
+        int32_t wi[kPacket];
+        double wd[kPacket];
+        if (WM != W_UNIT) load_weights<WM>(prm.w, lo + r_rel, wi, wd);
+        if (one_a) {
+          s1_packet_same_a<NC, WM>(v, baseA, baseB, cstride, s_lut, s_lut2, wi, wd, a32, a64, ad);
+        } else {
+          const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+          for (int k = 0; k < kPacket; ++k) {
+            const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
+            s1_eval<NC, WM>(baseA, baseB, cstride, s_lut, r, WM == W_INT32 ? wi[k] : 0,
+                            WM == W_F64 ? wd[k] : 0.0, a32, a64, ad);
+          }
+        }
+        r_rel += (int32_t)kChunk;
+        pre += kChunk;
+      }
+      w_rel += nrun * (int32_t)kChunk;
     }
   }
   cp_async_wait<0>();
@@ -316,6 +361,6 @@ int launch_stream1_nc(lxy_ctx* c, int nc, const Stream1Params& prm, int grid, si
 }
 
 inline size_t stream1_smem(int nc, int n) {
-  return (size_t)nc * ((n + kBlk - 1) & ~(kBlk - 1)) * 2 + 64 + (size_t)kS1Warps * nc * 8 + 16 + 512 +
+  return (size_t)nc * ((n + kBlk - 1) & ~(kBlk - 1)) * 2 + 64 + kS1Lut2Bytes + (size_t)kS1Warps * nc * 8 + 16 + 512 +
          (size_t)kS1Depth * kS1Stage;  // (alignment slack) table | lut | warp sums | start tile | record ring
 }
