@@ -125,6 +125,44 @@ __device__ __forceinline__ void s1_packet_same_a(const uint4 v, uint32_t baseA, 
   }
 }
 
+// Eight records inside the segment whose a's are two NEIGHBOURING ids (a packet that straddles the
+// change from a to a + 1; with ~250 records per a, as at n = 20,000 / 200 M records, two thirds of
+// the warps hold such a lane): both rows of table A are fetched, every record selects by comparing
+// its a with the first one.  Sorted records: a_last - a_first <= 1 means no third value.
+template <int NC, int WM>
+__device__ __forceinline__ void s1_packet_two_a(const uint4 v, uint32_t baseA, uint32_t baseB,
+                                                uint32_t cstride, const uint8_t* lut, const uint8_t* lut2,
+                                                const int32_t (&wi)[kPacket], const double (&wd)[kPacket],
+                                                int32_t (&a32)[NC], int64_t (&a64)[NC], double (&ad)[NC]) {
+  const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+  const uint32_t oa0 = (v.x >> 7) & 0x1FEu, oa1 = (v.w >> 23) & 0x1FEu;
+  const uint32_t rep = (v.x & 0xFF00u) * 0x00010001u;   // the first a at bits 8..15 and 24..31
+  int32_t p0[NC], p1[NC];
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    p0[c] = (kBias + 1) - lds_s16((baseA + c * cstride) | oa0);
+    p1[c] = (kBias + 1) - lds_s16((baseA + c * cstride) | oa1);
+  }
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const uint32_t x = words[q] ^ rep;
+    const bool f0 = (x & 0xFF00u) == 0u, f1 = (x & 0xFF000000u) == 0u;
+    const uint32_t o0 = (words[q] << 1) & 0x1FEu, o1 = (words[q] >> 15) & 0x1FEu;
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      const uint32_t bb = baseB + c * cstride;
+      const int32_t v0 = __viaddmin_s32_relu(lds_s16(bb | o0), f0 ? p0[c] : p1[c], kMiss + 1);
+      const int32_t v1 = __viaddmin_s32_relu(lds_s16(bb | o1), f1 ? p0[c] : p1[c], kMiss + 1);
+      if (WM == W_UNIT) {
+        a32[c] += lut2[v0 * kS1LutSide + v1];
+      } else {
+        s1_acc<WM>(lut[v0], wi[2 * q], wd[2 * q], a32[c], a64[c], ad[c]);
+        s1_acc<WM>(lut[v1], wi[2 * q + 1], wd[2 * q + 1], a32[c], a64[c], ad[c]);
+      }
+    }
+  }
+}
+
 struct S1Tile {  // a tile cursor: tile t = (I, J) holds records [.., end)
   int64_t t, end;
   int32_t I, J;
@@ -177,14 +215,30 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
   if (lo < hi) {
     const int64_t ntiles = (int64_t)prm.nblk * (prm.nblk + 1) / 2;
     for (int64_t t = tid; t < ntiles; t += kS1Threads)
-      if (prm.tile_start[t] <= lo && lo < prm.tile_start[t + 1]) s_tile[0] = t;
+      if (prm.tile_start[t] <= lo) {
+        const int64_t e = prm.tile_start[t + 1];
+        if (lo < e) { s_tile[0] = t; s_tile[1] = e; }
+      }
   }
   // ---- placement tables: pos[perm[i]] = i (pad candidates: identity, discarded) ----
   if (tid < kLutLen) s_lut[tid] = c_lut100[tid];
-  if (WM == W_UNIT)
+  if (WM == W_UNIT) {  // from the shared copy: divergent indices serialise on the constant cache (4 us)
+    __syncthreads();
     for (int i = tid; i < kS1Lut2Len; i += kS1Threads)
-      s_lut2[i] = (uint8_t)(c_lut100[i / kS1LutSide] + c_lut100[i % kS1LutSide]);
+      s_lut2[i] = (uint8_t)(s_lut[i / kS1LutSide] + s_lut[i % kS1LutSide]);
+  }
   int bad = 0;
+  // validation slice of this CTA (pos[perm[i]] == i for all i <=> the row is a permutation; CTA k
+  // checks slice k): its first element per thread is requested before the build, so that the check
+  // behind the barrier does not wait for global memory again
+  const int32_t vi0 = (int32_t)((int64_t)n * blockIdx.x / gridDim.x), vi1 = (int32_t)((int64_t)n * (blockIdx.x + 1) / gridDim.x);
+  constexpr int kVPre = NC <= 2 ? NC : 0;
+  int32_t vpre[kVPre > 0 ? kVPre : 1];
+  if (kVPre > 0 && prm.validate) {
+#pragma unroll
+    for (int c = 0; c < kVPre; ++c)
+      vpre[c] = (c < prm.P && vi0 + tid < vi1) ? prm.perm[(size_t)c * n + vi0 + tid] : -1;
+  }
 #pragma unroll 1
   for (int c = 0; c < NC; ++c) {
     const int32_t* row = prm.perm + (size_t)c * n;
@@ -195,11 +249,15 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
     }
   }
   __syncthreads();
-  if (prm.validate) {  // pos[perm[i]] == i for all i <=> the row is a permutation; CTA k checks slice k
-    const int32_t i0 = (int32_t)((int64_t)n * blockIdx.x / gridDim.x), i1 = (int32_t)((int64_t)n * (blockIdx.x + 1) / gridDim.x);
+  if (prm.validate) {
+#pragma unroll
+    for (int c = 0; c < kVPre; ++c) {
+      const int32_t cid = vpre[c];
+      if ((uint32_t)cid < (uint32_t)n && sPos[c * nstride + cid] != (int16_t)(32767 - (vi0 + tid))) bad |= 2;
+    }
     for (int c = 0; c < prm.P && c < NC; ++c) {
       const int32_t* row = prm.perm + (size_t)c * n;
-      for (int i = i0 + tid; i < i1; i += kS1Threads) {
+      for (int i = vi0 + tid + (c < kVPre ? kS1Threads : 0); i < vi1; i += kS1Threads) {
         const int32_t cid = row[i];
         if ((uint32_t)cid < (uint32_t)n && sPos[c * nstride + cid] != (int16_t)(32767 - i)) bad |= 2;
       }
@@ -226,7 +284,7 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
       cur.I = a;
     }
     cur.J = cur.I + (int32_t)(cur.t - tile_row_start(cur.I, prm.nblk));
-    cur.end = prm.tile_start[cur.t + 1];
+    cur.end = s_tile[1];
     // 32-bit offsets relative to `lo` from here on (a share is far below 2^31 records)
     const int32_t hi_rel = (int32_t)(hi - lo);
     int32_t w_rel = warp * (int32_t)kSlice;                   // first record of the warp's slice
@@ -296,6 +354,8 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
         if (WM != W_UNIT) load_weights<WM>(prm.w, lo + r_rel, wi, wd);
         if (one_a) {
           s1_packet_same_a<NC, WM>(v, baseA, baseB, cstride, s_lut, s_lut2, wi, wd, a32, a64, ad);
+        } else if (__all_sync(0xffffffffu, (v.w >> 24) - ((v.x >> 8) & 0xFFu) <= 1u)) {
+          s1_packet_two_a<NC, WM>(v, baseA, baseB, cstride, s_lut, s_lut2, wi, wd, a32, a64, ad);
         } else {
           const uint32_t words[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
