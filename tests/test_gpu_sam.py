@@ -149,3 +149,29 @@ def test_context_store_straight_from_sam(tmp_path):
     q.write_bytes(b"@HD\tVN:1.0\n")
     with N.Context(0) as c, pytest.raises(N.LxyError):
         N.NativeLinks.from_sam(str(q), ctx=c)
+
+
+def test_text_staged_through_the_pinned_ring(tmp_path, monkeypatch):
+    """Large texts reach the device through a page-locked ring filled by four threads (links_parse.cu,
+    h2d_through_ring); the threshold is lowered so that a 21 MB text (5 pieces + a partial one) takes it."""
+    p = str(tmp_path / "big.sam")
+    with open(p, "wb") as f:
+        f.write(S.random_sam(31, 230_000, 700).encode())
+    assert os.path.getsize(p) > 5 * (4 << 20)
+    monkeypatch.setenv("LXY_PARSE_RING_MIN_BYTES", "1")
+    g = N.NativeLinks.from_sam(p, device=0)
+    monkeypatch.setenv("LXY_PARSE_NO_RING", "1")
+    g2 = N.NativeLinks.from_sam(p, device=0)
+    monkeypatch.delenv("LXY_PARSE_NO_RING")
+    _same_table(g, g2)
+    _same_table(g, N.NativeLinks.from_sam(p))
+    out = str(tmp_path / "big.links")                           # the .links loader shares the staging
+    g.Write(out)
+    with open(out, "ab") as f:
+        f.write((b"# padding\n" * 10 + b"x y 1.5\n") * 200_000)
+    assert os.path.getsize(out) > (4 << 20)
+    a = N.NativeLinks(out, device=0)
+    monkeypatch.delenv("LXY_PARSE_RING_MIN_BYTES")
+    b = N.NativeLinks(out)
+    assert a.Decode(range(a.Size())) == b.Decode(range(b.Size()))
+    assert [x.tolist() for x in a.records()] == [x.tolist() for x in b.records()]
