@@ -640,8 +640,10 @@ static int prefer_max_carveout(lxy_ctx* c) {
 
 // Streaming regime (scaff_stream1.cuh): head look-ups on the side stream, one pass over the records
 // with lane = record, the same fixed-order finish as the batch path.
+// `first` / `last`: position of this pass in a multi-pass call (scaff_score_enqueue): the error flags
+// are cleared once, the timing events bracket all passes.
 static int scaff_score_stream1(lxy_ctx* c, const int32_t* perm_dev, int32_t P, int nc, size_t smem,
-                               double* out_dev, int64_t* x100_dev) {
+                               double* out_dev, int64_t* x100_dev, bool first, bool last) {
   ScaffLinks& S = c->scaff;
   cudaStream_t st = c->stream;
   const int n = S.n;
@@ -652,8 +654,10 @@ static int scaff_score_stream1(lxy_ctx* c, const int32_t* perm_dev, int32_t P, i
     LXY_CUDA(cudaMemcpyToSymbolAsync(c_lut100, h_lut100, kLutLen, 0, cudaMemcpyHostToDevice, st));
     g_lut_loaded[c->cfg.device & 63] = true;
   }
-  LXY_CUDA(cudaMemsetAsync(c->d_flag.p, 0, 64, st));
-  LXY_CUDA(record_timing_event(c, 0));
+  if (first) {
+    LXY_CUDA(cudaMemsetAsync(c->d_flag.p, 0, 64, st));
+    LXY_CUDA(record_timing_event(c, 0));
+  }
   {
     cudaStream_t s2 = c->stream2;
     LXY_CUDA(cudaEventRecord(c->ev_fork, st));
@@ -667,7 +671,7 @@ static int scaff_score_stream1(lxy_ctx* c, const int32_t* perm_dev, int32_t P, i
     LXY_CUDA(cudaGetLastError());
     LXY_CUDA(cudaEventRecord(c->ev_join, s2));
   }
-  LXY_CUDA(record_timing_event(c, 1));
+  if (first) LXY_CUDA(record_timing_event(c, 1));
   // persistent CTAs: as many as fit per SM (<= 2 x 512 threads), each an equal share of the packets
   const int per_sm = (2 * (smem + 1024) <= (size_t)c->max_smem_optin) ? 2 : 1;
   const int64_t npk = (S.L + kPacket - 1) / kPacket;
@@ -689,18 +693,19 @@ static int scaff_score_stream1(lxy_ctx* c, const int32_t* perm_dev, int32_t P, i
   LXY_TRY(S.wmode == W_UNIT ? launch_stream1_nc<W_UNIT>(c, nc, prm, (int)grid, smem)
         : S.wmode == W_INT32 ? launch_stream1_nc<W_INT32>(c, nc, prm, (int)grid, smem)
                              : launch_stream1_nc<W_F64>(c, nc, prm, (int)grid, smem));
-  LXY_CUDA(record_timing_event(c, 2));
+  if (last) LXY_CUDA(record_timing_event(c, 2));
   LXY_CUDA(cudaStreamWaitEvent(st, c->ev_join, 0));
   const int splits = (int)grid;
   if (S.wmode == W_UNIT) k_scaff_finish<W_UNIT><<<(P + 7) / 8, 256, 0, st>>>(P, nc, splits, c->d_partial.p, c->d_corr.p, out_dev, x100_dev);
   else if (S.wmode == W_INT32) k_scaff_finish<W_INT32><<<(P + 7) / 8, 256, 0, st>>>(P, nc, splits, c->d_partial.p, c->d_corr.p, out_dev, x100_dev);
   else k_scaff_finish<W_F64><<<(P + 7) / 8, 256, 0, st>>>(P, nc, splits, c->d_partial.p, c->d_corr.p, out_dev, x100_dev);
   LXY_CUDA(cudaGetLastError());
-  LXY_CUDA(record_timing_event(c, 3));
-  c->timing.launches = 3;
+  if (last) LXY_CUDA(record_timing_event(c, 3));
+  const int64_t link_bytes = S.L * (2 + (S.wmode == W_INT32 ? 4 : S.wmode == W_F64 ? 8 : 0));
+  c->timing.launches = (first ? 0 : c->timing.launches) + 3;
   c->timing.grid = (int)grid;
-  c->timing.link_bytes = S.L * (2 + (S.wmode == W_INT32 ? 4 : S.wmode == W_F64 ? 8 : 0));
-  c->timing.table_bytes = (int64_t)grid * nc * n * 4;
+  c->timing.link_bytes = (first ? 0 : c->timing.link_bytes) + link_bytes;
+  c->timing.table_bytes = (first ? 0 : c->timing.table_bytes) + (int64_t)grid * nc * n * 4;
   return LXY_OK;
 }
 
@@ -779,12 +784,30 @@ static int scaff_score_enqueue(lxy_ctx* c, const int32_t* perm_dev, int32_t P, d
   ScaffLinks& S = c->scaff;
   cudaStream_t st = c->stream;
   const int n = S.n;
-  // ---- streaming regime: up to 8 candidates (a lone Score() call is a batch of one) ----
-  if (P <= 8 && n <= 65536 && !(c->cfg.flags & LXY_FLAG_NO_STREAM1)) {
+  // ---- streaming regime: up to 8 candidates per pass (a lone Score() call is a batch of one) ----
+  // Small populations - the reference's own GA runs 40 orderings (scaff.go:94) - take several passes.
+  // Measured on B200 (tools/p_sweep.py, n = 5,000; 5 M and 200 M records): a pass of 8 costs about
+  // 26 + 1.8 L us (L in millions of records), the batch kernel 48 + 13.8 L us for anything up to 32
+  // orderings and little more up to 64: passes win up to 3 of them (24 orderings) at 5 M records and up
+  // to 7 (56) at 200 M - 16 orderings against 200 M records 2.80 -> 0.79 ms, 40 orderings 2.81 -> 1.93 ms.
+  constexpr int kS1Pass = 8;
+  const double l_m = (double)S.L * 1e-6;
+  int s1_passes = (int)((48.0 + 13.8 * l_m) / (26.0 + 1.8 * l_m));
+  s1_passes = s1_passes < 1 ? 1 : s1_passes > 7 ? 7 : s1_passes;
+  const int s1_max = s1_passes * kS1Pass;
+  if (P <= s1_max && n <= 65536 && !(c->cfg.flags & LXY_FLAG_NO_STREAM1)) {
     int nc = 1;
-    while (nc < P) nc *= 2;
-    const size_t smem = stream1_smem(nc, n);
-    if (smem <= (size_t)c->max_smem_optin) return scaff_score_stream1(c, perm_dev, P, nc, smem, out_dev, x100_dev);
+    while (nc < P && nc < kS1Pass) nc *= 2;
+    if (stream1_smem(nc, n) <= (size_t)c->max_smem_optin) {
+      for (int32_t p0 = 0; p0 < P; p0 += kS1Pass) {
+        const int32_t pp = P - p0 < kS1Pass ? P - p0 : kS1Pass;
+        int ncp = 1;
+        while (ncp < pp) ncp *= 2;
+        LXY_TRY(scaff_score_stream1(c, perm_dev + (size_t)p0 * n, pp, ncp, stream1_smem(ncp, n), out_dev + p0,
+                                    x100_dev ? x100_dev + p0 : nullptr, p0 == 0, p0 + kS1Pass >= P));
+      }
+      return LXY_OK;
+    }
   }
   // table mode: 0 = 16-bit entries (pos + 21 | -pos) summed modulo 2^16 (n <= 65515, see eval_record),
   // 128 candidates in the 128 KB of tables; 1 = 32-bit entries, 64 candidates.

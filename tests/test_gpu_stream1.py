@@ -121,3 +121,34 @@ def test_stream1_full_size_single_genome_score(ctxs):
         _, xb = cb.scaff_score_batch(g, want_x100=True)
         assert xs.tolist() == xb.tolist()
     assert cs.scaff_score_batch(true)[0] < cs.scaff_score_batch(rnd)[0]
+
+
+@pytest.mark.parametrize("n,L,P,passes", [(300, 1_000_000, 9, 2), (300, 1_000_000, 16, 2), (700, 6_000_000, 13, 2),
+                                          (700, 6_000_000, 24, 3), (5000, 6_000_000, 17, 3)])
+def test_small_populations_take_several_passes(ctxs, n, L, P, passes):
+    """Populations above 8 run as passes of <= 8 orderings while that beats the batch kernel (the
+    reference's own GA holds 40 orderings, scaff.go:94): same integers as the batch kernel and the
+    oracle, the error flags survive the passes, a repeated call (graph replay) returns the same."""
+    cs, cb = ctxs
+    a, b, w = S.scaff_links(n, L, 31)
+    perms = S.scaff_population(n, P, 131)
+    _, ox100 = O.scaff_score_links_batch(n, a, b, w, perms, nthreads=8)
+    cs.set_links(n, a, b, None)
+    cb.set_links(n, a, b, None)
+    got, x100 = cs.scaff_score_batch(perms, want_x100=True)
+    assert cs.timing()["launches"] == 3 * passes
+    gb, xb = cb.scaff_score_batch(perms, want_x100=True)
+    assert x100.tolist() == ox100.tolist()
+    assert x100.tolist() == xb.tolist() and got.tolist() == gb.tolist()
+    for _ in range(3):                                      # the second identical call is captured, then replayed
+        g2, x2 = cs.scaff_score_batch(perms, want_x100=True)
+        assert x2.tolist() == ox100.tolist() and g2.tolist() == got.tolist()
+    bad = perms.copy()
+    bad[P - 1, 5] = bad[P - 1, 6]                           # a repeated id in the LAST pass
+    with pytest.raises(N.LxyError):
+        cs.scaff_score_batch(bad)
+    bad = perms.copy()
+    bad[0, 5] = bad[0, 6]                                   # ... and in the FIRST one (flags are cleared once)
+    with pytest.raises(N.LxyError):
+        cs.scaff_score_batch(bad)
+    assert cs.scaff_score_batch(perms).tolist() == got.tolist()
