@@ -562,6 +562,7 @@ __global__ void k_scaff_finish(int32_t P, int32_t cand, int32_t splits,
 }
 
 #include "scaff_stream1.cuh"
+#include "scaff_stream1p.cuh"
 
 // ---- integer checks -----------------------------------------------------------------------------
 __global__ void k_positions(const int32_t* __restrict__ perm, int32_t P, int32_t n,
@@ -647,6 +648,10 @@ static int scaff_score_stream1(lxy_ctx* c, const int32_t* perm_dev, int32_t P, i
   ScaffLinks& S = c->scaff;
   cudaStream_t st = c->stream;
   const int n = S.n;
+  // two orderings per table word where that is exact (scaff_stream1p.cuh)
+  static const bool no_pack = getenv("LXY_S1_NOPACK") != nullptr;  // experiments
+  const bool pack = !no_pack && stream1p_applies(S.wmode, nc, n) && stream1p_smem(nc, n) <= (size_t)c->max_smem_optin;
+  if (pack) smem = stream1p_smem(nc, n);
   LXY_TRY(c->d_flag.reserve(64));
   LXY_TRY(c->d_corr.reserve(8 * (size_t)P));
   LXY_TRY(prefer_max_carveout(c));
@@ -690,7 +695,8 @@ static int scaff_score_stream1(lxy_ctx* c, const int32_t* perm_dev, int32_t P, i
   prm.nblk = S.nblk;
   prm.P = P;
   prm.validate = (c->cfg.flags & LXY_FLAG_NO_VALIDATE) ? 0 : 1;
-  LXY_TRY(S.wmode == W_UNIT ? launch_stream1_nc<W_UNIT>(c, nc, prm, (int)grid, smem)
+  LXY_TRY(pack ? launch_stream1p_nc(c, nc, prm, (int)grid, smem)
+        : S.wmode == W_UNIT ? launch_stream1_nc<W_UNIT>(c, nc, prm, (int)grid, smem)
         : S.wmode == W_INT32 ? launch_stream1_nc<W_INT32>(c, nc, prm, (int)grid, smem)
                              : launch_stream1_nc<W_F64>(c, nc, prm, (int)grid, smem));
   if (last) LXY_CUDA(record_timing_event(c, 2));
@@ -786,15 +792,19 @@ static int scaff_score_enqueue(lxy_ctx* c, const int32_t* perm_dev, int32_t P, d
   const int n = S.n;
   // ---- streaming regime: up to 8 candidates per pass (a lone Score() call is a batch of one) ----
   // Small populations - the reference's own GA runs 40 orderings (scaff.go:94) - take several passes.
-  // Measured on B200 (tools/p_sweep.py, n = 5,000; 5 M and 200 M records): a pass of 8 costs about
-  // 26 + 1.8 L us (L in millions of records), the batch kernel 48 + 13.8 L us for anything up to 32
-  // orderings and little more up to 64: passes win up to 3 of them (24 orderings) at 5 M records and up
-  // to 7 (56) at 200 M - 16 orderings against 200 M records 2.80 -> 0.79 ms, 40 orderings 2.81 -> 1.93 ms.
+  // Measured on B200 (tools/p_sweep.py, n = 5,000; 5 M and 200 M records; L in millions of records):
+  // a pass of 8 costs about 26 + 1.27 L us on the packed kernel (scaff_stream1p.cuh; 26 + 1.8 L us on
+  // k_scaff_stream1), one group of the batch kernel 48 + 13.8 L us up to 32 orderings, 48 + 14.5 L up
+  // to 64, 48 + 17.9 L up to 128.  Against 200 M records: 16 orderings 2.80 -> 0.55 ms, 40 orderings
+  // 2.81 -> 1.34 ms, 96 orderings 3.6 -> 3.3 ms; at 5 M records passes win up to 24 orderings.
   constexpr int kS1Pass = 8;
-  const double l_m = (double)S.L * 1e-6;
-  int s1_passes = (int)((48.0 + 13.8 * l_m) / (26.0 + 1.8 * l_m));
-  s1_passes = s1_passes < 1 ? 1 : s1_passes > 7 ? 7 : s1_passes;
-  const int s1_max = s1_passes * kS1Pass;
+  int s1_max = kS1Pass;
+  if (P > kS1Pass && P <= 128) {
+    const double l_m = (double)S.L * 1e-6;
+    const double pass_us = 26.0 + (stream1p_applies(S.wmode, kS1Pass, n) ? 1.27 : 1.8) * l_m;
+    const double batch_us = 48.0 + (P <= 32 ? 13.8 : P <= 64 ? 14.5 : 17.9) * l_m;
+    if ((double)((P + kS1Pass - 1) / kS1Pass) * pass_us < batch_us) s1_max = P;
+  }
   if (P <= s1_max && n <= 65536 && !(c->cfg.flags & LXY_FLAG_NO_STREAM1)) {
     int nc = 1;
     while (nc < P && nc < kS1Pass) nc *= 2;

@@ -152,3 +152,33 @@ def test_small_populations_take_several_passes(ctxs, n, L, P, passes):
     with pytest.raises(N.LxyError):
         cs.scaff_score_batch(bad)
     assert cs.scaff_score_batch(perms).tolist() == got.tolist()
+
+
+@pytest.mark.parametrize("n,streamed", [(65515, False), (37000, True), (32768, True), (32769, True), (18000, True)])
+def test_two_orderings_per_table_word_extreme_differences(ctxs, n, streamed):
+    """2..8 orderings with unit weights interleave two placement tables in one word and take differences
+    modulo 2^16 (scaff_stream1p.cuh; used up to n = 32,768, k_scaff_stream1 above while the tables fit
+    the shared memory, the batch kernel beyond).  Identity and reversed orderings
+    put the records (0, n-1), (0, n-2), (1, n-1) at the extreme differences, neighbours at the weighted ones."""
+    cs, cb = ctxs
+    rng = np.random.default_rng(n)
+    a = np.concatenate([[0, 0, 1, 5, 7], rng.integers(0, n, 200_000)]).astype(np.uint32)
+    b = np.concatenate([[n - 1, n - 2, n - 1, 6, 27], rng.integers(0, n, 200_000)]).astype(np.uint32)
+    keep = a != b
+    a, b = a[keep], b[keep]
+    near = rng.integers(0, n - 21, 100_000).astype(np.uint32)          # pairs at the six weighted steps
+    step = rng.choice([1, 2, 3, 5, 11, 20], 100_000).astype(np.uint32)
+    a, b = np.concatenate([a, near]), np.concatenate([b, near + step])
+    w = np.ones(len(a))
+    ident = np.arange(n, dtype=np.int32)
+    perms = np.stack([ident, ident[::-1], np.roll(ident, 1), rng.permutation(n).astype(np.int32)])
+    for P in (2, 3, 4):
+        _, ox100 = O.scaff_score_links_batch(n, a, b, w, perms[:P], nthreads=8)
+        cs.set_links(n, a, b, None)
+        cb.set_links(n, a, b, None)
+        got, x100 = cs.scaff_score_batch(perms[:P], want_x100=True)
+        if streamed and (P == 2 or n <= 18000):
+            assert cs.timing()["launches"] == 3
+        gb, xb = cb.scaff_score_batch(perms[:P], want_x100=True)
+        assert x100.tolist() == ox100.tolist()
+        assert x100.tolist() == xb.tolist() and got.tolist() == gb.tolist()
