@@ -42,12 +42,14 @@ if mode == "s1":      # streaming regime at config-3 size: one ordering against 
     import os
     n, L = 5000, int(float(os.environ.get("S1_L", "2e8")))
     ta, tb, order = bench.gen_links(n, L, 3, torch.device("cuda", 0))
-    perm = torch.from_numpy(np.random.default_rng(5).permutation(n).astype(np.int32)).cuda()
-    out = torch.zeros(8, dtype=torch.float64, device="cuda")
+    sP = int(os.environ.get("S1_P", "1"))      # S1_P=8: one pass of the packed kernel (k_scaff_stream1p)
+    rng5 = np.random.default_rng(5)
+    perm = torch.from_numpy(np.stack([rng5.permutation(n) for _ in range(sP)]).astype(np.int32)).cuda()
+    out = torch.zeros(max(8, sP), dtype=torch.float64, device="cuda")
     with N.Context(0) as ctx:
         ctx.set_links_dev(n, L, ta.data_ptr(), tb.data_ptr(), None)
         for _ in range(steps):
-            ctx.scaff_score_batch_dev(perm.data_ptr(), 1, out.data_ptr(), None)
+            ctx.scaff_score_batch_dev(perm.data_ptr(), sP, out.data_ptr(), None)
         print(ctx.timing())
     sys.exit(0)
 a, b, w = S.scaff_links(n, L, 2)
