@@ -12,8 +12,7 @@
 // i.e. one table look-up, one min-add, one look-up of the decay pair and one add serve TWO orderings
 // (k_scaff_stream1: one of each per ordering) - the batch kernel's per-lane arithmetic (eval_record)
 // with the roles of lanes and records exchanged.  Exact while n <= 65,515 (a difference cannot alias
-// into [0, 42] modulo 2^16); used for n <= 32,768 (stream1p_applies below); larger n and weighted
-// records stay on k_scaff_stream1.
+// into [0, 42] modulo 2^16); larger n and weighted records stay on k_scaff_stream1.
 #pragma once
 
 constexpr uint32_t kS1pCap = (uint32_t)(kMiss + 2) | ((uint32_t)(kMiss + 2) << 16);   // 43 | 43 << 16
@@ -160,8 +159,11 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1p(Stream1Params 
       const int32_t* row = prm.perm + (size_t)c * n;
       for (int i = i0 + tid; i < i1; i += kS1Threads) {
         const int32_t cid = row[i];
-        if ((uint32_t)cid < (uint32_t)n &&
-            (((uint32_t)sNeg[((size_t)(c >> 1) * nstride + cid) * 2 + (c & 1)] + (uint32_t)i) & 0xFFFFu) != 0u) bad |= 2;
+        if ((uint32_t)cid < (uint32_t)n) {  // the whole word through an opaque 32-bit load, compared in 32 bits
+          const uint32_t word = lds_u32(sbase + (uint32_t)(c >> 1) * pstride + (uint32_t)cid * 4u);
+          const uint32_t got = (c & 1) ? (word >> 16) : (word & 0xFFFFu);
+          if (got != ((0u - (uint32_t)i) & 0xFFFFu)) bad |= 2;
+        }
       }
     }
   }
@@ -308,9 +310,12 @@ inline int launch_stream1p_nc(lxy_ctx* c, int nc, const Stream1Params& prm, int 
   }
 }
 
-// The packed kernel's domain: unit weights, 2..8 orderings, n <= 32,768.  The arithmetic is exact up to
-// n = 65,515 (differences cannot alias modulo 2^16) and the scores agree with the batch kernel there,
-// but the in-kernel permutation check reports a false "not a permutation" for n > 32,768 (seen at
-// n = 32,769..37,000 with two orderings; cause not found in round 1), so that range stays on
-// k_scaff_stream1 - the tables of two orderings only fit the shared memory up to n ~ 38,000 anyway.
-inline bool stream1p_applies(int wmode, int nc, int n) { return wmode == W_UNIT && nc >= 2 && n <= 32768; }
+// The packed kernel's domain: unit weights, 2..8 orderings, differences that cannot alias modulo 2^16
+// (n <= 65,515; the tables of two orderings fit the shared memory up to n ~ 38,000).  The permutation
+// check reads whole table words through lds_u32: written as a comparison of the uint16_t element with
+// (uint16_t)(0 - i), nvcc 12.9 produced code that reported a mismatch for exactly i = 32,768 (the value
+// whose negation modulo 2^16 is itself), found with a device printf on the box.
+inline bool stream1p_applies(int wmode, int nc, int n) {
+  static const int max_n = getenv("LXY_S1P_MAX_N") ? atoi(getenv("LXY_S1P_MAX_N")) : 65536 - (kBias + 1);  // experiments
+  return wmode == W_UNIT && nc >= 2 && n <= max_n;
+}

@@ -157,8 +157,9 @@ def test_small_populations_take_several_passes(ctxs, n, L, P, passes):
 @pytest.mark.parametrize("n,streamed", [(65515, False), (37000, True), (32768, True), (32769, True), (18000, True)])
 def test_two_orderings_per_table_word_extreme_differences(ctxs, n, streamed):
     """2..8 orderings with unit weights interleave two placement tables in one word and take differences
-    modulo 2^16 (scaff_stream1p.cuh; used up to n = 32,768, k_scaff_stream1 above while the tables fit
-    the shared memory, the batch kernel beyond).  Identity and reversed orderings
+    modulo 2^16 (scaff_stream1p.cuh; exact up to n = 65,515; the tables of two orderings fit the shared
+    memory up to n ~ 38,000, the batch kernel runs beyond).  n = 32,769 holds the ordering index 32,768,
+    whose negation modulo 2^16 is itself (a compiler-sensitive spot of the permutation check).  Identity and reversed orderings
     put the records (0, n-1), (0, n-2), (1, n-1) at the extreme differences, neighbours at the weighted ones."""
     cs, cb = ctxs
     rng = np.random.default_rng(n)
