@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define LXY_ABI_VERSION 1
+#define LXY_ABI_VERSION 2
 
 typedef enum lxy_status {
   LXY_OK = 0,
@@ -48,11 +48,18 @@ typedef enum lxy_status {
 
 #define LXY_FLAG_NO_GRAPH 8u    /* never replay a repeated scoring call from a captured CUDA graph */
 
-/* which kernel scores the R-profile (lxy_scaff_score_batch*) */
-#define LXY_PATH_STREAM 0 /* stream every record for every candidate (north_star design; default)  */
-#define LXY_PATH_PAIRS 1  /* aggregate the records into a dense pair table at set_links and score a  \
-                             candidate with the reference's own 6n table gathers (cost independent  \
-                             of the number of records; same results)                                */
+/* which kernels score the R-profile (lxy_scaff_score_batch*); every path returns the same integers */
+#define LXY_PATH_AUTO 0   /* default (a zero-initialised lxy_cfg): chosen at lxy_ctx_set_links* from what is  \
+                             known then - the dense pair table when it fits (4 n^2 bytes, 8 n^2 with real      \
+                             weights, at most 16 GiB and a quarter of the free device memory) and the link   \
+                             set is dense enough for it to win (>= 256 records per contig); else the record \
+                             stream, with the records of a pair summed into one int32-weighted record        \
+                             (Links.Add, links.go:149-177) when that at least halves the stream.            \
+                             lxy_ctx_path reports the choice.                                               */
+#define LXY_PATH_STREAM 1 /* stream every record as given for every candidate (north_star design)             */
+#define LXY_PATH_PAIRS 2  /* aggregate the records into a dense pair table at set_links and score a         \
+                             candidate with the reference's own 6n table gathers (cost independent of the    \
+                             number of records)                                                             */
 
 typedef struct lxy_cfg {
   int32_t device;   /* CUDA ordinal                                                          */
@@ -87,6 +94,10 @@ void lxy_ctx_destroy(lxy_ctx* ctx);
 int lxy_ctx_get_timing(lxy_ctx* ctx, lxy_timing* out);
 int lxy_ctx_stream(lxy_ctx* ctx, void** cuda_stream); /* cudaStream_t the kernels run on       */
 int lxy_ctx_sync(lxy_ctx* ctx);
+/* The path the scaffolding scorer of this context takes (LXY_PATH_STREAM or LXY_PATH_PAIRS; for a
+ * LXY_PATH_AUTO context the choice made by the last lxy_ctx_set_links*), and the number of records the
+ * streaming kernels read per candidate (smaller than n_links when duplicates were summed). */
+int lxy_ctx_path(lxy_ctx* ctx, int32_t* path, int64_t* stream_records);
 
 /* ---- scaffolding, R-profile = the reference scorer (scaff.go:246-310) -------------------------
  * Link records (a, b, w): ids in [0, n_ids), w nullable (= 1 per record, what
@@ -150,6 +161,49 @@ int lxy_phase_score_batch(lxy_ctx* ctx, const uint8_t* genes, int32_t P, int64_t
                           double* out_f64);
 int lxy_phase_score_batch_dev(lxy_ctx* ctx, const uint8_t* genes_dev, int32_t P,
                               int64_t* out_i64_dev, double* out_f64_dev);
+/* The same scores from a ROW-PACKED population: words[P][ceil(n_ids / 32)], bit (i & 31) of word
+ * [p][i >> 5] = gene i of candidate p (bits past n_ids are ignored).  One eighth of the bytes over PCIe:
+ * the Go shim packs the []bool rows it copies anyway. */
+int lxy_phase_score_batch_bits(lxy_ctx* ctx, const uint32_t* words, int32_t P, int64_t* out_i64,
+                               double* out_f64);
+int lxy_phase_score_batch_bits_dev(lxy_ctx* ctx, const uint32_t* words_dev, int32_t P,
+                                   int64_t* out_i64_dev, double* out_f64_dev);
+
+/* ---- multi-GPU: one context per device, NCCL on the context's own stream ----------------------------
+ * north_star: "the population is sharded across GPUs for large populations, and the links are sharded
+ * with an NCCL allreduce of partial fitness for huge link sets; only the per-generation score vector
+ * moves between GPUs".  The reference's host is ONE Go process (scaff.go:88-94): it creates one context
+ * per device and either calls lxy_comm_init_all, or - one process per GPU (torchrun, MPI) - rank 0 calls
+ * lxy_comm_unique_id, ships the 128 bytes to the other ranks by any means, and every rank calls
+ * lxy_comm_init_rank.  NCCL (libnccl.so.2) is loaded on first use; single-GPU callers never need it.
+ * All ranks must make the same sharded calls in the same order; with several contexts in one process
+ * each context needs its own host thread (a goroutine locked to an OS thread), because a call returns
+ * only when its collective has completed.  Errors found on any rank (bad gene, range) are returned on
+ * every rank.  world <= 64. */
+#define LXY_COMM_ID_BYTES 128
+int lxy_comm_unique_id(void* id128);
+int lxy_comm_init_rank(lxy_ctx* ctx, int32_t world, int32_t rank, const void* id128);
+int lxy_comm_init_all(lxy_ctx* const* ctxs, int32_t world); /* rank i = ctxs[i], one process      */
+int lxy_comm_destroy(lxy_ctx* ctx);
+int lxy_comm_info(lxy_ctx* ctx, int32_t* world, int32_t* rank); /* (1, 0) without a communicator  */
+/* Rows [first, first + count) of `total` that rank `rank` of `world` scores (balanced contiguous split). */
+int lxy_comm_slice(int32_t total, int32_t world, int32_t rank, int32_t* first, int32_t* count);
+
+#define LXY_SHARD_POPULATION 0 /* links replicated on every rank; rank r scores its slice of the        \
+                                  population, ncclAllGather of the score slices                        */
+#define LXY_SHARD_LINKS 1      /* every rank holds a share of the records (its own lxy_ctx_set_links*)   \
+                                  and scores the whole population against it; exact int64 partial sums   \
+                                  are combined with ncclAllReduce (bit-identical to the unsharded result), \
+                                  fp64 partials are all-gathered and added in rank order                */
+/* perm[P][n_ids] is the WHOLE population on every rank (host pointer; _dev: resident on this rank's
+ * device); out[P] / x100[P] receive the whole result on every rank.  The host entry point moves each
+ * population row over PCIe once per box, not once per GPU: in LXY_SHARD_LINKS mode a rank uploads 1/world
+ * of the rows and the rest arrives by ncclAllGather over NVLink; in LXY_SHARD_POPULATION mode a rank
+ * uploads only the rows it scores. */
+int lxy_scaff_score_sharded(lxy_ctx* ctx, int32_t mode, const int32_t* perm, int32_t P, double* out,
+                            int64_t* x100);
+int lxy_scaff_score_sharded_dev(lxy_ctx* ctx, int32_t mode, const int32_t* perm_dev, int32_t P,
+                                double* out_dev, int64_t* x100_dev);
 
 /* ---- rank / elite (go-galib sorts by Score(); lower is better, ties keep population order) --- */
 int lxy_rank(const double* scores, int32_t P, int32_t* order);
@@ -272,6 +326,11 @@ int lxy_ga_init(lxy_ga* ga, const void* first, int32_t randomize);
 /* Population from the caller (popsize rows, host memory); scored and sorted. */
 int lxy_ga_set_population(lxy_ga* ga, const void* genes);
 int lxy_ga_optimize(lxy_ga* ga, int32_t generations);
+/* Shard the scoring of lxy_ga_init / lxy_ga_set_population / lxy_ga_optimize over the context's
+ * communicator (LXY_GA_SCAFF only): mode LXY_SHARD_POPULATION / LXY_SHARD_LINKS, or -1 for local scoring
+ * (the default).  Every rank runs the same deterministic plan and makes the same children; only the
+ * score vector crosses NVLink. */
+int lxy_ga_set_sharding(lxy_ga* ga, int32_t mode);
 /* One generation in two halves, for callers that score the children themselves (e.g. sharded
  * over several GPUs): begin makes the children on the device, the caller fills the score arrays
  * (fitness, lower is better; x100 optional, unused by the engine), end sorts and truncates. */
@@ -314,7 +373,8 @@ int lxy_eval_phasing_dev(lxy_ctx* ctx, const uint8_t* genes, const uint8_t* key,
  * without the quality metrics and plots): LoadLinks, the GA with the reference's parameters when
  * prm is NULL (population 40, PBreed .2, PMutate .6, tournament(0.7, 5), shift + switch + invert),
  * Decode, WriteScaffolding (one contig name per line).  lxy_phase_file = Phase (phase.go:34-111):
- * population 10, PBreed .7, PMutate .7, invert + switch; output `name<TAB>A|B` (phase.go:151-167).
+ * population 10, PBreed .7, PMutate .7, invert + switch; output `name 1` / `name 0`, one block per line, as writePhasing emits and
+ * readPhasing parses (phase.go:119-167).
  * best_score (nullable) receives Best().Score(). */
 int lxy_scaffold_file(const char* links_path, const char* out_path, int32_t iterations,
                       const lxy_ga_params* prm, int32_t device, double* best_score);

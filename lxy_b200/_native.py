@@ -36,10 +36,16 @@ SYMBOLS = [
     "lxy_links_from_sam", "lxy_links_from_sam_gpu", "lxy_scaffold_links_from_sam", "lxy_ctx_load_sam",
     "lxy_scaffold_file", "lxy_phase_file", "lxy_eval_scaffolding", "lxy_eval_phasing",
     "lxy_eval_phasing_dev",
+    "lxy_ctx_path", "lxy_phase_score_batch_bits", "lxy_phase_score_batch_bits_dev",
+    "lxy_comm_unique_id", "lxy_comm_init_rank", "lxy_comm_init_all", "lxy_comm_destroy", "lxy_comm_info",
+    "lxy_comm_slice", "lxy_scaff_score_sharded", "lxy_scaff_score_sharded_dev", "lxy_ga_set_sharding",
 ]
 
 ACC_AUTO, ACC_F64, ACC_INT = 0, 1, 2
-PATH_STREAM, PATH_PAIRS = 0, 1
+PATH_AUTO, PATH_STREAM, PATH_PAIRS = 0, 1, 2
+SHARD_POPULATION, SHARD_LINKS = 0, 1
+COMM_ID_BYTES = 128
+ABI_VERSION = 2
 FLAG_NO_VALIDATE = 1
 FLAG_NO_STREAM1 = 2
 FLAG_NO_GRAPH = 8
@@ -187,6 +193,18 @@ def lib():
         "lxy_eval_scaffolding": (i32, [vp, vp, vp, i32, i32, vp]),
         "lxy_eval_phasing": (i32, [vp, vp, vp, i32, i32, vp]),
         "lxy_eval_phasing_dev": (i32, [vp, vp, vp, vp, i32, i32, vp]),
+        "lxy_ctx_path": (i32, [vp, C.POINTER(i32), C.POINTER(i64)]),
+        "lxy_phase_score_batch_bits": (i32, [vp, vp, i32, vp, vp]),
+        "lxy_phase_score_batch_bits_dev": (i32, [vp, vp, i32, vp, vp]),
+        "lxy_comm_unique_id": (i32, [vp]),
+        "lxy_comm_init_rank": (i32, [vp, i32, i32, vp]),
+        "lxy_comm_init_all": (i32, [C.POINTER(vp), i32]),
+        "lxy_comm_destroy": (i32, [vp]),
+        "lxy_comm_info": (i32, [vp, C.POINTER(i32), C.POINTER(i32)]),
+        "lxy_comm_slice": (i32, [i32, i32, i32, C.POINTER(i32), C.POINTER(i32)]),
+        "lxy_scaff_score_sharded": (i32, [vp, i32, vp, i32, vp, vp]),
+        "lxy_scaff_score_sharded_dev": (i32, [vp, i32, vp, i32, vp, vp]),
+        "lxy_ga_set_sharding": (i32, [vp, i32]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -208,6 +226,35 @@ def _c(arr, dtype):
     return None if arr is None else np.ascontiguousarray(arr, dtype=dtype)
 
 
+def pack_bits(genes):
+    """genes[P][n] of 0/1 -> row-packed uint32 words [P][ceil(n / 32)], LSB first (what
+    lxy_phase_score_batch_bits takes; the Go shim does the same while it copies the []bool rows)."""
+    genes = np.ascontiguousarray(genes, np.uint8)
+    P, n = genes.shape
+    W = (n + 31) // 32
+    padded = np.zeros((P, W * 32), np.uint8)
+    padded[:, :n] = genes != 0
+    return np.ascontiguousarray(np.packbits(padded, axis=1, bitorder="little")).view(np.uint32).reshape(P, W)
+
+
+def comm_unique_id():
+    buf = C.create_string_buffer(COMM_ID_BYTES)
+    _check(lib().lxy_comm_unique_id(buf))
+    return buf.raw
+
+
+def comm_init_all(ctxs):
+    """One process, one context per device: rank i = ctxs[i] (lxy_comm_init_all)."""
+    arr = (C.c_void_p * len(ctxs))(*[c._h.value for c in ctxs])
+    _check(lib().lxy_comm_init_all(arr, len(ctxs)))
+
+
+def comm_slice(total, world, rank):
+    f, n = C.c_int32(0), C.c_int32(0)
+    _check(lib().lxy_comm_slice(total, world, rank, C.byref(f), C.byref(n)))
+    return f.value, n.value
+
+
 def device_count():
     n = C.c_int32(0)
     rc = lib().lxy_device_count(C.byref(n))
@@ -224,7 +271,7 @@ def rank(scores):
 class Context:
     """One lxy_ctx: a CUDA device, its stream, the resident link stores."""
 
-    def __init__(self, device=0, acc_mode=ACC_AUTO, flags=0, path=PATH_STREAM):
+    def __init__(self, device=0, acc_mode=ACC_AUTO, flags=0, path=PATH_AUTO):
         self._h = C.c_void_p()
         cfg = Cfg(device, acc_mode, flags, path)
         _check(lib().lxy_ctx_create(C.byref(cfg), C.byref(self._h)))
@@ -262,6 +309,40 @@ class Context:
 
     def sync(self):
         _check(lib().lxy_ctx_sync(self._h))
+
+    def path(self):
+        """(LXY_PATH_STREAM | LXY_PATH_PAIRS chosen for the current scaffolding store, records the
+        streaming kernels read per candidate)."""
+        p, r = C.c_int32(0), C.c_int64(0)
+        _check(lib().lxy_ctx_path(self._h, C.byref(p), C.byref(r)))
+        return p.value, r.value
+
+    # -- multi-GPU (comm.cu) -----------------------------------------------------------------
+    def comm_init_rank(self, world, rank, id128):
+        buf = C.create_string_buffer(bytes(id128), COMM_ID_BYTES)
+        _check(lib().lxy_comm_init_rank(self._h, world, rank, buf))
+
+    def comm_destroy(self):
+        _check(lib().lxy_comm_destroy(self._h))
+
+    def comm_info(self):
+        w, r = C.c_int32(0), C.c_int32(0)
+        _check(lib().lxy_comm_info(self._h, C.byref(w), C.byref(r)))
+        return w.value, r.value
+
+    def scaff_score_sharded(self, mode, perms, want_x100=False):
+        """The whole population on every rank (host memory) -> the whole score vector on every rank."""
+        perms = _c(perms, np.int32)
+        if perms.ndim != 2 or perms.shape[1] != self.n:
+            raise ValueError(f"perms must be [P][{self.n}]")
+        P = perms.shape[0]
+        out, x100 = np.zeros(P, np.float64), np.zeros(P, np.int64)
+        _check(lib().lxy_scaff_score_sharded(self._h, mode, _p(perms), P, _p(out), _p(x100)))
+        return (out, x100) if want_x100 else out
+
+    def scaff_score_sharded_dev(self, mode, perm_ptr, P, out_ptr, x100_ptr=None):
+        _check(lib().lxy_scaff_score_sharded_dev(self._h, mode, C.c_void_p(perm_ptr), P, C.c_void_p(out_ptr),
+                                                 C.c_void_p(x100_ptr) if x100_ptr else None))
 
     # -- scaffolding -----------------------------------------------------------------------
     def set_links(self, n_ids, a, b, w=None):
@@ -371,6 +452,22 @@ class Context:
         _check(lib().lxy_phase_score_batch(self._h, _p(genes), P, _p(oi), _p(of)))
         return oi, of
 
+    def phase_score_batch_bits(self, words):
+        """words[P][ceil(n / 32)] uint32, bit (i & 31) of word [p][i >> 5] = gene i (pack_bits)."""
+        words = _c(words, np.uint32)
+        W = (self.phase_n + 31) // 32
+        if words.ndim != 2 or words.shape[1] != W:
+            raise ValueError(f"words must be [P][{W}]")
+        P = words.shape[0]
+        oi, of = np.zeros(P, np.int64), np.zeros(P, np.float64)
+        _check(lib().lxy_phase_score_batch_bits(self._h, _p(words), P, _p(oi), _p(of)))
+        return oi, of
+
+    def phase_score_batch_bits_dev(self, words_ptr, P, out_i64_ptr, out_f64_ptr):
+        _check(lib().lxy_phase_score_batch_bits_dev(self._h, C.c_void_p(words_ptr), P,
+                                                    C.c_void_p(out_i64_ptr) if out_i64_ptr else None,
+                                                    C.c_void_p(out_f64_ptr) if out_f64_ptr else None))
+
     def phase_score_batch_dev(self, genes_ptr, P, out_i64_ptr, out_f64_ptr):
         _check(lib().lxy_phase_score_batch_dev(self._h, C.c_void_p(genes_ptr), P,
                                                C.c_void_p(out_i64_ptr) if out_i64_ptr else None,
@@ -416,6 +513,10 @@ class GA:
 
     def optimize(self, generations=1):
         _check(lib().lxy_ga_optimize(self._h, generations))
+
+    def set_sharding(self, mode):
+        """mode SHARD_POPULATION / SHARD_LINKS over the context's communicator, -1: local scoring."""
+        _check(lib().lxy_ga_set_sharding(self._h, mode))
 
     def step_begin(self):
         """-> (n_children, children device address, scores device address, x100 device address)"""

@@ -21,6 +21,11 @@ void set_error(const char* fmt, ...) {
   g_err = buf;
 }
 
+std::mutex& config_mutex() {
+  static std::mutex mu;
+  return mu;
+}
+
 void drop_score_graphs(lxy_ctx* c) {
   for (auto& g : c->graphs) {
     if (g.exec) cudaGraphExecDestroy(g.exec);
@@ -45,7 +50,7 @@ int pin_reserve(lxy_ctx* c, size_t bytes) {
 // offset pin_off, in 2 MB chunks copied by up to four host threads, each chunk's DMA queued as soon as
 // it is staged so the copy engine overlaps the remaining memcpys.  The caller's memory is not retained
 // past the return of the entry point in either case (the entry points synchronise before returning).
-int stage_h2d(lxy_ctx* c, void* dst_dev, const void* src, size_t bytes, size_t pin_off) {
+int stage_h2d(lxy_ctx* c, void* dst_dev, const void* src, size_t bytes, size_t pin_off) {  // declared in common.cuh
   if (bytes == 0) return LXY_OK;
   cudaPointerAttributes attr;
   if (cudaPointerGetAttributes(&attr, src) == cudaSuccess && attr.type == cudaMemoryTypeHost) {
@@ -91,6 +96,15 @@ static float ev_ms(cudaEvent_t a, cudaEvent_t b) {
 
 }  // namespace lxy
 
+// The scorer of the context's R-profile store: the dense pair table when the store has one
+// (LXY_PATH_PAIRS, or LXY_PATH_AUTO's choice), else the record stream.
+namespace lxy {
+int scaff_dispatch(lxy_ctx* c, const int32_t* perm_dev, int32_t P, double* out_dev, int64_t* x100_dev) {
+  if (c->scaff.ready && c->scaff.path == LXY_PATH_PAIRS) return pairs_score(c, perm_dev, P, out_dev, x100_dev);
+  return scaff_score(c, perm_dev, nullptr, P, out_dev, x100_dev);
+}
+}  // namespace lxy
+
 using namespace lxy;
 
 #define CHECK_CTX(c)                                                    \
@@ -132,7 +146,7 @@ int lxy_ctx_create(const lxy_cfg* cfg, lxy_ctx** out) {
   lxy_cfg cf{};
   if (cfg) cf = *cfg;
   if (cf.acc_mode < LXY_ACC_AUTO || cf.acc_mode > LXY_ACC_INT) { set_error("bad acc_mode"); return LXY_ERR_ARG; }
-  if (cf.path != LXY_PATH_STREAM && cf.path != LXY_PATH_PAIRS) { set_error("bad path"); return LXY_ERR_ARG; }
+  if (cf.path != LXY_PATH_AUTO && cf.path != LXY_PATH_STREAM && cf.path != LXY_PATH_PAIRS) { set_error("bad path"); return LXY_ERR_ARG; }
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || ndev <= 0) {
@@ -175,13 +189,14 @@ int lxy_ctx_create(const lxy_cfg* cfg, lxy_ctx** out) {
 
 void lxy_ctx_destroy(lxy_ctx* c) {
   if (!c) return;
+  if (c->comm) lxy_comm_destroy(c);
   cudaSetDevice(c->cfg.device);
   if (c->stream) cudaStreamSynchronize(c->stream);
   if (c->stream2) cudaStreamSynchronize(c->stream2);
   DevBuf* bufs[] = {&c->scaff.rec, &c->scaff.w, &c->scaff.tile_start, &c->scaff.len, &c->scaff.xa, &c->scaff.xb, &c->scaff.dense,
                     &c->phase.rec, &c->phase.w, &c->d_perm, &c->d_ori, &c->d_out, &c->d_x100,
                     &c->d_posA, &c->d_posB, &c->d_partial, &c->d_corr, &c->d_flag, &c->d_genes,
-                    &c->d_gbits, &c->d_tmp0, &c->d_tmp1, &c->d_tmp2, &c->d_tmp3, &c->d_start};
+                    &c->d_gbits, &c->d_tmp0, &c->d_tmp1, &c->d_tmp2, &c->d_tmp3, &c->d_start, &c->d_shard, &c->d_gather};
   for (DevBuf* b : bufs) b->release();
   if (c->h_pin) cudaFreeHost(c->h_pin);
   for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
@@ -217,14 +232,21 @@ int lxy_ctx_sync(lxy_ctx* c) {
   return LXY_OK;
 }
 
+int lxy_ctx_path(lxy_ctx* c, int32_t* path, int64_t* stream_records) {
+  CHECK_CTX(c);
+  if (!c->scaff.ready) { set_error("ctx_path: links not set"); return LXY_ERR_STATE; }
+  if (path) *path = c->scaff.path;
+  if (stream_records) *stream_records = c->scaff.L;
+  return LXY_OK;
+}
+
 // ---- scaffolding --------------------------------------------------------------------------------
 int lxy_ctx_set_links(lxy_ctx* c, int32_t n_ids, int64_t n_links, const uint32_t* a,
                       const uint32_t* b, const double* w) {
   CHECK_CTX(c);
   LinkInput in;
   in.n = n_ids; in.L = n_links; in.a = a; in.b = b; in.w = w;
-  LXY_TRY(build_scaff_links(c, in));
-  return c->cfg.path == LXY_PATH_PAIRS ? build_pair_table(c) : LXY_OK;
+  return build_scaff_links(c, in);
 }
 
 int lxy_ctx_set_links_dev(lxy_ctx* c, int32_t n_ids, int64_t n_links, const uint32_t* a_dev,
@@ -232,8 +254,7 @@ int lxy_ctx_set_links_dev(lxy_ctx* c, int32_t n_ids, int64_t n_links, const uint
   CHECK_CTX(c);
   LinkInput in;
   in.n = n_ids; in.L = n_links; in.a = a_dev; in.b = b_dev; in.w = w_dev; in.on_device = true;
-  LXY_TRY(build_scaff_links(c, in));
-  return c->cfg.path == LXY_PATH_PAIRS ? build_pair_table(c) : LXY_OK;
+  return build_scaff_links(c, in);
 }
 
 static int finish_flags(lxy_ctx* c, const char* what) {
@@ -247,10 +268,6 @@ static int finish_flags(lxy_ctx* c, const char* what) {
 }
 
 
-static int scaff_dispatch(lxy_ctx* c, const int32_t* perm_dev, int32_t P, double* out_dev, int64_t* x100_dev) {
-  if (c->cfg.path == LXY_PATH_PAIRS) return pairs_score(c, perm_dev, P, out_dev, x100_dev);
-  return scaff_score(c, perm_dev, nullptr, P, out_dev, x100_dev);
-}
 
 int lxy_scaff_score_batch_dev(lxy_ctx* c, const int32_t* perm_dev, int32_t P, double* out_dev,
                               int64_t* x100_dev) {
@@ -483,6 +500,43 @@ int lxy_phase_score_batch(lxy_ctx* c, const uint8_t* genes, int32_t P, int64_t* 
   LXY_CUDA(cudaEventRecord(c->ev[5], c->stream));
   c->timing_pending = 2;
   LXY_TRY(finish_flags(c, "phase score"));
+  if (out_f64) std::memcpy(out_f64, hout, 8 * (size_t)P);
+  if (out_i64) std::memcpy(out_i64, hout + 8 * (size_t)P, 8 * (size_t)P);
+  return LXY_OK;
+}
+
+// Row-packed populations: 1/8 of the bytes of the byte-per-gene entry point over PCIe.
+int lxy_phase_score_batch_bits_dev(lxy_ctx* c, const uint32_t* words_dev, int32_t P, int64_t* out_i64_dev,
+                                   double* out_f64_dev) {
+  CHECK_CTX(c);
+  if (P < 0 || (P > 0 && (!words_dev || (!out_i64_dev && !out_f64_dev)))) { set_error("phase_score_batch_bits_dev: bad argument"); return LXY_ERR_ARG; }
+  if (P == 0) return LXY_OK;
+  LXY_TRY(phase_score_any(c, nullptr, words_dev, P, out_i64_dev, out_f64_dev));
+  c->timing_pending = 1;
+  return LXY_OK;   // a packed bit is 0 or 1 by construction: nothing to validate
+}
+
+int lxy_phase_score_batch_bits(lxy_ctx* c, const uint32_t* words, int32_t P, int64_t* out_i64,
+                               double* out_f64) {
+  CHECK_CTX(c);
+  if (P < 0 || (P > 0 && (!words || (!out_i64 && !out_f64)))) { set_error("phase_score_batch_bits: bad argument"); return LXY_ERR_ARG; }
+  if (!c->phase.ready) { set_error("phase_score_batch_bits: links not set"); return LXY_ERR_STATE; }
+  if (P == 0) return LXY_OK;
+  const size_t W = ((size_t)c->phase.n + 31) / 32;
+  const size_t gbytes = 4 * W * (size_t)P;
+  LXY_TRY(pin_reserve(c, gbytes + 16 * (size_t)P));
+  LXY_TRY(c->d_genes.reserve(gbytes));
+  LXY_TRY(c->d_out.reserve(8 * (size_t)P));
+  LXY_TRY(c->d_x100.reserve(8 * (size_t)P));
+  LXY_CUDA(cudaEventRecord(c->ev[4], c->stream));
+  LXY_TRY(stage_h2d(c, c->d_genes.p, words, gbytes, 0));
+  LXY_TRY(phase_score_any(c, nullptr, c->d_genes.as<uint32_t>(), P, c->d_x100.as<int64_t>(), c->d_out.as<double>()));
+  char* hout = (char*)c->h_pin + gbytes;
+  LXY_CUDA(cudaMemcpyAsync(hout, c->d_out.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, c->stream));
+  LXY_CUDA(cudaMemcpyAsync(hout + 8 * (size_t)P, c->d_x100.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, c->stream));
+  LXY_CUDA(cudaEventRecord(c->ev[5], c->stream));
+  c->timing_pending = 2;
+  LXY_CUDA(cudaStreamSynchronize(c->stream));
   if (out_f64) std::memcpy(out_f64, hout, 8 * (size_t)P);
   if (out_i64) std::memcpy(out_i64, hout + 8 * (size_t)P, 8 * (size_t)P);
   return LXY_OK;

@@ -56,7 +56,9 @@ struct ScaffLinks {
   bool ready = false;
   bool gprofile = false;
   int32_t n = 0;            // ids
-  int64_t L = 0;            // records
+  int64_t L = 0;            // records of the store (after summing duplicates, when that was done)
+  int64_t L_in = 0;         // records handed to set_links
+  int path = LXY_PATH_STREAM;  // what a LXY_PATH_AUTO context chose for this store (STREAM or PAIRS)
   int32_t nblk = 0;         // ceil(n / kBlk)
   int64_t ntiles = 0;       // nblk * (nblk + 1) / 2
   int wmode = W_UNIT;
@@ -129,9 +131,18 @@ struct lxy_ctx {
       d_gbits, d_tmp0, d_tmp1, d_tmp2, d_tmp3, d_start;
   void* h_pin = nullptr;      // pinned staging for populations / scores
   size_t h_pin_cap = 0;
+  // multi-GPU (comm.cu): NCCL communicator of this context's device, collectives run on `stream`
+  void* comm = nullptr;       // ncclComm_t
+  int32_t world = 1, rank = 0;
+  lxy::DevBuf d_shard, d_gather;  // send / receive buffers of the score collectives
+  uint64_t agree_version = 0; // link-store version the ranks last agreed an accumulation mode for
+  int agree_f64 = 0;          // some rank's shard carries non-integral weights
 };
 
 namespace lxy {
+// Guards the process-global "kernel attributes set for device d" flags next to the launch helpers
+// (two contexts of one device may be driven from two threads; the context mutex does not cover them).
+std::mutex& config_mutex();
 int pin_reserve(lxy_ctx* c, size_t bytes);
 void drop_score_graphs(lxy_ctx* c);
 // timing event k of the context on its main stream; inside a capture the record must be an
@@ -171,6 +182,12 @@ int scaffg_link_distances(lxy_ctx* c, int64_t L, const uint32_t* a, const uint32
                           const uint32_t* b, const uint32_t* xb, const uint64_t* start_dev,
                           const int32_t* pos_dev, const uint8_t* ori_dev, uint64_t* dist_dev);
 
+// comm.cu
+int sharded_score_dev(lxy_ctx* c, int32_t mode, const int32_t* perm_dev, int32_t P, double* out_dev,
+                      int64_t* x100_dev, bool check_flags);
+int scaff_dispatch(lxy_ctx* c, const int32_t* perm_dev, int32_t P, double* out_dev, int64_t* x100_dev);
+int stage_h2d(lxy_ctx* c, void* dst_dev, const void* src, size_t bytes, size_t pin_off);
+
 // pair_kernels.cu
 int build_pair_table(lxy_ctx* c);
 int pairs_score(lxy_ctx* c, const int32_t* perm_dev, int32_t P, double* out_dev, int64_t* x100_dev);
@@ -178,4 +195,6 @@ int pairs_score(lxy_ctx* c, const int32_t* perm_dev, int32_t P, double* out_dev,
 // phase_kernels.cu
 int phase_score(lxy_ctx* c, const uint8_t* genes_dev, int32_t P, int64_t* out_i64_dev,
                 double* out_f64_dev);
+int phase_score_any(lxy_ctx* c, const uint8_t* genes_dev, const uint32_t* packed_dev, int32_t P,
+                    int64_t* out_i64_dev, double* out_f64_dev);
 }  // namespace lxy

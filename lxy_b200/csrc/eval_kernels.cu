@@ -249,6 +249,7 @@ int lxy_eval_scaffolding(lxy_ctx* c, const int32_t* perm, const int32_t* key_ran
   k_check_perm<<<(n + 255) / 256, 256, 0, st>>>(c->d_tmp0.as<int32_t>(), n, c->d_tmp1.as<int32_t>(), c->d_flag.as<int>());
   const int smem = 2 * n;
   static bool configured[64] = {};
+  std::lock_guard<std::mutex> cfg_lock(config_mutex());
   if (!configured[c->cfg.device & 63]) {
     LXY_CUDA(cudaFuncSetAttribute(k_eval_scaff, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 65536));
     configured[c->cfg.device & 63] = true;

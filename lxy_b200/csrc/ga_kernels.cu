@@ -25,6 +25,7 @@ struct lxy_ga {
   bool ready = false;       // population scored and sorted
   bool in_step = false;     // between step_begin and step_end
   int32_t n_children = 0;
+  int32_t shard_mode = -1;  // LXY_SHARD_* over the context's communicator, -1: score locally
   lxy::DevBuf pop[2], score[2], x100[2];
   lxy::DevBuf child, child_score, child_x100, plan, count, order, inv, scratch;
   cudaEvent_t ev[4]{};
@@ -272,8 +273,9 @@ int ga_score(lxy_ga* g, const void* genes, int32_t first, int32_t count, double*
   const char* rows = (const char*)genes + (size_t)first * g->n * g->esz;
   g->stats.scored += count;
   if (g->prm.kind == LXY_GA_PHASE) return phase_score(c, (const uint8_t*)rows, count, x + first, out + first);
-  if (c->cfg.path == LXY_PATH_PAIRS) return pairs_score(c, (const int32_t*)rows, count, out + first, x + first);
-  return scaff_score(c, (const int32_t*)rows, nullptr, count, out + first, x + first);
+  if (g->shard_mode >= 0)   // every rank holds the same rows; only the scores cross NVLink (comm.cu)
+    return sharded_score_dev(c, g->shard_mode, (const int32_t*)rows, count, out + first, x + first, false);
+  return scaff_dispatch(c, (const int32_t*)rows, count, out + first, x + first);
 }
 
 int ga_check_flags(lxy_ga* g, const char* what) {
@@ -493,6 +495,15 @@ int lxy_ga_optimize(lxy_ga* g, int32_t generations) {
     LXY_TRY(ga_score(g, g->child.p, 0, g->n_children, g->child_score.as<double>(), g->child_x100.as<int64_t>()));
     LXY_TRY(ga_end(g));
   }
+  return LXY_OK;
+}
+
+int lxy_ga_set_sharding(lxy_ga* g, int32_t mode) {
+  CHECK_GA(g);
+  if (mode < -1 || mode > LXY_SHARD_LINKS) { set_error("ga_set_sharding: bad mode"); return LXY_ERR_ARG; }
+  if (mode >= 0 && g->prm.kind != LXY_GA_SCAFF) { set_error("ga_set_sharding: only the scaffolding scorer shards"); return LXY_ERR_ARG; }
+  if (mode >= 0 && g->ctx->world > 1 && !g->ctx->comm) { set_error("ga_set_sharding: the context has no communicator"); return LXY_ERR_STATE; }
+  g->shard_mode = mode;
   return LXY_OK;
 }
 

@@ -7,6 +7,9 @@
 // blocks and, inside a tile, sorted by (a_local, b_local) — a blocked CSR.  A record is then two
 // bytes.  The sort uses cub::DeviceRadixSort (CUDA toolkit library; build time, not the hot path).
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_reduce.cuh>
+#include <cub/iterator/constant_input_iterator.cuh>
+#include <cub/iterator/transform_input_iterator.cuh>
 
 #include <algorithm>
 #include <cmath>
@@ -134,6 +137,22 @@ __global__ void k_gather_x(int64_t L, const uint32_t* __restrict__ idx, const ui
   }
 }
 
+// Duplicate summing (LXY_PATH_AUTO): weight of sorted record i as int64
+struct WeightAt {
+  const double* w;
+  __host__ __device__ int64_t operator()(uint32_t k) const { return (int64_t)w[k]; }
+};
+// aggregated weights back to int32; bit 8 of *flag: a sum does not fit
+__global__ void k_narrow_w(int64_t L, const int64_t* __restrict__ agg, int32_t* __restrict__ out, int* __restrict__ flag) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < L; i += stride) {
+    const int64_t v = agg[i];
+    if (v > 2147483647ll || v < -2147483648ll) atomicOr(flag, 8);
+    out[i] = (int32_t)v;
+  }
+}
+
 __global__ void k_iota(int64_t L, uint32_t* __restrict__ out) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -150,17 +169,19 @@ int build_scaff_links(lxy_ctx* c, const LinkInput& in) {
   const int32_t n = in.n;
   const int64_t L = in.L;
   const bool G = (in.len != nullptr);
+  if (n > (1 << 24)) { set_error("set_links: n_ids %d exceeds 2^24", n); return LXY_ERR_RANGE; }
+  if (L >= (int64_t)1 << 32) { set_error("set_links: more than 2^32-1 records per context"); return LXY_ERR_RANGE; }
   if (n <= 0 || L < 0 || (L > 0 && (!in.a || !in.b))) { set_error("set_links: bad argument"); return LXY_ERR_ARG; }
   if (G && (L > 0 && (!in.xa || !in.xb))) { set_error("set_links_g: null offsets"); return LXY_ERR_ARG; }
   if (G && in.unit == 0) { set_error("set_links_g: unit must be > 0"); return LXY_ERR_ARG; }
-  if (n > (1 << 24)) { set_error("set_links: n_ids %d exceeds 2^24", n); return LXY_ERR_RANGE; }
-  if (L >= (int64_t)1 << 32) { set_error("set_links: more than 2^32-1 records per context"); return LXY_ERR_RANGE; }
   cudaStream_t st = c->stream;
   const int sm = c->sm_count;
 
   S.gprofile = G;
   S.n = n;
   S.L = L;
+  S.L_in = L;
+  S.path = LXY_PATH_STREAM;
   S.nblk = (n + kBlk - 1) / kBlk;
   S.ntiles = (int64_t)S.nblk * (S.nblk + 1) / 2;
   S.unit = in.unit;
@@ -272,11 +293,71 @@ int build_scaff_links(lxy_ctx* c, const LinkInput& in) {
   }
   const uint64_t* sorted = kb.Current();
 
+  // ---- LXY_PATH_AUTO: the records of a pair summed into one (Links.Add, links.go:149-177) ----
+  // R-profile records carry nothing beyond their pair, so a run of equal sorted keys is one record with
+  // the run's summed weight; exact in integers (skipped for real weights, whose summation order the
+  // raw stream defines).  Adopted when it at least halves the stream: the weighted kernel variants pay
+  // for the int32 multiply, the unit-weight ones do not.
+  bool aggregated = false;
+  if (c->cfg.path == LXY_PATH_AUTO && !G && wmode != W_F64 && L >= 2) {
+    uint64_t* ukeys = kb.Alternate();
+    DevBuf dagg, druns;
+    auto drop = [&]() { dagg.release(); druns.release(); };
+    rc = dagg.reserve(8 * (size_t)L);
+    if (rc == LXY_OK) rc = druns.reserve(64);
+    if (rc != LXY_OK) { drop(); cleanup(); return rc; }
+    size_t rb = 0;
+    cudaError_t e;
+    if (wmode == W_UNIT) {
+      cub::ConstantInputIterator<int64_t> ones(1);
+      e = cub::DeviceReduce::ReduceByKey(nullptr, rb, sorted, ukeys, ones, dagg.as<int64_t>(), druns.as<int64_t>(), cub::Sum(), (int64_t)L, st);
+      if (e == cudaSuccess && dscratch.reserve(rb) != LXY_OK) e = cudaErrorMemoryAllocation;
+      if (e == cudaSuccess)
+        e = cub::DeviceReduce::ReduceByKey(dscratch.p, rb, sorted, ukeys, ones, dagg.as<int64_t>(), druns.as<int64_t>(), cub::Sum(), (int64_t)L, st);
+    } else {
+      cub::TransformInputIterator<int64_t, WeightAt, const uint32_t*> wit(sorted_idx, WeightAt{w});
+      e = cub::DeviceReduce::ReduceByKey(nullptr, rb, sorted, ukeys, wit, dagg.as<int64_t>(), druns.as<int64_t>(), cub::Sum(), (int64_t)L, st);
+      if (e == cudaSuccess && dscratch.reserve(rb) != LXY_OK) e = cudaErrorMemoryAllocation;
+      if (e == cudaSuccess)
+        e = cub::DeviceReduce::ReduceByKey(dscratch.p, rb, sorted, ukeys, wit, dagg.as<int64_t>(), druns.as<int64_t>(), cub::Sum(), (int64_t)L, st);
+    }
+    int64_t runs = 0;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&runs, druns.p, 8, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) { set_error("set_links: duplicate summing failed: %s", cudaGetErrorString(e)); drop(); cleanup(); return LXY_ERR_CUDA; }
+    if (runs > 0 && runs * 2 <= L) {
+      rc = S.w.reserve(4 * (size_t)runs + 256);
+      if (rc != LXY_OK) { drop(); cleanup(); return rc; }
+      int* nf = c->d_flag.as<int>() + 2;
+      k_narrow_w<<<grid_for(runs, 256, sm), 256, 0, st>>>(runs, dagg.as<int64_t>(), S.w.as<int32_t>(), nf);
+      int f = 0;
+      e = cudaMemcpyAsync(&f, nf, sizeof(int), cudaMemcpyDeviceToHost, st);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+      if (e != cudaSuccess) { set_error("set_links: duplicate summing failed: %s", cudaGetErrorString(e)); drop(); cleanup(); return LXY_ERR_CUDA; }
+      if (!(f & 8)) {   // every sum fits int32: adopt
+        aggregated = true;
+        B_CUDA(cudaMemsetAsync(S.w.as<int32_t>() + runs, 0, 256, st));
+        S.L = runs;
+        S.wmode = wmode = W_INT32;
+        k_keys_to_rec<<<grid_for(runs, 256, sm), 256, 0, st>>>(runs, ukeys, S.rec.as<uint16_t>());
+        B_CUDA(cudaMemsetAsync(S.rec.as<uint16_t>() + runs, 0, 64 * sizeof(uint16_t), st));
+        k_tile_starts<<<(int)((S.ntiles + 1 + 255) / 256), 256, 0, st>>>(runs, S.ntiles, ukeys, S.tile_start.as<int64_t>());
+        B_CUDA(cudaGetLastError());
+        B_CUDA(cudaStreamSynchronize(st));
+      }
+    }
+    drop();
+  }
+
   // ---- the resident store ----
+  if (!aggregated) {
   k_keys_to_rec<<<grid_for(L, 256, sm), 256, 0, st>>>(L, sorted, S.rec.as<uint16_t>());
   B_CUDA(cudaMemsetAsync(S.rec.as<uint16_t>() + L, 0, 64 * sizeof(uint16_t), st));  // vector-load pad
   k_tile_starts<<<(int)((S.ntiles + 1 + 255) / 256), 256, 0, st>>>(L, S.ntiles, sorted, S.tile_start.as<int64_t>());
-  if (wmode == W_INT32) {
+  }
+  if (aggregated) {
+    // weights already in place
+  } else if (wmode == W_INT32) {
     B_TRY(S.w.reserve(4 * (size_t)L + 256));
     k_gather_w<int32_t><<<grid_for(L, 256, sm), 256, 0, st>>>(L, sorted_idx, w, S.w.as<int32_t>());
     B_CUDA(cudaMemsetAsync(S.w.as<int32_t>() + L, 0, 256, st));
@@ -306,6 +387,28 @@ int build_scaff_links(lxy_ctx* c, const LinkInput& in) {
   S.ready = true;
   ++S.version;
   drop_score_graphs(c);
+  if (G) return LXY_OK;
+  // ---- the path of this store ----
+  bool pairs = (c->cfg.path == LXY_PATH_PAIRS);
+  if (c->cfg.path == LXY_PATH_AUTO && S.L_in >= (int64_t)256 * n) {
+    // the dense table costs 6n gathers per candidate whatever the number of records (0.25 ms for 1,024
+    // candidates at n = 5,000); the stream ~1.35e-7 ms per record and candidate: the table wins from a
+    // few hundred records per contig on, when it fits next to everything else
+    const size_t bytes = (size_t)n * (size_t)n * (S.wmode == W_F64 ? 8 : 4);
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) { (void)cudaGetLastError(); free_b = 0; }
+    pairs = bytes <= ((size_t)16 << 30) && bytes <= free_b / 4;
+  }
+  if (pairs) {
+    const int prc = build_pair_table(c);
+    if (prc != LXY_OK) {
+      if (c->cfg.path == LXY_PATH_PAIRS) { S.ready = false; return prc; }
+      S.dense.release();   // AUTO: the stream is always available
+      S.dense_ready = false;
+    } else {
+      S.path = LXY_PATH_PAIRS;
+    }
+  }
   return LXY_OK;
 }
 

@@ -303,7 +303,8 @@ int lxy_ctx_set_links_from(lxy_ctx* c, const lxy_links* l, int32_t kind) {
 // Scaffold (scaff.go:68-141) as `lxy scaff infer` drives it (scaff/cmd.go:135-202 minus the quality
 // metrics and plots): LoadLinks -> GA (the reference's parameters unless prm is given) -> Decode ->
 // WriteScaffolding (one contig name per line, scaff.go:24-39).  Phase (phase.go:34-111):
-// LoadLinks -> GA over bitstrings -> DecodePhasing -> writePhasing (`name<TAB>A|B`, phase.go:151-167).
+// LoadLinks -> GA over bitstrings -> DecodePhasing -> writePhasing (`name 1` / `name 0`, space separated, phase.go:151-167;
+// readPhasing, phase.go:119-149, accepts exactly that).
 namespace {
 
 int run_ga_file(const char* links_path, const char* out_path, int32_t iterations, const lxy_ga_params* prm_in,
@@ -350,7 +351,7 @@ int run_ga_file(const char* links_path, const char* out_path, int32_t iterations
     } else {
       for (int32_t i = 0; i < n; ++i) {
         if (kind == LXY_GA_SCAFF) std::fprintf(f, "%s\n", lxy_links_name(l, gene32[(size_t)i]));
-        else std::fprintf(f, "%s\t%s\n", lxy_links_name(l, i), gene8[(size_t)i] ? "A" : "B");
+        else std::fprintf(f, "%s %d\n", lxy_links_name(l, i), gene8[(size_t)i] ? 1 : 0);
       }
       std::fclose(f);
     }

@@ -74,6 +74,57 @@ __global__ void k_phase_bits4(const uint8_t* __restrict__ genes, int32_t P, int3
   for (int t = 0; t < 4; ++t) out[(size_t)t * G] = word[t];
 }
 
+
+// One butterfly stage of the 32 x 32 bit transpose (LSB first): rows k and k + J exchange the bits whose
+// index has bit J set / clear.
+template <int J>
+__device__ __forceinline__ void transpose_stage(uint32_t (&a)[32], uint32_t m) {
+#pragma unroll
+  for (int h = 0; h < 16; ++h) {
+    const int k = ((h & ~(J - 1)) << 1) | (h & (J - 1));   // the 16 rows with bit J clear
+    const uint32_t t = ((a[k] >> J) ^ a[k + J]) & m;
+    a[k + J] ^= t;
+    a[k] ^= t << J;
+  }
+}
+
+// Row-packed populations (lxy_phase_score_batch_bits): words[P][W], W = ceil(n / 32), bit (i & 31) of
+// word [p][i >> 5] = gene i of candidate p.  One CTA per (block q of G groups, span of 32 words = 1,024
+// variants); warp s takes group q * G + s: lane L reads word w0 + L of each of the group's 32 rows
+// (128 contiguous bytes per row), transposes its 32 x 32 bit block in registers (five butterfly
+// stages), and the CTA writes the [variant][G] words of the span as one contiguous run.
+template <int G>
+__global__ void __launch_bounds__(32 * G) k_phase_bits_packed(const uint32_t* __restrict__ words, int32_t P,
+                                                              int32_t n, int32_t W, int32_t groups,
+                                                              uint32_t* __restrict__ bits) {
+  constexpr int kRow = 32 * G + 1;              // words of one lane's 32 variants, padded against bank conflicts
+  __shared__ uint32_t tile[32 * kRow];
+  const int s = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q = blockIdx.y, g = q * G + s;
+  const int w0 = blockIdx.x * 32;
+  uint32_t a[32];
+#pragma unroll
+  for (int r = 0; r < 32; ++r) {
+    const int p = g * 32 + r;
+    a[r] = (g < groups && p < P && w0 + lane < W) ? __ldg(words + (size_t)p * W + w0 + lane) : 0u;
+  }
+  // a[t] bit r  <-  a[r] bit t
+  transpose_stage<16>(a, 0x0000FFFFu);
+  transpose_stage<8>(a, 0x00FF00FFu);
+  transpose_stage<4>(a, 0x0F0F0F0Fu);
+  transpose_stage<2>(a, 0x33333333u);
+  transpose_stage<1>(a, 0x55555555u);
+#pragma unroll
+  for (int t = 0; t < 32; ++t) tile[lane * kRow + t * G + s] = a[t];
+  __syncthreads();
+  const int64_t i0 = (int64_t)w0 * 32;
+  uint32_t* out = bits + ((size_t)q * n + (size_t)i0) * G;
+  for (int k = threadIdx.x; k < 1024 * G; k += 32 * G) {
+    const int vloc = k / G, ss = k - vloc * G;
+    if (i0 + vloc < n) out[k] = tile[(vloc >> 5) * kRow + (vloc & 31) * G + ss];
+  }
+}
+
 template <int G> struct GeneWords;
 template <> struct GeneWords<1> { typedef uint32_t type; };
 template <> struct GeneWords<2> { typedef uint2 type; };
@@ -210,6 +261,12 @@ int build_phase_links(lxy_ctx* c, int32_t n, int64_t L, const uint32_t* a, const
 
 int phase_score(lxy_ctx* c, const uint8_t* genes_dev, int32_t P, int64_t* out_i64_dev,
                 double* out_f64_dev) {
+  return phase_score_any(c, genes_dev, nullptr, P, out_i64_dev, out_f64_dev);
+}
+
+// genes_dev: one byte per gene, [P][n]; or packed_dev: row-packed bits, [P][ceil(n / 32)] words.
+int phase_score_any(lxy_ctx* c, const uint8_t* genes_dev, const uint32_t* packed_dev, int32_t P,
+                    int64_t* out_i64_dev, double* out_f64_dev) {
   PhaseLinks& S = c->phase;
   if (!S.ready) { set_error("phase score: links not set"); return LXY_ERR_STATE; }
   cudaStream_t st = c->stream;
@@ -225,7 +282,13 @@ int phase_score(lxy_ctx* c, const uint8_t* genes_dev, int32_t P, int64_t* out_i6
   LXY_CUDA(cudaEventRecord(c->ev[0], st));
   LXY_CUDA(cudaMemsetAsync(c->d_corr.p, 0, 8 * (size_t)qgroups * G * 32, st));
   if (groups % G) LXY_CUDA(cudaMemsetAsync(c->d_gbits.p, 0, bits_bytes, st));   // words of the absent groups
-  if ((n & 3) == 0 && ((uintptr_t)genes_dev & 3) == 0) {
+  if (packed_dev) {
+    const int W = (n + 31) / 32;
+    const dim3 pg((unsigned)((W + 31) / 32), (unsigned)qgroups);
+    if (G == 4) k_phase_bits_packed<4><<<pg, 128, 0, st>>>(packed_dev, P, n, W, groups, c->d_gbits.as<uint32_t>());
+    else if (G == 2) k_phase_bits_packed<2><<<pg, 64, 0, st>>>(packed_dev, P, n, W, groups, c->d_gbits.as<uint32_t>());
+    else k_phase_bits_packed<1><<<pg, 32, 0, st>>>(packed_dev, P, n, W, groups, c->d_gbits.as<uint32_t>());
+  } else if ((n & 3) == 0 && ((uintptr_t)genes_dev & 3) == 0) {
     const int64_t bwarps = (int64_t)((n + 127) / 128) * groups;
     k_phase_bits4<<<(unsigned)((bwarps * 32 + 255) / 256), 256, 0, st>>>(genes_dev, P, n, groups, G, c->d_gbits.as<uint32_t>());
   } else {

@@ -27,14 +27,15 @@ constexpr int kThreads = LXY_SCORE_THREADS;
 constexpr int kWarps = kThreads / 32;
 constexpr int kPacket = 8;  // records per 128-bit load
 
-__constant__ uint8_t c_lut100[kLutLen];  // T*100 by v = d + kBias + 1; 0 at the far entries 0, 42
-__constant__ int c_steps[6] = {1, 2, 3, 5, 11, 20};
-__constant__ int c_w100[6] = {100, 50, 33, 20, 10, 5};
-
-const uint8_t h_lut100[kLutLen] = {
+// T*100 by v = d + kBias + 1; 0 at the far entries 0, 42.  Initialised with the module (no copy at
+// run time: a lazily queued cudaMemcpyToSymbolAsync on one context's stream could be overtaken by a
+// second context of the same device).
+__constant__ uint8_t c_lut100[kLutLen] = {
     /* far */ 0, /* d=-20 */ 5, 0, 0, 0, 0, 0, 0, 0, 0, /* -11 */ 10, 0, 0, 0, 0, 0, /* -5 */ 20, 0,
     /* -3 */ 33, /* -2 */ 50, /* -1 */ 100, /* 0 */ 0, 100, 50, 33, 0, 20, 0, 0, 0, 0, 0,
     /* 11 */ 10, 0, 0, 0, 0, 0, 0, 0, 0, /* 20 */ 5, /* far */ 0, 0, 0, 0, 0, 0};
+__constant__ int c_steps[6] = {1, 2, 3, 5, 11, 20};
+__constant__ int c_w100[6] = {100, 50, 33, 20, 10, 5};
 
 // ---- k_scaff_layout -----------------------------------------------------------------------------
 // Tables are stored group-major: tab[g][contig][cand] with kCand = 32*CPL candidates per group, so
@@ -594,6 +595,7 @@ template <int CPL, int WIDE, int WM>
 int launch_score(lxy_ctx* c, const ScoreParams& prm, int grid) {
   constexpr int smem = 2 * kBlk * 32 * CPL * (WIDE == 1 ? 4 : 2) + 64 + 8 * kLutLen + 16 + 4 * kLut2Words;
   static bool configured[64] = {};
+  std::lock_guard<std::mutex> cfg_lock(config_mutex());   // process-global flags: not covered by the context mutex
   if (!configured[c->cfg.device & 63]) {
     LXY_CUDA(cudaFuncSetAttribute(k_scaff_score<CPL, WIDE, WM>,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -619,14 +621,13 @@ int launch_score_cpl(lxy_ctx* c, int cpl, const ScoreParams& prm, int grid) {
 
 }  // namespace
 
-static bool g_lut_loaded[64] = {};
-
 // The streaming kernels run with most of the SM's L1 carved out as shared memory; the small
 // kernels around them (layout, check, head, finish) use none.  Left to the default, the driver
 // switches the carve-out between consecutive launches and serialises them (measured: +20 us per
 // call around k_scaff_stream1).  Asking for the same carve-out everywhere removes the switch.
 static int prefer_max_carveout(lxy_ctx* c) {
   static bool done[64] = {};
+  std::lock_guard<std::mutex> cfg_lock(config_mutex());
   if (done[c->cfg.device & 63]) return LXY_OK;
   const void* fns[] = {
       (const void*)k_scaff_layout<0>, (const void*)k_scaff_layout<1>,
@@ -655,10 +656,6 @@ static int scaff_score_stream1(lxy_ctx* c, const int32_t* perm_dev, int32_t P, i
   LXY_TRY(c->d_flag.reserve(64));
   LXY_TRY(c->d_corr.reserve(8 * (size_t)P));
   LXY_TRY(prefer_max_carveout(c));
-  if (!g_lut_loaded[c->cfg.device & 63]) {
-    LXY_CUDA(cudaMemcpyToSymbolAsync(c_lut100, h_lut100, kLutLen, 0, cudaMemcpyHostToDevice, st));
-    g_lut_loaded[c->cfg.device & 63] = true;
-  }
   if (first) {
     LXY_CUDA(cudaMemsetAsync(c->d_flag.p, 0, 64, st));
     LXY_CUDA(record_timing_event(c, 0));
@@ -785,40 +782,70 @@ int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int
   return LXY_OK;
 }
 
+// Populations of up to 128 orderings as passes of <= 8 through the streaming-regime kernels.
+static int scaff_enqueue_passes(lxy_ctx* c, const int32_t* perm_dev, int32_t P, double* out_dev,
+                                int64_t* x100_dev, bool first, bool last) {
+  const int n = c->scaff.n;
+  constexpr int kS1Pass = 8;
+  for (int32_t p0 = 0; p0 < P; p0 += kS1Pass) {
+    const int32_t pp = P - p0 < kS1Pass ? P - p0 : kS1Pass;
+    int ncp = 1;
+    while (ncp < pp) ncp *= 2;
+    LXY_TRY(scaff_score_stream1(c, perm_dev + (size_t)p0 * n, pp, ncp, stream1_smem(ncp, n), out_dev + p0,
+                                x100_dev ? x100_dev + p0 : nullptr, first && p0 == 0, last && p0 + kS1Pass >= P));
+  }
+  return LXY_OK;
+}
+
+static int scaff_enqueue_batch(lxy_ctx* c, const int32_t* perm_dev, int32_t P, double* out_dev,
+                               int64_t* x100_dev, bool first, bool last);
+
+// Measured on B200 (tools/p_sweep.py, n = 5,000, unit weights; 5 M and 200 M records; L in millions of
+// records): a pass of <= 8 orderings costs about 26 + 1.27 L us on the packed kernel
+// (scaff_stream1p.cuh), one group of the batch kernel 48 + 13.8 L us up to 32 orderings, 48 + 14.5 L up
+// to 64, 48 + 17.9 L up to 128; a further group of a launch that already has full groups 17.9 L.
+// The model is only consulted inside that regime (unit weights, packed kernel applicable); weighted
+// stores keep the single-pass rule (<= 8 orderings stream, everything else in groups).
+static double pass_cost_us(int32_t P, double l_m) { return (double)((P + 7) / 8) * (26.0 + 1.27 * l_m); }
+
 static int scaff_score_enqueue(lxy_ctx* c, const int32_t* perm_dev, int32_t P, double* out_dev,
                                int64_t* x100_dev) {
   ScaffLinks& S = c->scaff;
+  const int n = S.n;
+  constexpr int kS1Pass = 8;
+  const double l_m = (double)S.L * 1e-6;
+  const bool s1_ok = n <= 65536 && !(c->cfg.flags & LXY_FLAG_NO_STREAM1) &&
+                     stream1_smem(P < kS1Pass ? (P <= 1 ? 1 : P <= 2 ? 2 : P <= 4 ? 4 : 8) : kS1Pass, n) <= (size_t)c->max_smem_optin;
+  const bool model_ok = s1_ok && S.wmode == W_UNIT && stream1p_applies(S.wmode, kS1Pass, n) &&
+                        stream1p_smem(kS1Pass, n) <= (size_t)c->max_smem_optin;
+  // ---- streaming regime: up to 8 candidates per pass (a lone Score() call is a batch of one) ----
+  // Small populations - the reference's own GA runs 40 orderings (scaff.go:94) - take several passes
+  // while the model says that wins: against 200 M records 16 orderings 2.80 -> 0.55 ms, 40 orderings
+  // 2.81 -> 1.34 ms, 96 orderings 3.6 -> 3.3 ms; at 5 M records passes win up to 24 orderings.
+  if (s1_ok && P <= kS1Pass) return scaff_enqueue_passes(c, perm_dev, P, out_dev, x100_dev, true, true);
+  if (model_ok && P <= 128) {
+    const double batch_us = 48.0 + (P <= 32 ? 13.8 : P <= 64 ? 14.5 : 17.9) * l_m;
+    if (pass_cost_us(P, l_m) < batch_us) return scaff_enqueue_passes(c, perm_dev, P, out_dev, x100_dev, true, true);
+  }
+  // ---- whole groups of 128 through the batch kernel; what is left over (P mod 128: a GA generation
+  // makes ~P +- 30 children) goes through passes when those cost less than one more group, which would
+  // score 128 - rem identity paddings at full price (cfg3, 1,028 children: 9 groups -> 8 groups + one
+  // pass of 4, 30.8 -> 27.6 ms) ----
+  const int32_t rem = P % 128;
+  if (model_ok && P > 128 && rem != 0 && pass_cost_us(rem, l_m) < 17.9 * l_m) {
+    const int32_t full = P - rem;
+    LXY_TRY(scaff_enqueue_batch(c, perm_dev, full, out_dev, x100_dev, true, false));
+    return scaff_enqueue_passes(c, perm_dev + (size_t)full * n, rem, out_dev + full,
+                                x100_dev ? x100_dev + full : nullptr, false, true);
+  }
+  return scaff_enqueue_batch(c, perm_dev, P, out_dev, x100_dev, true, true);
+}
+
+static int scaff_enqueue_batch(lxy_ctx* c, const int32_t* perm_dev, int32_t P, double* out_dev,
+                               int64_t* x100_dev, bool first, bool last) {
+  ScaffLinks& S = c->scaff;
   cudaStream_t st = c->stream;
   const int n = S.n;
-  // ---- streaming regime: up to 8 candidates per pass (a lone Score() call is a batch of one) ----
-  // Small populations - the reference's own GA runs 40 orderings (scaff.go:94) - take several passes.
-  // Measured on B200 (tools/p_sweep.py, n = 5,000; 5 M and 200 M records; L in millions of records):
-  // a pass of 8 costs about 26 + 1.27 L us on the packed kernel (scaff_stream1p.cuh; 26 + 1.8 L us on
-  // k_scaff_stream1), one group of the batch kernel 48 + 13.8 L us up to 32 orderings, 48 + 14.5 L up
-  // to 64, 48 + 17.9 L up to 128.  Against 200 M records: 16 orderings 2.80 -> 0.55 ms, 40 orderings
-  // 2.81 -> 1.34 ms, 96 orderings 3.6 -> 3.3 ms; at 5 M records passes win up to 24 orderings.
-  constexpr int kS1Pass = 8;
-  int s1_max = kS1Pass;
-  if (P > kS1Pass && P <= 128) {
-    const double l_m = (double)S.L * 1e-6;
-    const double pass_us = 26.0 + (stream1p_applies(S.wmode, kS1Pass, n) ? 1.27 : 1.8) * l_m;
-    const double batch_us = 48.0 + (P <= 32 ? 13.8 : P <= 64 ? 14.5 : 17.9) * l_m;
-    if ((double)((P + kS1Pass - 1) / kS1Pass) * pass_us < batch_us) s1_max = P;
-  }
-  if (P <= s1_max && n <= 65536 && !(c->cfg.flags & LXY_FLAG_NO_STREAM1)) {
-    int nc = 1;
-    while (nc < P && nc < kS1Pass) nc *= 2;
-    if (stream1_smem(nc, n) <= (size_t)c->max_smem_optin) {
-      for (int32_t p0 = 0; p0 < P; p0 += kS1Pass) {
-        const int32_t pp = P - p0 < kS1Pass ? P - p0 : kS1Pass;
-        int ncp = 1;
-        while (ncp < pp) ncp *= 2;
-        LXY_TRY(scaff_score_stream1(c, perm_dev + (size_t)p0 * n, pp, ncp, stream1_smem(ncp, n), out_dev + p0,
-                                    x100_dev ? x100_dev + p0 : nullptr, p0 == 0, p0 + kS1Pass >= P));
-      }
-      return LXY_OK;
-    }
-  }
   // table mode: 0 = 16-bit entries (pos + 21 | -pos) summed modulo 2^16 (n <= 65515, see eval_record),
   // 128 candidates in the 128 KB of tables; 1 = 32-bit entries, 64 candidates.
   static const int force_tm = getenv("LXY_TABLE_MODE") ? atoi(getenv("LXY_TABLE_MODE")) : -1;  // experiments
@@ -836,14 +863,10 @@ static int scaff_score_enqueue(lxy_ctx* c, const int32_t* perm_dev, int32_t P, d
   LXY_TRY(c->d_flag.reserve(64));
   LXY_TRY(c->d_corr.reserve(8 * (size_t)P));
   LXY_TRY(prefer_max_carveout(c));
-  if (!g_lut_loaded[c->cfg.device & 63]) {
-    LXY_CUDA(cudaMemcpyToSymbolAsync(c_lut100, h_lut100, kLutLen, 0, cudaMemcpyHostToDevice, st));
-    g_lut_loaded[c->cfg.device & 63] = true;
-  }
-  LXY_CUDA(cudaMemsetAsync(c->d_flag.p, 0, 64, st));
+  if (first) LXY_CUDA(cudaMemsetAsync(c->d_flag.p, 0, 64, st));
   int launches = 0;
 
-  LXY_CUDA(record_timing_event(c, 0));
+  if (first) LXY_CUDA(record_timing_event(c, 0));
   // The head-of-ordering look-ups only need the population and the link store: they run on a side
   // stream next to the layout and streaming kernels and are joined before k_scaff_finish.
   {
@@ -869,7 +892,7 @@ static int scaff_score_enqueue(lxy_ctx* c, const int32_t* perm_dev, int32_t P, d
     ++launches;
   }
   LXY_CUDA(cudaGetLastError());
-  LXY_CUDA(record_timing_event(c, 1));
+  if (first) LXY_CUDA(record_timing_event(c, 1));
 
   // work units: groups x splits, about two waves of one CTA per SM
   const int64_t npk = (S.L + kPacket - 1) / kPacket;
@@ -905,7 +928,7 @@ static int scaff_score_enqueue(lxy_ctx* c, const int32_t* perm_dev, int32_t P, d
   }
   LXY_TRY(rc);
   ++launches;
-  LXY_CUDA(record_timing_event(c, 2));
+  if (last) LXY_CUDA(record_timing_event(c, 2));
 
   LXY_CUDA(cudaStreamWaitEvent(st, c->ev_join, 0));
   if (S.wmode == W_UNIT) k_scaff_finish<W_UNIT><<<(P + 7) / 8, 256, 0, st>>>(P, cand, splits, c->d_partial.p, c->d_corr.p, out_dev, x100_dev);
@@ -913,7 +936,7 @@ static int scaff_score_enqueue(lxy_ctx* c, const int32_t* perm_dev, int32_t P, d
   else k_scaff_finish<W_F64><<<(P + 7) / 8, 256, 0, st>>>(P, cand, splits, c->d_partial.p, c->d_corr.p, out_dev, x100_dev);
   launches += 2;
   LXY_CUDA(cudaGetLastError());
-  LXY_CUDA(record_timing_event(c, 3));
+  if (last) LXY_CUDA(record_timing_event(c, 3));
 
   c->timing.launches = launches;
   c->timing.grid = grid;

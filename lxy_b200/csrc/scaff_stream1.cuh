@@ -228,17 +228,16 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
       s_lut2[i] = (uint8_t)(s_lut[i / kS1LutSide] + s_lut[i % kS1LutSide]);
   }
   int bad = 0;
-  // validation slice of this CTA (pos[perm[i]] == i for all i <=> the row is a permutation; CTA k
-  // checks slice k): its first element per thread is requested before the build, so that the check
-  // behind the barrier does not wait for global memory again
+  // validation slice of this CTA: CTA k checks the contig IDS of slice k.  Every gene is in [0, n)
+  // (checked during the build), so a row is a permutation <=> every id was written <=> for every id x
+  // the position p found in the table is in range and perm[p] == x.  An id that occurs twice leaves
+  // another one unwritten; the unwritten slot holds whatever the shared memory held, and whichever
+  // position that decodes to, perm[p] != x because x is nowhere in the row.  The outcome therefore
+  // does not depend on which of two racing stores to a duplicated id wins (a check by ordering
+  // position, slice by slice, did: each CTA could see its own store win).
   const int32_t vi0 = (int32_t)((int64_t)n * blockIdx.x / gridDim.x), vi1 = (int32_t)((int64_t)n * (blockIdx.x + 1) / gridDim.x);
-  constexpr int kVPre = NC <= 2 ? NC : 0;
-  int32_t vpre[kVPre > 0 ? kVPre : 1];
-  if (kVPre > 0 && prm.validate) {
-#pragma unroll
-    for (int c = 0; c < kVPre; ++c)
-      vpre[c] = (c < prm.P && vi0 + tid < vi1) ? prm.perm[(size_t)c * n + vi0 + tid] : -1;
-  }
+  constexpr int kVPre = NC <= 2 ? NC : 0;   // orderings whose first id per thread is compared at the end of the kernel
+  int32_t vgot[kVPre > 0 ? kVPre : 1];
 #pragma unroll 1
   for (int c = 0; c < NC; ++c) {
     const int32_t* row = prm.perm + (size_t)c * n;
@@ -250,16 +249,20 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
   }
   __syncthreads();
   if (prm.validate) {
+    // the gather perm[p] of the first id per thread stays in flight while the records are scored
 #pragma unroll
     for (int c = 0; c < kVPre; ++c) {
-      const int32_t cid = vpre[c];
-      if ((uint32_t)cid < (uint32_t)n && sPos[c * nstride + cid] != (int16_t)(32767 - (vi0 + tid))) bad |= 2;
+      vgot[c] = vi0 + tid;
+      if (c < prm.P && vi0 + tid < vi1) {
+        const uint32_t p = (uint32_t)(32767 - (int32_t)sPos[c * nstride + vi0 + tid]);
+        vgot[c] = p < (uint32_t)n ? prm.perm[(size_t)c * n + p] : -1;
+      }
     }
     for (int c = 0; c < prm.P && c < NC; ++c) {
       const int32_t* row = prm.perm + (size_t)c * n;
-      for (int i = vi0 + tid + (c < kVPre ? kS1Threads : 0); i < vi1; i += kS1Threads) {
-        const int32_t cid = row[i];
-        if ((uint32_t)cid < (uint32_t)n && sPos[c * nstride + cid] != (int16_t)(32767 - i)) bad |= 2;
+      for (int x = vi0 + tid + (c < kVPre ? kS1Threads : 0); x < vi1; x += kS1Threads) {
+        const uint32_t p = (uint32_t)(32767 - (int32_t)sPos[c * nstride + x]);
+        if (p >= (uint32_t)n || row[p] != x) bad |= 2;
       }
     }
   }
@@ -372,6 +375,12 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
     }
   }
   cp_async_wait<0>();
+  if (kVPre > 0 && prm.validate) {
+    bool miss = false;
+#pragma unroll
+    for (int c = 0; c < kVPre; ++c) miss |= (vgot[c] != vi0 + tid);
+    if (miss) atomicOr(prm.flag, 2);
+  }
 
   // ---- warp shuffle tree, then a fixed-order sum over the warps ----
 #pragma unroll
@@ -398,6 +407,7 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
 template <int NC, int WM>
 int launch_stream1(lxy_ctx* c, const Stream1Params& prm, int grid, size_t smem) {
   static size_t configured[64] = {};
+  std::lock_guard<std::mutex> cfg_lock(config_mutex());
   if (configured[c->cfg.device & 63] < smem) {
     LXY_CUDA(cudaFuncSetAttribute(k_scaff_stream1<NC, WM>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)smem));

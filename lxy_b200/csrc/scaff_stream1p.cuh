@@ -153,17 +153,18 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1p(Stream1Params 
     const int v0 = i % kLut2Stride, v1 = i / kLut2Stride;
     s_lutc[i] = (v0 < kLutLen ? (uint32_t)s_lut[v0] : 0u) | ((uint32_t)s_lut[v1] << 16);
   }
-  if (prm.validate) {  // -pos[perm[i]] == -i for all i <=> the row is a permutation; CTA k checks slice k
+  if (prm.validate) {
+    // CTA k checks the contig IDS of slice k: the position p decoded from the table entry of id x must be
+    // in range with perm[p] == x.  Independent of which store to a duplicated id won (see k_scaff_stream1):
+    // a duplicate leaves another id unwritten, and an unwritten slot cannot point at its own id.
     const int32_t i0 = (int32_t)((int64_t)n * blockIdx.x / gridDim.x), i1 = (int32_t)((int64_t)n * (blockIdx.x + 1) / gridDim.x);
     for (int c = 0; c < prm.P && c < NC; ++c) {
       const int32_t* row = prm.perm + (size_t)c * n;
-      for (int i = i0 + tid; i < i1; i += kS1Threads) {
-        const int32_t cid = row[i];
-        if ((uint32_t)cid < (uint32_t)n) {  // the whole word through an opaque 32-bit load, compared in 32 bits
-          const uint32_t word = lds_u32(sbase + (uint32_t)(c >> 1) * pstride + (uint32_t)cid * 4u);
-          const uint32_t got = (c & 1) ? (word >> 16) : (word & 0xFFFFu);
-          if (got != ((0u - (uint32_t)i) & 0xFFFFu)) bad |= 2;
-        }
+      for (int x = i0 + tid; x < i1; x += kS1Threads) {
+        // the whole word through an opaque 32-bit load, decoded in 32 bits
+        const uint32_t word = lds_u32(sbase + (uint32_t)(c >> 1) * pstride + (uint32_t)x * 4u);
+        const uint32_t p = (0u - ((c & 1) ? (word >> 16) : (word & 0xFFFFu))) & 0xFFFFu;
+        if (p >= (uint32_t)n || row[p] != x) bad |= 2;
       }
     }
   }
@@ -291,6 +292,7 @@ inline size_t stream1p_smem(int nc, int n) {
 template <int NC>
 int launch_stream1p(lxy_ctx* c, const Stream1Params& prm, int grid, size_t smem) {
   static size_t configured[64] = {};
+  std::lock_guard<std::mutex> cfg_lock(config_mutex());
   if (configured[c->cfg.device & 63] < smem) {
     LXY_CUDA(cudaFuncSetAttribute(k_scaff_stream1p<NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     LXY_CUDA(cudaFuncSetAttribute(k_scaff_stream1p<NC>, cudaFuncAttributePreferredSharedMemoryCarveout,

@@ -464,6 +464,7 @@ template <int WM, bool SGN, bool POW2>
 int launch_g3(lxy_ctx* c, const GParams& prm, int grid) {
   constexpr int smem = 2 * kTabG + 2 * kBitsG + 32 + 16;
   static bool configured[64] = {};
+  std::lock_guard<std::mutex> cfg_lock(config_mutex());
   if (!configured[c->cfg.device & 63]) {
     LXY_CUDA(cudaFuncSetAttribute(k_scaffg_score<WM, SGN, POW2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured[c->cfg.device & 63] = true;

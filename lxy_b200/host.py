@@ -460,10 +460,10 @@ def Scaffold(links, outPath, iterations, optReportFreq, device=0, seed=None, pop
     return scaffolding, intermediates
 
 
-def writePhasing(phasing, path):                      # phase.go:151-167: `name\tA|B`
+def writePhasing(phasing, path):                      # phase.go:151-167: `name 1` / `name 0`
     with open(path, "w") as f:
         for k, v in phasing.items():
-            f.write(f"{k}\t{'A' if v else 'B'}\n")
+            f.write(f"{k} {1 if v else 0}\n")
 
 
 def Phase(links, outPath, iterations, optReportFreq=0.01, device=0, seed=None, popsize=10):

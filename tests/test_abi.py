@@ -34,13 +34,36 @@ def test_library_exports_every_declared_symbol(native):
 
 
 def test_abi_version(native):
-    assert native.lxy_abi_version() == 1
+    assert native.lxy_abi_version() == N.ABI_VERSION == 2
 
 
 def test_rank_is_stable_ascending(native):
     s = np.array([3.0, -1.0, 3.0, -7.5, -1.0, 0.0])
     assert N.rank(s).tolist() == [3, 1, 4, 5, 0, 2]
     assert N.rank(np.zeros(0)).tolist() == []
+
+
+def test_comm_slice_is_a_balanced_contiguous_split(native):
+    """lxy_comm_slice needs no device: every row exactly once, sizes differ by at most one."""
+    for total, world in [(1024, 8), (1028, 8), (5, 8), (0, 3), (129, 1), (1000, 7)]:
+        at, sizes = 0, []
+        for r in range(world):
+            f, c = N.comm_slice(total, world, r)
+            assert f == at
+            at += c
+            sizes.append(c)
+        assert at == total and max(sizes) - min(sizes) <= 1
+    with pytest.raises(N.LxyError):
+        N.comm_slice(10, 0, 0)
+
+
+def test_pack_bits_layout():
+    g = np.zeros((2, 70), np.uint8)
+    g[0, [0, 31, 32, 69]] = 1
+    g[1, 33] = 1
+    w = N.pack_bits(g)
+    assert w.shape == (2, 3) and w.dtype == np.uint32
+    assert w[0].tolist() == [1 | (1 << 31), 1, 1 << 5] and w[1].tolist() == [0, 2, 0]
 
 
 def test_no_cpu_fallback_without_a_device(native):

@@ -36,7 +36,7 @@ def _check_generation(ga, seed, gen, bits=False):
                                          (2500, 200000, 64, 4)])
 def test_scaff_generation_matches_oracle(n, L, P, seed):
     a, b, w = S.scaff_links(n, L, seed)
-    with N.Context(0) as ctx:
+    with N.Context(0, path=N.PATH_STREAM) as ctx:
         ctx.set_links(n, a, b, None)
         with N.GA(ctx, N.GA_SCAFF, popsize=P, seed=seed, **PRM) as ga:
             ga.init()
@@ -61,7 +61,7 @@ def test_scaff_generation_matches_oracle(n, L, P, seed):
 def test_scaff_optimize_equals_split_steps_and_improves():
     n, L, P, seed = 400, 60000, 40, 11
     a, b, _ = S.scaff_links(n, L, seed)
-    with N.Context(0) as ctx:
+    with N.Context(0, path=N.PATH_STREAM) as ctx:
         ctx.set_links(n, a, b, None)
         kw = dict(popsize=P, seed=seed, p_breed=0.2, p_mutate=0.6, tour_p=0.7, tour_k=5, mutators=7)
         with N.GA(ctx, N.GA_SCAFF, **kw) as g1, N.GA(ctx, N.GA_SCAFF, **kw) as g2:
@@ -89,14 +89,14 @@ def test_scaff_ga_recovers_a_small_hidden_order():
     n = 11
     ia, ib = np.triu_indices(n, 1)
     w = (10 - (ib - ia - 1)).astype(np.float64)
-    with N.Context(0) as ctx:
+    with N.Context(0, path=N.PATH_STREAM) as ctx:
         ctx.set_links(n, ia.astype(np.uint32), ib.astype(np.uint32), w)
         with N.GA(ctx, N.GA_SCAFF, popsize=40, seed=5) as ga:      # the reference's parameters
             ga.init()
             ga.optimize(300)
             gene, sc = ga.best()
     ident = ctx_score = None
-    with N.Context(0) as ctx:
+    with N.Context(0, path=N.PATH_STREAM) as ctx:
         ctx.set_links(n, ia.astype(np.uint32), ib.astype(np.uint32), w)
         ident = ctx.scaff_score_batch(np.arange(n, dtype=np.int32)[None, :])[0]
     assert sc <= ident + 1e-9                                       # at least as good as the true order
@@ -105,7 +105,7 @@ def test_scaff_ga_recovers_a_small_hidden_order():
 @pytest.mark.parametrize("n,P,seed", [(300, 10, 1), (2000, 64, 2)])
 def test_phase_generation_matches_oracle(n, P, seed):
     pa, pb, pw, truth = S.phase_links(n, seed)
-    with N.Context(0) as ctx:
+    with N.Context(0, path=N.PATH_STREAM) as ctx:
         ctx.set_phase_links(n, pa, pb, pw)
         with N.GA(ctx, N.GA_PHASE, popsize=P, seed=seed, **PRM) as ga:
             ga.init()
@@ -122,7 +122,7 @@ def test_phase_generation_matches_oracle(n, P, seed):
 
 
 def test_ga_error_paths():
-    with N.Context(0) as ctx:
+    with N.Context(0, path=N.PATH_STREAM) as ctx:
         with pytest.raises(N.LxyError):                 # links not set
             N.GA(ctx, N.GA_SCAFF)
         a, b, _ = S.scaff_links(30, 500, 1)

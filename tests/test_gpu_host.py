@@ -92,6 +92,7 @@ def test_phase_workflow_on_the_reference_fixture(golden_files, tmp_path):
     key = [c == "A" for c in "AABAAAAAABA"]
     assert bits == key or bits == [not x for x in key]
     assert len(out.read_text().splitlines()) == 11
+    assert H.readPhasing(str(out)) == links.DecodePhasing([1 if b else 0 for b in bits])   # phase.go:119-167 round trip
 
 
 def test_native_links_attach_and_file_workflows(golden, golden_files, tmp_path):
@@ -112,8 +113,12 @@ def test_native_links_attach_and_file_workflows(golden, golden_files, tmp_path):
     pout = tmp_path / "p.txt"
     pbest = N.phase_file(golden_files["test_var"], str(pout), 300)
     assert pbest == -679.0                                           # the global optimum
-    rows = [r.split("\t") for r in pout.read_text().splitlines()]
-    assert len(rows) == 11 and {r[1] for r in rows} <= {"A", "B"}
+    # writePhasing's format (phase.go:151-167): `name 1` / `name 0`; round trip through readPhasing
+    rows = [r.split(" ") for r in pout.read_text().splitlines()]
+    assert len(rows) == 11 and {r[1] for r in rows} <= {"0", "1"}
+    back = H.readPhasing(str(pout))
+    nv = N.NativeLinks(golden_files["test_var"])
+    assert list(back) == nv.Decode(range(11))
     with pytest.raises(N.LxyError):
         N.scaffold_file(str(tmp_path / "nope.links"), str(out), 10)
 

@@ -14,7 +14,7 @@ REL = 1e-9
 
 @pytest.fixture(scope="module")
 def ctxs():
-    p, s = N.Context(0, path=N.PATH_PAIRS), N.Context(0)
+    p, s = N.Context(0, path=N.PATH_PAIRS), N.Context(0, path=N.PATH_STREAM)
     yield p, s
     p.close(); s.close()
 

@@ -17,7 +17,7 @@ REL = 1e-9   # tolerance stated by north_star for fp64 fitness
 
 @pytest.fixture(scope="module")
 def ctx():
-    c = N.Context(0)
+    c = N.Context(0, path=N.PATH_STREAM)
     yield c
     c.close()
 
@@ -109,7 +109,7 @@ def test_forced_fp64_matches_integer_mode():
     n, L, P = 400, 60000, 64
     a, b, w = S.scaff_links(n, L, 31)
     perms = S.scaff_population(n, P, 131)
-    with N.Context(0, acc_mode=N.ACC_F64) as cf, N.Context(0, acc_mode=N.ACC_INT) as ci:
+    with N.Context(0, path=N.PATH_STREAM, acc_mode=N.ACC_F64) as cf, N.Context(0, path=N.PATH_STREAM, acc_mode=N.ACC_INT) as ci:
         cf.set_links(n, a, b, w)
         ci.set_links(n, a, b, w)
         f = cf.scaff_score_batch(perms)
@@ -273,7 +273,7 @@ def test_full_size_config3_properties():
     a, b, order = bench.gen_links(n, L, 3, dev)
     perms = bench.gen_population(n, P, 103, order.cpu().numpy())
     torch.cuda.synchronize()
-    with N.Context(0) as c, N.Context(0, path=N.PATH_PAIRS) as pc:
+    with N.Context(0, path=N.PATH_STREAM) as c, N.Context(0, path=N.PATH_PAIRS) as pc:
         c.set_links_dev(n, L, a.data_ptr(), b.data_ptr())
         full, xf = c.scaff_score_batch(perms, want_x100=True)
         pc.set_links_dev(n, L, a.data_ptr(), b.data_ptr())
@@ -302,7 +302,7 @@ def test_repeated_calls_replay_a_graph_with_identical_results():
     a2, b2, _ = S.scaff_links(n, L, 92)
     pops = [S.scaff_population(n, 96, 190 + k) for k in range(4)]
     big = S.scaff_population(n, 400, 199)
-    with N.Context(0) as cg, N.Context(0, flags=N.FLAG_NO_GRAPH) as cd:
+    with N.Context(0, path=N.PATH_STREAM) as cg, N.Context(0, path=N.PATH_STREAM, flags=N.FLAG_NO_GRAPH) as cd:
         for ctx in (cg, cd):
             ctx.set_links(n, a, b, None)
         dev = torch.device("cuda", 0)

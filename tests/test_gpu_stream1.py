@@ -17,7 +17,7 @@ REL = 1e-9
 
 @pytest.fixture(scope="module")
 def ctxs():
-    s, b = N.Context(0), N.Context(0, flags=N.FLAG_NO_STREAM1)
+    s, b = N.Context(0, path=N.PATH_STREAM), N.Context(0, path=N.PATH_STREAM, flags=N.FLAG_NO_STREAM1)
     yield s, b
     s.close()
     b.close()
@@ -100,6 +100,30 @@ def test_stream1_rejects_bad_orderings(ctxs):
     with pytest.raises(N.LxyError):
         cs.scaff_score_batch(bad)
     assert np.isfinite(cs.scaff_score_batch(perms)).all()
+
+
+@pytest.mark.parametrize("P", [1, 2, 8])
+def test_stream1_duplicate_far_apart_is_always_rejected(ctxs, P):
+    """A contig id repeated at ordering positions that lie in different warps and different
+    validation slices (every CTA builds its own table with unordered stores, so which duplicate wins
+    the slot differs from CTA to CTA): the check goes by contig id — the id the duplicate displaced
+    was never written — and must fire on every one of many repeats, for both streaming kernels."""
+    cs, _ = ctxs
+    n = 5000
+    a, b, _ = S.scaff_links(n, 400_000, 43)          # enough records for one CTA per 512: many CTAs
+    cs.set_links(n, a, b, None)
+    rng = np.random.default_rng(143)
+    perms = S.scaff_population(n, P, 143)
+    assert np.isfinite(cs.scaff_score_batch(perms)).all()
+    for rep in range(40):
+        bad = perms.copy()
+        row = int(rng.integers(0, P))
+        i1 = int(rng.integers(0, n // 4))
+        i2 = int(rng.integers(3 * n // 4, n))
+        bad[row, i2] = bad[row, i1]
+        with pytest.raises(N.LxyError) as e:
+            cs.scaff_score_batch(bad)
+        assert e.value.status == -4, rep
 
 
 def test_stream1_full_size_single_genome_score(ctxs):

@@ -135,3 +135,17 @@ def test_memo_contract_and_operators():
     x, y = b.Crossover(H.NewFixedBitstringGenome([1] * 5, None), 1, 2)
     assert x.Gene == [False, True, True, True, True] and y.Gene == [True, False, False, True, True]
     assert b.Valid() and b.String() == "[false false false true true]"
+
+
+def test_phasing_file_format_round_trip(tmp_path):
+    """writePhasing emits `name 1` / `name 0`, space separated (phase.go:151-167), which is what
+    readPhasing accepts (phase.go:119-149); a TAB / A|B file is rejected like the reference does."""
+    ph = {"chr1_0": True, "chr1_1": False, "chr1_2": True}
+    p = tmp_path / "x.phasing.txt"
+    H.writePhasing(ph, str(p))
+    assert p.read_text() == "chr1_0 1\nchr1_1 0\nchr1_2 1\n"
+    assert H.readPhasing(str(p)) == ph
+    bad = tmp_path / "bad.txt"
+    bad.write_text("chr1_0\tA\n")
+    with pytest.raises(ValueError):
+        H.readPhasing(str(bad))

@@ -18,7 +18,7 @@ rng = np.random.default_rng(5)
 Ps = [int(x) for x in os.environ.get("PS_P", "1,2,4,8,9,12,16,24,32,48,64,128").split(",")]
 perms = torch.from_numpy(np.stack([rng.permutation(n) for _ in range(max(Ps))]).astype(np.int32)).cuda()
 out = torch.zeros(max(Ps), dtype=torch.float64, device="cuda")
-with N.Context(0, flags=int(os.environ.get("S1_FLAGS", "0"))) as ctx:
+with N.Context(0, path=N.PATH_STREAM, flags=int(os.environ.get("S1_FLAGS", "0"))) as ctx:
     ctx.set_links_dev(n, L, ta.data_ptr(), tb.data_ptr(), None)
     for P in Ps:
         ts = []

@@ -17,7 +17,7 @@ if mode == "phase":
     pn, pP = 300_000, 1024       # the bench's phasing shape (BASELINE config 5)
     a, b, w, truth = S.phase_links(pn, 5)
     genes = S.phase_population(pn, pP, 105, truth)
-    with N.Context(0) as ctx:
+    with N.Context(0, path=N.PATH_STREAM) as ctx:
         ctx.set_phase_links(pn, a, b, w)
         for _ in range(steps):
             ctx.phase_score_batch(genes)
@@ -30,7 +30,7 @@ if mode in ("r3", "r4"):   # r3: the bench default (config 3, population 1024, b
     ta, tb, order = bench.gen_links(n, L, 3 if mode == "r3" else 4, torch.device("cuda", 0))
     perms = torch.from_numpy(bench.gen_population(n, P, 103, order.cpu().numpy())).cuda()
     out = torch.zeros(P, dtype=torch.float64, device="cuda")
-    with N.Context(0) as ctx:
+    with N.Context(0, path=N.PATH_STREAM) as ctx:
         ctx.set_links_dev(n, L, ta.data_ptr(), tb.data_ptr(), None)
         for _ in range(steps):
             ctx.scaff_score_batch_dev(perms.data_ptr(), P, out.data_ptr(), None)
@@ -46,7 +46,7 @@ if mode == "s1":      # streaming regime at config-3 size: one ordering against 
     rng5 = np.random.default_rng(5)
     perm = torch.from_numpy(np.stack([rng5.permutation(n) for _ in range(sP)]).astype(np.int32)).cuda()
     out = torch.zeros(max(8, sP), dtype=torch.float64, device="cuda")
-    with N.Context(0) as ctx:
+    with N.Context(0, path=N.PATH_STREAM) as ctx:
         ctx.set_links_dev(n, L, ta.data_ptr(), tb.data_ptr(), None)
         for _ in range(steps):
             ctx.scaff_score_batch_dev(perm.data_ptr(), sP, out.data_ptr(), None)
@@ -60,7 +60,7 @@ if mode == "g":
     xa = (rng.random(L) * lens[a]).astype(np.uint32)
     xb = (rng.random(L) * lens[b]).astype(np.uint32)
     oris = S.orientations(n, P, 2)
-    with N.Context(0) as ctx:
+    with N.Context(0, path=N.PATH_STREAM) as ctx:
         ctx.set_links_g(lens, int(np.median(lens)), a, xa, b, xb, None)
         for _ in range(steps):
             ctx.scaffg_score_batch(perms, oris)

@@ -17,7 +17,7 @@ Lmax = 400_000_000
 ta, tb, order = bench.gen_links(n, Lmax, 3, dev)
 perm = torch.from_numpy(np.random.default_rng(5).permutation(n).astype(np.int32)).cuda()
 out = torch.zeros(8, dtype=torch.float64, device="cuda")
-with N.Context(0, flags=int(os.environ.get("S1_FLAGS", "0"))) as ctx:
+with N.Context(0, path=N.PATH_STREAM, flags=int(os.environ.get("S1_FLAGS", "0"))) as ctx:
     Ls = [int(float(x)) for x in os.environ.get("S1_LS", "1e6,1e7,5e7,1e8,2e8,4e8").split(",")]
     for L in Ls:
         ctx.set_links_dev(n, L, ta.data_ptr(), tb.data_ptr(), None)
