@@ -103,3 +103,14 @@ def test_shard_range_partitions():
             assert all(spans[i][1] == spans[i + 1][0] for i in range(world - 1))
             sizes = [b - a for a, b in spans]
             assert max(sizes) - min(sizes) <= 1 and sizes == SH.shard_counts(total, world)
+
+
+def test_python_slicing_mirrors_the_library():
+    """lxy_b200/sharding.py is the CPU-testable mirror of the split comm.cu uses on the GPUs
+    (lxy_comm_slice): same balanced contiguous ranges."""
+    import lxy_b200._native as N
+    from lxy_b200 import sharding as SH
+    for total, world in [(1024, 8), (1028, 8), (5, 8), (0, 3), (1000, 7), (129, 2)]:
+        for r in range(world):
+            lo, hi = SH.shard_range(total, world, r)
+            assert (lo, hi - lo) == N.comm_slice(total, world, r)
