@@ -451,13 +451,16 @@ def check_multi_gpu(job, name, ctx, link_mode, n, L_loc, P, a, b, perms_all, per
                         ra, rb = a, b
                     else:
                         ra, rb, _ = gen_links(n, L_loc, seed, dev, stream_seed=seed * 1000 + r)
+                    torch.cuda.synchronize()   # the library's stream does not wait for torch's
                     sc.set_links_dev(n, L_loc, ra.data_ptr(), rb.data_ptr(), None)
                     sc.scaff_score_batch_dev(perm_dev.data_ptr(), P, tmp_o.data_ptr(), tmp_x.data_ptr())
                     sc.sync()
                     one += tmp_x
                     del ra, rb
         if not bool((one == got).all().item()):
-            fails.append(f"{int((one != got).sum().item())} of {P} sharded scores differ from the single-GPU result")
+            bad = torch.nonzero(one != got).flatten()[:3].tolist()
+            fails.append(f"{int((one != got).sum().item())} of {P} sharded scores differ from the single-GPU result "
+                         f"(first: {[(i, int(one[i]), int(got[i])) for i in bad]})")
     # (3) the oracle on two sampled candidates, over all records
     pick = np.array([1, P // 2 + 1], np.int64)
     cores = max(1, (os.cpu_count() or 1) // (job.world if link_mode else 1))

@@ -280,6 +280,22 @@ int lxy_scaffold_links_from_sam(const char* sam_path, const char* out_path, int3
                                 lxy_load_stats* stats);
 int lxy_ctx_load_sam(lxy_ctx* ctx, const char* sam_path, lxy_links** out, lxy_load_stats* stats);
 
+/* ---- TabulateVariantBlockLinks (src/sequtil/links.go:372-420): read pairs -> phasing link table -------
+ * The accumulation step of BlockLinksFromSam (src/sequtil/alignment.go:461-555, `lxy phase links`), i.e.
+ * what produces every phasing `.links` file.  For n_pairs read pairs of ONE chromosome: mate 1 of pair p
+ * holds the entries blk1[4 * off1[p] .. 4 * off1[p+1]), mate 2 blk2[4 * off2[p] .. 4 * off2[p+1]); an
+ * entry is the map entry GetVariantBlocks builds (alignment.go:265-323): {block number, #ref, #alt,
+ * #other} (block numbers distinct within a mate).  For every (k1 of mate 1, k2 of mate 2) with k1 > k2
+ * and #other == 0 on both sides, Links.Add(ID("chrom_k1"), ID("chrom_k2"), +1) when both blocks were read
+ * ref-major or both alt-major (strictly), else -1.  *ct = number of such additions, *balance = their sum
+ * (the function's return values).  device >= 0: the tabulation runs on that GPU (count / scan / emit /
+ * radix sort / reduce by key, varblock_links.cu); device < 0: the host loop.  Both leave the same table:
+ * new names get their ids in ascending (k1, k2) order of the pairs they first occur in, id1 before id2
+ * (the reference's order is Go map iteration order, random from run to run - compare tables by name). */
+int lxy_links_tabulate_varblocks(lxy_links* l, const char* chrom, int64_t n_pairs, const int64_t* off1,
+                                 const int32_t* blk1, const int64_t* off2, const int32_t* blk2,
+                                 int32_t device, int64_t* ct, int64_t* balance);
+
 /* ---- device-resident GA generation loop --------------------------------------------------------
  * Replaces the loop `gao.Optimize(1); best := gao.Best()` of Scaffold / Phase (scaff.go:105-126,
  * phase.go:74-95) and the genome operators it drives (scaff/genome.go:47-91,93-97,125-138,161-209;

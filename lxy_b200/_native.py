@@ -39,6 +39,7 @@ SYMBOLS = [
     "lxy_ctx_path", "lxy_phase_score_batch_bits", "lxy_phase_score_batch_bits_dev",
     "lxy_comm_unique_id", "lxy_comm_init_rank", "lxy_comm_init_all", "lxy_comm_destroy", "lxy_comm_info",
     "lxy_comm_slice", "lxy_scaff_score_sharded", "lxy_scaff_score_sharded_dev", "lxy_ga_set_sharding",
+    "lxy_links_tabulate_varblocks",
 ]
 
 ACC_AUTO, ACC_F64, ACC_INT = 0, 1, 2
@@ -205,6 +206,7 @@ def lib():
         "lxy_scaff_score_sharded": (i32, [vp, i32, vp, i32, vp, vp]),
         "lxy_scaff_score_sharded_dev": (i32, [vp, i32, vp, i32, vp, vp]),
         "lxy_ga_set_sharding": (i32, [vp, i32]),
+        "lxy_links_tabulate_varblocks": (i32, [vp, C.c_char_p, i64, vp, vp, vp, vp, i32, C.POINTER(i64), C.POINTER(i64)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -652,6 +654,26 @@ class NativeLinks:
         a, b, w = np.zeros(m, np.uint32), np.zeros(m, np.uint32), np.zeros(m, np.float64)
         _check(lib().lxy_links_records(self._h, _p(a), _p(b), _p(w)))
         return a, b, w
+
+    def TabulateVariantBlockLinks(self, chrom, off1, blk1, off2, blk2, device=None):
+        """TabulateVariantBlockLinks (links.go:372-420) over a batch of read pairs of one chromosome ->
+        (ct, balance).  off*: int64 CSR offsets [n_pairs + 1]; blk*: int32 [entries][4] = (block, #ref,
+        #alt, #other) as GetVariantBlocks builds them.  device=None: the host loop; device=d: on GPU d."""
+        off1, off2 = _c(off1, np.int64), _c(off2, np.int64)
+        blk1, blk2 = _c(blk1, np.int32).reshape(-1, 4), _c(blk2, np.int32).reshape(-1, 4)
+        if len(off1) != len(off2) or len(off1) < 1:
+            raise ValueError("off1 and off2 must both have n_pairs + 1 entries")
+        ct, bal = C.c_int64(0), C.c_int64(0)
+        _check(lib().lxy_links_tabulate_varblocks(self._h, chrom.encode(), len(off1) - 1, _p(off1), _p(blk1),
+                                                  _p(off2), _p(blk2), -1 if device is None else int(device),
+                                                  C.byref(ct), C.byref(bal)))
+        return ct.value, bal.value
+
+    def by_name(self):
+        """{(name, name) sorted: value}: how tables with differently assigned ids compare."""
+        a, b, w = self.records()
+        names = self.Decode(range(self.Size()))
+        return {tuple(sorted((names[int(x)], names[int(y)]))): float(v) for x, y, v in zip(a, b, w)}
 
     def attach(self, ctx, phase=False):
         _check(lib().lxy_ctx_set_links_from(ctx._h, self._h, 1 if phase else 0))

@@ -106,7 +106,8 @@ template <class T, bool BITS>
 __global__ void __launch_bounds__(256) k_ga_children(const lxy_ga_child* __restrict__ plan,
                                                      const int32_t* __restrict__ count, int32_t n,
                                                      const T* __restrict__ pop, const int32_t* __restrict__ inv,
-                                                     T* __restrict__ child, int32_t* __restrict__ scratch) {
+                                                     T* __restrict__ child, int32_t* __restrict__ scratch,
+                                                     int use_smem) {
   const int32_t c = blockIdx.x;
   if (c >= *count) return;
   const lxy_ga_child k = plan[c];
@@ -141,9 +142,13 @@ __global__ void __launch_bounds__(256) k_ga_children(const lxy_ga_child* __restr
   const int32_t* inva = inv + (size_t)k.pa * n;
   const int32_t* invb = inv + (size_t)k.pb * n;
   const int32_t w = p2 - p1 + 1;
-  int32_t* hitA = scratch + (size_t)k.slot * 3 * n;  // position outside the window, or -1
+  // hit lists + stack: in shared memory when 3 n ints fit (the replay below is one thread walking
+  // them: out of global memory every step paid a DRAM / L2 round trip), else in the global scratch
+  extern __shared__ int32_t s_pmx[];
+  int32_t* hitA = use_smem ? s_pmx : scratch + (size_t)k.slot * 3 * n;  // position outside the window, or -1
   int32_t* hitB = hitA + n;
   int32_t* stack = hitB + n;
+  __shared__ int32_t s_matches;
   for (int32_t j = tid; j < w; j += blockDim.x) {
     const int32_t qa = inva[(int32_t)b[p1 + j]], qb = invb[(int32_t)a[p1 + j]];
     hitA[j] = (qa < p1 || qa > p2) ? qa : -1;
@@ -151,15 +156,19 @@ __global__ void __launch_bounds__(256) k_ga_children(const lxy_ga_child* __restr
   }
   __syncthreads();  // hit lists and both proto-children are complete
   if (tid == 0) {
+    // The replay only PAIRS the hits (which a-side hit meets which b-side hit is what the reference's
+    // two stacks decide); the swaps themselves are independent of one another and are applied by the
+    // whole CTA afterwards.  Match m is written over slot m of the hit lists: after step j at most
+    // j + 1 matches exist (a match consumes two of the <= 2 (j + 1) events seen), so the slot has been read.
     int32_t depth = 0;   // > 0: `depth` entries of amap on the stack; < 0: -depth entries of bmap
+    int32_t m = 0;
     for (int32_t j = 0; j < w; ++j) {
       const int32_t ha = hitA[j], hb = hitB[j];
       if (ha >= 0) {
         if (depth < 0) {                 // bmap non-empty: pop it, pair with this hit
           const int32_t i2 = stack[-depth - 1];
           ++depth;
-          out[ha] = b[i2];               // ca[i1], cb[i2] = cb[i2], ca[i1]
-          outb[i2] = a[ha];
+          hitA[m] = ha; hitB[m] = i2; ++m;   // ca[i1], cb[i2] = cb[i2], ca[i1]
         } else {
           stack[depth++] = ha;
         }
@@ -168,14 +177,20 @@ __global__ void __launch_bounds__(256) k_ga_children(const lxy_ga_child* __restr
         if (depth > 0) {                 // amap non-empty
           const int32_t i1 = stack[depth - 1];
           --depth;
-          out[i1] = b[hb];
-          outb[hb] = a[i1];
+          hitA[m] = i1; hitB[m] = hb; ++m;
         } else {
           stack[-depth] = hb;
           --depth;
         }
       }
     }
+    s_matches = m;
+  }
+  __syncthreads();
+  for (int32_t q = tid; q < s_matches; q += blockDim.x) {
+    const int32_t i1 = hitA[q], i2 = hitB[q];
+    out[i1] = b[i2];
+    outb[i2] = a[i1];
   }
 }
 
@@ -322,11 +337,22 @@ int ga_begin(lxy_ga* g) {
   k_ga_plan<<<1, kPlanThreads, 0, st>>>(g->prm, g->gen, g->n, g->plan.as<lxy_ga_child>(), g->count.as<int32_t>());
   if (g->prm.kind == LXY_GA_PHASE) {
     k_ga_children<uint8_t, true><<<3 * P, 256, 0, st>>>(g->plan.as<lxy_ga_child>(), g->count.as<int32_t>(), g->n,
-        g->pop[g->cur].as<uint8_t>(), nullptr, g->child.as<uint8_t>(), nullptr);
+        g->pop[g->cur].as<uint8_t>(), nullptr, g->child.as<uint8_t>(), nullptr, 0);
   } else {
     LXY_TRY(scaff_positions(c, g->pop[g->cur].as<int32_t>(), P, g->n, g->inv.as<int32_t>()));
-    k_ga_children<int32_t, false><<<3 * P, 256, 0, st>>>(g->plan.as<lxy_ga_child>(), g->count.as<int32_t>(), g->n,
-        g->pop[g->cur].as<int32_t>(), g->inv.as<int32_t>(), g->child.as<int32_t>(), g->scratch.as<int32_t>());
+    // PMX hit lists + stack in shared memory when they fit (3 n ints)
+    const size_t pmx_smem = 12 * (size_t)g->n;
+    const bool in_smem = pmx_smem + 1024 <= (size_t)c->max_smem_optin;
+    if (in_smem && pmx_smem > 48 * 1024) {
+      static size_t configured[64] = {};
+      std::lock_guard<std::mutex> cfg_lock(config_mutex());
+      if (configured[c->cfg.device & 63] < pmx_smem) {
+        LXY_CUDA(cudaFuncSetAttribute(k_ga_children<int32_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pmx_smem));
+        configured[c->cfg.device & 63] = pmx_smem;
+      }
+    }
+    k_ga_children<int32_t, false><<<3 * P, 256, in_smem ? pmx_smem : 0, st>>>(g->plan.as<lxy_ga_child>(), g->count.as<int32_t>(), g->n,
+        g->pop[g->cur].as<int32_t>(), g->inv.as<int32_t>(), g->child.as<int32_t>(), g->scratch.as<int32_t>(), in_smem ? 1 : 0);
   }
   LXY_CUDA(cudaGetLastError());
   LXY_CUDA(cudaEventRecord(g->ev[1], st));

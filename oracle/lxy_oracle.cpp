@@ -453,6 +453,40 @@ lxyo_links* lxyo_links_from_records(int n, int64_t L, const uint32_t* a, const u
   return h;
 }
 
+// TabulateVariantBlockLinks (links.go:372-420) over a batch of read pairs of one chromosome: the
+// accumulation step of BlockLinksFromSam (alignment.go:524-535).  Mate 1 of pair p holds the entries
+// f1[off1[p] .. off1[p+1]), mate 2 the entries f2[off2[p] .. off2[p+1]); an entry is the map entry
+// GetVariantBlocks builds (alignment.go:265-323): {block number, #ref, #alt, #other}.  The Go code
+// ranges over two maps (random order); here the entries are visited in the order given, which is one
+// of the orders the reference can take - ids therefore compare by NAME, never by value.
+// PARITY UNPINNED by reference tests (TestBlockLinksFromSam is commented out, alignment_test.go:282-299,
+// and toy.varblock.links is the output of an older implementation); pinned by the source text and by
+// the independent Python restatement in tests/golden/gen_varblock_golden.py.
+void lxyo_links_tabulate_varblocks(lxyo_links* h, const char* chrom, int64_t n_pairs, const int64_t* off1,
+                                   const int32_t* f1, const int64_t* off2, const int32_t* f2,
+                                   int64_t* ct_out, int64_t* balance_out) {
+  int64_t ct = 0, balance = 0;
+  const std::string c(chrom);
+  for (int64_t p = 0; p < n_pairs; ++p) {
+    for (int64_t i = off1[p]; i < off1[p + 1]; ++i) {        // for k1 := range fgp1        :378
+      const int32_t* e1 = f1 + 4 * i;
+      for (int64_t j = off2[p]; j < off2[p + 1]; ++j) {      // for k2 := range fgp2        :381
+        const int32_t* e2 = f2 + 4 * j;
+        if (!(e1[0] > e2[0])) continue;                      // if k1 > k2                  :385
+        if (!(e1[3] == 0 && e2[3] == 0)) continue;           // neither ambiguous           :392
+        const std::string id1 = c + "_" + std::to_string(e1[0]), id2 = c + "_" + std::to_string(e2[0]);
+        const bool one = e1[1] > e1[2] && e2[1] > e2[2];     // inPhaseCaseOne              :394
+        const bool two = e1[1] < e1[2] && e2[1] < e2[2];     // inPhaseCaseTwo              :395
+        const int a = id_of(h->l, id1), b = id_of(h->l, id2);  // ID(id1) then ID(id2)      :402/:409
+        if (one || two) { add_val(h->l, a, b, 1.0); balance += 1; ct += 1; }
+        else            { add_val(h->l, a, b, -1.0); balance -= 1; ct += 1; }
+      }
+    }
+  }
+  if (ct_out) *ct_out = ct;
+  if (balance_out) *balance_out = balance;
+}
+
 // ---- reference-order scorers -------------------------------------------------------------
 double lxyo_scaff_score_ref(const lxyo_links* h, const int64_t* gene, int n) {
   if (size_of(h->l) > n) return std::numeric_limits<double>::quiet_NaN();  // Go would panic

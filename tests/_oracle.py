@@ -41,6 +41,7 @@ def _load():
         "lxyo_links_npairs": (i64, [vp]),
         "lxyo_links_export": (i64, [vp, vp, vp, vp, i64]),
         "lxyo_links_from_records": (vp, [i32, i64, vp, vp, vp]),
+        "lxyo_links_tabulate_varblocks": (None, [vp, C.c_char_p, i64, vp, vp, vp, vp, vp, vp]),
         "lxyo_scaff_score_ref": (f64, [vp, vp, i32]),
         "lxyo_phase_score_ref": (f64, [vp, vp, i32]),
         "lxyo_scaff_score_ref_batch": (None, [vp, vp, i32, i32, i32, vp]),
@@ -111,6 +112,21 @@ class Links:
     def from_records(cls, n, a, b, w):
         a, b, w = _c(a, np.uint32), _c(b, np.uint32), _c(w, np.float64)
         return cls(lib.lxyo_links_from_records(n, len(a), _p(a), _p(b), _p(w)))
+
+    def tabulate_varblocks(self, chrom, off1, blk1, off2, blk2):
+        """TabulateVariantBlockLinks (links.go:372-420) over a batch of read pairs -> (ct, balance)."""
+        off1, off2 = _c(off1, np.int64), _c(off2, np.int64)
+        blk1, blk2 = _c(blk1, np.int32), _c(blk2, np.int32)
+        ct, bal = C.c_int64(0), C.c_int64(0)
+        lib.lxyo_links_tabulate_varblocks(self.h, chrom.encode(), len(off1) - 1, _p(off1), _p(blk1), _p(off2),
+                                          _p(blk2), C.cast(C.byref(ct), C.c_void_p), C.cast(C.byref(bal), C.c_void_p))
+        return ct.value, bal.value
+
+    def by_name(self):
+        """{(name_lo, name_hi): value} with the two names sorted - tables whose ids were assigned in a
+        different order (Go map iteration is random) compare equal through this."""
+        a, b, w = self.export()
+        return {tuple(sorted((self.name(int(x)), self.name(int(y))))): float(v) for x, y, v in zip(a, b, w)}
 
     def add_key(self, name):
         lib.lxyo_links_add_key(self.h, name.encode())
