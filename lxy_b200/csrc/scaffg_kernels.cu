@@ -473,6 +473,8 @@ int launch_g3(lxy_ctx* c, const GParams& prm, int grid) {
   LXY_CUDA(cudaGetLastError());
   return LXY_OK;
 }
+#include "scaffg2.cuh"
+
 template <int WM>
 int launch_g(lxy_ctx* c, const GParams& prm, int grid, bool sgn, bool pow2) {
   if (sgn) return pow2 ? launch_g3<WM, true, true>(c, prm, grid) : launch_g3<WM, true, false>(c, prm, grid);
@@ -481,11 +483,93 @@ int launch_g(lxy_ctx* c, const GParams& prm, int grid, bool sgn, bool pow2) {
 
 }  // namespace
 
+// Unit-weight records, signed 32-bit coordinates, a unit the one-multiply division covers: scaffg2.cuh
+static int scaffg2_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int32_t P, double* out_dev,
+                         int64_t* x100_dev, uint32_t K, uint32_t m, uint32_t sh) {
+  ScaffLinks& S = c->scaff;
+  cudaStream_t st = c->stream;
+  const int n = S.n;
+  const int groups = (P + kCand2 - 1) / kCand2;
+  const int Ppad = groups * kCand2;
+  LXY_TRY(c->d_posA.reserve(4 * (size_t)Ppad * n));           // origin table
+  LXY_TRY(c->d_posB.reserve(32 * (size_t)groups * n + 32));   // first-bit rows
+  LXY_TRY(c->d_start.reserve(4 * (size_t)P * n));             // pos (validation)
+  LXY_TRY(c->d_flag.reserve(64));
+  LXY_CUDA(cudaMemsetAsync(c->d_flag.p, 0, 64, st));
+  LXY_CUDA(cudaEventRecord(c->ev[0], st));
+  LXY_CUDA(cudaMemsetAsync(c->d_posB.p, 0, 32 * (size_t)groups * n, st));
+  int launches = 0;
+  k_scaffg2_layout<<<(Ppad * 32 + 255) / 256, 256, 0, st>>>(perm_dev, ori_dev, S.len.as<uint32_t>(), P, Ppad, n,
+                                                           c->d_posA.as<int32_t>(), c->d_posB.as<uint32_t>(),
+                                                           c->d_start.as<int32_t>(), c->d_flag.as<int>());
+  ++launches;
+  if (!(c->cfg.flags & LXY_FLAG_NO_VALIDATE)) {
+    k_scaffg_check<<<grid_for((int64_t)P * n, 256, c->sm_count), 256, 0, st>>>(perm_dev, P, n, c->d_start.as<int32_t>(), c->d_flag.as<int>());
+    ++launches;
+  }
+  LXY_CUDA(cudaGetLastError());
+  LXY_CUDA(cudaEventRecord(c->ev[1], st));
+  const int64_t npk = (S.L + kPacket - 1) / kPacket;
+  int splits = (2 * c->sm_count) / groups;  // two full waves of one CTA per SM, never a third
+  if (splits < 1) splits = 1;
+  if ((int64_t)splits * 64 > npk) splits = (int)(npk / 64 > 0 ? npk / 64 : 1);
+  // a warp keeps int32 sums per unit: at most 2^31 / 100 records per warp and unit (kept far below)
+  while (S.L / splits > ((int64_t)1 << 28)) splits *= 2;
+  const int units = groups * splits;
+  const int grid = units < c->sm_count ? units : c->sm_count;
+  LXY_TRY(c->d_partial.reserve(8 * (size_t)units * 2 * kCand2));
+  G2Params prm;
+  prm.rec = S.rec.as<uint16_t>();
+  prm.xa = S.xa.as<uint32_t>();
+  prm.xb = S.xb.as<uint32_t>();
+  prm.tile_start = S.tile_start.as<int64_t>();
+  prm.origin = c->d_posA.as<int32_t>();
+  prm.firstw = c->d_posB.as<uint32_t>();
+  prm.partial = c->d_partial.as<int64_t>();
+  prm.L = S.L;
+  prm.n = n;
+  prm.nblk = S.nblk;
+  prm.groups = groups;
+  prm.splits = splits;
+  prm.K = K; prm.m = m; prm.sh = sh;
+  if (S.L > 0) {
+    static bool configured[64] = {};
+    {
+      std::lock_guard<std::mutex> cfg_lock(config_mutex());
+      if (!configured[c->cfg.device & 63]) {
+        LXY_CUDA(cudaFuncSetAttribute(k_scaffg2_score, cudaFuncAttributeMaxDynamicSharedMemorySize, kG2Smem));
+        configured[c->cfg.device & 63] = true;
+      }
+    }
+    k_scaffg2_score<<<grid, kG2Threads, kG2Smem, st>>>(prm);
+    LXY_CUDA(cudaGetLastError());
+    ++launches;
+  } else {
+    LXY_CUDA(cudaMemsetAsync(c->d_partial.p, 0, 8 * (size_t)units * 2 * kCand2, st));
+  }
+  LXY_CUDA(cudaEventRecord(c->ev[2], st));
+  k_scaffg2_finish<<<(P + 7) / 8, 256, 0, st>>>(P, splits, c->d_partial.as<int64_t>(), out_dev, x100_dev);
+  ++launches;
+  LXY_CUDA(cudaGetLastError());
+  LXY_CUDA(cudaEventRecord(c->ev[3], st));
+  c->timing.launches = launches;
+  c->timing.grid = grid;
+  c->timing.link_bytes = (int64_t)groups * S.L * 10;
+  c->timing.table_bytes = 0;
+  return LXY_OK;
+}
+
 int scaffg_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int32_t P,
                  double* out_dev, int64_t* x100_dev) {
   ScaffLinks& S = c->scaff;
   if (!S.ready || !S.gprofile) { set_error("scaffg score: G-profile links not set"); return LXY_ERR_STATE; }
   if (P <= 0) return LXY_OK;
+  {
+    uint32_t K, m, sh;
+    static const bool g2_off = getenv("LXY_G2_OFF") != nullptr;   // experiments: the 64-candidate kernel everywhere
+    if (!g2_off && S.wmode == W_UNIT && S.total_len < 0x7FFFFFF0ull && g2_magic(S.unit, K, m, sh))
+      return scaffg2_score(c, perm_dev, ori_dev, P, out_dev, x100_dev, K, m, sh);
+  }
   cudaStream_t st = c->stream;
   const int n = S.n;
   const int groups = (P + kCandG - 1) / kCandG;

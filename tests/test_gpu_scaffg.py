@@ -103,3 +103,60 @@ def test_hand_case_and_errors(ctx):
         ctx.set_links_g(np.array([5, 0], np.uint32), 1, [0], [0], [1], [0], None)   # zero length
     with pytest.raises(N.LxyError):
         ctx.set_links_g(np.full(3, 2_000_000_000, np.uint32), 1, [0], [0], [1], [0], None)  # > 2^32
+
+
+@pytest.mark.parametrize("unit", [2, 3, 7, 4096, 13_971, 13_973, 318_574, 999_983, 1 << 20, 50_000_001, 190_000_000])
+def test_one_multiply_division_is_exact_at_the_bucket_edges(ctx, unit):
+    """k_scaffg2_score divides the clamped distance by `unit` with one multiply-high (scaffg2.cuh,
+    g2_magic).  Distances of exactly k * unit - 1, k * unit and k * unit + 1 for every k up to 23 — and
+    far beyond the clamp — must land in the oracle's bucket, for units on either side of the magic's
+    regime changes (22 unit^2 < 2^32 up to 13,972; the fall-back to k_scaffg_score above ~1.9e8)."""
+    n = 40
+    span = 30 * unit + 10
+    lens = np.full(n, min(span, (2**31 - 1000) // n), np.uint32)
+    lens[0] = min(span, 2**31 - 1000 - int(lens[1:].sum(dtype=np.int64)))
+    rng = np.random.default_rng(unit % 1000)
+    a, xa, b, xb = [], [], [], []
+    for k in list(range(0, 24)) + [30, 100, 1000]:
+        for delta in (-1, 0, 1):
+            d = k * unit + delta
+            if d < 0 or d >= int(lens[0]):
+                continue
+            lo = int(rng.integers(0, int(lens[0]) - d))
+            # two records inside contig 0 (distance d whatever the ordering) ... impossible: a != b is
+            # required, so use contigs 0 and 1 adjacent in the identity ordering instead
+            x0 = int(lens[0]) - 1 - lo if lo < int(lens[0]) else 0
+            need = d - (int(lens[0]) - 1 - x0) - 1          # offset inside contig 1 (identity order, forward)
+            if 0 <= need < int(lens[1]):
+                a.append(0); xa.append(x0); b.append(1); xb.append(need)
+    a, xa, b, xb = (np.array(v, np.uint32) for v in (a, xa, b, xb))
+    assert len(a) > 20
+    perms = np.stack([np.arange(n, dtype=np.int32)] + [rng.permutation(n).astype(np.int32) for _ in range(140)])
+    oris = (rng.random(perms.shape) < 0.5).astype(np.uint8)
+    oris[0] = 0
+    w = np.ones(len(a))
+    want, ox = O.scaffg_score_links_batch(lens, unit, a, xa, b, xb, w, perms, oris, nthreads=4)
+    _, _, dist = O.scaffg_score_links(lens, unit, a, xa, b, xb, w, perms[0], oris[0], want_dist=True)
+    assert {int(d) % unit for d in dist} >= {0, 1, unit - 1} or unit == 2     # the edges are really hit
+    ctx.set_links_g(lens, unit, a, xa, b, xb, None)
+    got, x100 = ctx.scaffg_score_batch(perms, oris, want_x100=True)
+    assert x100.tolist() == ox.tolist()
+
+
+@pytest.mark.parametrize("n,L,P,unit", [(900, 300_000, 129, 250_000), (2100, 500_000, 300, 1 << 19), (300, 100_000, 1024, 123_457)])
+def test_128_candidate_groups_vs_oracle(ctx, n, L, P, unit):
+    """Populations above one group, group boundaries inside the population, both orientations, the
+    first contig of many candidates among the records (the `i-k > 0` multiplicity path)."""
+    lens = S.contig_lengths(n, 31)
+    a, xa, b, xb, w = S.scaffg_links(n, L, 31, lens)
+    perms = S.scaff_population(n, P, 131)
+    oris = S.orientations(n, P, 31)
+    want, ox100 = O.scaffg_score_links_batch(lens, unit, a, xa, b, xb, w, perms, oris, nthreads=8)
+    ctx.set_links_g(lens, unit, a, xa, b, xb, None)
+    got, x100 = ctx.scaffg_score_batch(perms, oris, want_x100=True)
+    assert x100.tolist() == ox100.tolist()
+    np.testing.assert_allclose(got, want, rtol=REL, atol=0)
+    bad = perms.copy()
+    bad[P - 1, 0] = bad[P - 1, 1]
+    with pytest.raises(N.LxyError):
+        ctx.scaffg_score_batch(bad, oris)
