@@ -98,6 +98,30 @@ def gen_links(n, L, seed, device, stream_seed=None):
     return a, b, order
 
 
+def link_owners(a, b, n, world):
+    """torch mirror of lxy_comm_link_owners (comm.cu): contiguous tile ranges of the sorted store."""
+    import torch
+    nblk = (n + 255) // 256
+    ntiles = nblk * (nblk + 1) // 2
+    lo, hi = torch.minimum(a, b).long() >> 8, torch.maximum(a, b).long() >> 8
+    t = lo * nblk - lo * (lo - 1) // 2 + (hi - lo)
+    return ((t + 1) * world - 1) // ntiles
+
+
+def gen_links_tile_shard(n, L, seed, device, world, rank):
+    """The same L records as the `world` per-rank streams of gen_links(..., stream_seed=seed * 1000 + r)
+    together, but rank `rank` keeps the ones lxy_comm_link_owners assigns to it (whole tiles per rank)."""
+    import torch
+    keep_a, keep_b, order = [], [], None
+    for r in range(world):
+        a, b, order = gen_links(n, L // world, seed, device, stream_seed=seed * 1000 + r)
+        mine = link_owners(a, b, n, world) == rank
+        keep_a.append(a[mine])
+        keep_b.append(b[mine])
+        del a, b, mine
+    return torch.cat(keep_a), torch.cat(keep_b), order
+
+
 def gen_population(n, P, seed, order):
     """The true order, its reverse, k-swap neighbours of it, random permutations (int32 [P][n])."""
     rng = np.random.default_rng(seed)
@@ -416,6 +440,7 @@ def time_path(job, cx, dev_call, host_call, steps, warmup, sample_clocks=False):
 
 
 def check_multi_gpu(job, name, ctx, link_mode, n, L_loc, P, a, b, perms_all, perm_dev, x100_dev, seed):
+    L_all = WORKLOADS[name][1]
     """Outside the timed region: is the sharded result the single-GPU result, and the oracle's?
     (1) every rank holds the same [P] vector of exact integers; (2) rank 0 scores the whole population
     against ALL records on its own GPU (link-sharded: shard by shard, the other ranks' record streams
@@ -446,13 +471,10 @@ def check_multi_gpu(job, name, ctx, link_mode, n, L_loc, P, a, b, perms_all, per
             ctx.sync()
         else:
             with N.Context(job.local, path=N.PATH_STREAM) as sc:
-                for r in range(job.world):
-                    if r == 0:
-                        ra, rb = a, b
-                    else:
-                        ra, rb, _ = gen_links(n, L_loc, seed, dev, stream_seed=seed * 1000 + r)
+                for r in range(job.world):   # the `world` record streams the shards were cut from, one at a time
+                    ra, rb, _ = gen_links(n, L_all // job.world, seed, dev, stream_seed=seed * 1000 + r)
                     torch.cuda.synchronize()   # the library's stream does not wait for torch's
-                    sc.set_links_dev(n, L_loc, ra.data_ptr(), rb.data_ptr(), None)
+                    sc.set_links_dev(n, int(ra.numel()), ra.data_ptr(), rb.data_ptr(), None)
                     sc.scaff_score_batch_dev(perm_dev.data_ptr(), P, tmp_o.data_ptr(), tmp_x.data_ptr())
                     sc.sync()
                     one += tmp_x
@@ -488,9 +510,12 @@ def run_scoring(job, name, steps, warmup, sample_clocks, check):
     torch, N, dev, rank, world = job.torch, job.N, job.dev, job.rank, job.world
     n, L, P, seed, pseed = WORKLOADS[name]
     link_mode = name in LINK_SHARDED
-    if link_mode:       # records sharded, the whole population on every rank
-        L_loc = L // world
-        a, b, order = gen_links(n, L_loc, seed, dev, stream_seed=seed * 1000 + rank)
+    if link_mode:       # records sharded by tile range (lxy_comm_link_owners), the whole population on every rank
+        if world > 1:
+            a, b, order = gen_links_tile_shard(n, L, seed, dev, world, rank)
+        else:
+            a, b, order = gen_links(n, L, seed, dev, stream_seed=seed * 1000)
+        L_loc = int(a.numel())
     else:               # links replicated, the population sharded by the library
         L_loc = L
         a, b, order = gen_links(n, L, seed, dev)
@@ -518,7 +543,7 @@ def run_scoring(job, name, steps, warmup, sample_clocks, check):
            "link_mode": link_mode, "ctx": ctx, "a": a, "b": b, "perms_all": perms_all, "perms": perms,
            "perm_dev": perm_dev, "out_dev": out_dev, "x100_dev": x100_dev, "t_build": t_build, "main": main,
            "P_loc": P if link_mode else N.comm_slice(P, world, rank)[1]}
-    L_total = L_loc * world if link_mode else L
+    L_total = (L // world) * world if link_mode else L
     evals = float(P) * float(L_total)
     res["L_total"] = L_total
     res["value"] = evals * steps / (main["ms_dev"] * 1e-3)

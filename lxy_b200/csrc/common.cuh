@@ -92,7 +92,7 @@ struct ScoreGraph {
   cudaGraphExec_t exec = nullptr;
   lxy_timing timing{};
   uint64_t stamp = 0;              // last use (eviction)
-  const void* scratch[5] = {};     // the context's scratch buffers the graph writes to: a later, larger
+  const void* scratch[6] = {};     // the context's scratch buffers the graph writes to: a later, larger
                                    // call may have reallocated them
 };
 

@@ -87,6 +87,61 @@ __global__ void k_scaff_check(const int32_t* __restrict__ perm, int32_t P, int32
   }
 }
 
+// ---- placement tables in two coalesced passes (16-bit tables) ---------------------------------------
+// k_scaff_layout scatters 2-byte stores over the whole table (one 32-byte sector per store: 2.2 ms of a
+// 41 ms step at 50,000 contigs x 1,024 candidates, and it does not shrink when the records are sharded).
+// Here the inverse permutation of ONE candidate is built in shared memory (the scatter stays on chip),
+// checked there (pos[perm[i]] == i for all i <=> permutation; one table per CTA, so the loser of two
+// stores to a duplicated id always sees a mismatch), and written out as a contiguous row; a second
+// kernel transposes [candidate][contig] into the group-major [group][contig][candidate] tables.
+__global__ void __launch_bounds__(512) k_scaff_inv16(const int32_t* __restrict__ perm, int32_t n,
+                                                     uint16_t* __restrict__ inv, int validate, int* __restrict__ flag) {
+  extern __shared__ uint16_t s_inv[];
+  const int p = blockIdx.x;
+  const int32_t* row = perm + (size_t)p * n;
+  int bad = 0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const int32_t cid = row[i];
+    if ((uint32_t)cid >= (uint32_t)n) bad |= 1;
+    else s_inv[cid] = (uint16_t)i;
+  }
+  __syncthreads();
+  if (validate) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const int32_t cid = row[i];
+      if ((uint32_t)cid < (uint32_t)n && (uint32_t)s_inv[cid] != (uint32_t)(i & 0xFFFF)) bad |= 2;
+    }
+  }
+  if (bad) atomicOr(flag, bad);
+  uint16_t* out = inv + (size_t)p * n;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) out[i] = s_inv[i];
+}
+
+// One CTA per (64 contigs, candidate group): inv[p][c] -> tabA[g][c][pc] = pos + kBias + 1, tabB = -pos.
+template <int CAND>
+__global__ void __launch_bounds__(256) k_scaff_tables16(const uint16_t* __restrict__ inv, int32_t P, int32_t n,
+                                                        uint16_t* __restrict__ tabA, uint16_t* __restrict__ tabB) {
+  constexpr int kC = 64;
+  __shared__ uint16_t tile[CAND][kC + 2];
+  const int c0 = blockIdx.x * kC, g = blockIdx.y;
+  for (int k = threadIdx.x; k < CAND * kC; k += 256) {
+    const int pc = k / kC, c = k - pc * kC, p = g * CAND + pc;
+    uint16_t v = (uint16_t)(c0 + c);                       // pad candidates: identity ordering (discarded)
+    if (p < P && c0 + c < n) v = inv[(size_t)p * n + c0 + c];
+    tile[pc][c] = v;
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < CAND * kC; k += 256) {
+    const int c = k / CAND, pc = k - c * CAND;
+    if (c0 + c < n) {
+      const uint32_t pos = tile[pc][c];
+      const size_t at = ((size_t)g * n + c0 + c) * CAND + pc;
+      tabA[at] = (uint16_t)(pos + kBias + 1);
+      tabB[at] = (uint16_t)(0u - pos);
+    }
+  }
+}
+
 // ---- k_scaff_score ------------------------------------------------------------------------------
 struct ScoreParams {
   const uint16_t* rec;        // sorted records
@@ -745,7 +800,7 @@ int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int
   g->stamp = ++c->graph_clock;
   ++g->seen;
   if (g->failed) return scaff_score_enqueue(c, perm_dev, P, out_dev, x100_dev);
-  const void* scratch[5] = {c->d_posA.p, c->d_posB.p, c->d_partial.p, c->d_corr.p, c->d_flag.p};
+  const void* scratch[6] = {c->d_posA.p, c->d_posB.p, c->d_partial.p, c->d_corr.p, c->d_flag.p, c->d_start.p};
   if (g->exec && std::memcmp(scratch, g->scratch, sizeof(scratch)) != 0) {  // a scratch buffer moved
     cudaGraphExecDestroy(g->exec);
     g->exec = nullptr;
@@ -771,7 +826,7 @@ int scaff_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori_dev, int
     }
     cudaGraphDestroy(graph);
     g->timing = c->timing;
-    const void* now[5] = {c->d_posA.p, c->d_posB.p, c->d_partial.p, c->d_corr.p, c->d_flag.p};
+    const void* now[6] = {c->d_posA.p, c->d_posB.p, c->d_partial.p, c->d_corr.p, c->d_flag.p, c->d_start.p};
     std::memcpy(g->scratch, now, sizeof(now));
   }
   LXY_CUDA(cudaGraphLaunch(g->exec, c->stream));
@@ -883,13 +938,35 @@ static int scaff_enqueue_batch(lxy_ctx* c, const int32_t* perm_dev, int32_t P, d
     LXY_CUDA(cudaEventRecord(c->ev_join, s2));
   }
   const int lg = grid_for((int64_t)Ppad * n, 256, c->sm_count);
-  if (tm == 1) k_scaff_layout<1><<<lg, 256, 0, st>>>(perm_dev, P, Ppad, n, cand, c->d_posA.p, c->d_posB.p, c->d_flag.as<int>());
-  else k_scaff_layout<0><<<lg, 256, 0, st>>>(perm_dev, P, Ppad, n, cand, c->d_posA.p, c->d_posB.p, c->d_flag.as<int>());
-  ++launches;
-  if (!(c->cfg.flags & LXY_FLAG_NO_VALIDATE)) {
-    if (tm == 1) k_scaff_check<1><<<lg, 256, 0, st>>>(perm_dev, P, n, cand, c->d_posB.p, c->d_flag.as<int>());
-    else k_scaff_check<0><<<lg, 256, 0, st>>>(perm_dev, P, n, cand, c->d_posB.p, c->d_flag.as<int>());
+  static const bool old_layout = getenv("LXY_OLD_LAYOUT") != nullptr;   // experiments
+  if (tm == 0 && !old_layout && 2 * (size_t)n + 64 <= (size_t)c->max_smem_optin) {
+    // two coalesced passes: inverse permutation per candidate in shared memory (+ validation), transpose
+    LXY_TRY(c->d_start.reserve(2 * (size_t)P * n + 64));
+    const size_t inv_smem = 2 * (size_t)n;
+    if (inv_smem > 48 * 1024) {
+      static size_t configured[64] = {};
+      std::lock_guard<std::mutex> cfg_lock(config_mutex());
+      if (configured[c->cfg.device & 63] < inv_smem) {
+        LXY_CUDA(cudaFuncSetAttribute(k_scaff_inv16, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)inv_smem));
+        configured[c->cfg.device & 63] = inv_smem;
+      }
+    }
+    k_scaff_inv16<<<P, 512, inv_smem, st>>>(perm_dev, n, c->d_start.as<uint16_t>(),
+                                           (c->cfg.flags & LXY_FLAG_NO_VALIDATE) ? 0 : 1, c->d_flag.as<int>());
+    const dim3 tg((unsigned)((n + 63) / 64), (unsigned)groups);
+    if (cand == 128) k_scaff_tables16<128><<<tg, 256, 0, st>>>(c->d_start.as<uint16_t>(), P, n, c->d_posA.as<uint16_t>(), c->d_posB.as<uint16_t>());
+    else if (cand == 64) k_scaff_tables16<64><<<tg, 256, 0, st>>>(c->d_start.as<uint16_t>(), P, n, c->d_posA.as<uint16_t>(), c->d_posB.as<uint16_t>());
+    else k_scaff_tables16<32><<<tg, 256, 0, st>>>(c->d_start.as<uint16_t>(), P, n, c->d_posA.as<uint16_t>(), c->d_posB.as<uint16_t>());
+    launches += 2;
+  } else {
+    if (tm == 1) k_scaff_layout<1><<<lg, 256, 0, st>>>(perm_dev, P, Ppad, n, cand, c->d_posA.p, c->d_posB.p, c->d_flag.as<int>());
+    else k_scaff_layout<0><<<lg, 256, 0, st>>>(perm_dev, P, Ppad, n, cand, c->d_posA.p, c->d_posB.p, c->d_flag.as<int>());
     ++launches;
+    if (!(c->cfg.flags & LXY_FLAG_NO_VALIDATE)) {
+      if (tm == 1) k_scaff_check<1><<<lg, 256, 0, st>>>(perm_dev, P, n, cand, c->d_posB.p, c->d_flag.as<int>());
+      else k_scaff_check<0><<<lg, 256, 0, st>>>(perm_dev, P, n, cand, c->d_posB.p, c->d_flag.as<int>());
+      ++launches;
+    }
   }
   LXY_CUDA(cudaGetLastError());
   if (first) LXY_CUDA(record_timing_event(c, 1));

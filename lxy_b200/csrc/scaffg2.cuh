@@ -49,6 +49,7 @@ struct G2Params {
   int32_t n, nblk;
   int32_t groups, splits;
   uint32_t K, m, sh;         // clamp, magic multiplier, post-shift
+  uint32_t shmul;            // 2^(32 - sh) (sh > 0)
 };
 
 // Smallest sh with m = ceil(2^(32 + sh) / unit) < 2^32 and K * (m * unit - 2^(32 + sh)) < 2^(32 + sh).
@@ -142,7 +143,8 @@ struct G2Acc {
   }
 };
 
-// One record against the four candidates of this lane.
+// One record against the four candidates of this lane.  SH0: the magic needs no post-shift.
+template <bool SH0>
 __device__ __forceinline__ void g2_eval(const G2RowA& A, uint32_t b_loc, uint32_t xa, uint32_t xb,
                                         const uint8_t* sB, const uint8_t* sFirstB,
                                         uint32_t lut, int lane, const G2Params& prm, G2Acc& acc) {
@@ -154,7 +156,10 @@ __device__ __forceinline__ void g2_eval(const G2RowA& A, uint32_t b_loc, uint32_
     const uint32_t ca = __sad((int)xa, ea[j], 0u);    // |x - e|: start + x, or start + len - 1 - x
     const uint32_t cb = __sad((int)xb, ebv[j], 0u);
     const uint32_t d = __usad(ca, cb, 0u);
-    q[j] = __umulhi(min(d, prm.K), prm.m) >> prm.sh;  // bucket, 21 when far
+    // bucket, 21 when far; the post-shift is a second multiply-high by 2^(32 - sh): IMAD.HI runs on the
+    // FMA pipe, which idles here, SHF on the ALU pipe, which is the busy one (VABSDIFF, VIMNMX)
+    const uint32_t h = __umulhi(min(d, prm.K), prm.m);
+    q[j] = SH0 ? h : __umulhi(h, prm.shmul);
   }
   const uint32_t e01 = lds_u32g(lut + q[0] * 4u + q[1] * (4u * kLutG2Stride));
   const uint32_t e23 = lds_u32g(lut + q[2] * 4u + q[3] * (4u * kLutG2Stride));
@@ -181,6 +186,7 @@ __device__ __forceinline__ G2Packet g2_load_packet(const G2Params& prm, int64_t 
 }
 
 // Eight records with one a: row A comes in registers.
+template <bool SH0>
 __device__ __forceinline__ void g2_eval_packet(const G2Packet& pk, const G2RowA& A, const uint8_t* sB,
                                                const uint8_t* sFirstB, uint32_t lut,
                                                int lane, const G2Params& prm, G2Acc& acc) {
@@ -190,12 +196,13 @@ __device__ __forceinline__ void g2_eval_packet(const G2Packet& pk, const G2RowA&
 #pragma unroll
   for (int k = 0; k < kPacket; ++k) {
     const uint32_t b_loc = (k & 1) ? ((words[k >> 1] >> 16) & 0xFFu) : (words[k >> 1] & 0xFFu);
-    g2_eval(A, b_loc, xav[k], xbv[k], sB, sFirstB, lut, lane, prm, acc);
+    g2_eval<SH0>(A, b_loc, xav[k], xbv[k], sB, sFirstB, lut, lane, prm, acc);
   }
 }
 
 // Records k in [k0, k1) of a packet, row A fetched per record (boundary packets, packets that span
 // several a's).
+template <bool SH0>
 __device__ __forceinline__ void g2_eval_records(const G2Packet& pk, int k0, int k1, size_t rowA0,
                                                 const uint8_t* sB, const uint8_t* sFirstB,
                                                 uint32_t lut, int lane,
@@ -212,10 +219,11 @@ __device__ __forceinline__ void g2_eval_records(const G2Packet& pk, int k0, int 
     const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
     const uint32_t a_loc = r >> 8;
     if (a_loc != a_prev) { A = g2_load_row_a(prm, rowA0 + a_loc, lane); a_prev = a_loc; }   // warp-uniform
-    g2_eval(A, r & 0xFFu, xav[k], xbv[k], sB, sFirstB, lut, lane, prm, acc);
+    g2_eval<SH0>(A, r & 0xFFu, xav[k], xbv[k], sB, sFirstB, lut, lane, prm, acc);
   }
 }
 
+template <bool SH0>
 __global__ void __launch_bounds__(kG2Threads, 1) k_scaffg2_score(G2Params prm) {
   extern __shared__ __align__(128) uint8_t smem[];
   uint8_t* sB = smem;
@@ -294,14 +302,14 @@ __global__ void __launch_bounds__(kG2Threads, 1) k_scaffg2_score(G2Params prm) {
         if (head_partial && warp == 0) {   // boundary packets: masked, one warp each
           const int64_t base = p_first * kPacket;
           const G2Packet pk = g2_load_packet(prm, base);
-          g2_eval_records(pk, (int)(cur - base), (int)min((int64_t)kPacket, seg_end - base), rowA0, sB, sFirstB,
+          g2_eval_records<SH0>(pk, (int)(cur - base), (int)min((int64_t)kPacket, seg_end - base), rowA0, sB, sFirstB,
                           lut, lane, prm, acc);
           acc.flush16();
         }
         if (tail_partial && warp == 1 && !(head_partial && p_last == p_first)) {
           const int64_t base = p_last * kPacket;
           const G2Packet pk = g2_load_packet(prm, base);
-          g2_eval_records(pk, 0, (int)(seg_end - base), rowA0, sB, sFirstB, lut, lane, prm, acc);
+          g2_eval_records<SH0>(pk, 0, (int)(seg_end - base), rowA0, sB, sFirstB, lut, lane, prm, acc);
           acc.flush16();
         }
         const int64_t f0 = p_first + (head_partial ? 1 : 0);
@@ -312,25 +320,52 @@ __global__ void __launch_bounds__(kG2Threads, 1) k_scaffg2_score(G2Params prm) {
             const int32_t cnt = (int32_t)min((int64_t)kG2Warps << 16, nfull - c0);
             const int64_t pbase = (f0 + c0) * kPacket;
             int32_t it = warp;
-            // two packets in flight; row a of the next packet is requested while this one is scored
-            G2Packet pk, nx;
-            G2RowA A, An;
-            if (it < cnt) pk = g2_load_packet(prm, pbase + (int64_t)it * kPacket);
-            if (it + kG2Warps < cnt) nx = g2_load_packet(prm, pbase + (int64_t)(it + kG2Warps) * kPacket);
-            if (it < cnt) A = g2_load_row_a(prm, rowA0 + ((pk.rec.x >> 8) & 0xFFu), lane);
+            // Two packets per iteration, ping-pong (no register rotation): while one is scored the other's
+            // records are in flight.  Row a of a packet must be requested a whole packet ahead of its use,
+            // but the row index is in the packet itself - so the FIRST WORD of each packet is fetched one
+            // step earlier still (w_next), and the row request goes out together with the packet's loads.
+            const uint16_t* rbase = prm.rec + pbase;
+            auto first_word = [&](int32_t i) -> uint32_t {
+              return i < cnt ? __ldg(reinterpret_cast<const uint32_t*>(rbase + (int64_t)i * kPacket)) : 0u;
+            };
+            G2Packet pkA, pkB;
+            G2RowA RA, RB;
+            RA.e = RB.e = make_int4(0, 0, 0, 0); RA.fw = RB.fw = RA.any = RB.any = 0;
+            if (it < cnt) {
+              pkA = g2_load_packet(prm, pbase + (int64_t)it * kPacket);
+              RA = g2_load_row_a(prm, rowA0 + ((first_word(it) >> 8) & 0xFFu), lane);
+            }
+            if (it + kG2Warps < cnt) {
+              pkB = g2_load_packet(prm, pbase + (int64_t)(it + kG2Warps) * kPacket);
+              RB = g2_load_row_a(prm, rowA0 + ((first_word(it + kG2Warps) >> 8) & 0xFFu), lane);
+            }
+            uint32_t w_next = first_word(it + 2 * kG2Warps);
             int32_t since = 0;
 #pragma unroll 1
-            for (; it < cnt; it += kG2Warps) {
-              G2Packet nn;
-              if (it + 2 * kG2Warps < cnt) nn = g2_load_packet(prm, pbase + (int64_t)(it + 2 * kG2Warps) * kPacket);
-              if (it + kG2Warps < cnt) An = g2_load_row_a(prm, rowA0 + ((nx.rec.x >> 8) & 0xFFu), lane);
-              if (++since == kG2Flush) { acc.flush16(); since = 0; }
+            for (; it < cnt; it += 2 * kG2Warps) {
               // sorted by (a, b): first a == last a  <=>  one a for the whole packet (warp-uniform)
-              if (((pk.rec.x >> 8) & 0xFFu) == (pk.rec.w >> 24))
-                g2_eval_packet(pk, A, sB, sFirstB, lut, lane, prm, acc);
+              if (((pkA.rec.x >> 8) & 0xFFu) == (pkA.rec.w >> 24))
+                g2_eval_packet<SH0>(pkA, RA, sB, sFirstB, lut, lane, prm, acc);
               else
-                g2_eval_records(pk, 0, kPacket, rowA0, sB, sFirstB, lut, lane, prm, acc);
-              pk = nx; nx = nn; A = An;
+                g2_eval_records<SH0>(pkA, 0, kPacket, rowA0, sB, sFirstB, lut, lane, prm, acc);
+              if (it + 2 * kG2Warps < cnt) {
+                pkA = g2_load_packet(prm, pbase + (int64_t)(it + 2 * kG2Warps) * kPacket);
+                RA = g2_load_row_a(prm, rowA0 + ((w_next >> 8) & 0xFFu), lane);
+              }
+              w_next = first_word(it + 3 * kG2Warps);
+              if (it + kG2Warps < cnt) {
+                if (((pkB.rec.x >> 8) & 0xFFu) == (pkB.rec.w >> 24))
+                  g2_eval_packet<SH0>(pkB, RB, sB, sFirstB, lut, lane, prm, acc);
+                else
+                  g2_eval_records<SH0>(pkB, 0, kPacket, rowA0, sB, sFirstB, lut, lane, prm, acc);
+              }
+              if (it + 3 * kG2Warps < cnt) {
+                pkB = g2_load_packet(prm, pbase + (int64_t)(it + 3 * kG2Warps) * kPacket);
+                RB = g2_load_row_a(prm, rowA0 + ((w_next >> 8) & 0xFFu), lane);
+              }
+              w_next = first_word(it + 4 * kG2Warps);
+              since += 2;
+              if (since >= kG2Flush - 1) { acc.flush16(); since = 0; }
             }
             acc.flush16();
           }

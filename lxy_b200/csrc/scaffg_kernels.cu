@@ -537,11 +537,14 @@ static int scaffg2_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori
     {
       std::lock_guard<std::mutex> cfg_lock(config_mutex());
       if (!configured[c->cfg.device & 63]) {
-        LXY_CUDA(cudaFuncSetAttribute(k_scaffg2_score, cudaFuncAttributeMaxDynamicSharedMemorySize, kG2Smem));
+        LXY_CUDA(cudaFuncSetAttribute(k_scaffg2_score<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kG2Smem));
+        LXY_CUDA(cudaFuncSetAttribute(k_scaffg2_score<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kG2Smem));
         configured[c->cfg.device & 63] = true;
       }
     }
-    k_scaffg2_score<<<grid, kG2Threads, kG2Smem, st>>>(prm);
+    prm.shmul = sh ? (1u << (32 - sh)) : 0u;
+    if (sh == 0) k_scaffg2_score<true><<<grid, kG2Threads, kG2Smem, st>>>(prm);
+    else k_scaffg2_score<false><<<grid, kG2Threads, kG2Smem, st>>>(prm);
     LXY_CUDA(cudaGetLastError());
     ++launches;
   } else {

@@ -83,3 +83,27 @@ def test_product_package_never_touches_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "lxy_oracle" not in src and "_oracle" not in src, os.path.join(dirpath, f)
+
+
+def test_link_owners_split_whole_tiles_and_match_the_bench_mirror(native):
+    """lxy_comm_link_owners: contiguous tile ranges of the sorted store; bench.py's torch mirror of
+    the formula (used to cut the cfg4 shards on the device) must agree record for record."""
+    import torch
+    import bench
+    rng = np.random.default_rng(7)
+    for n, world in [(5000, 8), (50_000, 8), (300, 2), (257, 3), (1000, 1)]:
+        a = rng.integers(0, n, 20_000).astype(np.uint32)
+        b = rng.integers(0, n, 20_000).astype(np.uint32)
+        own = N.comm_link_owners(n, a, b, world)
+        assert own.min() >= 0 and own.max() <= world - 1
+        mirror = bench.link_owners(torch.from_numpy(a.astype(np.int32)), torch.from_numpy(b.astype(np.int32)), n, world)
+        assert own.tolist() == mirror.tolist()
+        nblk = (n + 255) // 256
+        lo, hi = np.minimum(a, b) >> 8, np.maximum(a, b) >> 8
+        t = lo.astype(np.int64) * nblk - lo.astype(np.int64) * (lo.astype(np.int64) - 1) // 2 + (hi - lo)
+        order = np.argsort(t, kind="stable")
+        assert (np.diff(own[order]) >= 0).all()                      # owners are monotone in the tile index
+        for tile in np.unique(t)[:50]:
+            assert len(set(own[t == tile].tolist())) == 1            # a tile is never split
+    with pytest.raises(N.LxyError):
+        N.comm_link_owners(10, [11], [0], 2)

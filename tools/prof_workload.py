@@ -36,6 +36,42 @@ if mode in ("r3", "r4"):   # r3: the bench default (config 3, population 1024, b
             ctx.scaff_score_batch_dev(perms.data_ptr(), P, out.data_ptr(), None)
         print(ctx.timing())
     sys.exit(0)
+if mode == "g3":      # G-profile at config-3 size (bench.py's g_profile inputs): k_scaffg2_score
+    import torch
+    import bench
+    n, L, P = 5000, int(float(os.environ.get("G3_L", "2e8"))), 1024
+    dev = torch.device("cuda", 0)
+    ta, tb, order = bench.gen_links(n, L, 3, dev)
+    g = torch.Generator(device=dev)
+    g.manual_seed(3 + 17)
+    lens_t = torch.exp(torch.randn(n, generator=g, device=dev, dtype=torch.float64) * 0.6
+                       + float(np.log(min(1_000_000, 1_600_000_000 // n)))).clamp_(1000).long()
+    xa = (torch.rand(L, generator=g, device=dev, dtype=torch.float64) * lens_t[ta.long()]).int()
+    xb = (torch.rand(L, generator=g, device=dev, dtype=torch.float64) * lens_t[tb.long()]).int()
+    perms = torch.from_numpy(bench.gen_population(n, P, 103, order.cpu().numpy())).cuda()
+    oris = torch.from_numpy((np.random.default_rng(134).random((P, n)) < 0.5).astype(np.uint8)).cuda()
+    out = torch.zeros(P, dtype=torch.float64, device="cuda")
+    unit = int(lens_t.double().median().item())
+    with N.Context(0) as ctx:
+        ctx.set_links_g_dev(lens_t.cpu().numpy().astype(np.uint32), unit, L, ta.data_ptr(), xa.data_ptr(),
+                            tb.data_ptr(), xb.data_ptr(), None)
+        for _ in range(steps):
+            ctx.scaffg_score_batch_dev(perms.data_ptr(), oris.data_ptr(), P, out.data_ptr(), None)
+        print(ctx.timing())
+    sys.exit(0)
+if mode == "ga":      # GA generations at config-3 shape on the pair-table path: the operators dominate
+    import torch
+    import bench
+    n, L, P = 5000, 20_000_000, 1024
+    ta, tb, order = bench.gen_links(n, L, 3, torch.device("cuda", 0))
+    torch.cuda.synchronize()
+    with N.Context(0) as ctx:
+        ctx.set_links_dev(n, L, ta.data_ptr(), tb.data_ptr(), None)
+        with N.GA(ctx, N.GA_SCAFF, popsize=P, seed=1234) as ga:
+            ga.init()
+            ga.optimize(steps)
+            print(ga.stats())
+    sys.exit(0)
 if mode == "s1":      # streaming regime at config-3 size: one ordering against 200 M records
     import torch
     import bench
