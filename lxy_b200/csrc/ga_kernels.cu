@@ -145,42 +145,48 @@ __global__ void __launch_bounds__(256) k_ga_children(const lxy_ga_child* __restr
   // hit lists + stack: in shared memory when 3 n ints fit (the replay below is one thread walking
   // them: out of global memory every step paid a DRAM / L2 round trip), else in the global scratch
   extern __shared__ int32_t s_pmx[];
-  int32_t* hitA = use_smem ? s_pmx : scratch + (size_t)k.slot * 3 * n;  // position outside the window, or -1
-  int32_t* hitB = hitA + n;
-  int32_t* stack = hitB + n;
+  int2* hit = reinterpret_cast<int2*>(use_smem ? s_pmx : scratch + (size_t)k.slot * 3 * n);  // (hit of ca, hit of cb) per window index: position outside the window, or -1
+  int32_t* stack = reinterpret_cast<int32_t*>(hit + n);
   __shared__ int32_t s_matches;
   for (int32_t j = tid; j < w; j += blockDim.x) {
     const int32_t qa = inva[(int32_t)b[p1 + j]], qb = invb[(int32_t)a[p1 + j]];
-    hitA[j] = (qa < p1 || qa > p2) ? qa : -1;
-    hitB[j] = (qb < p1 || qb > p2) ? qb : -1;
+    hit[j] = make_int2((qa < p1 || qa > p2) ? qa : -1, (qb < p1 || qb > p2) ? qb : -1);
   }
   __syncthreads();  // hit lists and both proto-children are complete
   if (tid == 0) {
     // The replay only PAIRS the hits (which a-side hit meets which b-side hit is what the reference's
     // two stacks decide); the swaps themselves are independent of one another and are applied by the
-    // whole CTA afterwards.  Match m is written over slot m of the hit lists: after step j at most
-    // j + 1 matches exist (a match consumes two of the <= 2 (j + 1) events seen), so the slot has been read.
+    // whole CTA afterwards.  Match m is written over slot m of the hit list: after step j at most
+    // j + 1 matches exist (a match consumes two of the <= 2 (j + 1) events seen), so the slot has been
+    // read.  Eight steps' hits are fetched before any of them is replayed: the loads overlap, and the
+    // chain that remains is the depth counter (the popped values only feed the match list).
     int32_t depth = 0;   // > 0: `depth` entries of amap on the stack; < 0: -depth entries of bmap
     int32_t m = 0;
-    for (int32_t j = 0; j < w; ++j) {
-      const int32_t ha = hitA[j], hb = hitB[j];
-      if (ha >= 0) {
-        if (depth < 0) {                 // bmap non-empty: pop it, pair with this hit
-          const int32_t i2 = stack[-depth - 1];
-          ++depth;
-          hitA[m] = ha; hitB[m] = i2; ++m;   // ca[i1], cb[i2] = cb[i2], ca[i1]
-        } else {
-          stack[depth++] = ha;
+    for (int32_t j0 = 0; j0 < w; j0 += 8) {
+      int2 h[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) h[u] = (j0 + u < w) ? hit[j0 + u] : make_int2(-1, -1);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int32_t ha = h[u].x, hb = h[u].y;
+        if (ha >= 0) {
+          if (depth < 0) {                 // bmap non-empty: pop it, pair with this hit
+            const int32_t i2 = stack[-depth - 1];
+            ++depth;
+            hit[m++] = make_int2(ha, i2);  // ca[i1], cb[i2] = cb[i2], ca[i1]
+          } else {
+            stack[depth++] = ha;
+          }
         }
-      }
-      if (hb >= 0) {
-        if (depth > 0) {                 // amap non-empty
-          const int32_t i1 = stack[depth - 1];
-          --depth;
-          hitA[m] = i1; hitB[m] = hb; ++m;
-        } else {
-          stack[-depth] = hb;
-          --depth;
+        if (hb >= 0) {
+          if (depth > 0) {                 // amap non-empty
+            const int32_t i1 = stack[depth - 1];
+            --depth;
+            hit[m++] = make_int2(i1, hb);
+          } else {
+            stack[-depth] = hb;
+            --depth;
+          }
         }
       }
     }
@@ -188,7 +194,7 @@ __global__ void __launch_bounds__(256) k_ga_children(const lxy_ga_child* __restr
   }
   __syncthreads();
   for (int32_t q = tid; q < s_matches; q += blockDim.x) {
-    const int32_t i1 = hitA[q], i2 = hitB[q];
+    const int32_t i1 = hit[q].x, i2 = hit[q].y;
     out[i1] = b[i2];
     outb[i2] = a[i1];
   }

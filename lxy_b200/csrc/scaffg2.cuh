@@ -32,7 +32,10 @@ constexpr int kFirst2 = kBlk * kFirstRow2;
 constexpr int kQ2 = 22;                    // bucket indices 0..21; 21 = far (T = 0)
 constexpr int kLutG2Stride = 23;
 constexpr int kLutG2Words = kQ2 * kLutG2Stride;
-constexpr int kG2Threads = 512;
+#ifndef LXY_G2_THREADS
+#define LXY_G2_THREADS 512
+#endif
+constexpr int kG2Threads = LXY_G2_THREADS;
 constexpr int kG2Warps = kG2Threads / 32;
 constexpr int kG2Flush = 64;               // packets between flushes of the packed sums: 64 * 8 * 100 < 2^16
 constexpr int kG2Smem = kTab2 + kFirst2 + 4 * ((kLutG2Words + 3) & ~3) + 64;
