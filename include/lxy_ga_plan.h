@@ -20,6 +20,13 @@
  * score, walk from the best and accept each with probability `tour_p`; the last one is the
  * fallback.  Selection reads the population as it was at the start of the generation.
  *
+ * Known deviation from the reference's trajectory (not from its scorer): phase/genome.go:95-109 `Invert`
+ * flips bits WITHOUT calling Reset(), and Copy() carries `hasscore` (phase/genome.go:80), so from the
+ * second generation on an invert-mutated bitstring child keeps its parent's memoised score in the
+ * reference.  Here every child is scored (the scaffolding genome's Invert does Reset(),
+ * scaff/genome.go:161-177, so only the phasing workflow differs); the stale memo looks like a reference
+ * bug, and since the engine and its RNG cannot be replayed anyway nothing could be compared against it.
+ *
  * Plain C, included by host code, CUDA code and the oracle alike. */
 #ifndef LXY_GA_PLAN_H_
 #define LXY_GA_PLAN_H_

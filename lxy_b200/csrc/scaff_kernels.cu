@@ -483,7 +483,10 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
             // to consecutive warps and kWarps is a multiple of 8, so warps 0, 8 and 16 between them see every
             // line exactly once.  (A deeper register pipeline is slower: the loads share one scoreboard.)
             static_assert(kWarps % 8 == 0, "a packet's line index must be fixed per warp");
-            constexpr int kPfAhead = 6;
+#ifndef LXY_PF_AHEAD
+#define LXY_PF_AHEAD 6
+#endif
+            constexpr int kPfAhead = LXY_PF_AHEAD;
             const bool pf_warp = prm.prefetch && (warp & 7) == 0;
             int32_t since = 0;  // packets since the 16-bit pair sums were unpacked: 64 * 8 * 100 < 2^16
 #pragma unroll 1
@@ -973,7 +976,8 @@ static int scaff_enqueue_batch(lxy_ctx* c, const int32_t* perm_dev, int32_t P, d
 
   // work units: groups x splits, about two waves of one CTA per SM
   const int64_t npk = (S.L + kPacket - 1) / kPacket;
-  int splits = (2 * c->sm_count) / groups;  // two full waves of one CTA per SM, never a third
+  static const int waves = getenv("LXY_WAVES") ? atoi(getenv("LXY_WAVES")) : 2;   // experiments
+  int splits = (waves * c->sm_count) / groups;  // two full waves of one CTA per SM, never a third
   if (splits < 1) splits = 1;
   const int64_t min_pk = 64;  // do not split below 512 records per unit
   if ((int64_t)splits * min_pk > npk) splits = (int)(npk / min_pk > 0 ? npk / min_pk : 1);

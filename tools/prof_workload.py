@@ -26,7 +26,7 @@ if mode == "phase":
 if mode in ("r3", "r4"):   # r3: the bench default (config 3, population 1024, batch kernel); r4: config-4 contigs
     import torch
     import bench
-    n, L, P = (5000, 200_000_000, 1024) if mode == "r3" else (50000, 250_000_000, 1024)   # r4: one GPU's shard of config 4
+    n, L, P = (5000, 200_000_000, int(os.environ.get("R3_P", "1024"))) if mode == "r3" else (50000, 250_000_000, 1024)   # r4: one GPU's shard of config 4
     ta, tb, order = bench.gen_links(n, L, 3 if mode == "r3" else 4, torch.device("cuda", 0))
     perms = torch.from_numpy(bench.gen_population(n, P, 103, order.cpu().numpy())).cuda()
     out = torch.zeros(P, dtype=torch.float64, device="cuda")
