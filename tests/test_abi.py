@@ -107,3 +107,17 @@ def test_link_owners_split_whole_tiles_and_match_the_bench_mirror(native):
             assert len(set(own[t == tile].tolist())) == 1            # a tile is never split
     with pytest.raises(N.LxyError):
         N.comm_link_owners(10, [11], [0], 2)
+
+
+def test_go_shim_binds_only_what_the_header_declares():
+    """go/**/*.go (the cgo files a maintainer copies into the reference; no Go toolchain here to compile
+    them): every C.lxy_* / C.LXY_* they use must exist in include/*.h."""
+    hdr = open(os.path.join(ROOT, "include", "lxy_b200.h")).read() + open(os.path.join(ROOT, "include", "lxy_ga_plan.h")).read()
+    declared = set(re.findall(r"\b(lxy_[a-z0-9_]+|LXY_[A-Z0-9_]+)\b", hdr))
+    used = set()
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "go")):
+        for f in files:
+            if f.endswith(".go"):
+                used |= set(re.findall(r"\bC\.((?:lxy|LXY)_[A-Za-z0-9_]+)", open(os.path.join(dirpath, f)).read()))
+    assert used, "no cgo files found under go/"
+    assert used <= declared, sorted(used - declared)
