@@ -102,6 +102,24 @@ __global__ void __launch_bounds__(kPlanThreads) k_ga_plan(lxy_ga_params prm, uin
 // "inv_a[b[i]] outside the window" and its position is inv_a[b[i]]: both are known up front from the
 // inverse permutations.  The CTA computes the two hit lists in parallel and one thread replays the
 // stack discipline, which is what fixes the pairing.
+// Largest index i in [lo, hi] with sgn * v[i] >= key, or lo - 1; eight independent loads per step (the
+// one-at-a-time loop paid a shared-memory round trip per element).
+__device__ __forceinline__ int32_t pmx_scan_back(const int16_t* v, int32_t hi, int32_t lo, int32_t sgn, int32_t key) {
+  int32_t i = hi;
+  while (i - 7 >= lo) {
+    int32_t x[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) x[q] = sgn * (int32_t)v[i - q];
+#pragma unroll
+    for (int q = 0; q < 8; ++q)
+      if (x[q] >= key) return i - q;
+    i -= 8;
+  }
+  for (; i >= lo; --i)
+    if (sgn * (int32_t)v[i] >= key) return i;
+  return lo - 1;
+}
+
 template <class T, bool BITS>
 __global__ void __launch_bounds__(256) k_ga_children(const lxy_ga_child* __restrict__ plan,
                                                      const int32_t* __restrict__ count, int32_t n,
@@ -153,6 +171,68 @@ __global__ void __launch_bounds__(256) k_ga_children(const lxy_ga_child* __restr
     hit[j] = make_int2((qa < p1 || qa > p2) ? qa : -1, (qb < p1 || qb > p2) ? qb : -1);
   }
   __syncthreads();  // hit lists and both proto-children are complete
+  if (use_smem) {
+    // ---- the two-stack replay as a parallel bracket matching ----
+    // Events in the reference's order: slot 2j = "ca[i] is duplicated outside the window" (+1), slot
+    // 2j + 1 = the same for cb (-1), 0 where there is no hit; S = their prefix sum = the signed stack depth
+    // (> 0: amap holds S entries, < 0: bmap holds -S).  An event that moves S towards 0 is a pop, and what
+    // it pops is the most recent push that arrived at the level it leaves: the first event after the
+    // LAST EARLIER SLOT u WITH S[u] == S[t] (S moves by at most 1 per slot, so everything between u and
+    // t lies strictly on the far side of S[t]; u = -1, S = 0, when there is none).  Checked against the
+    // stack replay on random event strings (tests/test_oracle_ga.py) and, through the children, against
+    // the reference's O(n^2) code restated in oracle/ga_oracle.cpp.
+    // Each thread owns a contiguous chunk of slots: chunk sums -> block scan -> S, chunk minima / maxima;
+    // a pop searches backwards in its own chunk, then over the chunk extrema, then inside the chunk found.
+    int16_t* S = reinterpret_cast<int16_t*>(hit + n);   // [2 n]; |S| <= w <= n < 2^15 on this path
+    __shared__ int32_t s_part[256];
+    __shared__ int16_t s_cmin[256], s_cmax[256];
+    const int32_t m2 = 2 * w, C = (m2 + 255) / 256;
+    const int32_t t0 = min(tid * C, m2), t1 = min(t0 + C, m2);
+    auto delta = [&](int32_t t) -> int32_t {
+      const int2 h = hit[t >> 1];
+      return (t & 1) ? (h.y >= 0 ? -1 : 0) : (h.x >= 0 ? 1 : 0);
+    };
+    int32_t loc = 0;
+    for (int32_t t = t0; t < t1; ++t) loc += delta(t);
+    s_part[tid] = loc;
+    __syncthreads();
+    int32_t run = 0;
+    for (int32_t q = 0; q < tid; ++q) run += s_part[q];   // 256 partial sums: not worth a shuffle scan
+    int32_t mn = 32767, mx = -32768;
+    for (int32_t t = t0; t < t1; ++t) {
+      run += delta(t);
+      S[t] = (int16_t)run;
+      mn = min(mn, run);
+      mx = max(mx, run);
+    }
+    s_cmin[tid] = (int16_t)mn;
+    s_cmax[tid] = (int16_t)mx;
+    __syncthreads();
+    for (int32_t t = t0; t < t1; ++t) {
+      const int32_t d = delta(t);
+      if (d == 0) continue;
+      const int32_t cur = S[t], prev = cur - d;
+      if (!((d < 0 && prev > 0) || (d > 0 && prev < 0))) continue;   // a push
+      // d < 0: leaving a positive level, everything since u is > cur (look for S[u] <= cur);
+      // d > 0: leaving a negative level, everything since u is < cur (look for S[u] >= cur).
+      // With sgn = d both read "sgn * S[u] >= sgn * cur".
+      const int32_t sgn = d, key = sgn * cur;
+      int32_t u = pmx_scan_back(S, t - 1, t0, sgn, key);
+      if (u < t0) {
+        const int16_t* ext = d < 0 ? s_cmin : s_cmax;
+        const int32_t c = pmx_scan_back(ext, tid - 1, 0, sgn, key);
+        u = c < 0 ? -1 : pmx_scan_back(S, min((c + 1) * C, m2) - 1, c * C, sgn, key);
+      }
+      int32_t pslot = u + 1;
+      while (delta(pslot) == 0) ++pslot;                  // the push: first event after u
+      // ca[i1], cb[i2] = cb[i2], ca[i1]  with i1 the ca-side hit, i2 the cb-side hit (genome.go:73-85)
+      const int32_t i1 = d > 0 ? hit[t >> 1].x : hit[pslot >> 1].x;
+      const int32_t i2 = d > 0 ? hit[pslot >> 1].y : hit[t >> 1].y;
+      out[i1] = b[i2];
+      outb[i2] = a[i1];
+    }
+    return;
+  }
   if (tid == 0) {
     // The replay only PAIRS the hits (which a-side hit meets which b-side hit is what the reference's
     // two stacks decide); the swaps themselves are independent of one another and are applied by the
@@ -348,7 +428,7 @@ int ga_begin(lxy_ga* g) {
     LXY_TRY(scaff_positions(c, g->pop[g->cur].as<int32_t>(), P, g->n, g->inv.as<int32_t>()));
     // PMX hit lists + stack in shared memory when they fit (3 n ints)
     const size_t pmx_smem = 12 * (size_t)g->n;
-    const bool in_smem = pmx_smem + 1024 <= (size_t)c->max_smem_optin;
+    const bool in_smem = pmx_smem + 4096 <= (size_t)c->max_smem_optin && g->n < 32768;
     if (in_smem && pmx_smem > 48 * 1024) {
       static size_t configured[64] = {};
       std::lock_guard<std::mutex> cfg_lock(config_mutex());

@@ -131,3 +131,54 @@ def test_eval_phasing_dev_oracle_against_a_second_restatement():
         got = G.eval_phasing_dev([phasing[nm] for nm in common], [key[nm] for nm in common],
                                  [int(nm.split("_")[1]) for nm in common])
         assert got.tolist() == [m / c, m3 / c3, m1 / c1]
+
+
+def test_parallel_bracket_matching_rule_equals_the_two_stack_replay():
+    """k_ga_children pairs PMX's hits without walking them one by one: with S the prefix sum of the
+    events (+1: a ca-side hit, -1: a cb-side hit, 0: none), an event that moves S towards 0 pops the
+    first event after the last earlier slot u with S[u] == S[t].  This is the rule, stated in Python,
+    against the reference's stack discipline (scaff/genome.go:60-88) on random event strings."""
+    import random
+
+    def replay(ev):
+        depth, st, pairs = 0, [], set()
+        for t, d in enumerate(ev):
+            if d == 1:
+                if depth < 0:
+                    pairs.add((t, st.pop()))
+                else:
+                    st.append(t)
+                depth += 1
+            elif d == -1:
+                if depth > 0:
+                    pairs.add((st.pop(), t))
+                else:
+                    st.append(t)
+                depth -= 1
+        return pairs
+
+    def matched(ev):
+        S, s = [], 0
+        for d in ev:
+            s += d
+            S.append(s)
+        pairs = set()
+        for t, d in enumerate(ev):
+            if d == 0:
+                continue
+            cur, prev = S[t], S[t] - d
+            if abs(cur) >= abs(prev):
+                continue
+            u = t - 1
+            while u >= 0 and S[u] != cur:
+                u -= 1
+            p = u + 1
+            while ev[p] == 0:
+                p += 1
+            pairs.add((p, t) if ev[p] == 1 else (t, p))
+        return pairs
+
+    rng = random.Random(7)
+    for _ in range(2000):
+        ev = [rng.choice([0, 0, 1, -1]) for _ in range(rng.randint(1, 80))]
+        assert replay(ev) == matched(ev)
