@@ -130,6 +130,20 @@ def lib():
         raise RuntimeError(
             f"{LIB_PATH} is missing: build it with `make -C {CSRC}` (or __graft_entry__.build()). "
             "lxy_b200 has no CPU fallback.")
+    if "LXY_NCCL_LIB" not in os.environ:
+        # comm.cu binds NCCL with dlopen on first use.  In a Python process that may import torch LATER,
+        # it must be torch's bundled libnccl.so.2: the dynamic loader resolves torch's dependency by
+        # soname to whatever copy is already mapped, and an older system NCCL lacks symbols torch needs.
+        try:
+            import importlib.util
+            spec = importlib.util.find_spec("nvidia.nccl")
+            for d in (spec.submodule_search_locations or []) if spec else []:
+                cand = os.path.join(d, "lib", "libnccl.so.2")
+                if os.path.exists(cand):
+                    os.environ["LXY_NCCL_LIB"] = cand
+                    break
+        except Exception:
+            pass
     L = C.CDLL(LIB_PATH)
     vp, i32, i64, u32, f64 = C.c_void_p, C.c_int32, C.c_int64, C.c_uint32, C.c_double
     sig = {

@@ -201,6 +201,7 @@ void lxy_ctx_destroy(lxy_ctx* c) {
   if (c->h_pin) cudaFreeHost(c->h_pin);
   for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
   lxy::drop_score_graphs(c);
+  for (auto& e : c->ev_slice) if (e) cudaEventDestroy(e);
   if (c->ev_join) cudaEventDestroy(c->ev_join);
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   if (c->stream2) cudaStreamDestroy(c->stream2);
@@ -529,8 +530,38 @@ int lxy_phase_score_batch_bits(lxy_ctx* c, const uint32_t* words, int32_t P, int
   LXY_TRY(c->d_out.reserve(8 * (size_t)P));
   LXY_TRY(c->d_x100.reserve(8 * (size_t)P));
   LXY_CUDA(cudaEventRecord(c->ev[4], c->stream));
-  LXY_TRY(stage_h2d(c, c->d_genes.p, words, gbytes, 0));
-  LXY_TRY(phase_score_any(c, nullptr, c->d_genes.as<uint32_t>(), P, c->d_x100.as<int64_t>(), c->d_out.as<double>()));
+  // Page-locked caller memory and a population of several candidate blocks: the rows go up in slices on
+  // the side stream while the slices already there are scored (candidates are independent; a slice is a
+  // multiple of the 128 candidates one warp scores), so the copy engine and the SMs overlap: 38 MB of
+  // genes at 300,000 blocks x 1,024 genomes cost 1.5 ms over PCIe against 1.0 ms of scoring.
+  cudaPointerAttributes attr;
+  const bool pinned = cudaPointerGetAttributes(&attr, words) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+  if (!pinned) (void)cudaGetLastError();
+  if (pinned && P >= 512) {
+    const int32_t nsl = P / 256 < 8 ? P / 256 : 8;
+    const int32_t rows = ((P + nsl - 1) / nsl + 127) / 128 * 128;
+    for (auto& e : c->ev_slice)
+      if (!e) LXY_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    LXY_CUDA(cudaEventRecord(c->ev_fork, c->stream));          // the device buffer may still be read by the previous call
+    LXY_CUDA(cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));
+    int32_t k = 0;
+    for (int32_t p0 = 0; p0 < P; p0 += rows, ++k) {
+      const int32_t cnt = P - p0 < rows ? P - p0 : rows;
+      LXY_CUDA(cudaMemcpyAsync(c->d_genes.as<uint32_t>() + (size_t)p0 * W, words + (size_t)p0 * W, 4 * W * (size_t)cnt,
+                               cudaMemcpyHostToDevice, c->stream2));
+      LXY_CUDA(cudaEventRecord(c->ev_slice[k], c->stream2));
+    }
+    k = 0;
+    for (int32_t p0 = 0; p0 < P; p0 += rows, ++k) {
+      const int32_t cnt = P - p0 < rows ? P - p0 : rows;
+      LXY_CUDA(cudaStreamWaitEvent(c->stream, c->ev_slice[k], 0));
+      LXY_TRY(phase_score_any(c, nullptr, c->d_genes.as<uint32_t>() + (size_t)p0 * W, cnt, c->d_x100.as<int64_t>() + p0,
+                              c->d_out.as<double>() + p0));
+    }
+  } else {
+    LXY_TRY(stage_h2d(c, c->d_genes.p, words, gbytes, 0));
+    LXY_TRY(phase_score_any(c, nullptr, c->d_genes.as<uint32_t>(), P, c->d_x100.as<int64_t>(), c->d_out.as<double>()));
+  }
   char* hout = (char*)c->h_pin + gbytes;
   LXY_CUDA(cudaMemcpyAsync(hout, c->d_out.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, c->stream));
   LXY_CUDA(cudaMemcpyAsync(hout + 8 * (size_t)P, c->d_x100.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, c->stream));

@@ -40,7 +40,13 @@ Nccl* nccl() {
   static Nccl lib;
   static std::once_flag once;
   std::call_once(once, [] {
-    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    // One NCCL per process: the copy that is already mapped (a torch process), else the one the host
+    // names in LXY_NCCL_LIB (the Python binding points it at torch's bundled copy, so that a later
+    // `import torch` finds its own libnccl.so.2 under that soname and not an older system one), else
+    // the system library.
+    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL | RTLD_NOLOAD);
+    if (!h && getenv("LXY_NCCL_LIB")) h = dlopen(getenv("LXY_NCCL_LIB"), RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
     if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
     if (!h) return;
     Nccl l;

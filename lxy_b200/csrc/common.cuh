@@ -117,6 +117,7 @@ struct lxy_ctx {
   cudaEvent_t ev_join = nullptr;
   cudaEvent_t ev_fork = nullptr;
   cudaEvent_t ev[8]{};
+  cudaEvent_t ev_slice[8]{};        // upload slices of a packed phasing population (api.cu)
   bool capturing = false;           // the scoring pass is being captured into a graph
   lxy::ScoreGraph graphs[4];
   uint64_t graph_clock = 0;

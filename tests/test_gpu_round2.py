@@ -211,3 +211,27 @@ def test_total_length_boundary_of_the_g_profile():
         with pytest.raises(N.LxyError) as e:                    # the record-count limit is checked before any pointer is read
             N._check(N.lib().lxy_ctx_set_links(c._h, n, (1 << 32), None, None, None))
         assert e.value.status == -5
+
+
+@pytest.mark.parametrize("P", [512, 1000, 1300])
+def test_packed_phasing_from_page_locked_memory_uploads_in_slices(P):
+    """Page-locked caller memory and P >= 512: the rows go up in slices on the side stream while the
+    slices already there are scored (api.cu).  Same integers as the byte entry point and the oracle,
+    call after call (the device buffer is reused)."""
+    torch = pytest.importorskip("torch")
+    n = 20_011
+    pa, pb, pw, truth = S.phase_links(n, 9, far_pairs=50)
+    genes = S.phase_population(n, P, 109, truth)
+    _, exact = O.phase_score_links_batch(n, pa, pb, pw, genes, nthreads=8)
+    words = torch.from_numpy(N.pack_bits(genes).view(np.int32)).pin_memory().numpy().view(np.uint32)
+    with N.Context(0) as c:
+        c.set_phase_links(n, pa, pb, pw)
+        for _ in range(3):
+            assert c.phase_score_batch_bits(words)[0].tolist() == exact.tolist()
+        flipped = words.copy()                                  # pageable copy of a different population
+        flipped[:, 0] ^= np.uint32(1)
+        g2 = genes.copy()
+        g2[:, 0] ^= 1
+        _, exact2 = O.phase_score_links_batch(n, pa, pb, pw, g2, nthreads=8)
+        assert c.phase_score_batch_bits(flipped)[0].tolist() == exact2.tolist()
+        assert c.phase_score_batch_bits(words)[0].tolist() == exact.tolist()
