@@ -179,8 +179,8 @@ __global__ void __launch_bounds__(256) k_ga_children(const lxy_ga_child* __restr
     // it pops is the most recent push that arrived at the level it leaves: the first event after the
     // LAST EARLIER SLOT u WITH S[u] == S[t] (S moves by at most 1 per slot, so everything between u and
     // t lies strictly on the far side of S[t]; u = -1, S = 0, when there is none).  Checked against the
-    // stack replay on random event strings (tests/test_oracle_ga.py) and, through the children, against
-    // the reference's O(n^2) code restated in oracle/ga_oracle.cpp.
+    // stack replay on random event strings and, through the children, against the reference's O(n^2)
+    // code as the CPU checker restates it (tests/).
     // Each thread owns a contiguous chunk of slots: chunk sums -> block scan -> S, chunk minima / maxima;
     // a pop searches backwards in its own chunk, then over the chunk extrema, then inside the chunk found.
     int16_t* S = reinterpret_cast<int16_t*>(hit + n);   // [2 n]; |S| <= w <= n < 2^15 on this path
