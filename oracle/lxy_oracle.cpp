@@ -17,6 +17,9 @@
 //     pinned only by the reference source text.  Mitigation: an independent second restatement in
 //     Python (tests/golden/gen_golden.py) generated tests/golden/fixtures.json from the
 //     reference's own fixture files; this file must reproduce those values bit for bit.
+//   * TabulateVariantBlockLinks (links.go:372-420): PARITY UNPINNED by reference tests
+//     (TestBlockLinksFromSam is commented out, alignment_test.go:282-299); second restatement:
+//     tests/golden/gen_varblock_golden.py -> tests/golden/varblock_fixtures.json.
 //   * The generalised G-profile (contig lengths, orientations, in-contig link offsets) has NO
 //     reference counterpart; this file DEFINES it (see lxyo_scaffg_*), constrained to collapse to
 //     the reference semantics for len==1, x==0, unit==1.
