@@ -27,7 +27,7 @@ struct lxy_ga {
   int32_t n_children = 0;
   int32_t shard_mode = -1;  // LXY_SHARD_* over the context's communicator, -1: score locally
   lxy::DevBuf pop[2], score[2], x100[2];
-  lxy::DevBuf child, child_score, child_x100, plan, count, order, inv, scratch;
+  lxy::DevBuf child, child_score, child_x100, plan, count, order, inv, scratch, breed;
   cudaEvent_t ev[4]{};
   lxy_ga_stats stats{};
 };
@@ -43,11 +43,12 @@ constexpr int kPlanThreads = 1024;
 // mutation child).
 __global__ void __launch_bounds__(kPlanThreads) k_ga_plan(lxy_ga_params prm, uint64_t gen, int32_t len,
                                                          lxy_ga_child* __restrict__ plan,
-                                                         int32_t* __restrict__ count) {
+                                                         int32_t* __restrict__ count,
+                                                         int32_t* __restrict__ breed) {
   __shared__ int32_t s_warp[kPlanThreads / 32];
-  __shared__ int32_t s_base;
+  __shared__ int32_t s_base, s_nbreed;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) s_base = 0;
+  if (tid == 0) { s_base = 0; s_nbreed = 0; }
   __syncthreads();
   for (int32_t p0 = 0; p0 < prm.popsize; p0 += kPlanThreads) {
     const int32_t p = p0 + tid;
@@ -78,13 +79,16 @@ __global__ void __launch_bounds__(kPlanThreads) k_ga_plan(lxy_ga_params prm, uin
     }
     __syncthreads();
     int32_t at = s_base + (warp ? s_warp[warp - 1] : 0) + incl - cnt;
-    if (k[0].kind != LXY_CHILD_NONE) { plan[at++] = k[0]; plan[at++] = k[1]; }
+    if (k[0].kind != LXY_CHILD_NONE) {
+      breed[atomicAdd(&s_nbreed, 1)] = at;   // the crossover children, any order: k_ga_children launches over them
+      plan[at++] = k[0]; plan[at++] = k[1];
+    }
     if (k[2].kind != LXY_CHILD_NONE) plan[at++] = k[2];
     __syncthreads();
     if (tid == 0) s_base += s_warp[kPlanThreads / 32 - 1];
     __syncthreads();
   }
-  if (tid == 0) *count = s_base;
+  if (tid == 0) { count[0] = s_base; count[1] = s_nbreed; }
 }
 
 // ---- k_ga_children ----------------------------------------------------------------------------------
@@ -121,17 +125,26 @@ __device__ __forceinline__ int32_t pmx_scan_back(const int16_t* v, int32_t hi, i
 }
 
 template <class T, bool BITS>
-__global__ void __launch_bounds__(256) k_ga_children(const lxy_ga_child* __restrict__ plan,
+__global__ void __launch_bounds__(1024) k_ga_children(const lxy_ga_child* __restrict__ plan,
                                                      const int32_t* __restrict__ count, int32_t n,
                                                      const T* __restrict__ pop, const int32_t* __restrict__ inv,
                                                      T* __restrict__ child, int32_t* __restrict__ scratch,
-                                                     int use_smem) {
-  const int32_t c = blockIdx.x;
+                                                     int use_smem, int which, const int32_t* __restrict__ breed) {
+  int32_t c = blockIdx.x;
+  if (which == 2) {   // launched over the crossover list (count[1] entries)
+    if (c >= count[1]) return;
+    c = breed[c];
+  }
   if (c >= *count) return;
   const lxy_ga_child k = plan[c];
   const int tid = threadIdx.x;
   const int32_t p1 = k.p1, p2 = k.p2;
   if (k.kind == LXY_CHILD_BREED_B) return;  // written by the CTA of its sibling
+  // which: 0 = every child; 1 = mutation children only; 2 = crossover children only.  The permutation
+  // genome launches the two kinds separately: the ~P/5 crossover CTAs need 12 n bytes of shared memory
+  // (3 CTAs per SM at n = 5,000) and tens of microseconds each, the ~3P/5 mutation CTAs are plain
+  // copies - in one launch the copies queued behind the crossovers, wave after wave.
+  if ((which == 1 && k.kind == LXY_CHILD_BREED_A) || (which == 2 && k.kind != LXY_CHILD_BREED_A)) return;
   const T* a = pop + (size_t)k.pa * n;
   T* out = child + (size_t)c * n;
   if (k.kind != LXY_CHILD_BREED_A) {
@@ -184,9 +197,10 @@ __global__ void __launch_bounds__(256) k_ga_children(const lxy_ga_child* __restr
     // Each thread owns a contiguous chunk of slots: chunk sums -> block scan -> S, chunk minima / maxima;
     // a pop searches backwards in its own chunk, then over the chunk extrema, then inside the chunk found.
     int16_t* S = reinterpret_cast<int16_t*>(hit + n);   // [2 n]; |S| <= w <= n < 2^15 on this path
-    __shared__ int32_t s_part[256];
-    __shared__ int16_t s_cmin[256], s_cmax[256];
-    const int32_t m2 = 2 * w, C = (m2 + 255) / 256;
+    __shared__ int32_t s_wsum[32];
+    __shared__ int16_t s_cmin[1024], s_cmax[1024], s_wmin[32], s_wmax[32];
+    const int32_t NT = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarps = NT >> 5;
+    const int32_t m2 = 2 * w, C = (m2 + NT - 1) / NT;
     const int32_t t0 = min(tid * C, m2), t1 = min(t0 + C, m2);
     auto delta = [&](int32_t t) -> int32_t {
       const int2 h = hit[t >> 1];
@@ -194,10 +208,16 @@ __global__ void __launch_bounds__(256) k_ga_children(const lxy_ga_child* __restr
     };
     int32_t loc = 0;
     for (int32_t t = t0; t < t1; ++t) loc += delta(t);
-    s_part[tid] = loc;
+    int32_t incl = loc;   // block exclusive scan of the chunk sums: shuffle scan per warp, then over the warps
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_wsum[warp] = incl;
     __syncthreads();
-    int32_t run = 0;
-    for (int32_t q = 0; q < tid; ++q) run += s_part[q];   // 256 partial sums: not worth a shuffle scan
+    int32_t run = incl - loc;
+    for (int32_t q = 0; q < warp; ++q) run += s_wsum[q];
     int32_t mn = 32767, mx = -32768;
     for (int32_t t = t0; t < t1; ++t) {
       run += delta(t);
@@ -207,7 +227,10 @@ __global__ void __launch_bounds__(256) k_ga_children(const lxy_ga_child* __restr
     }
     s_cmin[tid] = (int16_t)mn;
     s_cmax[tid] = (int16_t)mx;
+    const int32_t wmn = __reduce_min_sync(0xffffffffu, mn), wmx = __reduce_max_sync(0xffffffffu, mx);
+    if (lane == 0) { s_wmin[warp] = (int16_t)wmn; s_wmax[warp] = (int16_t)wmx; }
     __syncthreads();
+    (void)nwarps;
     for (int32_t t = t0; t < t1; ++t) {
       const int32_t d = delta(t);
       if (d == 0) continue;
@@ -215,12 +238,17 @@ __global__ void __launch_bounds__(256) k_ga_children(const lxy_ga_child* __restr
       if (!((d < 0 && prev > 0) || (d > 0 && prev < 0))) continue;   // a push
       // d < 0: leaving a positive level, everything since u is > cur (look for S[u] <= cur);
       // d > 0: leaving a negative level, everything since u is < cur (look for S[u] >= cur).
-      // With sgn = d both read "sgn * S[u] >= sgn * cur".
+      // With sgn = d both read "sgn * S[u] >= sgn * cur".  Search order: own chunk, the earlier chunks of
+      // the own warp (chunk extrema), the earlier warps (warp extrema), then down again.
       const int32_t sgn = d, key = sgn * cur;
       int32_t u = pmx_scan_back(S, t - 1, t0, sgn, key);
       if (u < t0) {
         const int16_t* ext = d < 0 ? s_cmin : s_cmax;
-        const int32_t c = pmx_scan_back(ext, tid - 1, 0, sgn, key);
+        int32_t c = pmx_scan_back(ext, tid - 1, warp * 32, sgn, key);
+        if (c < warp * 32) {
+          const int32_t wq = pmx_scan_back(d < 0 ? s_wmin : s_wmax, warp - 1, 0, sgn, key);
+          c = wq < 0 ? -1 : pmx_scan_back(ext, wq * 32 + 31, wq * 32, sgn, key);
+        }
         u = c < 0 ? -1 : pmx_scan_back(S, min((c + 1) * C, m2) - 1, c * C, sgn, key);
       }
       int32_t pslot = u + 1;
@@ -420,10 +448,10 @@ int ga_begin(lxy_ga* g) {
   const int32_t P = g->prm.popsize;
   cudaStream_t st = c->stream;
   LXY_CUDA(cudaEventRecord(g->ev[0], st));
-  k_ga_plan<<<1, kPlanThreads, 0, st>>>(g->prm, g->gen, g->n, g->plan.as<lxy_ga_child>(), g->count.as<int32_t>());
+  k_ga_plan<<<1, kPlanThreads, 0, st>>>(g->prm, g->gen, g->n, g->plan.as<lxy_ga_child>(), g->count.as<int32_t>(), g->breed.as<int32_t>());
   if (g->prm.kind == LXY_GA_PHASE) {
     k_ga_children<uint8_t, true><<<3 * P, 256, 0, st>>>(g->plan.as<lxy_ga_child>(), g->count.as<int32_t>(), g->n,
-        g->pop[g->cur].as<uint8_t>(), nullptr, g->child.as<uint8_t>(), nullptr, 0);
+        g->pop[g->cur].as<uint8_t>(), nullptr, g->child.as<uint8_t>(), nullptr, 0, 0, nullptr);
   } else {
     LXY_TRY(scaff_positions(c, g->pop[g->cur].as<int32_t>(), P, g->n, g->inv.as<int32_t>()));
     // PMX hit lists + stack in shared memory when they fit (3 n ints)
@@ -437,8 +465,11 @@ int ga_begin(lxy_ga* g) {
         configured[c->cfg.device & 63] = pmx_smem;
       }
     }
-    k_ga_children<int32_t, false><<<3 * P, 256, in_smem ? pmx_smem : 0, st>>>(g->plan.as<lxy_ga_child>(), g->count.as<int32_t>(), g->n,
-        g->pop[g->cur].as<int32_t>(), g->inv.as<int32_t>(), g->child.as<int32_t>(), g->scratch.as<int32_t>(), in_smem ? 1 : 0);
+    k_ga_children<int32_t, false><<<P, 1024, in_smem ? pmx_smem : 0, st>>>(g->plan.as<lxy_ga_child>(), g->count.as<int32_t>(), g->n,
+        g->pop[g->cur].as<int32_t>(), g->inv.as<int32_t>(), g->child.as<int32_t>(), g->scratch.as<int32_t>(), in_smem ? 1 : 0, 2,
+        g->breed.as<int32_t>());
+    k_ga_children<int32_t, false><<<3 * P, 256, 0, st>>>(g->plan.as<lxy_ga_child>(), g->count.as<int32_t>(), g->n,
+        g->pop[g->cur].as<int32_t>(), g->inv.as<int32_t>(), g->child.as<int32_t>(), g->scratch.as<int32_t>(), 0, 1, nullptr);
   }
   LXY_CUDA(cudaGetLastError());
   LXY_CUDA(cudaEventRecord(g->ev[1], st));
@@ -523,6 +554,7 @@ int lxy_ga_create(lxy_ctx* ctx, const lxy_ga_params* prm, lxy_ga** out) {
   if (rc == LXY_OK) rc = g->plan.reserve(sizeof(lxy_ga_child) * 3 * P);
   if (rc == LXY_OK) rc = g->count.reserve(64);
   if (rc == LXY_OK) rc = g->order.reserve(4 * P);
+  if (rc == LXY_OK) rc = g->breed.reserve(4 * P + 16);
   if (rc == LXY_OK && prm->kind == LXY_GA_SCAFF) {
     rc = g->inv.reserve(4 * P * (size_t)n);
     if (rc == LXY_OK) rc = g->scratch.reserve(4 * P * 3 * (size_t)n);  // hit lists + stack per breeding slot
@@ -541,7 +573,7 @@ void lxy_ga_destroy(lxy_ga* g) {
     cudaSetDevice(g->ctx->cfg.device);
     cudaStreamSynchronize(g->ctx->stream);
     DevBuf* bufs[] = {&g->pop[0], &g->pop[1], &g->score[0], &g->score[1], &g->x100[0], &g->x100[1], &g->child,
-                      &g->child_score, &g->child_x100, &g->plan, &g->count, &g->order, &g->inv, &g->scratch};
+                      &g->child_score, &g->child_x100, &g->plan, &g->count, &g->order, &g->inv, &g->scratch, &g->breed};
     for (DevBuf* b : bufs) b->release();
     for (auto& e : g->ev) if (e) cudaEventDestroy(e);
   }

@@ -1,9 +1,13 @@
-"""Multi-GPU composition of the fitness path (one process per GPU, torch.distributed for the
-plumbing: NCCL on the GPUs, gloo in the CPU tests).  No fitness is computed here — these helpers
-only split the work and combine what the per-rank lxy_ctx produced.
+"""CPU-testable mirror of the multi-GPU split / combine arithmetic.
+
+On GPUs the composition lives inside liblxyb200 (lxy_b200/csrc/comm.cu: lxy_comm_*,
+lxy_scaff_score_sharded*, lxy_ga_set_sharding - NCCL on the context's own stream).  This module restates
+the same arithmetic over torch.distributed so that the world-size-2 tests can run it on the gloo backend
+without a GPU (tests/test_sharding_gloo.py; tests/test_abi.py checks shard_range against lxy_comm_slice).
+No fitness is computed here - these helpers only split the work and combine what a per-rank scorer produced.
 
   population-sharded (BASELINE.json configs[2]): links replicated, candidates split across ranks,
-      all-gather of the [P/G] score vector; nothing else moves.
+      all-gather of the score slices; nothing else moves.
   link-sharded (configs[3]): records split across ranks, every rank scores the whole population
       against its shard, the partial sums are combined: exact int64 partials by all-reduce(SUM)
       (order-independent, bit-identical to the unsharded sum), fp64 partials by all-gather and a
