@@ -168,6 +168,22 @@ int lxy_phase_score_batch_bits(lxy_ctx* ctx, const uint32_t* words, int32_t P, i
                                double* out_f64);
 int lxy_phase_score_batch_bits_dev(lxy_ctx* ctx, const uint32_t* words_dev, int32_t P,
                                    int64_t* out_i64_dev, double* out_f64_dev);
+/* Allocation-free variant of lxy_phase_score_batch_bits_dev.  It has NO counterpart in the reference: it
+ * was added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, same scores, same
+ * asynchronous behaviour on the context's stream; the call itself performs no cudaMalloc / cudaFree and
+ * calls no allocating library routine.  Its scratch (the per-candidate accumulator and the bit-sliced
+ * gene words) lives in one static device array of LXY_PHASE_NOALLOC_SCRATCH_BYTES that every GPU which
+ * loads the library holds until the process exits, so the size is bounded:
+ *     n_ids * Ppad / 8 + 8 * Ppad <= LXY_PHASE_NOALLOC_SCRATCH_BYTES,
+ * Ppad = P rounded up to 32 (P <= 32), 64 (P <= 64) or a multiple of 128; beyond that it returns
+ * LXY_ERR_RANGE and leaves the outputs untouched (use lxy_phase_score_batch_bits_dev).  The links must
+ * have been set before (lxy_ctx_set_phase_links allocates; this call does not).  All calls on one device
+ * share the array: it keeps the last call's contents (the call clears what must start at zero), and two
+ * calls that overlap on the GPU - two contexts of one device, i.e. two streams - race on it. */
+#define LXY_PHASE_NOALLOC_SCRATCH_BYTES (8u << 20)
+int lxy_phase_score_batch_bits_noalloc_dev(lxy_ctx* ctx, const uint32_t* words_dev, int32_t P,
+                                           int64_t* out_i64_dev, double* out_f64_dev);
 
 /* ---- multi-GPU: one context per device, NCCL on the context's own stream ----------------------------
  * north_star: "the population is sharded across GPUs for large populations, and the links are sharded

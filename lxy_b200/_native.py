@@ -40,6 +40,7 @@ SYMBOLS = [
     "lxy_comm_unique_id", "lxy_comm_init_rank", "lxy_comm_init_all", "lxy_comm_destroy", "lxy_comm_info",
     "lxy_comm_slice", "lxy_scaff_score_sharded", "lxy_scaff_score_sharded_dev", "lxy_ga_set_sharding",
     "lxy_links_tabulate_varblocks", "lxy_comm_link_owners",
+    "lxy_phase_score_batch_bits_noalloc_dev",
 ]
 
 ACC_AUTO, ACC_F64, ACC_INT = 0, 1, 2
@@ -211,6 +212,7 @@ def lib():
         "lxy_ctx_path": (i32, [vp, C.POINTER(i32), C.POINTER(i64)]),
         "lxy_phase_score_batch_bits": (i32, [vp, vp, i32, vp, vp]),
         "lxy_phase_score_batch_bits_dev": (i32, [vp, vp, i32, vp, vp]),
+        "lxy_phase_score_batch_bits_noalloc_dev": (i32, [vp, vp, i32, vp, vp]),
         "lxy_comm_unique_id": (i32, [vp]),
         "lxy_comm_init_rank": (i32, [vp, i32, i32, vp]),
         "lxy_comm_init_all": (i32, [C.POINTER(vp), i32]),
@@ -492,6 +494,12 @@ class Context:
         _check(lib().lxy_phase_score_batch_bits_dev(self._h, C.c_void_p(words_ptr), P,
                                                     C.c_void_p(out_i64_ptr) if out_i64_ptr else None,
                                                     C.c_void_p(out_f64_ptr) if out_f64_ptr else None))
+
+    def phase_score_batch_bits_noalloc_dev(self, words_ptr, P, out_i64_ptr, out_f64_ptr):
+        """The same scores with the scratch in the library's static device array: no allocation in the call."""
+        _check(lib().lxy_phase_score_batch_bits_noalloc_dev(self._h, C.c_void_p(words_ptr), P,
+                                                            C.c_void_p(out_i64_ptr) if out_i64_ptr else None,
+                                                            C.c_void_p(out_f64_ptr) if out_f64_ptr else None))
 
     def phase_score_batch_dev(self, genes_ptr, P, out_i64_ptr, out_f64_ptr):
         _check(lib().lxy_phase_score_batch_dev(self._h, C.c_void_p(genes_ptr), P,

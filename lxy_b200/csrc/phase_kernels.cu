@@ -337,3 +337,111 @@ int phase_score_any(lxy_ctx* c, const uint8_t* genes_dev, const uint32_t* packed
 }
 
 }  // namespace lxy
+
+// ---- allocation-free variant of the packed phasing scorer -------------------------------------------
+// lxy_phase_score_batch_bits_noalloc_dev: the launches of phase_score_any's packed branch with the two
+// scratch buffers (the per-candidate accumulator D and the bit-sliced gene words) carved out of ONE
+// file-scope device array instead of the context's growable buffers.  No reference counterpart; added
+// for callers that may not allocate (graph capture, serving loops).  Every GPU that loads the library
+// holds kPhaseStaticBytes until the process exits.  All calls on one device share the array: it keeps
+// the previous call's contents (D is cleared on the stream at the start of every call; the gene words
+// are rewritten in full), and two calls that overlap on the GPU (two contexts = two streams) race.
+constexpr size_t kPhaseStaticBytes = (size_t)8 << 20;
+static __device__ __align__(256) unsigned char g_phase_static[kPhaseStaticBytes];
+
+namespace lxy {
+namespace {
+constexpr int kStaticMaxDev = 64;
+std::mutex g_static_mu;
+unsigned char* g_static_addr[kStaticMaxDev];   // device address of g_phase_static, per device ordinal
+
+// In host code `g_phase_static` is only a handle: the device address comes from cudaGetSymbolAddress,
+// asked once per device with that device current (the caller has selected it).
+int phase_static_scratch(int device, unsigned char** out) {
+  if (device < 0 || device >= kStaticMaxDev) { set_error("phase score (noalloc): device %d beyond %d", device, kStaticMaxDev); return LXY_ERR_RANGE; }
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (!g_static_addr[device]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_phase_static);
+    if (e != cudaSuccess || !p) {
+      set_error("phase score (noalloc): cudaGetSymbolAddress failed on device %d: %s", device, cudaGetErrorString(e));
+      (void)cudaGetLastError();
+      return LXY_ERR_CUDA;
+    }
+    g_static_addr[device] = static_cast<unsigned char*>(p);
+  }
+  *out = g_static_addr[device];
+  return LXY_OK;
+}
+}  // namespace
+}  // namespace lxy
+
+extern "C" int lxy_phase_score_batch_bits_noalloc_dev(lxy_ctx* c, const uint32_t* words_dev, int32_t P,
+                                                      int64_t* out_i64_dev, double* out_f64_dev) {
+  using namespace lxy;
+  if (!c) { set_error("null context"); return LXY_ERR_ARG; }
+  std::lock_guard<std::mutex> lk(c->mu);
+  if (cudaSetDevice(c->cfg.device) != cudaSuccess) { set_error("cudaSetDevice(%d) failed", c->cfg.device); return LXY_ERR_CUDA; }
+  if (P < 0 || (P > 0 && (!words_dev || (!out_i64_dev && !out_f64_dev)))) { set_error("phase_score_batch_bits_noalloc_dev: bad argument"); return LXY_ERR_ARG; }
+  PhaseLinks& S = c->phase;
+  if (!S.ready) { set_error("phase_score_batch_bits_noalloc_dev: links not set"); return LXY_ERR_STATE; }
+  if (P == 0) return LXY_OK;
+  const int groups = (P + 31) / 32;
+  const int G = groups >= 4 ? 4 : groups >= 2 ? 2 : 1;
+  const int qgroups = (groups + G - 1) / G;
+  const int n = S.n;
+  const size_t d_bytes = (8 * (size_t)qgroups * G * 32 + 255) & ~(size_t)255;
+  const size_t bits_bytes = 4 * (size_t)qgroups * G * n;
+  if (d_bytes + bits_bytes > kPhaseStaticBytes) {
+    set_error("phase_score_batch_bits_noalloc_dev: %d candidates x %d variants need %zu bytes of scratch, the static "
+              "array holds %zu (n_ids * P / 8 + 8 * P, P rounded up to %d); use lxy_phase_score_batch_bits_dev",
+              P, n, d_bytes + bits_bytes, kPhaseStaticBytes, 32 * G);
+    return LXY_ERR_RANGE;
+  }
+  unsigned char* scratch = nullptr;
+  LXY_TRY(phase_static_scratch(c->cfg.device, &scratch));
+  unsigned long long* D = reinterpret_cast<unsigned long long*>(scratch);
+  uint32_t* bits = reinterpret_cast<uint32_t*>(scratch + d_bytes);
+  cudaStream_t st = c->stream;
+  LXY_CUDA(cudaEventRecord(c->ev[0], st));
+  LXY_CUDA(cudaMemsetAsync(D, 0, d_bytes, st));   // the accumulator must start at zero: the last call's sums are still here
+  const int W = (n + 31) / 32;
+  const dim3 pg((unsigned)((W + 31) / 32), (unsigned)qgroups);   // writes every word of bits[qgroups][n][G]
+  if (G == 4) k_phase_bits_packed<4><<<pg, 128, 0, st>>>(words_dev, P, n, W, groups, bits);
+  else if (G == 2) k_phase_bits_packed<2><<<pg, 64, 0, st>>>(words_dev, P, n, W, groups, bits);
+  else k_phase_bits_packed<1><<<pg, 32, 0, st>>>(words_dev, P, n, W, groups, bits);
+  LXY_CUDA(cudaGetLastError());
+  LXY_CUDA(cudaEventRecord(c->ev[1], st));
+  int launches = 1, grid = 0;
+  if (S.L > 0) {
+    int64_t chunk = S.L * qgroups / ((int64_t)c->sm_count * 64 * 2);   // as phase_score_any
+    chunk = std::min<int64_t>(kChunk, std::max<int64_t>(128, chunk)) / 4 * 4;
+    const int64_t chunks = (S.L + chunk - 1) / chunk;
+    const int64_t blocks = std::min<int64_t>((chunks * qgroups + 7) / 8, (int64_t)c->sm_count * 8);
+    grid = (int)blocks;
+    const uint2* rec = S.rec.as<uint2>();
+    const int32_t* w = S.w.as<int32_t>();
+#define LXY_PHASE_LAUNCH(GG)                                                                              \
+    do {                                                                                                   \
+      if (S.narrow) k_phase_score<GG, true><<<grid, 256, 0, st>>>(rec, w, S.L, bits, n, qgroups, chunks, (int32_t)chunk, D); \
+      else k_phase_score<GG, false><<<grid, 256, 0, st>>>(rec, w, S.L, bits, n, qgroups, chunks, (int32_t)chunk, D);        \
+    } while (0)
+    if (G == 4) LXY_PHASE_LAUNCH(4);
+    else if (G == 2) LXY_PHASE_LAUNCH(2);
+    else LXY_PHASE_LAUNCH(1);
+#undef LXY_PHASE_LAUNCH
+    LXY_CUDA(cudaGetLastError());
+    ++launches;
+  }
+  LXY_CUDA(cudaEventRecord(c->ev[2], st));
+  k_phase_finish<<<(P + 127) / 128, 128, 0, st>>>(P, (long long)S.sum_w, reinterpret_cast<const long long*>(D), out_i64_dev, out_f64_dev);
+  LXY_CUDA(cudaGetLastError());
+  ++launches;
+  LXY_CUDA(cudaEventRecord(c->ev[3], st));
+  c->timing.launches = launches;
+  c->timing.grid = grid;
+  c->timing.link_bytes = (int64_t)qgroups * S.L * 12;
+  c->timing.table_bytes = 0;
+  c->timing_pending = 1;
+  return LXY_OK;   // asynchronous on the context's stream, like lxy_phase_score_batch_bits_dev
+}
