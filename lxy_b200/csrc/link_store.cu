@@ -187,7 +187,7 @@ int build_scaff_links(lxy_ctx* c, const LinkInput& in) {
   S.unit = in.unit;
   S.total_len = 0;
   LXY_TRY(S.tile_start.reserve(sizeof(int64_t) * (size_t)(S.ntiles + 1)));
-  LXY_TRY(S.rec.reserve(sizeof(uint16_t) * (size_t)(L + 64)));
+  LXY_TRY(S.rec.reserve(sizeof(uint16_t) * (size_t)(L + 64 + 4096)));   // + the 8 KB bulk copy of a CTA's last chunk may run past L (scaff_stream1.cuh)
   LXY_TRY(c->d_flag.reserve(64));
   LXY_CUDA(cudaMemsetAsync(c->d_flag.p, 0, 64, st));
   if (G) {

@@ -733,7 +733,7 @@ static int scaff_score_stream1(lxy_ctx* c, const int32_t* perm_dev, int32_t P, i
   }
   if (first) LXY_CUDA(record_timing_event(c, 1));
   // persistent CTAs: as many as fit per SM (<= 2 x 512 threads), each an equal share of the packets
-  const int per_sm = (2 * (smem + 1024) <= (size_t)c->max_smem_optin) ? 2 : 1;
+  const int per_sm = (kS1MinBlocks == 2 && 2 * (smem + 1024) <= (size_t)c->max_smem_optin) ? 2 : 1;
   const int64_t npk = (S.L + kPacket - 1) / kPacket;
   int64_t grid = (int64_t)c->sm_count * per_sm;
   if (grid * 64 > npk) grid = npk / 64 > 0 ? npk / 64 : 1;  // at least 512 records per CTA
@@ -1046,3 +1046,9 @@ int scaff_link_distances(lxy_ctx* c, int32_t n, int64_t L, const uint32_t* a_dev
 }
 
 }  // namespace lxy
+
+#ifdef LXY_S1_TRACE
+extern "C" int lxy_debug_s1_trace(unsigned long long* out, int n) {
+  return (int)cudaMemcpyFromSymbol(out, lxy::g_s1_trace, sizeof(unsigned long long) * (size_t)n);
+}
+#endif

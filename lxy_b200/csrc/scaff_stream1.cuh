@@ -14,13 +14,24 @@
 // path (fitness = -(2S - H)/100), so both paths return identical integers.
 #pragma once
 
-constexpr int kS1Threads = 512;
+#ifndef LXY_S1_THREADS
+#define LXY_S1_THREADS 512
+#endif
+constexpr int kS1Threads = LXY_S1_THREADS;
+constexpr int kS1MinBlocks = kS1Threads > 512 ? 1 : 2;
 constexpr int kS1Warps = kS1Threads / 32;
 #ifndef LXY_S1_DEPTH
 #define LXY_S1_DEPTH 8
 #endif
 constexpr int kS1Depth = LXY_S1_DEPTH;     // 16-byte record copies in flight per lane
+constexpr int kS1DepthLog2 = kS1Depth == 8 ? 3 : kS1Depth == 4 ? 2 : kS1Depth == 16 ? 4 : -1;
+static_assert(kS1DepthLog2 > 0, "ring depth");
 constexpr int kS1Stage = kS1Threads * 16;  // bytes of one ring stage (one packet per thread)
+#ifndef LXY_S1_BLOCK
+#define LXY_S1_BLOCK 4
+#endif
+constexpr int kS1BlockMax = LXY_S1_BLOCK;     // chunks per unrolled block of the hot loop (divides kS1Depth)
+static_assert(kS1Depth % kS1BlockMax == 0, "ring blocks");
 // Unit weights: the two records of a 32-bit word share ONE decay look-up, lut2[v0 * 43 + v1] =
 // 100*T[v0] + 100*T[v1] (<= 200: a byte).  Saves one of the two look-ups, one add and moves the index
 // arithmetic to an IMAD (the FMA pipe idles in this kernel): 25 -> 21 shared-pipe wavefronts per packet.
@@ -28,6 +39,44 @@ constexpr int kS1LutSide = kMiss + 2;                  // 43 values of v
 constexpr int kS1Lut2Len = kS1LutSide * kS1LutSide;    // 1849
 constexpr int kS1Lut2Bytes = 1856;
 
+
+// The 43-entry decay table (padded to 64 bytes) followed by the pair sums lut2, built at compile time and
+// copied into shared memory as 120 16-byte pieces (one load per thread, requested with the other prologue
+// loads): no constant-bank reads with divergent indices, no barrier between "table in shared memory" and
+// "pair sums built from it".
+struct S1Luts { uint8_t v[64 + kS1Lut2Bytes]; };
+constexpr uint8_t s1_lut100_at(int v) {   // c_lut100[v], v = d + kBias + 1
+  const int d = v - (kBias + 1), ad = d < 0 ? -d : d;
+  return ad == 1 ? 100 : ad == 2 ? 50 : ad == 3 ? 33 : ad == 5 ? 20 : ad == 11 ? 10 : ad == 20 ? 5 : 0;
+}
+constexpr S1Luts s1_make_luts() {
+  S1Luts t{};
+  for (int i = 0; i < kS1LutSide; ++i) t.v[i] = s1_lut100_at(i);
+  for (int i = 0; i < kS1Lut2Len; ++i) t.v[64 + i] = (uint8_t)(s1_lut100_at(i / kS1LutSide) + s1_lut100_at(i % kS1LutSide));
+  return t;
+}
+__device__ const S1Luts g_s1_luts = s1_make_luts();
+constexpr int kS1LutPieces = (64 + kS1Lut2Bytes) / 16;   // 120
+static_assert((64 + kS1Lut2Bytes) % 16 == 0, "lut pieces");
+constexpr int kS1Pre = 8192 / kS1Threads;                // genes per thread requested ahead of the record ring
+
+// Ordered loads: volatile asm statements keep their order among themselves, so these are issued before
+// the cp.async copies that follow them in the source (a plain __ldg may be scheduled below them).
+__device__ __forceinline__ int32_t ldg_s32_ordered(const int32_t* p) {
+  int32_t v;
+  asm volatile("ld.global.nc.s32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ int64_t ldg_s64_ordered(const int64_t* p) {
+  int64_t v;
+  asm volatile("ld.global.nc.s64 %0, [%1];" : "=l"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint4 ldg_v4_ordered(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
 
 struct Stream1Params {
   const uint16_t* rec;
@@ -163,6 +212,9 @@ __device__ __forceinline__ void s1_packet_two_a(const uint4 v, uint32_t baseA, u
   }
 }
 
+struct S1Yes { static constexpr bool value = true; };
+struct S1No { static constexpr bool value = false; };
+
 struct S1Tile {  // a tile cursor: tile t = (I, J) holds records [.., end)
   int64_t t, end;
   int32_t I, J;
@@ -175,8 +227,20 @@ struct S1Tile {  // a tile cursor: tile t = (I, J) holds records [.., end)
   }
 };
 
+#ifdef LXY_S1_TRACE
+__device__ unsigned long long g_s1_trace[1024 * 8 + 8 * 32];
+__device__ __forceinline__ unsigned long long s1_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define S1_STAMP(k) do { if (threadIdx.x == 0 && blockIdx.x < 1024) g_s1_trace[blockIdx.x * 8 + (k)] = s1_now(); } while (0)
+#else
+#define S1_STAMP(k) do { } while (0)
+#endif
+
 template <int NC, int WM>
-__global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params prm) {
+__global__ void __launch_bounds__(kS1Threads + (kS1MinBlocks == 2 && NC <= 2 ? 64 : 0), kS1MinBlocks) k_scaff_stream1(Stream1Params prm) {
   typedef typename Acc<WM>::type acc_t;
   extern __shared__ __align__(128) uint8_t smem_raw1[];
   // contig blocks of the table must start on 512-byte boundaries of the shared window
@@ -190,14 +254,17 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
   int64_t* s_tile = (int64_t*)(s_red + kS1Warps * NC);
   const uint32_t sbase = smem_u32(sPos), cstride = (uint32_t)nstride * 2;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  S1_STAMP(0);
+#ifdef LXY_S1_TRACE
+  if (threadIdx.x == 0 && blockIdx.x < 1024) { unsigned sm; asm("mov.u32 %0, %smid;" : "=r"(sm)); g_s1_trace[blockIdx.x * 8 + 4] = sm; }
+#endif
 
   // ---- this CTA's share of the record stream: an even split of the 8-record packets, walked in
   // chunks of one packet per thread (8 KB; a warp owns 256 consecutive records of each chunk).
   // Every lane keeps kS1Depth 16-byte cp.async copies (LDGSTS, L1 bypass) in flight into its own
   // slots of a shared-memory ring: the depth is set by cp.async.wait_group, not by register
   // scoreboards (prefetching loads all land on one scoreboard, so waiting for the oldest also waits
-  // for the newest — measured: no gain from any depth).  The first kS1Depth chunks are requested
-  // right away; their latency hides behind the table build. ----
+  // for the newest — measured: no gain from any depth). ----
   const int64_t npk_all = (prm.L + kPacket - 1) / kPacket;
   const int64_t lo = (npk_all * blockIdx.x / gridDim.x) * kPacket;
   const int64_t hi = min((npk_all * (blockIdx.x + 1) / gridDim.x) * kPacket, prm.L);
@@ -206,6 +273,22 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
   const int32_t nchunks = (int32_t)((hi - lo + kChunk - 1) / kChunk);
   const uint32_t my_slot = smem_u32(s_tile + 2) + (uint32_t)tid * 16;  // ring: [kS1Depth][threads] x 16 B
   int64_t r0 = lo + (int64_t)tid * kPacket;                         // this thread's packet of chunk 0
+
+  // ---- prologue loads, requested BEFORE the ring is filled: behind 64 KB of record copies per CTA
+  // (19 MB over the GPU) they waited 2 us in the memory system's queues (per-CTA time stamps: prologue
+  // 3.2 us against 1 M records, 5.2 us against 200 M).  The first kS1Pre genes per thread of ordering 0,
+  // the first two tile boundaries per thread, one 16-byte piece of the decay tables. ----
+  const int64_t ntiles = (int64_t)prm.nblk * (prm.nblk + 1) / 2;
+  int32_t pv[kS1Pre];
+#pragma unroll
+  for (int k = 0; k < kS1Pre; ++k) {
+    const int i = tid + k * kS1Threads;
+    pv[k] = i < n ? ldg_s32_ordered(prm.perm + i) : 0;
+  }
+  int64_t ts0 = 0, ts1 = 0;
+  if (tid < ntiles) { ts0 = ldg_s64_ordered(prm.tile_start + tid); ts1 = ldg_s64_ordered(prm.tile_start + tid + 1); }
+  uint4 lutv = make_uint4(0, 0, 0, 0);
+  if (tid < kS1LutPieces) lutv = ldg_v4_ordered(g_s1_luts.v + tid * 16);
 #pragma unroll
   for (int q = 0; q < kS1Depth; ++q) {
     if (r0 + q * kChunk < hi) cp_async16(my_slot + q * kS1Stage, prm.rec + r0 + q * kChunk);
@@ -213,20 +296,14 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
   }
   // the tile holding record `lo` (the only t with tile_start[t] <= lo < tile_start[t+1])
   if (lo < hi) {
-    const int64_t ntiles = (int64_t)prm.nblk * (prm.nblk + 1) / 2;
-    for (int64_t t = tid; t < ntiles; t += kS1Threads)
+    if (tid < ntiles && ts0 <= lo && lo < ts1) { s_tile[0] = tid; s_tile[1] = ts1; }
+    for (int64_t t = tid + kS1Threads; t < ntiles; t += kS1Threads)
       if (prm.tile_start[t] <= lo) {
         const int64_t e = prm.tile_start[t + 1];
         if (lo < e) { s_tile[0] = t; s_tile[1] = e; }
       }
   }
-  // ---- placement tables: pos[perm[i]] = i (pad candidates: identity, discarded) ----
-  if (tid < kLutLen) s_lut[tid] = c_lut100[tid];
-  if (WM == W_UNIT) {  // from the shared copy: divergent indices serialise on the constant cache (4 us)
-    __syncthreads();
-    for (int i = tid; i < kS1Lut2Len; i += kS1Threads)
-      s_lut2[i] = (uint8_t)(s_lut[i / kS1LutSide] + s_lut[i % kS1LutSide]);
-  }
+  if (tid < kS1LutPieces) reinterpret_cast<uint4*>(s_lut)[tid] = lutv;   // decay table | pair sums
   int bad = 0;
   // validation slice of this CTA: CTA k checks the contig IDS of slice k.  Every gene is in [0, n)
   // (checked during the build), so a row is a permutation <=> every id was written <=> for every id x
@@ -238,10 +315,18 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
   const int32_t vi0 = (int32_t)((int64_t)n * blockIdx.x / gridDim.x), vi1 = (int32_t)((int64_t)n * (blockIdx.x + 1) / gridDim.x);
   constexpr int kVPre = NC <= 2 ? NC : 0;   // orderings whose first id per thread is compared at the end of the kernel
   int32_t vgot[kVPre > 0 ? kVPre : 1];
+#pragma unroll
+  for (int k = 0; k < kS1Pre; ++k) {   // ordering 0 (P >= 1), the genes requested above
+    const int i = tid + k * kS1Threads;
+    if (i < n) {
+      if ((uint32_t)pv[k] >= (uint32_t)n) bad |= 1;
+      else sPos[pv[k]] = (int16_t)(32767 - i);
+    }
+  }
 #pragma unroll 1
   for (int c = 0; c < NC; ++c) {
     const int32_t* row = prm.perm + (size_t)c * n;
-    for (int i = tid; i < n; i += kS1Threads) {
+    for (int i = tid + (c == 0 ? kS1Pre * kS1Threads : 0); i < n; i += kS1Threads) {
       const int32_t cid = (c < prm.P) ? row[i] : i;
       if ((uint32_t)cid >= (uint32_t)n) bad |= 1;
       else sPos[c * nstride + cid] = (int16_t)(32767 - i);
@@ -267,6 +352,7 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
     }
   }
   if (bad) atomicOr(prm.flag, bad);
+  S1_STAMP(1);
 
   int32_t a32[NC];
   int64_t a64[NC];
@@ -312,8 +398,8 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
       if (w_rel + (int32_t)kSlice <= lim_rel) nrun = min((lim_rel - (int32_t)kSlice - w_rel) / (int32_t)kChunk + 1, nchunks - c);
       if (nrun == 0) {
         // the slice crosses a tile boundary or the end of the share: per-lane tile cursor
-        cp_async_wait<kS1Depth - 1>();
         const uint32_t slot = my_slot + (uint32_t)(c & (kS1Depth - 1)) * kS1Stage;
+        cp_async_wait<kS1Depth - 1>();
         const uint4 v = lds_v4(slot);
         cp_async16_zfill(slot, pre, r_rel + kS1Depth * (int32_t)kChunk < hi_rel);
         cp_async_commit();
@@ -342,19 +428,19 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
       }
       const int32_t c_end = c + nrun;
       const int32_t r_pf_end = hi_rel - kS1Depth * (int32_t)kChunk;   // refill while r_rel < r_pf_end
-#pragma unroll 1
-      for (; c < c_end; ++c) {
+      // One chunk of a run.  FULL: the refill is known to be inside the share for every lane.
+      auto step = [&](const uint32_t slot, const uint16_t* src, const int32_t rr, auto full) {
         cp_async_wait<kS1Depth - 1>();
-        const uint32_t slot = my_slot + (uint32_t)(c & (kS1Depth - 1)) * kS1Stage;
         const uint4 v = lds_v4(slot);
         // one a for the whole packet (sorted by (a, b): first a == last a)
         const bool one_a = __all_sync(0xffffffffu, ((v.x ^ (v.w >> 16)) & 0xFF00u) == 0u);
         // v is in registers (the vote consumed it): the slot can be refilled
-        cp_async16_zfill(slot, pre, r_rel < r_pf_end);
+        if (decltype(full)::value) cp_async16(slot, src);
+        else cp_async16_zfill(slot, src, rr < r_pf_end);
         cp_async_commit();
         int32_t wi[kPacket];
         double wd[kPacket];
-        if (WM != W_UNIT) load_weights<WM>(prm.w, lo + r_rel, wi, wd);
+        if (WM != W_UNIT) load_weights<WM>(prm.w, lo + rr, wi, wd);
         if (one_a) {
           s1_packet_same_a<NC, WM>(v, baseA, baseB, cstride, s_lut, s_lut2, wi, wd, a32, a64, ad);
         } else if (__all_sync(0xffffffffu, (v.w >> 24) - ((v.x >> 8) & 0xFFu) <= 1u)) {
@@ -368,6 +454,31 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
                             WM == W_F64 ? wd[k] : 0.0, a32, a64, ad);
           }
         }
+      };
+      // up to the next multiple of the block size in the ring
+#pragma unroll 1
+      for (; c < c_end && (c & (kS1BlockMax - 1)) != 0; ++c) {
+        step(my_slot + (uint32_t)(c & (kS1Depth - 1)) * kS1Stage, pre, r_rel, S1No());
+        r_rel += (int32_t)kChunk;
+        pre += kChunk;
+      }
+      // blocks of kS1Block chunks: ring slots and source addresses at immediate offsets, unconditional
+      // refills, one loop test per block (per chunk: 25 -> ~12 instructions around the 52 that score it)
+      constexpr int kS1Block = NC <= 2 ? kS1BlockMax : 1;   // more orderings: the unrolled block spills
+      const int32_t full_end = hi_rel - (kS1Depth + kS1Block - 1) * (int32_t)kChunk - (int32_t)kSlice;
+#pragma unroll 1
+      while (kS1Block > 1 && c + kS1Block <= c_end && w_rel + (c - (c_end - nrun)) * (int32_t)kChunk <= full_end) {
+        const uint32_t sb = my_slot + (uint32_t)(c & (kS1Depth - 1)) * kS1Stage;
+#pragma unroll
+        for (int j = 0; j < kS1Block; ++j)
+          step(sb + (uint32_t)j * kS1Stage, pre + (int64_t)j * kChunk, r_rel + j * (int32_t)kChunk, S1Yes());
+        c += kS1Block;
+        r_rel += kS1Block * (int32_t)kChunk;
+        pre += kS1Block * kChunk;
+      }
+#pragma unroll 1
+      for (; c < c_end; ++c) {
+        step(my_slot + (uint32_t)(c & (kS1Depth - 1)) * kS1Stage, pre, r_rel, S1No());
         r_rel += (int32_t)kChunk;
         pre += kChunk;
       }
@@ -375,6 +486,10 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
     }
   }
   cp_async_wait<0>();
+  S1_STAMP(2);
+#ifdef LXY_S1_TRACE
+  if (lane == 0 && blockIdx.x < 8) g_s1_trace[1024 * 8 + blockIdx.x * 32 + warp] = s1_now();
+#endif
   if (kVPre > 0 && prm.validate) {
     bool miss = false;
 #pragma unroll
@@ -402,6 +517,7 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1(Stream1Params p
     for (int wq = 0; wq < kS1Warps; ++wq) sum += s_red[wq * NC + tid];
     ((acc_t*)prm.partial)[(size_t)blockIdx.x * NC + tid] = sum;
   }
+  S1_STAMP(3);
 }
 
 template <int NC, int WM>

@@ -98,7 +98,7 @@ __device__ __forceinline__ void s1p_flush(uint32_t (&p32)[NP], int32_t (&a32)[2 
 }
 
 template <int NC>
-__global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1p(Stream1Params prm) {
+__global__ void __launch_bounds__(kS1Threads, kS1MinBlocks) k_scaff_stream1p(Stream1Params prm) {
   typedef typename Acc<W_UNIT>::type acc_t;
   constexpr int NP = NC / 2;
   extern __shared__ __align__(128) uint8_t smem_raw1p[];
@@ -113,6 +113,10 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1p(Stream1Params 
   int64_t* s_tile = (int64_t*)(s_red + kS1Warps * NC);
   const uint32_t sbase = smem_u32(sNeg), pstride = (uint32_t)nstride * 4, lutc = smem_u32(s_lutc);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  S1_STAMP(0);
+#ifdef LXY_S1_TRACE
+  if (threadIdx.x == 0 && blockIdx.x < 1024) { unsigned sm; asm("mov.u32 %0, %smid;" : "=r"(sm)); g_s1_trace[blockIdx.x * 8 + 4] = sm; }
+#endif
 
   // share of the record stream and the first ring fill: as in k_scaff_stream1
   const int64_t npk_all = (prm.L + kPacket - 1) / kPacket;
@@ -169,6 +173,7 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1p(Stream1Params 
     }
   }
   if (bad) atomicOr(prm.flag, bad);
+  S1_STAMP(1);
   __syncthreads();
 
   int32_t a32[NC];
@@ -266,6 +271,7 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1p(Stream1Params 
     }
   }
   cp_async_wait<0>();
+  S1_STAMP(2);
   s1p_flush<NP>(p32, a32);
 
   // ---- warp shuffle tree, then a fixed-order sum over the warps ----
@@ -282,6 +288,7 @@ __global__ void __launch_bounds__(kS1Threads, 2) k_scaff_stream1p(Stream1Params 
     for (int wq = 0; wq < kS1Warps; ++wq) sum += s_red[wq * NC + tid];
     ((acc_t*)prm.partial)[(size_t)blockIdx.x * NC + tid] = sum;
   }
+  S1_STAMP(3);
 }
 
 inline size_t stream1p_smem(int nc, int n) {
