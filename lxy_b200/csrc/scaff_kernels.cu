@@ -710,7 +710,19 @@ static int scaff_score_stream1(lxy_ctx* c, const int32_t* perm_dev, int32_t P, i
   // two orderings per table word where that is exact (scaff_stream1p.cuh)
   static const bool no_pack = getenv("LXY_S1_NOPACK") != nullptr;  // experiments
   const bool pack = !no_pack && stream1p_applies(S.wmode, nc, n) && stream1p_smem(nc, n) <= (size_t)c->max_smem_optin;
-  if (pack) smem = stream1p_smem(nc, n);
+  // The ring: two 2 KB stages per warp while two CTAs per SM fit (64 bulk copies in flight per SM; with
+  // three stages = 96 in flight single SMs ran 1.7 x slower than the rest in some launches -
+  // tools/s1_trace.py, 250 M and 300 M records - and nothing was gained elsewhere), else up to four
+  int stages = 2;
+  {
+    const size_t cap = (size_t)c->max_smem_optin;
+    auto need = [&](int sg) { return pack ? stream1p_smem(nc, n, sg) : stream1_smem(nc, n, sg); };
+    if (2 * (need(2) + 1024) > cap)
+      while (stages < 4 && need(stages + 1) <= cap) ++stages;
+    static const char* force_stages = getenv("LXY_S1_STAGES");   // experiments
+    if (force_stages) stages = atoi(force_stages);
+    smem = need(stages);
+  }
   LXY_TRY(c->d_flag.reserve(64));
   LXY_TRY(c->d_corr.reserve(8 * (size_t)P));
   LXY_TRY(prefer_max_carveout(c));
@@ -750,6 +762,7 @@ static int scaff_score_stream1(lxy_ctx* c, const int32_t* perm_dev, int32_t P, i
   prm.nblk = S.nblk;
   prm.P = P;
   prm.validate = (c->cfg.flags & LXY_FLAG_NO_VALIDATE) ? 0 : 1;
+  prm.stages = stages;
   LXY_TRY(pack ? launch_stream1p_nc(c, nc, prm, (int)grid, smem)
         : S.wmode == W_UNIT ? launch_stream1_nc<W_UNIT>(c, nc, prm, (int)grid, smem)
         : S.wmode == W_INT32 ? launch_stream1_nc<W_INT32>(c, nc, prm, (int)grid, smem)
@@ -849,7 +862,7 @@ static int scaff_enqueue_passes(lxy_ctx* c, const int32_t* perm_dev, int32_t P, 
     const int32_t pp = P - p0 < kS1Pass ? P - p0 : kS1Pass;
     int ncp = 1;
     while (ncp < pp) ncp *= 2;
-    LXY_TRY(scaff_score_stream1(c, perm_dev + (size_t)p0 * n, pp, ncp, stream1_smem(ncp, n), out_dev + p0,
+    LXY_TRY(scaff_score_stream1(c, perm_dev + (size_t)p0 * n, pp, ncp, stream1_smem(ncp, n, 2), out_dev + p0,
                                 x100_dev ? x100_dev + p0 : nullptr, first && p0 == 0, last && p0 + kS1Pass >= P));
   }
   return LXY_OK;
@@ -873,7 +886,7 @@ static int scaff_score_enqueue(lxy_ctx* c, const int32_t* perm_dev, int32_t P, d
   constexpr int kS1Pass = 8;
   const double l_m = (double)S.L * 1e-6;
   const bool s1_ok = n <= 65536 && !(c->cfg.flags & LXY_FLAG_NO_STREAM1) &&
-                     stream1_smem(P < kS1Pass ? (P <= 1 ? 1 : P <= 2 ? 2 : P <= 4 ? 4 : 8) : kS1Pass, n) <= (size_t)c->max_smem_optin;
+                     stream1_smem(P < kS1Pass ? (P <= 1 ? 1 : P <= 2 ? 2 : P <= 4 ? 4 : 8) : kS1Pass, n, 2) <= (size_t)c->max_smem_optin;
   const bool model_ok = s1_ok && S.wmode == W_UNIT && stream1p_applies(S.wmode, kS1Pass, n) &&
                         stream1p_smem(kS1Pass, n) <= (size_t)c->max_smem_optin;
   // ---- streaming regime: up to 8 candidates per pass (a lone Score() call is a batch of one) ----

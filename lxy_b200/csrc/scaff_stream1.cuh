@@ -27,6 +27,13 @@ constexpr int kS1Depth = LXY_S1_DEPTH;     // 16-byte record copies in flight pe
 constexpr int kS1DepthLog2 = kS1Depth == 8 ? 3 : kS1Depth == 4 ? 2 : kS1Depth == 16 ? 4 : -1;
 static_assert(kS1DepthLog2 > 0, "ring depth");
 constexpr int kS1Stage = kS1Threads * 16;  // bytes of one ring stage (one packet per thread)
+// Ring geometry of k_scaff_stream1: every warp owns kS1Sub packets per lane (2 KB) of each chunk and
+// keeps `stages` such slices in flight, each filled by ONE bulk copy (UBLKCP) counted on the warp's own
+// mbarrier of that stage: warps stay independent of each other (a ring stage shared by the CTA couples
+// them to the slowest, measured 100 us against 82), and the copy engine sees 2 KB requests (512-byte
+// ones cost 158 us: its cost is per request).
+constexpr int kS1Sub = 4;
+constexpr int kS1WarpStage = kS1Sub * 512;             // bytes per warp and ring stage
 #ifndef LXY_S1_BLOCK
 #define LXY_S1_BLOCK 4
 #endif
@@ -88,6 +95,7 @@ struct Stream1Params {
   int64_t L;
   int32_t n, nblk, P;
   int32_t validate;
+  int32_t stages;       // ring stages per warp (k_scaff_stream1: 2 or 3)
 };
 
 // Table entries are tab[x] = 32767 - pos[x] as int16 (pos in [0, 65535]), so that
@@ -212,6 +220,25 @@ __device__ __forceinline__ void s1_packet_two_a(const uint4 v, uint32_t baseA, u
   }
 }
 
+__device__ __forceinline__ void s1_bulk_fill(uint32_t dst_smem, const void* src, uint32_t bar_smem) {
+  asm volatile(
+      "mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %3;\n\t"
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%1], [%2], %3, [%0];" ::"r"(bar_smem),
+      "r"(dst_smem), "l"(src), "n"(kS1WarpStage)
+      : "memory");
+}
+__device__ __forceinline__ void s1_bar_wait(uint32_t bar_smem, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(bar_smem),
+      "r"(parity)
+      : "memory");
+}
+
 struct S1Yes { static constexpr bool value = true; };
 struct S1No { static constexpr bool value = false; };
 
@@ -260,19 +287,24 @@ __global__ void __launch_bounds__(kS1Threads + (kS1MinBlocks == 2 && NC <= 2 ? 6
 #endif
 
   // ---- this CTA's share of the record stream: an even split of the 8-record packets, walked in
-  // chunks of one packet per thread (8 KB; a warp owns 256 consecutive records of each chunk).
-  // Every lane keeps kS1Depth 16-byte cp.async copies (LDGSTS, L1 bypass) in flight into its own
-  // slots of a shared-memory ring: the depth is set by cp.async.wait_group, not by register
-  // scoreboards (prefetching loads all land on one scoreboard, so waiting for the oldest also waits
-  // for the newest — measured: no gain from any depth). ----
+  // chunks of kS1Sub packets per thread (32 KB; a warp owns 1,024 consecutive records = 2 KB of each
+  // chunk).  The warp's slices arrive in its own ring of `stages` 2 KB slots, each filled by one bulk
+  // copy that lane 0 requests and whose completion the warp awaits on the slot's mbarrier: the L1 data
+  // pipe, which bounds the stream phase (one wavefront per cycle; per warp-packet 4 for the packet's own
+  // LDS.128, 1 + 8 table look-ups, 4 pair look-ups), no longer carries the 4 wavefronts of 32 lanes'
+  // LDGSTS writes, and the three `@!PT LDS` issue slots ptxas pads every LDGSTS with are gone. ----
   const int64_t npk_all = (prm.L + kPacket - 1) / kPacket;
   const int64_t lo = (npk_all * blockIdx.x / gridDim.x) * kPacket;
   const int64_t hi = min((npk_all * (blockIdx.x + 1) / gridDim.x) * kPacket, prm.L);
-  constexpr int64_t kSlice = 32 * kPacket;                          // records per warp per chunk
-  constexpr int64_t kChunk = (int64_t)kS1Threads * kPacket;         // records per CTA per chunk
+  constexpr int32_t kSub = 32 * kPacket;                            // records per warp-packet
+  constexpr int32_t kSlice = kSub * kS1Sub;                         // records per warp per chunk
+  constexpr int32_t kChunk = kS1Warps * kSlice;                     // records per CTA per chunk
   const int32_t nchunks = (int32_t)((hi - lo + kChunk - 1) / kChunk);
-  const uint32_t my_slot = smem_u32(s_tile + 2) + (uint32_t)tid * 16;  // ring: [kS1Depth][threads] x 16 B
-  int64_t r0 = lo + (int64_t)tid * kPacket;                         // this thread's packet of chunk 0
+  const int32_t stages = prm.stages;
+  const uint32_t ring_w = smem_u32(s_tile + 2) + (uint32_t)warp * (uint32_t)(stages * kS1WarpStage);   // this warp's slots
+  const uint32_t bar_w = smem_u32(s_tile + 2) + (uint32_t)(kS1Warps * stages * kS1WarpStage) + (uint32_t)warp * (uint32_t)(stages * 8);
+  const uint16_t* rec_w = prm.rec + lo + (int64_t)warp * kSlice;    // the warp's slice of chunk 0
+  const int32_t hi_rel = (int32_t)(hi - lo);                        // a share is far below 2^31 records
 
   // ---- prologue loads, requested BEFORE the ring is filled: behind 64 KB of record copies per CTA
   // (19 MB over the GPU) they waited 2 us in the memory system's queues (per-CTA time stamps: prologue
@@ -289,11 +321,15 @@ __global__ void __launch_bounds__(kS1Threads + (kS1MinBlocks == 2 && NC <= 2 ? 6
   if (tid < ntiles) { ts0 = ldg_s64_ordered(prm.tile_start + tid); ts1 = ldg_s64_ordered(prm.tile_start + tid + 1); }
   uint4 lutv = make_uint4(0, 0, 0, 0);
   if (tid < kS1LutPieces) lutv = ldg_v4_ordered(g_s1_luts.v + tid * 16);
-#pragma unroll
-  for (int q = 0; q < kS1Depth; ++q) {
-    if (r0 + q * kChunk < hi) cp_async16(my_slot + q * kS1Stage, prm.rec + r0 + q * kChunk);
-    cp_async_commit();
+  if (lane == 0) {
+    for (int q = 0; q < stages; ++q)
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_w + q * 8) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    for (int q = 0; q < stages; ++q)
+      if (warp * kSlice + (int64_t)q * kChunk < hi_rel)
+        s1_bulk_fill(ring_w + q * kS1WarpStage, rec_w + (int64_t)q * kChunk, bar_w + q * 8);
   }
+  __syncwarp();
   // the tile holding record `lo` (the only t with tile_start[t] <= lo < tile_start[t+1])
   if (lo < hi) {
     if (tid < ntiles && ts0 <= lo && lo < ts1) { s_tile[0] = tid; s_tile[1] = ts1; }
@@ -374,118 +410,131 @@ __global__ void __launch_bounds__(kS1Threads + (kS1MinBlocks == 2 && NC <= 2 ? 6
     }
     cur.J = cur.I + (int32_t)(cur.t - tile_row_start(cur.I, prm.nblk));
     cur.end = s_tile[1];
-    // 32-bit offsets relative to `lo` from here on (a share is far below 2^31 records)
-    const int32_t hi_rel = (int32_t)(hi - lo);
-    int32_t w_rel = warp * (int32_t)kSlice;                   // first record of the warp's slice
-    int32_t r_rel = tid * kPacket;                            // this lane's packet
+    int32_t w_rel = warp * kSlice;                            // first record of the warp's slice (relative to lo)
     int32_t lim_rel = 0;                                      // end of (share ∩ current tile); 0 forces the set-up
     uint32_t baseA = sbase, baseB = sbase;
-    const uint16_t* pre = prm.rec + lo + r_rel + (int64_t)kS1Depth * kChunk;  // next packet to request
+    int32_t st = 0;                                           // ring stage of chunk c, and its mbarrier phase
+    uint32_t ph = 0;
+    // Hand the stage back: lane 0 requests the warp's slice of chunk c + stages into it.
+    auto refill = [&]() {
+      if (lane == 0 && w_rel + stages * kChunk < hi_rel)
+        s1_bulk_fill(ring_w + (uint32_t)st * kS1WarpStage, rec_w + (int64_t)w_rel - (int64_t)warp * kSlice + (int64_t)stages * kChunk,
+                     bar_w + (uint32_t)st * 8);
+    };
+    // One warp-packet whose 256 records lie in the current tile: one a for the whole packet (sorted by
+    // (a, b): first a == last a) is the common case, two neighbouring a's the next.
+    auto score_packet = [&](const uint4 v, const int32_t (&wi)[kPacket], const double (&wd)[kPacket]) {
+      if (__all_sync(0xffffffffu, ((v.x ^ (v.w >> 16)) & 0xFF00u) == 0u)) {
+        s1_packet_same_a<NC, WM>(v, baseA, baseB, cstride, s_lut, s_lut2, wi, wd, a32, a64, ad);
+      } else if (__all_sync(0xffffffffu, (v.w >> 24) - ((v.x >> 8) & 0xFFu) <= 1u)) {
+        s1_packet_two_a<NC, WM>(v, baseA, baseB, cstride, s_lut, s_lut2, wi, wd, a32, a64, ad);
+      } else {
+        const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int k = 0; k < kPacket; ++k) {
+          const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
+          s1_eval<NC, WM>(baseA, baseB, cstride, s_lut, r, WM == W_INT32 ? wi[k] : 0,
+                          WM == W_F64 ? wd[k] : 0.0, a32, a64, ad);
+        }
+      }
+    };
     // Chunks are walked in RUNS: as long as the warp's slice lies inside (share ∩ current tile) nothing
-    // but the ring and the packet itself is touched (the hot loop below: no tile test, branch-free
-    // refill).  A slice that crosses a tile boundary or the end of the share takes the per-lane path,
-    // one chunk, and the next run starts behind it.
+    // but the ring and the packets themselves are touched.  A slice that crosses a tile boundary or the
+    // end of the share takes the per-lane path, one chunk, and the next run starts behind it.
     int32_t c = 0;
 #pragma unroll 1
     while (c < nchunks) {
-      if (w_rel < hi_rel && w_rel + (int32_t)kSlice > lim_rel) {   // next tile (or the first one)
+      if (w_rel < hi_rel && w_rel + kSlice > lim_rel) {            // next tile (or the first one)
         cur.advance_to(lo + w_rel, prm.tile_start, prm.nblk);
         lim_rel = (int32_t)(min(hi, cur.end) - lo);
         baseA = sbase + (uint32_t)cur.I * (kBlk * 2);
         baseB = sbase + (uint32_t)cur.J * (kBlk * 2);
       }
       int32_t nrun = 0;                                            // warp-uniform
-      if (w_rel + (int32_t)kSlice <= lim_rel) nrun = min((lim_rel - (int32_t)kSlice - w_rel) / (int32_t)kChunk + 1, nchunks - c);
+      if (w_rel + kSlice <= lim_rel) nrun = min((lim_rel - kSlice - w_rel) / kChunk + 1, nchunks - c);
       if (nrun == 0) {
-        // the slice crosses a tile boundary or the end of the share: per-lane tile cursor
-        const uint32_t slot = my_slot + (uint32_t)(c & (kS1Depth - 1)) * kS1Stage;
-        cp_async_wait<kS1Depth - 1>();
-        const uint4 v = lds_v4(slot);
-        cp_async16_zfill(slot, pre, r_rel + kS1Depth * (int32_t)kChunk < hi_rel);
-        cp_async_commit();
-        if (r_rel < hi_rel) {
-          int32_t wi[kPacket];
-          double wd[kPacket];
-          if (WM != W_UNIT) load_weights<WM>(prm.w, lo + r_rel, wi, wd);
-          S1Tile mine = cur;
-          const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+        // The slice crosses a tile boundary or the end of the share.  Its packets are taken one by one: a
+        // warp-packet that lies inside one tile and the share goes through the fast path with that tile's
+        // rows, only the one that straddles takes a per-lane tile cursor.
+        if (w_rel < hi_rel) {                                      // warp-uniform: a copy was requested
+          s1_bar_wait(bar_w + (uint32_t)st * 8, ph);
+          const uint32_t slot = ring_w + (uint32_t)st * kS1WarpStage + (uint32_t)lane * 16;
+#pragma unroll 1
+          for (int j = 0; j < kS1Sub; ++j) {
+            const int32_t ws = w_rel + j * kSub;                   // first record of the warp-packet
+            if (ws >= hi_rel) break;
+            if (ws >= lim_rel) {                                   // the packet starts in a later tile
+              cur.advance_to(lo + ws, prm.tile_start, prm.nblk);
+              lim_rel = (int32_t)(min(hi, cur.end) - lo);
+              baseA = sbase + (uint32_t)cur.I * (kBlk * 2);
+              baseB = sbase + (uint32_t)cur.J * (kBlk * 2);
+            }
+            const int32_t rr = ws + lane * kPacket;
+            const uint4 v = lds_v4(slot + (uint32_t)j * 512);
+            int32_t wi[kPacket];
+            double wd[kPacket];
+            if (ws + kSub <= lim_rel) {
+              if (WM != W_UNIT) load_weights<WM>(prm.w, lo + rr, wi, wd);
+              score_packet(v, wi, wd);
+            } else if (rr < hi_rel) {
+              if (WM != W_UNIT) load_weights<WM>(prm.w, lo + rr, wi, wd);
+              S1Tile mine = cur;
+              const uint32_t words[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-          for (int k = 0; k < kPacket; ++k) {  // unrolled: words[] stays in registers
-            if (r_rel + k < hi_rel) {
-              mine.advance_to(lo + r_rel + k, prm.tile_start, prm.nblk);
-              const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
-              s1_eval<NC, WM>(sbase + (uint32_t)mine.I * (kBlk * 2), sbase + (uint32_t)mine.J * (kBlk * 2),
-                              cstride, s_lut, r, WM == W_INT32 ? wi[k] : 0, WM == W_F64 ? wd[k] : 0.0,
-                              a32, a64, ad);
+              for (int k = 0; k < kPacket; ++k) {  // unrolled: words[] stays in registers
+                if (rr + k < hi_rel) {
+                  mine.advance_to(lo + rr + k, prm.tile_start, prm.nblk);
+                  const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
+                  s1_eval<NC, WM>(sbase + (uint32_t)mine.I * (kBlk * 2), sbase + (uint32_t)mine.J * (kBlk * 2),
+                                  cstride, s_lut, r, WM == W_INT32 ? wi[k] : 0, WM == W_F64 ? wd[k] : 0.0,
+                                  a32, a64, ad);
+                }
+              }
             }
           }
+          fence_proxy_async();   // every lane's reads of the slot are complete before it is handed back
+          __syncwarp();
+          refill();
         }
         ++c;
-        w_rel += (int32_t)kChunk;
-        r_rel += (int32_t)kChunk;
-        pre += kChunk;
+        w_rel += kChunk;
+        if (++st == stages) { st = 0; ph ^= 1u; }
         continue;
       }
       const int32_t c_end = c + nrun;
-      const int32_t r_pf_end = hi_rel - kS1Depth * (int32_t)kChunk;   // refill while r_rel < r_pf_end
-      // One chunk of a run.  FULL: the refill is known to be inside the share for every lane.
-      auto step = [&](const uint32_t slot, const uint16_t* src, const int32_t rr, auto full) {
-        cp_async_wait<kS1Depth - 1>();
-        const uint4 v = lds_v4(slot);
-        // one a for the whole packet (sorted by (a, b): first a == last a)
-        const bool one_a = __all_sync(0xffffffffu, ((v.x ^ (v.w >> 16)) & 0xFF00u) == 0u);
-        // v is in registers (the vote consumed it): the slot can be refilled
-        if (decltype(full)::value) cp_async16(slot, src);
-        else cp_async16_zfill(slot, src, rr < r_pf_end);
-        cp_async_commit();
-        int32_t wi[kPacket];
-        double wd[kPacket];
-        if (WM != W_UNIT) load_weights<WM>(prm.w, lo + rr, wi, wd);
-        if (one_a) {
-          s1_packet_same_a<NC, WM>(v, baseA, baseB, cstride, s_lut, s_lut2, wi, wd, a32, a64, ad);
-        } else if (__all_sync(0xffffffffu, (v.w >> 24) - ((v.x >> 8) & 0xFFu) <= 1u)) {
-          s1_packet_two_a<NC, WM>(v, baseA, baseB, cstride, s_lut, s_lut2, wi, wd, a32, a64, ad);
-        } else {
-          const uint32_t words[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-          for (int k = 0; k < kPacket; ++k) {
-            const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
-            s1_eval<NC, WM>(baseA, baseB, cstride, s_lut, r, WM == W_INT32 ? wi[k] : 0,
-                            WM == W_F64 ? wd[k] : 0.0, a32, a64, ad);
-          }
-        }
-      };
-      // up to the next multiple of the block size in the ring
-#pragma unroll 1
-      for (; c < c_end && (c & (kS1BlockMax - 1)) != 0; ++c) {
-        step(my_slot + (uint32_t)(c & (kS1Depth - 1)) * kS1Stage, pre, r_rel, S1No());
-        r_rel += (int32_t)kChunk;
-        pre += kChunk;
-      }
-      // blocks of kS1Block chunks: ring slots and source addresses at immediate offsets, unconditional
-      // refills, one loop test per block (per chunk: 25 -> ~12 instructions around the 52 that score it)
-      constexpr int kS1Block = NC <= 2 ? kS1BlockMax : 1;   // more orderings: the unrolled block spills
-      const int32_t full_end = hi_rel - (kS1Depth + kS1Block - 1) * (int32_t)kChunk - (int32_t)kSlice;
-#pragma unroll 1
-      while (kS1Block > 1 && c + kS1Block <= c_end && w_rel + (c - (c_end - nrun)) * (int32_t)kChunk <= full_end) {
-        const uint32_t sb = my_slot + (uint32_t)(c & (kS1Depth - 1)) * kS1Stage;
-#pragma unroll
-        for (int j = 0; j < kS1Block; ++j)
-          step(sb + (uint32_t)j * kS1Stage, pre + (int64_t)j * kChunk, r_rel + j * (int32_t)kChunk, S1Yes());
-        c += kS1Block;
-        r_rel += kS1Block * (int32_t)kChunk;
-        pre += kS1Block * kChunk;
-      }
 #pragma unroll 1
       for (; c < c_end; ++c) {
-        step(my_slot + (uint32_t)(c & (kS1Depth - 1)) * kS1Stage, pre, r_rel, S1No());
-        r_rel += (int32_t)kChunk;
-        pre += kChunk;
+        s1_bar_wait(bar_w + (uint32_t)st * 8, ph);
+        const uint32_t slot = ring_w + (uint32_t)st * kS1WarpStage + (uint32_t)lane * 16;
+#pragma unroll
+        for (int j = 0; j < kS1Sub; ++j) {
+          const uint4 v = lds_v4(slot + (uint32_t)j * 512);
+          // one a for the whole packet (sorted by (a, b): first a == last a)
+          const bool one_a = __all_sync(0xffffffffu, ((v.x ^ (v.w >> 16)) & 0xFF00u) == 0u);
+          // the last packet of the slot is in registers (the vote consumed it): the slot can be refilled
+          if (j == kS1Sub - 1) refill();
+          int32_t wi[kPacket];
+          double wd[kPacket];
+          if (WM != W_UNIT) load_weights<WM>(prm.w, lo + w_rel + j * kSub + lane * kPacket, wi, wd);
+          if (one_a) {
+            s1_packet_same_a<NC, WM>(v, baseA, baseB, cstride, s_lut, s_lut2, wi, wd, a32, a64, ad);
+          } else if (__all_sync(0xffffffffu, (v.w >> 24) - ((v.x >> 8) & 0xFFu) <= 1u)) {
+            s1_packet_two_a<NC, WM>(v, baseA, baseB, cstride, s_lut, s_lut2, wi, wd, a32, a64, ad);
+          } else {
+            const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int k = 0; k < kPacket; ++k) {
+              const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
+              s1_eval<NC, WM>(baseA, baseB, cstride, s_lut, r, WM == W_INT32 ? wi[k] : 0,
+                              WM == W_F64 ? wd[k] : 0.0, a32, a64, ad);
+            }
+          }
+        }
+        w_rel += kChunk;
+        if (++st == stages) { st = 0; ph ^= 1u; }
       }
-      w_rel += nrun * (int32_t)kChunk;
     }
   }
-  cp_async_wait<0>();
   S1_STAMP(2);
 #ifdef LXY_S1_TRACE
   if (lane == 0 && blockIdx.x < 8) g_s1_trace[1024 * 8 + blockIdx.x * 32 + warp] = s1_now();
@@ -546,7 +595,7 @@ int launch_stream1_nc(lxy_ctx* c, int nc, const Stream1Params& prm, int grid, si
   }
 }
 
-inline size_t stream1_smem(int nc, int n) {
+inline size_t stream1_smem(int nc, int n, int stages = 3) {
   return (size_t)nc * ((n + kBlk - 1) & ~(kBlk - 1)) * 2 + 64 + kS1Lut2Bytes + (size_t)kS1Warps * nc * 8 + 16 + 512 +
-         (size_t)kS1Depth * kS1Stage;  // (alignment slack) table | lut | warp sums | start tile | record ring
+         (size_t)kS1Warps * stages * (kS1WarpStage + 8);  // (alignment slack) table | lut | warp sums | start tile | record ring | ring barriers
 }

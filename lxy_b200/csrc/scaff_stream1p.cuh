@@ -97,8 +97,25 @@ __device__ __forceinline__ void s1p_flush(uint32_t (&p32)[NP], int32_t (&a32)[2 
   }
 }
 
+// The decay table (64 bytes) and the pair table lutc[v1][v0] = 100 T[v0] | 100 T[v1] << 16, built at
+// compile time and copied into shared memory as 16-byte pieces requested with the other prologue loads.
+struct S1pLuts { uint8_t lut[64]; uint32_t lutc[kLut2Words]; };
+constexpr S1pLuts s1p_make_luts() {
+  S1pLuts t{};
+  for (int i = 0; i < kLutLen; ++i) t.lut[i] = s1_lut100_at(i);
+  for (int i = 0; i < kLut2Words; ++i) {
+    const int v0 = i % kLut2Stride, v1 = i / kLut2Stride;
+    t.lutc[i] = (v0 < kLutLen ? (uint32_t)s1_lut100_at(v0) : 0u) | ((uint32_t)s1_lut100_at(v1) << 16);
+  }
+  return t;
+}
+__device__ const S1pLuts g_s1p_luts = s1p_make_luts();
+constexpr int kS1PreP = 5120 / kS1Threads;                    // genes per thread and ordering requested ahead of the ring
+constexpr int kS1pLutPieces = (int)(sizeof(S1pLuts) / 16);   // 544
+static_assert(sizeof(S1pLuts) % 16 == 0 && kS1pLutPieces <= 2 * kS1Threads, "lut pieces");
+
 template <int NC>
-__global__ void __launch_bounds__(kS1Threads, kS1MinBlocks) k_scaff_stream1p(Stream1Params prm) {
+__global__ void __launch_bounds__(kS1Threads + (kS1MinBlocks == 2 && NC <= 2 ? 64 : 0), kS1MinBlocks) k_scaff_stream1p(Stream1Params prm) {
   typedef typename Acc<W_UNIT>::type acc_t;
   constexpr int NP = NC / 2;
   extern __shared__ __align__(128) uint8_t smem_raw1p[];
@@ -118,63 +135,146 @@ __global__ void __launch_bounds__(kS1Threads, kS1MinBlocks) k_scaff_stream1p(Str
   if (threadIdx.x == 0 && blockIdx.x < 1024) { unsigned sm; asm("mov.u32 %0, %smid;" : "=r"(sm)); g_s1_trace[blockIdx.x * 8 + 4] = sm; }
 #endif
 
-  // share of the record stream and the first ring fill: as in k_scaff_stream1
+  // share of the record stream, per-warp ring of 2 KB bulk copies: as in k_scaff_stream1
   const int64_t npk_all = (prm.L + kPacket - 1) / kPacket;
   const int64_t lo = (npk_all * blockIdx.x / gridDim.x) * kPacket;
   const int64_t hi = min((npk_all * (blockIdx.x + 1) / gridDim.x) * kPacket, prm.L);
-  constexpr int64_t kSlice = 32 * kPacket;
-  constexpr int64_t kChunk = (int64_t)kS1Threads * kPacket;
+  constexpr int32_t kSub = 32 * kPacket;
+  constexpr int32_t kSlice = kSub * kS1Sub;
+  constexpr int32_t kChunk = kS1Warps * kSlice;
   const int32_t nchunks = (int32_t)((hi - lo + kChunk - 1) / kChunk);
-  const uint32_t my_slot = smem_u32(s_tile + 2) + (uint32_t)tid * 16;
-  const int64_t r0 = lo + (int64_t)tid * kPacket;
+  const int32_t stages = prm.stages;
+  const uint32_t ring_w = smem_u32(s_tile + 2) + (uint32_t)warp * (uint32_t)(stages * kS1WarpStage);
+  const uint32_t bar_w = smem_u32(s_tile + 2) + (uint32_t)(kS1Warps * stages * kS1WarpStage) + (uint32_t)warp * (uint32_t)(stages * 8);
+  const uint16_t* rec_w = prm.rec + lo + (int64_t)warp * kSlice;
+  const int32_t hi_rel = (int32_t)(hi - lo);
+  const int64_t ntiles = (int64_t)prm.nblk * (prm.nblk + 1) / 2;
+  auto fill_ring = [&]() {
+    if (lane == 0) {
+      for (int q = 0; q < stages; ++q)
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_w + q * 8) : "memory");
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      for (int q = 0; q < stages; ++q)
+        if (warp * kSlice + (int64_t)q * kChunk < hi_rel)
+          s1_bulk_fill(ring_w + q * kS1WarpStage, rec_w + (int64_t)q * kChunk, bar_w + q * 8);
+    }
+    __syncwarp();
+  };
+
+  // ---- prologue loads ahead of the record copies (see k_scaff_stream1): with two orderings the first
+  // kS1Pre genes per thread of both; with more the tables are built before the ring is filled ----
+  constexpr int kPreC = NC <= 2 ? NC : 0;
+  int32_t pv[kPreC > 0 ? kPreC : 1][kS1PreP];
 #pragma unroll
-  for (int q = 0; q < kS1Depth; ++q) {
-    if (r0 + q * kChunk < hi) cp_async16(my_slot + q * kS1Stage, prm.rec + r0 + q * kChunk);
-    cp_async_commit();
-  }
+  for (int c = 0; c < kPreC; ++c)
+#pragma unroll
+    for (int k = 0; k < kS1PreP; ++k) {
+      const int i = tid + k * kS1Threads;
+      pv[c][k] = (i < n && c < prm.P) ? ldg_s32_ordered(prm.perm + (size_t)c * n + i) : i;
+    }
+  int64_t ts0 = 0, ts1 = 0;
+  if (tid < ntiles) { ts0 = ldg_s64_ordered(prm.tile_start + tid); ts1 = ldg_s64_ordered(prm.tile_start + tid + 1); }
+  uint4 lutv0 = ldg_v4_ordered(reinterpret_cast<const uint8_t*>(&g_s1p_luts) + tid * 16), lutv1 = make_uint4(0, 0, 0, 0);
+  if (tid + kS1Threads < kS1pLutPieces) lutv1 = ldg_v4_ordered(reinterpret_cast<const uint8_t*>(&g_s1p_luts) + (tid + kS1Threads) * 16);
+  if (kPreC > 0) fill_ring();
+  S1_STAMP(5);
   if (lo < hi) {
-    const int64_t ntiles = (int64_t)prm.nblk * (prm.nblk + 1) / 2;
-    for (int64_t t = tid; t < ntiles; t += kS1Threads)
+    if (tid < ntiles && ts0 <= lo && lo < ts1) { s_tile[0] = tid; s_tile[1] = ts1; }
+    for (int64_t t = tid + kS1Threads; t < ntiles; t += kS1Threads)
       if (prm.tile_start[t] <= lo) {
         const int64_t e = prm.tile_start[t + 1];
         if (lo < e) { s_tile[0] = t; s_tile[1] = e; }
       }
   }
+  reinterpret_cast<uint4*>(s_lut)[tid] = lutv0;                                   // decay table | pair table
+  if (tid + kS1Threads < kS1pLutPieces) reinterpret_cast<uint4*>(s_lut)[tid + kS1Threads] = lutv1;
+  S1_STAMP(6);
   // ---- placement tables: half-word (c & 1) of word [c >> 1][perm_c[i]] = -i (pad orderings: identity) ----
-  if (tid < kLutLen) s_lut[tid] = c_lut100[tid];
   int bad = 0;
-#pragma unroll 1
-  for (int c = 0; c < NC; ++c) {
-    const int32_t* row = prm.perm + (size_t)c * n;
-    for (int i = tid; i < n; i += kS1Threads) {
-      const int32_t cid = (c < prm.P) ? row[i] : i;
-      if ((uint32_t)cid >= (uint32_t)n) bad |= 1;
-      else sNeg[((size_t)(c >> 1) * nstride + cid) * 2 + (c & 1)] = (uint16_t)(0 - i);
+#pragma unroll
+  for (int c = 0; c < kPreC; ++c)
+#pragma unroll
+    for (int k = 0; k < kS1PreP; ++k) {
+      const int i = tid + k * kS1Threads;
+      if (i < n) {
+        if ((uint32_t)pv[c][k] >= (uint32_t)n) bad |= 1;
+        else sNeg[((size_t)(c >> 1) * nstride + pv[c][k]) * 2 + (c & 1)] = (uint16_t)(0 - i);
+      }
     }
+  if (kPreC > 0) {
+#pragma unroll 1
+    for (int c = 0; c < NC; ++c) {   // what the requests above did not cover (n > 5,120)
+      const int32_t* row = prm.perm + (size_t)c * n;
+      for (int i = tid + kS1PreP * kS1Threads; i < n; i += kS1Threads) {
+        const int32_t cid = (c < prm.P) ? row[i] : i;
+        if ((uint32_t)cid >= (uint32_t)n) bad |= 1;
+        else sNeg[((size_t)(c >> 1) * nstride + cid) * 2 + (c & 1)] = (uint16_t)(0 - i);
+      }
+    }
+  } else {
+    // all orderings as ONE sequence of (ordering, gene) items, 16 loads in flight per thread: ordering by
+    // ordering the loop waited one memory round trip per ordering and four genes (12 us for four orderings)
+    constexpr int kB = 16;
+    const int K = (n + kS1Threads - 1) / kS1Threads, total = NC * K;
+    int c_ld = 0, k_ld = 0, c_st = 0, k_st = 0;
+#pragma unroll 1
+    for (int q0 = 0; q0 < total; q0 += kB) {
+      int32_t buf[kB];
+#pragma unroll
+      for (int j = 0; j < kB; ++j) {
+        const int i = tid + k_ld * kS1Threads;
+        buf[j] = (q0 + j < total && i < n && c_ld < prm.P) ? ldg_s32_ordered(prm.perm + (size_t)c_ld * n + i) : i;
+        if (++k_ld == K) { k_ld = 0; ++c_ld; }
+      }
+#pragma unroll
+      for (int j = 0; j < kB; ++j) {
+        const int i = tid + k_st * kS1Threads;
+        if (q0 + j < total && i < n) {
+          if ((uint32_t)buf[j] >= (uint32_t)n) bad |= 1;
+          else sNeg[((size_t)(c_st >> 1) * nstride + buf[j]) * 2 + (c_st & 1)] = (uint16_t)(0 - i);
+        }
+        if (++k_st == K) { k_st = 0; ++c_st; }
+      }
+    }
+    fill_ring();
   }
+  S1_STAMP(7);
   __syncthreads();
-  for (int i = tid; i < kLut2Words; i += kS1Threads) {  // from the shared copy of the decay table
-    const int v0 = i % kLut2Stride, v1 = i / kLut2Stride;
-    s_lutc[i] = (v0 < kLutLen ? (uint32_t)s_lut[v0] : 0u) | ((uint32_t)s_lut[v1] << 16);
-  }
+  // CTA k checks the contig IDS of slice k: the position p decoded from the table entry of id x must be in
+  // range with perm[p] == x.  Independent of which store to a duplicated id won (see k_scaff_stream1): a
+  // duplicate leaves another id unwritten, and an unwritten slot cannot point at its own id.  The gathers
+  // perm[p] of the first id per thread are requested for all orderings at once; with two orderings they
+  // stay in flight while the records are scored.
+  const int32_t i0 = (int32_t)((int64_t)n * blockIdx.x / gridDim.x), i1 = (int32_t)((int64_t)n * (blockIdx.x + 1) / gridDim.x);
+  int32_t vgot[NC];
+#pragma unroll
+  for (int c = 0; c < NC; ++c) vgot[c] = i0 + tid;
   if (prm.validate) {
-    // CTA k checks the contig IDS of slice k: the position p decoded from the table entry of id x must be
-    // in range with perm[p] == x.  Independent of which store to a duplicated id won (see k_scaff_stream1):
-    // a duplicate leaves another id unwritten, and an unwritten slot cannot point at its own id.
-    const int32_t i0 = (int32_t)((int64_t)n * blockIdx.x / gridDim.x), i1 = (int32_t)((int64_t)n * (blockIdx.x + 1) / gridDim.x);
+    if (i0 + tid < i1) {
+#pragma unroll
+      for (int c = 0; c < NC; ++c)
+        if (c < prm.P) {
+          // the whole word through an opaque 32-bit load, decoded in 32 bits
+          const uint32_t word = lds_u32(sbase + (uint32_t)(c >> 1) * pstride + (uint32_t)(i0 + tid) * 4u);
+          const uint32_t p = (0u - ((c & 1) ? (word >> 16) : (word & 0xFFFFu))) & 0xFFFFu;
+          vgot[c] = p < (uint32_t)n ? prm.perm[(size_t)c * n + p] : -1;
+        }
+    }
     for (int c = 0; c < prm.P && c < NC; ++c) {
       const int32_t* row = prm.perm + (size_t)c * n;
-      for (int x = i0 + tid; x < i1; x += kS1Threads) {
-        // the whole word through an opaque 32-bit load, decoded in 32 bits
+      for (int x = i0 + tid + kS1Threads; x < i1; x += kS1Threads) {
         const uint32_t word = lds_u32(sbase + (uint32_t)(c >> 1) * pstride + (uint32_t)x * 4u);
         const uint32_t p = (0u - ((c & 1) ? (word >> 16) : (word & 0xFFFFu))) & 0xFFFFu;
         if (p >= (uint32_t)n || row[p] != x) bad |= 2;
       }
     }
+    if (NC > 2) {
+#pragma unroll
+      for (int c = 0; c < NC; ++c) if (vgot[c] != i0 + tid) bad |= 2;
+    }
   }
   if (bad) atomicOr(prm.flag, bad);
   S1_STAMP(1);
-  __syncthreads();
 
   int32_t a32[NC];
   uint32_t p32[NP];
@@ -196,83 +296,128 @@ __global__ void __launch_bounds__(kS1Threads, kS1MinBlocks) k_scaff_stream1p(Str
     }
     cur.J = cur.I + (int32_t)(cur.t - tile_row_start(cur.I, prm.nblk));
     cur.end = s_tile[1];
-    const int32_t hi_rel = (int32_t)(hi - lo);
-    int32_t w_rel = warp * (int32_t)kSlice;
-    int32_t r_rel = tid * kPacket;
+    int32_t w_rel = warp * kSlice;
     int32_t lim_rel = 0;
     uint32_t baseA = sbase, baseB = sbase;
-    const uint16_t* pre = prm.rec + lo + r_rel + (int64_t)kS1Depth * kChunk;
-    int32_t c = 0, since = 0;  // since: packets added to the packed sums since the last flush
+    int32_t st = 0;
+    uint32_t ph = 0;
+    int32_t since = 0;  // packets added to the packed sums since the last flush
+    auto refill = [&]() {
+      if (lane == 0 && w_rel + stages * kChunk < hi_rel)
+        s1_bulk_fill(ring_w + (uint32_t)st * kS1WarpStage, rec_w + (int64_t)w_rel - (int64_t)warp * kSlice + (int64_t)stages * kChunk,
+                     bar_w + (uint32_t)st * 8);
+    };
+    auto score_packet = [&](const uint4 v) {
+      if (__all_sync(0xffffffffu, ((v.x ^ (v.w >> 16)) & 0xFF00u) == 0u)) {
+        s1p_packet_same_a<NP>(v, baseA, baseB, pstride, lutc, p32);
+      } else if (__all_sync(0xffffffffu, (v.w >> 24) - ((v.x >> 8) & 0xFFu) <= 1u)) {
+        s1p_packet_two_a<NP>(v, baseA, baseB, pstride, lutc, p32);
+      } else {
+        const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int k = 0; k < kPacket; ++k) {
+          const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
+          s1p_eval<NP>(baseA, baseB, pstride, s_lut, r, a32);
+        }
+      }
+      if (++since == kS1pFlush) {  // warp-uniform
+        s1p_flush<NP>(p32, a32);
+        since = 0;
+      }
+    };
+    int32_t c = 0;
 #pragma unroll 1
     while (c < nchunks) {
-      if (w_rel < hi_rel && w_rel + (int32_t)kSlice > lim_rel) {   // next tile (or the first one)
+      if (w_rel < hi_rel && w_rel + kSlice > lim_rel) {   // next tile (or the first one)
         cur.advance_to(lo + w_rel, prm.tile_start, prm.nblk);
         lim_rel = (int32_t)(min(hi, cur.end) - lo);
         baseA = sbase + (uint32_t)cur.I * (kBlk * 4);
         baseB = sbase + (uint32_t)cur.J * (kBlk * 4);
       }
       int32_t nrun = 0;
-      if (w_rel + (int32_t)kSlice <= lim_rel) nrun = min((lim_rel - (int32_t)kSlice - w_rel) / (int32_t)kChunk + 1, nchunks - c);
-      if (nrun == 0) {  // the slice crosses a tile boundary or the end of the share: per-lane tile cursor
-        cp_async_wait<kS1Depth - 1>();
-        const uint32_t slot = my_slot + (uint32_t)(c & (kS1Depth - 1)) * kS1Stage;
-        const uint4 v = lds_v4(slot);
-        cp_async16_zfill(slot, pre, r_rel + kS1Depth * (int32_t)kChunk < hi_rel);
-        cp_async_commit();
-        if (r_rel < hi_rel) {
-          S1Tile mine = cur;
-          const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+      if (w_rel + kSlice <= lim_rel) nrun = min((lim_rel - kSlice - w_rel) / kChunk + 1, nchunks - c);
+      if (nrun == 0) {  // the slice crosses a tile boundary or the end of the share: packet by packet
+        if (w_rel < hi_rel) {
+          s1_bar_wait(bar_w + (uint32_t)st * 8, ph);
+          const uint32_t slot = ring_w + (uint32_t)st * kS1WarpStage + (uint32_t)lane * 16;
+#pragma unroll 1
+          for (int j = 0; j < kS1Sub; ++j) {
+            const int32_t ws = w_rel + j * kSub;
+            if (ws >= hi_rel) break;
+            if (ws >= lim_rel) {
+              cur.advance_to(lo + ws, prm.tile_start, prm.nblk);
+              lim_rel = (int32_t)(min(hi, cur.end) - lo);
+              baseA = sbase + (uint32_t)cur.I * (kBlk * 4);
+              baseB = sbase + (uint32_t)cur.J * (kBlk * 4);
+            }
+            const int32_t rr = ws + lane * kPacket;
+            const uint4 v = lds_v4(slot + (uint32_t)j * 512);
+            if (ws + kSub <= lim_rel) {
+              score_packet(v);
+            } else if (rr < hi_rel) {
+              S1Tile mine = cur;
+              const uint32_t words[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-          for (int k = 0; k < kPacket; ++k) {
-            if (r_rel + k < hi_rel) {
-              mine.advance_to(lo + r_rel + k, prm.tile_start, prm.nblk);
-              const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
-              s1p_eval<NP>(sbase + (uint32_t)mine.I * (kBlk * 4), sbase + (uint32_t)mine.J * (kBlk * 4), pstride, s_lut,
-                           r, a32);
+              for (int k = 0; k < kPacket; ++k) {
+                if (rr + k < hi_rel) {
+                  mine.advance_to(lo + rr + k, prm.tile_start, prm.nblk);
+                  const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
+                  s1p_eval<NP>(sbase + (uint32_t)mine.I * (kBlk * 4), sbase + (uint32_t)mine.J * (kBlk * 4), pstride, s_lut,
+                               r, a32);
+                }
+              }
             }
           }
+          fence_proxy_async();
+          __syncwarp();
+          refill();
         }
         ++c;
-        w_rel += (int32_t)kChunk;
-        r_rel += (int32_t)kChunk;
-        pre += kChunk;
+        w_rel += kChunk;
+        if (++st == stages) { st = 0; ph ^= 1u; }
         continue;
       }
       const int32_t c_end = c + nrun;
-      const int32_t r_pf_end = hi_rel - kS1Depth * (int32_t)kChunk;
 #pragma unroll 1
       for (; c < c_end; ++c) {
-        cp_async_wait<kS1Depth - 1>();
-        const uint32_t slot = my_slot + (uint32_t)(c & (kS1Depth - 1)) * kS1Stage;
-        const uint4 v = lds_v4(slot);
-        const bool one_a = __all_sync(0xffffffffu, ((v.x ^ (v.w >> 16)) & 0xFF00u) == 0u);
-        cp_async16_zfill(slot, pre, r_rel < r_pf_end);
-        cp_async_commit();
-        if (one_a) {
-          s1p_packet_same_a<NP>(v, baseA, baseB, pstride, lutc, p32);
-        } else if (__all_sync(0xffffffffu, (v.w >> 24) - ((v.x >> 8) & 0xFFu) <= 1u)) {
-          s1p_packet_two_a<NP>(v, baseA, baseB, pstride, lutc, p32);
-        } else {
-          const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+        s1_bar_wait(bar_w + (uint32_t)st * 8, ph);
+        const uint32_t slot = ring_w + (uint32_t)st * kS1WarpStage + (uint32_t)lane * 16;
 #pragma unroll
-          for (int k = 0; k < kPacket; ++k) {
-            const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
-            s1p_eval<NP>(baseA, baseB, pstride, s_lut, r, a32);
+        for (int j = 0; j < kS1Sub; ++j) {
+          const uint4 v = lds_v4(slot + (uint32_t)j * 512);
+          const bool one_a = __all_sync(0xffffffffu, ((v.x ^ (v.w >> 16)) & 0xFF00u) == 0u);
+          if (j == kS1Sub - 1) refill();   // the slot's last packet is in registers (the vote consumed it)
+          if (one_a) {
+            s1p_packet_same_a<NP>(v, baseA, baseB, pstride, lutc, p32);
+          } else if (__all_sync(0xffffffffu, (v.w >> 24) - ((v.x >> 8) & 0xFFu) <= 1u)) {
+            s1p_packet_two_a<NP>(v, baseA, baseB, pstride, lutc, p32);
+          } else {
+            const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int k = 0; k < kPacket; ++k) {
+              const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
+              s1p_eval<NP>(baseA, baseB, pstride, s_lut, r, a32);
+            }
           }
         }
-        if (++since == kS1pFlush) {  // warp-uniform
+        since += kS1Sub;
+        if (since >= kS1pFlush) {  // warp-uniform; kS1pFlush is a multiple of kS1Sub away from overflow
           s1p_flush<NP>(p32, a32);
           since = 0;
         }
-        r_rel += (int32_t)kChunk;
-        pre += kChunk;
+        w_rel += kChunk;
+        if (++st == stages) { st = 0; ph ^= 1u; }
       }
-      w_rel += nrun * (int32_t)kChunk;
     }
   }
-  cp_async_wait<0>();
   S1_STAMP(2);
   s1p_flush<NP>(p32, a32);
+  if (NC <= 2 && prm.validate) {
+    bool miss = false;
+#pragma unroll
+    for (int c = 0; c < NC; ++c) miss |= (vgot[c] != i0 + tid);
+    if (miss) atomicOr(prm.flag, 2);
+  }
 
   // ---- warp shuffle tree, then a fixed-order sum over the warps ----
 #pragma unroll
@@ -291,9 +436,9 @@ __global__ void __launch_bounds__(kS1Threads, kS1MinBlocks) k_scaff_stream1p(Str
   S1_STAMP(3);
 }
 
-inline size_t stream1p_smem(int nc, int n) {
+inline size_t stream1p_smem(int nc, int n, int stages = 2) {
   return (size_t)nc * ((n + kBlk - 1) & ~(kBlk - 1)) * 2 + 64 + (size_t)kLut2Words * 4 + (size_t)kS1Warps * nc * 8 + 16 +
-         1024 + (size_t)kS1Depth * kS1Stage;  // (alignment slack) table | lut | pair lut | warp sums | start tile | ring
+         1024 + (size_t)kS1Warps * stages * (kS1WarpStage + 8);  // (alignment slack) table | lut | pair lut | warp sums | start tile | ring | ring barriers
 }
 
 template <int NC>

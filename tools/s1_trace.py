@@ -45,6 +45,9 @@ with N.Context(0, path=N.PATH_STREAM) as ctx:
         print("  stream done", q(r[:, 2]))
         print("  end        ", q(r[:, 3]))
         print("  prologue   ", q(r[:, 1] - r[:, 0]))
+        if full[:, 5].max() > 0:
+            e = (full[:, 5:8] - t0) / 1000.0
+            print("    loads requested + ring filled", q(e[:, 0] - r[:, 0]), "\n    luts + tile stored", q(e[:, 1] - r[:, 0]), "\n    tables scattered", q(e[:, 2] - r[:, 0]))
         print("  stream     ", q(r[:, 2] - r[:, 1]))
         print("  epilogue   ", q(r[:, 3] - r[:, 2]))
         st = r[:, 2] - r[:, 1]
@@ -60,3 +63,6 @@ with N.Context(0, path=N.PATH_STREAM) as ctx:
         print("  smid -> stream us:", " ".join("%d:%.0f" % (k, np.mean(v)) for k, v in sorted(per_sm.items())))
         for b in range(2):
             print("  CTA", b, "warps done at (us):", " ".join("%.1f" % ((x - t0) / 1000.0) for x in wst[b] if x > 0))
+        worst = np.argsort(-st)[:4]
+        for b in worst:
+            print("  slowest CTA %d on SM %d: start %.1f table %.1f stream done %.1f end %.1f" % (b, smid[b], r[b, 0], r[b, 1], r[b, 2], r[b, 3]))
