@@ -114,6 +114,12 @@ constexpr int kS1PreP = 5120 / kS1Threads;                    // genes per threa
 constexpr int kS1pLutPieces = (int)(sizeof(S1pLuts) / 16);   // 544
 static_assert(sizeof(S1pLuts) % 16 == 0 && kS1pLutPieces <= 2 * kS1Threads, "lut pieces");
 
+__device__ __forceinline__ uint32_t s1_atom_inc(uint32_t addr_smem) {
+  uint32_t old;
+  asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(addr_smem) : "memory");
+  return old;
+}
+
 template <int NC>
 __global__ void __launch_bounds__(kS1Threads + (kS1MinBlocks == 2 && NC <= 2 ? 64 : 0), kS1MinBlocks) k_scaff_stream1p(Stream1Params prm) {
   typedef typename Acc<W_UNIT>::type acc_t;
@@ -147,6 +153,7 @@ __global__ void __launch_bounds__(kS1Threads + (kS1MinBlocks == 2 && NC <= 2 ? 6
   const uint32_t ring_w = smem_u32(s_tile + 2) + (uint32_t)warp * (uint32_t)(stages * kS1WarpStage);
   const uint32_t bar_w = smem_u32(s_tile + 2) + (uint32_t)(kS1Warps * stages * kS1WarpStage) + (uint32_t)warp * (uint32_t)(stages * 8);
   const uint16_t* rec_w = prm.rec + lo + (int64_t)warp * kSlice;
+  const uint32_t s_next = smem_u32(s_tile + 2) + (uint32_t)(kS1Warps * stages * (kS1WarpStage + 8));   // the CTA's slice counter
   const int32_t hi_rel = (int32_t)(hi - lo);
   const int64_t ntiles = (int64_t)prm.nblk * (prm.nblk + 1) / 2;
   auto fill_ring = [&]() {
@@ -157,6 +164,7 @@ __global__ void __launch_bounds__(kS1Threads + (kS1MinBlocks == 2 && NC <= 2 ? 6
       for (int q = 0; q < stages; ++q)
         if (warp * kSlice + (int64_t)q * kChunk < hi_rel)
           s1_bulk_fill(ring_w + q * kS1WarpStage, rec_w + (int64_t)q * kChunk, bar_w + q * 8);
+      if (warp == 0) asm volatile("st.shared.u32 [%0], %1;" ::"r"(s_next), "r"(kS1Warps * stages) : "memory");
     }
     __syncwarp();
   };
@@ -325,22 +333,65 @@ __global__ void __launch_bounds__(kS1Threads + (kS1MinBlocks == 2 && NC <= 2 ? 6
         since = 0;
       }
     };
-    int32_t c = 0;
-#pragma unroll 1
-    while (c < nchunks) {
-      if (w_rel < hi_rel && w_rel + kSlice > lim_rel) {   // next tile (or the first one)
-        cur.advance_to(lo + w_rel, prm.tile_start, prm.nblk);
-        lim_rel = (int32_t)(min(hi, cur.end) - lo);
-        baseA = sbase + (uint32_t)cur.I * (kBlk * 4);
-        baseB = sbase + (uint32_t)cur.J * (kBlk * 4);
-      }
-      int32_t nrun = 0;
-      if (w_rel + kSlice <= lim_rel) nrun = min((lim_rel - kSlice - w_rel) / kChunk + 1, nchunks - c);
-      if (nrun == 0) {  // the slice crosses a tile boundary or the end of the share: packet by packet
-        if (w_rel < hi_rel) {
-          s1_bar_wait(bar_w + (uint32_t)st * 8, ph);
-          const uint32_t slot = ring_w + (uint32_t)st * kS1WarpStage + (uint32_t)lane * 16;
-#pragma unroll 1
+    // Eight orderings (one CTA per SM, 16 warps): slices of the share are taken from the CTA's counter, so
+    // that all warps finish within one slice of each other (statically assigned the last warp finished up
+    // to 14 us after the first: 280 -> 258 us per pass).  With two CTAs per SM the run loop below is 4 us
+    // per pass faster than this per-slice loop and the warps' pace evens out by itself.
+    constexpr bool kDyn = NC >= 8;
+    if (kDyn) {
+      // slices of the share taken from the CTA's counter, as in k_scaff_stream1
+      const int32_t nslices = (hi_rel + kSlice - 1) / kSlice;
+      int32_t q0 = warp, q1 = warp + kS1Warps, q2 = warp + 2 * kS1Warps, q3 = warp + 3 * kS1Warps;
+      int32_t newest = warp + (stages - 1) * kS1Warps;
+      constexpr bool kDyn = NC >= 8;
+      uint32_t claimed = 0;
+      auto claim = [&]() {   // asked at the start of a slice, read when the slot is handed back
+        if (kDyn && lane == 0) claimed = s1_atom_inc(s_next);
+      };
+      auto hand_back = [&]() {   // whole warp, converged
+        const int32_t nxt = !kDyn ? newest + kS1Warps : (int32_t)__shfl_sync(0xffffffffu, claimed, 0);
+        if (lane == 0 && nxt < nslices)
+          s1_bulk_fill(ring_w + (uint32_t)st * kS1WarpStage, prm.rec + lo + (int64_t)nxt * kSlice, bar_w + (uint32_t)st * 8);
+        newest = nxt;
+      };
+  #pragma unroll 1
+      while (q0 < nslices) {
+        claim();
+        const int32_t w_rel = q0 * kSlice;
+        if (w_rel >= lim_rel) {   // the slice starts in a later tile (or is the first)
+          cur.advance_to(lo + w_rel, prm.tile_start, prm.nblk);
+          lim_rel = (int32_t)(min(hi, cur.end) - lo);
+          baseA = sbase + (uint32_t)cur.I * (kBlk * 4);
+          baseB = sbase + (uint32_t)cur.J * (kBlk * 4);
+        }
+        s1_bar_wait(bar_w + (uint32_t)st * 8, ph);
+        const uint32_t slot = ring_w + (uint32_t)st * kS1WarpStage + (uint32_t)lane * 16;
+        if (w_rel + kSlice <= lim_rel) {
+  #pragma unroll
+          for (int j = 0; j < kS1Sub; ++j) {
+            const uint4 v = lds_v4(slot + (uint32_t)j * 512);
+            const bool one_a = __all_sync(0xffffffffu, ((v.x ^ (v.w >> 16)) & 0xFF00u) == 0u);
+            if (j == kS1Sub - 1) hand_back();   // the slot's last packet is in registers (the vote consumed it)
+            if (one_a) {
+              s1p_packet_same_a<NP>(v, baseA, baseB, pstride, lutc, p32);
+            } else if (__all_sync(0xffffffffu, (v.w >> 24) - ((v.x >> 8) & 0xFFu) <= 1u)) {
+              s1p_packet_two_a<NP>(v, baseA, baseB, pstride, lutc, p32);
+            } else {
+              const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+  #pragma unroll
+              for (int k = 0; k < kPacket; ++k) {
+                const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
+                s1p_eval<NP>(baseA, baseB, pstride, s_lut, r, a32);
+              }
+            }
+          }
+          since += kS1Sub;
+          if (since >= kS1pFlush) {  // warp-uniform
+            s1p_flush<NP>(p32, a32);
+            since = 0;
+          }
+        } else {  // the slice crosses a tile boundary or the end of the share: packet by packet
+  #pragma unroll 1
           for (int j = 0; j < kS1Sub; ++j) {
             const int32_t ws = w_rel + j * kSub;
             if (ws >= hi_rel) break;
@@ -357,7 +408,7 @@ __global__ void __launch_bounds__(kS1Threads + (kS1MinBlocks == 2 && NC <= 2 ? 6
             } else if (rr < hi_rel) {
               S1Tile mine = cur;
               const uint32_t words[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
+  #pragma unroll
               for (int k = 0; k < kPacket; ++k) {
                 if (rr + k < hi_rel) {
                   mine.advance_to(lo + rr + k, prm.tile_start, prm.nblk);
@@ -370,44 +421,101 @@ __global__ void __launch_bounds__(kS1Threads + (kS1MinBlocks == 2 && NC <= 2 ? 6
           }
           fence_proxy_async();
           __syncwarp();
-          refill();
+          hand_back();
         }
-        ++c;
-        w_rel += kChunk;
+        q0 = q1;
+        q1 = stages > 2 ? q2 : newest;
+        q2 = stages > 3 ? q3 : newest;
+        q3 = newest;
         if (++st == stages) { st = 0; ph ^= 1u; }
-        continue;
       }
-      const int32_t c_end = c + nrun;
-#pragma unroll 1
-      for (; c < c_end; ++c) {
-        s1_bar_wait(bar_w + (uint32_t)st * 8, ph);
-        const uint32_t slot = ring_w + (uint32_t)st * kS1WarpStage + (uint32_t)lane * 16;
-#pragma unroll
-        for (int j = 0; j < kS1Sub; ++j) {
-          const uint4 v = lds_v4(slot + (uint32_t)j * 512);
-          const bool one_a = __all_sync(0xffffffffu, ((v.x ^ (v.w >> 16)) & 0xFF00u) == 0u);
-          if (j == kS1Sub - 1) refill();   // the slot's last packet is in registers (the vote consumed it)
-          if (one_a) {
-            s1p_packet_same_a<NP>(v, baseA, baseB, pstride, lutc, p32);
-          } else if (__all_sync(0xffffffffu, (v.w >> 24) - ((v.x >> 8) & 0xFFu) <= 1u)) {
-            s1p_packet_two_a<NP>(v, baseA, baseB, pstride, lutc, p32);
-          } else {
-            const uint32_t words[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-            for (int k = 0; k < kPacket; ++k) {
-              const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
-              s1p_eval<NP>(baseA, baseB, pstride, s_lut, r, a32);
+
+    } else {
+      int32_t c = 0;
+  #pragma unroll 1
+      while (c < nchunks) {
+        if (w_rel < hi_rel && w_rel + kSlice > lim_rel) {   // next tile (or the first one)
+          cur.advance_to(lo + w_rel, prm.tile_start, prm.nblk);
+          lim_rel = (int32_t)(min(hi, cur.end) - lo);
+          baseA = sbase + (uint32_t)cur.I * (kBlk * 4);
+          baseB = sbase + (uint32_t)cur.J * (kBlk * 4);
+        }
+        int32_t nrun = 0;
+        if (w_rel + kSlice <= lim_rel) nrun = min((lim_rel - kSlice - w_rel) / kChunk + 1, nchunks - c);
+        if (nrun == 0) {  // the slice crosses a tile boundary or the end of the share: packet by packet
+          if (w_rel < hi_rel) {
+            s1_bar_wait(bar_w + (uint32_t)st * 8, ph);
+            const uint32_t slot = ring_w + (uint32_t)st * kS1WarpStage + (uint32_t)lane * 16;
+  #pragma unroll 1
+            for (int j = 0; j < kS1Sub; ++j) {
+              const int32_t ws = w_rel + j * kSub;
+              if (ws >= hi_rel) break;
+              if (ws >= lim_rel) {
+                cur.advance_to(lo + ws, prm.tile_start, prm.nblk);
+                lim_rel = (int32_t)(min(hi, cur.end) - lo);
+                baseA = sbase + (uint32_t)cur.I * (kBlk * 4);
+                baseB = sbase + (uint32_t)cur.J * (kBlk * 4);
+              }
+              const int32_t rr = ws + lane * kPacket;
+              const uint4 v = lds_v4(slot + (uint32_t)j * 512);
+              if (ws + kSub <= lim_rel) {
+                score_packet(v);
+              } else if (rr < hi_rel) {
+                S1Tile mine = cur;
+                const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+  #pragma unroll
+                for (int k = 0; k < kPacket; ++k) {
+                  if (rr + k < hi_rel) {
+                    mine.advance_to(lo + rr + k, prm.tile_start, prm.nblk);
+                    const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
+                    s1p_eval<NP>(sbase + (uint32_t)mine.I * (kBlk * 4), sbase + (uint32_t)mine.J * (kBlk * 4), pstride, s_lut,
+                                 r, a32);
+                  }
+                }
+              }
+            }
+            fence_proxy_async();
+            __syncwarp();
+            refill();
+          }
+          ++c;
+          w_rel += kChunk;
+          if (++st == stages) { st = 0; ph ^= 1u; }
+          continue;
+        }
+        const int32_t c_end = c + nrun;
+  #pragma unroll 1
+        for (; c < c_end; ++c) {
+          s1_bar_wait(bar_w + (uint32_t)st * 8, ph);
+          const uint32_t slot = ring_w + (uint32_t)st * kS1WarpStage + (uint32_t)lane * 16;
+  #pragma unroll
+          for (int j = 0; j < kS1Sub; ++j) {
+            const uint4 v = lds_v4(slot + (uint32_t)j * 512);
+            const bool one_a = __all_sync(0xffffffffu, ((v.x ^ (v.w >> 16)) & 0xFF00u) == 0u);
+            if (j == kS1Sub - 1) refill();   // the slot's last packet is in registers (the vote consumed it)
+            if (one_a) {
+              s1p_packet_same_a<NP>(v, baseA, baseB, pstride, lutc, p32);
+            } else if (__all_sync(0xffffffffu, (v.w >> 24) - ((v.x >> 8) & 0xFFu) <= 1u)) {
+              s1p_packet_two_a<NP>(v, baseA, baseB, pstride, lutc, p32);
+            } else {
+              const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+  #pragma unroll
+              for (int k = 0; k < kPacket; ++k) {
+                const uint32_t r = (k & 1) ? (words[k >> 1] >> 16) : (words[k >> 1] & 0xFFFFu);
+                s1p_eval<NP>(baseA, baseB, pstride, s_lut, r, a32);
+              }
             }
           }
+          since += kS1Sub;
+          if (since >= kS1pFlush) {  // warp-uniform; kS1pFlush is a multiple of kS1Sub away from overflow
+            s1p_flush<NP>(p32, a32);
+            since = 0;
+          }
+          w_rel += kChunk;
+          if (++st == stages) { st = 0; ph ^= 1u; }
         }
-        since += kS1Sub;
-        if (since >= kS1pFlush) {  // warp-uniform; kS1pFlush is a multiple of kS1Sub away from overflow
-          s1p_flush<NP>(p32, a32);
-          since = 0;
-        }
-        w_rel += kChunk;
-        if (++st == stages) { st = 0; ph ^= 1u; }
       }
+
     }
   }
   S1_STAMP(2);
@@ -438,7 +546,7 @@ __global__ void __launch_bounds__(kS1Threads + (kS1MinBlocks == 2 && NC <= 2 ? 6
 
 inline size_t stream1p_smem(int nc, int n, int stages = 2) {
   return (size_t)nc * ((n + kBlk - 1) & ~(kBlk - 1)) * 2 + 64 + (size_t)kLut2Words * 4 + (size_t)kS1Warps * nc * 8 + 16 +
-         1024 + (size_t)kS1Warps * stages * (kS1WarpStage + 8);  // (alignment slack) table | lut | pair lut | warp sums | start tile | ring | ring barriers
+         1024 + (size_t)kS1Warps * stages * (kS1WarpStage + 8) + 16;  // (alignment slack) table | lut | pair lut | warp sums | start tile | ring | ring barriers | slice counter
 }
 
 template <int NC>
