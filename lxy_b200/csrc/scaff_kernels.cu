@@ -948,13 +948,20 @@ static int scaff_enqueue_passes(lxy_ctx* c, const int32_t* perm_dev, int32_t P, 
 static int scaff_enqueue_batch(lxy_ctx* c, const int32_t* perm_dev, int32_t P, double* out_dev,
                                int64_t* x100_dev, bool first, bool last);
 
-// Measured on B200 (tools/p_sweep.py, n = 5,000, unit weights; 5 M and 200 M records; L in millions of
-// records): a pass of <= 8 orderings costs about 26 + 1.27 L us on the packed kernel
-// (scaff_stream1p.cuh), one group of the batch kernel 48 + 13.8 L us up to 32 orderings, 48 + 14.5 L up
-// to 64, 48 + 17.9 L up to 128; a further group of a launch that already has full groups 17.9 L.
+// Measured on B200 (tools/p_sweep.py, n = 5,000, unit weights; 5 M, 50 M and 200 M records; L in
+// millions of records), after both kernels moved to the bulk-copy rings: a pass of <= 8 orderings on the
+// packed kernel (scaff_stream1p.cuh) costs 40 / 108 / 259 us = 33 + 1.5 L up to 50 M records and
+// 108 + 1.0 (L - 50) beyond; one group of the batch kernel 55 + 11.1 L us up to 32 orderings, 58 + 10.5 L up
+// to 64, 58 + 15.4 L up to 128; a further group of a launch that already has full groups 15.4 L.
 // The model is only consulted inside that regime (unit weights, packed kernel applicable); weighted
 // stores keep the single-pass rule (<= 8 orderings stream, everything else in groups).
-static double pass_cost_us(int32_t P, double l_m) { return (double)((P + 7) / 8) * (26.0 + 1.27 * l_m); }
+static double pass_cost_us(int32_t P, double l_m) {
+  return (double)((P + 7) / 8) * (l_m <= 50.0 ? 33.0 + 1.5 * l_m : 108.0 + 1.0 * (l_m - 50.0));
+}
+static double group_cost_us(int32_t P, double l_m) {   // one group of up to 128 orderings, its own launch
+  return P <= 32 ? 55.0 + 11.1 * l_m : P <= 64 ? 58.0 + 10.5 * l_m : 58.0 + 15.4 * l_m;
+}
+constexpr double kNextGroupUsPerM = 15.4;             // one more group in a launch that has full groups
 
 static int scaff_score_enqueue(lxy_ctx* c, const int32_t* perm_dev, int32_t P, double* out_dev,
                                int64_t* x100_dev) {
@@ -968,19 +975,18 @@ static int scaff_score_enqueue(lxy_ctx* c, const int32_t* perm_dev, int32_t P, d
                         stream1p_smem(kS1Pass, n) <= (size_t)c->max_smem_optin;
   // ---- streaming regime: up to 8 candidates per pass (a lone Score() call is a batch of one) ----
   // Small populations - the reference's own GA runs 40 orderings (scaff.go:94) - take several passes
-  // while the model says that wins: against 200 M records 16 orderings 2.80 -> 0.55 ms, 40 orderings
-  // 2.81 -> 1.34 ms, 96 orderings 3.6 -> 3.3 ms; at 5 M records passes win up to 24 orderings.
+  // while the model says that wins: against 200 M records 16 orderings 2.27 -> 0.52 ms, 40 orderings
+  // 2.15 -> 1.27 ms, 96 orderings 3.13 -> 3.03 ms; at 5 M records passes win up to 16 orderings.
   if (s1_ok && P <= kS1Pass) return scaff_enqueue_passes(c, perm_dev, P, out_dev, x100_dev, true, true);
   if (model_ok && P <= 128) {
-    const double batch_us = 48.0 + (P <= 32 ? 13.8 : P <= 64 ? 14.5 : 17.9) * l_m;
-    if (pass_cost_us(P, l_m) < batch_us) return scaff_enqueue_passes(c, perm_dev, P, out_dev, x100_dev, true, true);
+    if (pass_cost_us(P, l_m) < group_cost_us(P, l_m)) return scaff_enqueue_passes(c, perm_dev, P, out_dev, x100_dev, true, true);
   }
   // ---- whole groups of 128 through the batch kernel; what is left over (P mod 128: a GA generation
   // makes ~P +- 30 children) goes through passes when those cost less than one more group, which would
   // score 128 - rem identity paddings at full price (cfg3, 1,028 children: 9 groups -> 8 groups + one
-  // pass of 4, 30.8 -> 27.6 ms) ----
+  // pass of 4) ----
   const int32_t rem = P % 128;
-  if (model_ok && P > 128 && rem != 0 && pass_cost_us(rem, l_m) < 17.9 * l_m) {
+  if (model_ok && P > 128 && rem != 0 && pass_cost_us(rem, l_m) < kNextGroupUsPerM * l_m) {
     const int32_t full = P - rem;
     LXY_TRY(scaff_enqueue_batch(c, perm_dev, full, out_dev, x100_dev, true, false));
     return scaff_enqueue_passes(c, perm_dev + (size_t)full * n, rem, out_dev + full,

@@ -147,8 +147,8 @@ def test_stream1_full_size_single_genome_score(ctxs):
     assert cs.scaff_score_batch(true)[0] < cs.scaff_score_batch(rnd)[0]
 
 
-@pytest.mark.parametrize("n,L,P,passes", [(300, 1_000_000, 9, 2), (300, 1_000_000, 16, 2), (700, 6_000_000, 13, 2),
-                                          (700, 6_000_000, 24, 3), (5000, 6_000_000, 17, 3)])
+@pytest.mark.parametrize("n,L,P,passes", [(300, 3_000_000, 9, 2), (300, 3_000_000, 16, 2), (700, 6_000_000, 13, 2),
+                                          (700, 20_000_000, 24, 3), (5000, 20_000_000, 17, 3)])
 def test_small_populations_take_several_passes(ctxs, n, L, P, passes):
     """Populations above 8 run as passes of <= 8 orderings while that beats the batch kernel (the
     reference's own GA holds 40 orderings, scaff.go:94): same integers as the batch kernel and the
