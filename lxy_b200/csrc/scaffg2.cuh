@@ -394,6 +394,232 @@ __global__ void __launch_bounds__(kG2Threads, 1) k_scaffg2_score(G2Params prm) {
   }
 }
 
+// ---- k_scaffg2r_score: the same scorer with the records arriving through a per-warp ring of bulk copies ----
+#ifndef LXY_G2R_THREADS
+#define LXY_G2R_THREADS 1024
+#endif
+constexpr int kG2RThreads = LXY_G2R_THREADS;
+constexpr int kG2RWarps = kG2RThreads / 32;
+constexpr int kG2RingPackets = 16;                         // packets per ring slot
+constexpr int kG2SlotBytes = kG2RingPackets * 80;          // 16 B of records + 2 x 32 B of offsets per packet
+constexpr int kG2RSmem = kG2Smem + kG2RWarps * (2 * kG2SlotBytes + 16);
+__device__ __forceinline__ uint32_t g2_lds_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint2 g2_lds_v2(uint32_t addr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 g2_lds_v4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void g2_bar_wait(uint32_t bar_smem, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(bar_smem),
+      "r"(parity)
+      : "memory");
+}
+
+template <bool SH0>
+__global__ void __launch_bounds__(kG2RThreads, 1) k_scaffg2r_score(G2Params prm) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* sB = smem;
+  uint8_t* sFirstB = smem + kTab2;
+  uint32_t* s_lut2 = (uint32_t*)(sFirstB + kFirst2);
+  uint64_t* bar = (uint64_t*)(s_lut2 + ((kLutG2Words + 3) & ~3));
+  const uint32_t lut = smem_u32(s_lut2);
+  // per-warp record ring: two slots of kG2RingPackets packets (records | offsets a | offsets b) and their mbarriers
+  const uint32_t ring_w = smem_u32(bar + 8) + (uint32_t)(threadIdx.x >> 5) * (2 * kG2SlotBytes);
+  const uint32_t ring_bar = smem_u32(bar + 8) + (uint32_t)kG2RWarps * (2 * kG2SlotBytes) + (uint32_t)(threadIdx.x >> 5) * 16;
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < kLutG2Words; i += kG2RThreads) {
+    const int q1 = i / kLutG2Stride, q0 = i - q1 * kLutG2Stride;
+    s_lut2[i] = (q0 < kQ2 ? (uint32_t)c_lutg[q0] : 0u) | ((uint32_t)c_lutg[q1] << 16);
+  }
+  if (tid == 0) mbar_init(bar, 1);
+  if (lane == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(ring_bar) : "memory");
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(ring_bar + 8) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  uint32_t ring_ph = 0;   // bit s: phase of slot s's mbarrier
+  __syncthreads();
+  uint32_t parity = 0;
+
+  const int units = prm.groups * prm.splits;
+  const int64_t npk_all = (prm.L + kPacket - 1) / kPacket;
+  const int64_t ntiles = (int64_t)prm.nblk * (prm.nblk + 1) / 2;
+  for (int u = blockIdx.x; u < units; u += gridDim.x) {
+    const int g = u / prm.splits, s = u - g * prm.splits;
+    const int64_t lo = (npk_all * s / prm.splits) * kPacket;
+    const int64_t hi = min((npk_all * (s + 1) / prm.splits) * kPacket, prm.L);
+    G2Acc acc;
+    acc.clear();
+    int32_t loadedJ = -1;
+    if (lo < hi) {
+      int64_t tl = 0, th = ntiles;
+      while (th - tl > 1) {
+        const int64_t mid = (tl + th) >> 1;
+        if (prm.tile_start[mid] <= lo) tl = mid; else th = mid;
+      }
+      int64_t t = tl;
+      int32_t I = 0;
+      {
+        int32_t a = 0, b = prm.nblk;
+        while (b - a > 1) {
+          const int32_t m = (a + b) >> 1;
+          if (tile_row_start(m, prm.nblk) <= t) a = m; else b = m;
+        }
+        I = a;
+      }
+      int32_t J = I + (int32_t)(t - tile_row_start(I, prm.nblk));
+      int64_t cur = lo;
+      while (cur < hi) {
+        const int64_t tend = prm.tile_start[t + 1];
+        if (tend <= cur) {
+          ++t; ++J;
+          if (J == prm.nblk) { ++I; J = I; }
+          continue;
+        }
+        const int64_t seg_end = min(hi, tend);
+        if (J != loadedJ) {   // stage block J of the origin table, its first-bits and any-first bytes
+          __syncthreads();
+          if (tid == 0) {
+            const int rowsB = min(kBlk, prm.n - J * kBlk);
+            const size_t rb = (size_t)g * prm.n + (size_t)J * kBlk;
+            fence_proxy_async();
+            mbar_expect_tx(bar, (uint32_t)rowsB * (kRow2 + kFirstRow2));
+            tma_bulk_g2s(sB, prm.origin + rb * kCand2, (uint32_t)rowsB * kRow2, bar);
+            tma_bulk_g2s(sFirstB, prm.firstw + rb * 8, (uint32_t)rowsB * kFirstRow2, bar);
+          }
+          loadedJ = J;
+          mbar_wait(bar, parity);
+          parity ^= 1;
+        }
+        const size_t rowA0 = (size_t)g * prm.n + (size_t)I * kBlk;
+
+        const int64_t p_first = cur / kPacket, p_last = (seg_end - 1) / kPacket;
+        const bool head_partial = (p_first * kPacket < cur);
+        const bool tail_partial = ((p_last + 1) * kPacket > seg_end);
+        if (head_partial && warp == 0) {   // boundary packets: masked, one warp each
+          const int64_t base = p_first * kPacket;
+          const G2Packet pk = g2_load_packet(prm, base);
+          g2_eval_records<SH0>(pk, (int)(cur - base), (int)min((int64_t)kPacket, seg_end - base), rowA0, sB, sFirstB,
+                          lut, lane, prm, acc);
+          acc.flush16();
+        }
+        if (tail_partial && warp == 1 && !(head_partial && p_last == p_first)) {
+          const int64_t base = p_last * kPacket;
+          const G2Packet pk = g2_load_packet(prm, base);
+          g2_eval_records<SH0>(pk, 0, (int)(seg_end - base), rowA0, sB, sFirstB, lut, lane, prm, acc);
+          acc.flush16();
+        }
+        const int64_t f0 = p_first + (head_partial ? 1 : 0);
+        const int64_t f1 = p_last - (tail_partial ? 1 : 0);  // inclusive
+        const int64_t nfull = f1 - f0 + 1;
+        if (nfull > 0) {
+          // Every warp takes a contiguous run of the segment's packets, in slices of kG2RingPackets that arrive
+          // in its own two-slot ring (three bulk copies per slice: records, offsets a, offsets b, counted on
+          // the slot's mbarrier).  The packets are read from shared memory as they are scored, two records at a
+          // time (one word of records, two words of each offset: 5 registers), so a thread needs ~60
+          // registers instead of the 128 that two whole packets in flight took, and the SM holds 32 warps.
+          const int64_t w_lo = nfull * warp / kG2RWarps, w_hi = nfull * (warp + 1) / kG2RWarps;
+          const int64_t nsl = (w_hi - w_lo + kG2RingPackets - 1) / kG2RingPackets;
+          auto fill = [&](int64_t sl) {   // lane 0
+            const int64_t p0 = f0 + w_lo + sl * kG2RingPackets;               // first packet of the slice (absolute)
+            const uint32_t np = (uint32_t)min((int64_t)kG2RingPackets, w_hi - w_lo - sl * kG2RingPackets);
+            const uint32_t b = ring_bar + (uint32_t)(sl & 1) * 8, dst = ring_w + (uint32_t)(sl & 1) * kG2SlotBytes;
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(np * 80u) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                         "l"(prm.rec + p0 * kPacket), "r"(np * 16u), "r"(b) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst + kG2RingPackets * 16),
+                         "l"(prm.xa + p0 * kPacket), "r"(np * 32u), "r"(b) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst + kG2RingPackets * 48),
+                         "l"(prm.xb + p0 * kPacket), "r"(np * 32u), "r"(b) : "memory");
+          };
+          if (lane == 0) {
+            if (nsl > 0) fill(0);
+            if (nsl > 1) fill(1);
+          }
+          int32_t since = 0;
+#pragma unroll 1
+          for (int64_t sl = 0; sl < nsl; ++sl) {
+            const uint32_t sb = (uint32_t)(sl & 1);
+            g2_bar_wait(ring_bar + sb * 8, (ring_ph >> sb) & 1u);
+            ring_ph ^= 1u << sb;
+            const int32_t cnt = (int32_t)min((int64_t)kG2RingPackets, w_hi - w_lo - sl * kG2RingPackets);
+            const uint32_t s_rec = ring_w + sb * kG2SlotBytes, s_xa = s_rec + kG2RingPackets * 16, s_xb = s_rec + kG2RingPackets * 48;
+            // row a of a packet is requested one packet ahead (its index is the packet's first word, already in
+            // shared memory); the first packet of a slice waits for it
+            G2RowA RA = g2_load_row_a(prm, rowA0 + ((g2_lds_u32(s_rec) >> 8) & 0xFFu), lane);
+#pragma unroll 1
+            for (int32_t k = 0; k < cnt; ++k) {
+              const uint4 w = g2_lds_v4(s_rec + (uint32_t)k * 16);
+              G2RowA RN = RA;
+              if (k + 1 < cnt) RN = g2_load_row_a(prm, rowA0 + ((g2_lds_u32(s_rec + (uint32_t)(k + 1) * 16) >> 8) & 0xFFu), lane);
+              const uint32_t words[4] = {w.x, w.y, w.z, w.w};
+              if (((w.x >> 8) & 0xFFu) == (w.w >> 24)) {   // one a for the whole packet (warp-uniform)
+#pragma unroll
+                for (int h = 0; h < 4; ++h) {
+                  const uint2 xa2 = g2_lds_v2(s_xa + (uint32_t)k * 32 + (uint32_t)h * 8);
+                  const uint2 xb2 = g2_lds_v2(s_xb + (uint32_t)k * 32 + (uint32_t)h * 8);
+                  g2_eval<SH0>(RA, words[h] & 0xFFu, xa2.x, xb2.x, sB, sFirstB, lut, lane, prm, acc);
+                  g2_eval<SH0>(RA, (words[h] >> 16) & 0xFFu, xa2.y, xb2.y, sB, sFirstB, lut, lane, prm, acc);
+                }
+              } else {                                     // several a's: row a per record (L2)
+                uint32_t a_prev = 0xFFFFFFFFu;
+                G2RowA A;
+                A.e = make_int4(0, 0, 0, 0); A.fw = 0; A.any = 0;
+#pragma unroll 1
+                for (int r8 = 0; r8 < kPacket; ++r8) {
+                  const uint32_t r = (r8 & 1) ? (words[r8 >> 1] >> 16) : (words[r8 >> 1] & 0xFFFFu);
+                  const uint32_t a_loc = r >> 8;
+                  if (a_loc != a_prev) { A = g2_load_row_a(prm, rowA0 + a_loc, lane); a_prev = a_loc; }
+                  g2_eval<SH0>(A, r & 0xFFu, g2_lds_u32(s_xa + (uint32_t)k * 32 + (uint32_t)r8 * 4),
+                               g2_lds_u32(s_xb + (uint32_t)k * 32 + (uint32_t)r8 * 4), sB, sFirstB, lut, lane, prm, acc);
+                }
+              }
+              RA = RN;
+              if (++since == kG2Flush) { acc.flush16(); since = 0; }
+            }
+            // the slot's packets have all been read (their values were consumed): hand it back
+            __syncwarp();
+            if (lane == 0 && sl + 2 < nsl) fill(sl + 2);
+          }
+          acc.flush16();
+        }
+        cur = seg_end;
+      }
+    }
+    acc.flush16();
+    __syncthreads();
+    loadedJ = -1;                        // the table area is reused by the reduction
+    int64_t* red = (int64_t*)smem;       // [kG2RWarps][2][128]
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      red[(warp * 2 + 0) * kCand2 + lane * 4 + j] = acc.s32[j];
+      red[(warp * 2 + 1) * kCand2 + lane * 4 + j] = acc.h32[j];
+    }
+    __syncthreads();
+    if (tid < 2 * kCand2) {
+      int64_t sum = 0;
+      for (int wq = 0; wq < kG2RWarps; ++wq) sum += red[wq * 2 * kCand2 + tid];
+      prm.partial[(size_t)u * 2 * kCand2 + tid] = sum;
+    }
+  }
+}
+
 __global__ void k_scaffg2_finish(int32_t P, int32_t splits, const int64_t* __restrict__ partial,
                                  double* __restrict__ out, int64_t* __restrict__ x100) {
   const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
