@@ -414,14 +414,17 @@ def time_path(job, cx, dev_call, host_call, steps, warmup, sample_clocks=False):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(stream)
     tms = {"ms_score": [], "ms_layout": [], "ms_finish": []}
-    launches = 0
+    # The calls queue back to back: the library's own event times are read once, after the K steps (reading
+    # them per step waits for the step).  A context with LXY_FLAG_DEFER_ERRORS does not wait for its
+    # validation flags either; cx.sync() below reports them (and raises if any step saw a bad row).
     for _ in range(steps):
         dev_call()
-        t = cx.timing()
-        for k in tms:
-            tms[k].append(t[k])
-        launches += t["launches"]
     ev1.record(stream)
+    cx.sync()
+    t = cx.timing()
+    for k in tms:
+        tms[k].append(t[k])
+    launches = t["launches"] * steps
     job.bracket()
     clk = sampler.stop() if sampler else None
     ms_d = ev0.elapsed_time(ev1)
@@ -435,8 +438,14 @@ def time_path(job, cx, dev_call, host_call, steps, warmup, sample_clocks=False):
     job.bracket()
     ms_h = 1e3 * (time.perf_counter() - t0)
     ms_d, ms_h = job.max_over_ranks(ms_d, ms_h)
+    by_rank = None
+    if job.dist is not None:   # every rank's own kernel time: the step waits for the slowest (collective per step)
+        mine = torch.tensor([float(np.mean(tms["ms_score"]))], dtype=torch.float64, device=job.dev)
+        allr = [torch.zeros_like(mine) for _ in range(job.world)]
+        job.dist.all_gather(allr, mine)
+        by_rank = [round(float(t.item()), 4) for t in allr]
     return {"ms_dev": ms_d, "ms_e2e": ms_h, "launches": launches, "clocks": clk, "last": last,
-            "kernel_ms": {k: float(np.mean(v)) for k, v in tms.items()}}
+            "kernel_ms": {k: float(np.mean(v)) for k, v in tms.items()}, "ms_score_by_rank": by_rank}
 
 
 def check_multi_gpu(job, name, ctx, link_mode, n, L_loc, P, a, b, perms_all, perm_dev, x100_dev, seed):
@@ -522,7 +531,10 @@ def run_scoring(job, name, steps, warmup, sample_clocks, check):
     perms_all = gen_population(n, P, pseed, order.cpu().numpy())
     perms = pinned(perms_all)
     torch.cuda.synchronize()
-    ctx = N.Context(job.local, path=N.PATH_STREAM)   # the raw record stream: what `value` is defined on
+    # the raw record stream: what `value` is defined on.  LXY_FLAG_DEFER_ERRORS: the device-pointer calls of the
+    # timed region run their on-device validation every step and hand its verdict to the one lxy_ctx_sync()
+    # after the K steps; the host-buffer calls of the e2e leg wait for results and errors as always
+    ctx = N.Context(job.local, path=N.PATH_STREAM, flags=N.FLAG_DEFER_ERRORS)
     t0 = time.perf_counter()
     ctx.set_links_dev(n, L_loc, a.data_ptr(), b.data_ptr(), None)
     t_build = time.perf_counter() - t0
@@ -903,7 +915,9 @@ def main():
                        "population_per_gpu": P_loc, "records_per_gpu": L_loc,
                        "l2_policy": f"inputs larger than L2 ({2 * L_loc / 1e6:.0f} MB of records per pass)"
                                     if 2 * L_loc > 130e6 else "records fit L2; no flush (steady-state GA loop)",
-                       "link_store_build_s": round(R["t_build"], 3)},
+                       "link_store_build_s": round(R["t_build"], 3),
+                       "validation": "every step runs the on-device permutation check; `value`: its verdict is read "
+                                     "by one lxy_ctx_sync() after the K steps (LXY_FLAG_DEFER_ERRORS); `e2e`: per call"},
             "candidates_per_sec": P * args.steps / (ms_dev * 1e-3),
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                     "candidates_per_sec": P * args.steps / (ms_e2e * 1e-3),
@@ -913,6 +927,7 @@ def main():
             "gpu_launches": int(launches),
             "kernel_ms": {"k_scaff_score": k_ms, "layout+check": main_t["kernel_ms"]["ms_layout"],
                           "head+finish": main_t["kernel_ms"]["ms_finish"]},
+            "k_scaff_score_ms_by_rank": main_t.get("ms_score_by_rank"),
             "roofline": roofline,
             "clocks": clocks,
         }

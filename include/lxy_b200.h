@@ -47,6 +47,13 @@ typedef enum lxy_status {
                                    (default: the lane = record streaming kernel, HBM-bound)     */
 
 #define LXY_FLAG_NO_GRAPH 8u    /* never replay a repeated scoring call from a captured CUDA graph */
+#define LXY_FLAG_DEFER_ERRORS 16u /* device-pointer scoring calls (lxy_*_dev) do not wait for their validation  \
+                                     result: the on-device checks still run in every call, their flags are        \
+                                     copied to the host asynchronously and reported by the next lxy_ctx_sync()    \
+                                     (LXY_ERR_BAD_GENE / LXY_ERR_RANGE for "one of the calls since the last       \
+                                     sync").  Calls then queue back to back on the context's stream, as CUDA's    \
+                                     own asynchronous errors do; host-buffer entry points return results and    \
+                                     therefore errors synchronously as before. */
 
 /* which kernels score the R-profile (lxy_scaff_score_batch*); every path returns the same integers */
 #define LXY_PATH_AUTO 0   /* default (a zero-initialised lxy_cfg): chosen at lxy_ctx_set_links* from what is  \

@@ -51,6 +51,7 @@ ABI_VERSION = 2
 FLAG_NO_VALIDATE = 1
 FLAG_NO_STREAM1 = 2
 FLAG_NO_GRAPH = 8
+FLAG_DEFER_ERRORS = 16
 
 
 class LxyError(RuntimeError):

@@ -96,6 +96,41 @@ static float ev_ms(cudaEvent_t a, cudaEvent_t b) {
 
 }  // namespace lxy
 
+namespace lxy {
+static int flags_to_status(int flag, const char* what, const char* where) {
+  if (flag & 1) { set_error("%s: gene value outside [0, n)%s", what, where); return LXY_ERR_BAD_GENE; }
+  if (flag & 2) { set_error("%s: a population row is not a permutation%s", what, where); return LXY_ERR_BAD_GENE; }
+  if (flag & 4) { set_error("%s: placement offsets overflow the device format%s", what, where); return LXY_ERR_RANGE; }
+  return LXY_OK;
+}
+constexpr int kDeferredSlots = 64;
+int report_deferred_flags(lxy_ctx* c) {   // the stream has been synchronised
+  int all = 0;
+  for (int i = 0; i < c->n_deferred; ++i) all |= c->h_deferred[i];
+  const int n = c->n_deferred;
+  c->n_deferred = 0;
+  if (!all) return LXY_OK;
+  char where[96];
+  snprintf(where, sizeof where, " (deferred: in one of the %d scoring calls since the last sync)", n);
+  return flags_to_status(all, "scoring", where);
+}
+int read_flags(lxy_ctx* c, const char* what, const char* where) {
+  if (c->cfg.flags & LXY_FLAG_DEFER_ERRORS) {
+    if (!c->h_deferred) LXY_CUDA(cudaMallocHost((void**)&c->h_deferred, sizeof(int) * kDeferredSlots));
+    if (c->n_deferred == kDeferredSlots) {   // every slot holds an unreported call: report them first
+      LXY_CUDA(cudaStreamSynchronize(c->stream));
+      LXY_TRY(report_deferred_flags(c));
+    }
+    LXY_CUDA(cudaMemcpyAsync(&c->h_deferred[c->n_deferred++], c->d_flag.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    return LXY_OK;
+  }
+  int flag = 0;
+  LXY_CUDA(cudaMemcpyAsync(&flag, c->d_flag.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  LXY_CUDA(cudaStreamSynchronize(c->stream));
+  return flags_to_status(flag, what, where);
+}
+}  // namespace lxy
+
 // The scorer of the context's R-profile store: the dense pair table when the store has one
 // (LXY_PATH_PAIRS, or LXY_PATH_AUTO's choice), else the record stream.
 namespace lxy {
@@ -198,6 +233,7 @@ void lxy_ctx_destroy(lxy_ctx* c) {
                     &c->d_posA, &c->d_posB, &c->d_partial, &c->d_corr, &c->d_flag, &c->d_genes,
                     &c->d_gbits, &c->d_tmp0, &c->d_tmp1, &c->d_tmp2, &c->d_tmp3, &c->d_start, &c->d_shard, &c->d_gather};
   for (DevBuf* b : bufs) b->release();
+  if (c->h_deferred) cudaFreeHost(c->h_deferred);
   if (c->h_pin) cudaFreeHost(c->h_pin);
   for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
   lxy::drop_score_graphs(c);
@@ -230,7 +266,7 @@ int lxy_ctx_stream(lxy_ctx* c, void** s) {
 int lxy_ctx_sync(lxy_ctx* c) {
   CHECK_CTX(c);
   LXY_CUDA(cudaStreamSynchronize(c->stream));
-  return LXY_OK;
+  return report_deferred_flags(c);   // LXY_FLAG_DEFER_ERRORS: the validation results of the calls since the last sync
 }
 
 int lxy_ctx_path(lxy_ctx* c, int32_t* path, int64_t* stream_records) {
@@ -258,16 +294,16 @@ int lxy_ctx_set_links_dev(lxy_ctx* c, int32_t n_ids, int64_t n_links, const uint
   return build_scaff_links(c, in);
 }
 
+
+// Host-buffer entry points copy their results back and wait for them: their flags are read now.
 static int finish_flags(lxy_ctx* c, const char* what) {
   int flag = 0;
   LXY_CUDA(cudaMemcpyAsync(&flag, c->d_flag.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
   LXY_CUDA(cudaStreamSynchronize(c->stream));
-  if (flag & 1) { set_error("%s: gene value outside [0, n)", what); return LXY_ERR_BAD_GENE; }
-  if (flag & 2) { set_error("%s: a population row is not a permutation", what); return LXY_ERR_BAD_GENE; }
-  if (flag & 4) { set_error("%s: placement offsets overflow the device format", what); return LXY_ERR_RANGE; }
-  return LXY_OK;
+  return lxy::flags_to_status(flag, what, "");
 }
-
+// Device-pointer entry points: now, or deferred to lxy_ctx_sync (LXY_FLAG_DEFER_ERRORS).
+static int finish_flags_dev(lxy_ctx* c, const char* what) { return lxy::read_flags(c, what, ""); }
 
 
 int lxy_scaff_score_batch_dev(lxy_ctx* c, const int32_t* perm_dev, int32_t P, double* out_dev,
@@ -280,7 +316,7 @@ int lxy_scaff_score_batch_dev(lxy_ctx* c, const int32_t* perm_dev, int32_t P, do
   // With LXY_FLAG_NO_VALIDATE nothing has to come back to the host: the call is asynchronous on
   // the context's stream (lxy_ctx_sync / lxy_ctx_get_timing wait for it).
   if (c->cfg.flags & LXY_FLAG_NO_VALIDATE) return LXY_OK;
-  return finish_flags(c, "scaff score");
+  return finish_flags_dev(c, "scaff score");
 }
 
 int lxy_scaff_score_batch(lxy_ctx* c, const int32_t* perm, int32_t P, double* out, int64_t* x100) {
@@ -412,7 +448,7 @@ int lxy_scaffg_score_batch_dev(lxy_ctx* c, const int32_t* perm_dev, const uint8_
   LXY_TRY(scaffg_score(c, perm_dev, ori_dev, P, out_dev, x100_dev));
   c->timing_pending = 1;
   if (c->cfg.flags & LXY_FLAG_NO_VALIDATE) return LXY_OK;
-  return finish_flags(c, "scaffg score");
+  return finish_flags_dev(c, "scaffg score");
 }
 
 int lxy_scaffg_layout(lxy_ctx* c, const int32_t* perm, int32_t P, uint64_t* start_by_pos,
@@ -478,7 +514,7 @@ int lxy_phase_score_batch_dev(lxy_ctx* c, const uint8_t* genes_dev, int32_t P, i
   LXY_TRY(phase_score(c, genes_dev, P, out_i64_dev, out_f64_dev));
   c->timing_pending = 1;
   if (c->cfg.flags & LXY_FLAG_NO_VALIDATE) return LXY_OK;
-  return finish_flags(c, "phase score");
+  return finish_flags_dev(c, "phase score");
 }
 
 int lxy_phase_score_batch(lxy_ctx* c, const uint8_t* genes, int32_t P, int64_t* out_i64,

@@ -148,7 +148,8 @@ __global__ void k_links_finish_f64(int32_t P, int32_t world, const double* __res
   if (x100) x100[p] = INT64_MIN;
 }
 
-int check_flags(lxy_ctx* c, const char* what) {
+int check_flags(lxy_ctx* c, const char* what) { return read_flags(c, what, " (on some rank)"); }
+int check_flags_now(lxy_ctx* c, const char* what) {   // host-buffer entry points: results and errors are waited for
   int flag = 0;
   LXY_CUDA(cudaMemcpyAsync(&flag, c->d_flag.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
   LXY_CUDA(cudaStreamSynchronize(c->stream));
@@ -415,7 +416,7 @@ int lxy_scaff_score_sharded(lxy_ctx* c, int32_t mode, const int32_t* perm, int32
   LXY_CUDA(cudaMemcpyAsync(hout + 8 * (size_t)P, c->d_x100.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, st));
   LXY_CUDA(cudaEventRecord(c->ev[5], st));
   c->timing_pending = 2;
-  LXY_TRY(check_flags(c, "sharded scaff score"));   // synchronises; the flags are checked even with NO_VALIDATE (they are then 0)
+  LXY_TRY(check_flags_now(c, "sharded scaff score"));   // synchronises; the flags are checked even with NO_VALIDATE (they are then 0)
   std::memcpy(out, hout, 8 * (size_t)P);
   if (x100) std::memcpy(x100, hout + 8 * (size_t)P, 8 * (size_t)P);
   return LXY_OK;

@@ -130,6 +130,8 @@ struct lxy_ctx {
   // per-call scratch
   lxy::DevBuf d_perm, d_ori, d_out, d_x100, d_posA, d_posB, d_partial, d_corr, d_flag, d_genes,
       d_gbits, d_tmp0, d_tmp1, d_tmp2, d_tmp3, d_start;
+  int* h_deferred = nullptr;  // pinned: validation flags of calls not yet reported (LXY_FLAG_DEFER_ERRORS)
+  int n_deferred = 0;
   void* h_pin = nullptr;      // pinned staging for populations / scores
   size_t h_pin_cap = 0;
   // multi-GPU (comm.cu): NCCL communicator of this context's device, collectives run on `stream`
@@ -145,6 +147,10 @@ namespace lxy {
 // (two contexts of one device may be driven from two threads; the context mutex does not cover them).
 std::mutex& config_mutex();
 int pin_reserve(lxy_ctx* c, size_t bytes);
+// Validation flags of the call just queued: read back now (a host sync) or, with LXY_FLAG_DEFER_ERRORS,
+// copied asynchronously and reported by report_deferred_flags() (lxy_ctx_sync).
+int read_flags(lxy_ctx* c, const char* what, const char* where);
+int report_deferred_flags(lxy_ctx* c);
 void drop_score_graphs(lxy_ctx* c);
 // timing event k of the context on its main stream; inside a capture the record must be an
 // "external" one to become a node whose time stamp can be read after the graph ran

@@ -235,3 +235,41 @@ def test_packed_phasing_from_page_locked_memory_uploads_in_slices(P):
         _, exact2 = O.phase_score_links_batch(n, pa, pb, pw, g2, nthreads=8)
         assert c.phase_score_batch_bits(flipped)[0].tolist() == exact2.tolist()
         assert c.phase_score_batch_bits(words)[0].tolist() == exact.tolist()
+
+
+def test_deferred_errors_are_reported_by_the_next_sync():
+    """LXY_FLAG_DEFER_ERRORS: device-pointer scoring calls queue back to back; the on-device validation
+    still runs in every call and its verdict comes with lxy_ctx_sync(), as one status for the calls since
+    the last sync.  Host-buffer calls on the same context keep reporting at once."""
+    torch = pytest.importorskip("torch")
+    n, L, P = 600, 200_000, 40
+    a, b, w = S.scaff_links(n, L, 12)
+    perms = S.scaff_population(n, P, 112)
+    _, ox100 = O.scaff_score_links_batch(n, a, b, w, perms, nthreads=4)
+    bad = perms.copy()
+    bad[7, 3] = bad[7, 4]
+    with N.Context(0, path=N.PATH_STREAM, flags=N.FLAG_DEFER_ERRORS) as c:
+        c.set_links(n, a, b, None)
+        good_d, bad_d = torch.from_numpy(perms).cuda(), torch.from_numpy(bad).cuda()
+        out = torch.zeros(P, dtype=torch.float64, device="cuda")
+        x = torch.zeros(P, dtype=torch.int64, device="cuda")
+        torch.cuda.synchronize()
+        for _ in range(3):                                      # good calls: nothing to report
+            c.scaff_score_batch_dev(good_d.data_ptr(), P, out.data_ptr(), x.data_ptr())
+        c.sync()
+        assert x.cpu().numpy().tolist() == ox100.tolist()
+        c.scaff_score_batch_dev(good_d.data_ptr(), P, out.data_ptr(), x.data_ptr())
+        c.scaff_score_batch_dev(bad_d.data_ptr(), P, out.data_ptr(), x.data_ptr())      # returns at once
+        c.scaff_score_batch_dev(good_d.data_ptr(), P, out.data_ptr(), x.data_ptr())
+        with pytest.raises(N.LxyError) as e:
+            c.sync()
+        assert e.value.status == -4 and "deferred" in str(e.value) and "3 scoring calls" in str(e.value)
+        c.sync()                                                # reported once
+        assert x.cpu().numpy().tolist() == ox100.tolist()       # the good call after the bad one is intact
+        for _ in range(70):                                     # more unreported calls than slots
+            c.scaff_score_batch_dev(good_d.data_ptr(), P, out.data_ptr(), x.data_ptr())
+        c.sync()
+        with pytest.raises(N.LxyError) as e:                    # host buffers: reported at once, as without the flag
+            c.scaff_score_batch(bad)
+        assert e.value.status == -4
+        assert c.scaff_score_batch(perms, want_x100=True)[1].tolist() == ox100.tolist()
