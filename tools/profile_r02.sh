@@ -14,7 +14,7 @@ run python tools/prof_workload.py r3 2 &&
       python tools/prof_workload.py r3 2 > $O/r02_ncu_r3.log 2>&1
 # 3. G-profile at config-3 size
 run python tools/prof_workload.py g3 2 &&
-  ncu --set full --clock-control none --import-source on -k regex:k_scaffg2_score -s 1 -c 1 -o $O/r02_k_scaffg2_score \
+  ncu --set full --clock-control none --import-source on -k regex:k_scaffg2r_score -s 1 -c 1 -o $O/r02_k_scaffg2_score \
       python tools/prof_workload.py g3 2 > $O/r02_ncu_g3.log 2>&1
 # 4. streaming regime, one and two orderings
 run python tools/prof_workload.py s1 5 &&
