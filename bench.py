@@ -653,11 +653,13 @@ def main():
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             reps = max(args.steps, 10)
-            kms = []
+            kms, tms_call = [], []
             e0.record(stream)
             for _ in range(reps):
                 call()
-                kms.append(ctx.timing()["ms_score"])
+                tt = ctx.timing()
+                kms.append(tt["ms_score"])
+                tms_call.append(tt["ms_total"])
             e1.record(stream)
             torch.cuda.synchronize()
             ms = e0.elapsed_time(e1) / reps
@@ -692,7 +694,10 @@ def main():
             if ps <= 4:
                 streaming[f"P{ps}"] = {"kernel": "k_scaff_stream1" if ps == 1 else "k_scaff_stream1p",
                                        "kernel_ms": k, "bytes": alg, "achieved_GBps": alg / (k * 1e-3) / 1e9,
-                                       "frac": frac, "call_ms_device": ms, "call_ms_device_no_validate": ms_nv}
+                                       "frac": frac, "call_ms_device": ms, "call_ms_device_no_validate": ms_nv,
+                                       # first to last CUDA event of one call, by the library's own events
+                                       # (call_ms_device also holds the host's turn-around between calls)
+                                       "call_ms_library_events": float(np.mean(tms_call))}
         nv_ctx.close()
         extras["streaming_regime"] = {
             "what": "lone Score() calls / tiny batches on the same resident link store: lane = record, "

@@ -21,7 +21,7 @@ rng5 = np.random.default_rng(5)
 perm = torch.from_numpy(np.stack([rng5.permutation(n) for _ in range(sP)]).astype(np.int32)).cuda()
 out = torch.zeros(8, dtype=torch.float64, device="cuda")
 torch.cuda.synchronize()
-with N.Context(0, path=N.PATH_STREAM) as ctx:
+with N.Context(0, path=N.PATH_STREAM, flags=int(os.environ.get("S1_FLAGS", "0"))) as ctx:
     ctx.set_links_dev(n, L, ta.data_ptr(), tb.data_ptr(), None)
     for _ in range(6):
         ctx.scaff_score_batch_dev(perm.data_ptr(), sP, out.data_ptr(), None)
