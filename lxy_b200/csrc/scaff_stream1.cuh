@@ -130,6 +130,18 @@ __device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
   return r;
 }
 
+// Right shifts as multiply-high by a power of two that the compiler cannot see (constant bank): the
+// stream phase is bound by the ALU pipe (80 % busy: LOP3, SHF, VIADDMNMX, IADD3), the FMA pipe idles at
+// 14 %, and IMAD.HI runs there.  c_s1_mul[k] = 2^(32 - k-th shift).
+__constant__ uint32_t c_s1_mul[4] = {1u << 17, 1u << 25, 1u << 18, 1u << 26};   // >> 15, >> 7 (stream1), >> 14, >> 6 (stream1p)
+__device__ __forceinline__ uint32_t s1_shr15(uint32_t w) { return w >> 15; }
+__device__ __forceinline__ uint32_t s1_shr7(uint32_t w) { return w >> 7; }
+__device__ __forceinline__ uint32_t lds_u8(uint32_t addr) {
+  uint32_t v;
+  asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+
 template <int WM>
 __device__ __forceinline__ void s1_acc(int32_t t, int32_t wi, double wd, int32_t& a32, int64_t& a64,
                                        double& ad) {
@@ -160,20 +172,21 @@ __device__ __forceinline__ void s1_packet_same_a(const uint4 v, uint32_t baseA, 
                                                  const int32_t (&wi)[kPacket], const double (&wd)[kPacket],
                                                  int32_t (&a32)[NC], int64_t (&a64)[NC], double (&ad)[NC]) {
   const uint32_t words[4] = {v.x, v.y, v.z, v.w};
-  const uint32_t oa = (v.x >> 7) & 0x1FEu;
+  const uint32_t oa = s1_shr7(v.x) & 0x1FEu;
+  const uint32_t lut2_s = smem_u32(lut2);
   int32_t pterm[NC];
 #pragma unroll
   for (int c = 0; c < NC; ++c) pterm[c] = (kBias + 1) - lds_s16((baseA + c * cstride) | oa);
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
-    const uint32_t o0 = (words[q] << 1) & 0x1FEu, o1 = (words[q] >> 15) & 0x1FEu;
+    const uint32_t o0 = (words[q] << 1) & 0x1FEu, o1 = s1_shr15(words[q]) & 0x1FEu;
 #pragma unroll
     for (int c = 0; c < NC; ++c) {
       const uint32_t bb = baseB + c * cstride;
       const int32_t v0 = __viaddmin_s32_relu(lds_s16(bb | o0), pterm[c], kMiss + 1);
       const int32_t v1 = __viaddmin_s32_relu(lds_s16(bb | o1), pterm[c], kMiss + 1);
       if (WM == W_UNIT) {
-        a32[c] += lut2[v0 * kS1LutSide + v1];
+        a32[c] += (int32_t)lds_u8(lut2_s + ((uint32_t)v0 * kS1LutSide + (uint32_t)v1));
       } else {
         s1_acc<WM>(lut[v0], wi[2 * q], wd[2 * q], a32[c], a64[c], ad[c]);
         s1_acc<WM>(lut[v1], wi[2 * q + 1], wd[2 * q + 1], a32[c], a64[c], ad[c]);
