@@ -130,12 +130,13 @@ __device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
   return r;
 }
 
-// Right shifts as multiply-high by a power of two that the compiler cannot see (constant bank): the
-// stream phase is bound by the ALU pipe (80 % busy: LOP3, SHF, VIADDMNMX, IADD3), the FMA pipe idles at
-// 14 %, and IMAD.HI runs there.  c_s1_mul[k] = 2^(32 - k-th shift).
-__constant__ uint32_t c_s1_mul[4] = {1u << 17, 1u << 25, 1u << 18, 1u << 26};   // >> 15, >> 7 (stream1), >> 14, >> 6 (stream1p)
-__device__ __forceinline__ uint32_t s1_shr15(uint32_t w) { return w >> 15; }
-__device__ __forceinline__ uint32_t s1_shr7(uint32_t w) { return w >> 7; }
+// The stream phase was bound by the ALU pipe (80 % busy: LOP3, SHF, VIADDMNMX, IADD3) while the FMA pipe idled
+// at 14 %.  Two changes move work across: the pair-table index is one multiply-add in front of an
+// address-only LDS (was IMAD + a three-input IADD3), and the row address of a word's second record is
+// PRMT + IMAD (byte * entry size + base, the entry size read from the constant bank so that it stays a
+// multiply) instead of SHF + LOP3: 77.8 -> 73.7 us for one ordering against 200 M records.  Right shifts as
+// IMAD.HI by 2^(32 - s) were measured too (half-rate on that pipe): 79.9 us, not kept.
+__constant__ uint32_t c_s1_mul[6] = {0u, 0u, 0u, 0u, 2u, 4u};   // [4], [5]: table entry sizes (k_scaff_stream1, k_scaff_stream1p)
 __device__ __forceinline__ uint32_t lds_u8(uint32_t addr) {
   uint32_t v;
   asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
@@ -172,19 +173,20 @@ __device__ __forceinline__ void s1_packet_same_a(const uint4 v, uint32_t baseA, 
                                                  const int32_t (&wi)[kPacket], const double (&wd)[kPacket],
                                                  int32_t (&a32)[NC], int64_t (&a64)[NC], double (&ad)[NC]) {
   const uint32_t words[4] = {v.x, v.y, v.z, v.w};
-  const uint32_t oa = s1_shr7(v.x) & 0x1FEu;
+  const uint32_t oa = (v.x >> 7) & 0x1FEu;
   const uint32_t lut2_s = smem_u32(lut2);
   int32_t pterm[NC];
 #pragma unroll
   for (int c = 0; c < NC; ++c) pterm[c] = (kBias + 1) - lds_s16((baseA + c * cstride) | oa);
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
-    const uint32_t o0 = (words[q] << 1) & 0x1FEu, o1 = s1_shr15(words[q]) & 0x1FEu;
+    const uint32_t o0 = (words[q] << 1) & 0x1FEu;
+    const uint32_t b1 = __byte_perm(words[q], 0u, 0x4442u);   // b of the second record, zero-extended (PRMT)
 #pragma unroll
     for (int c = 0; c < NC; ++c) {
       const uint32_t bb = baseB + c * cstride;
       const int32_t v0 = __viaddmin_s32_relu(lds_s16(bb | o0), pterm[c], kMiss + 1);
-      const int32_t v1 = __viaddmin_s32_relu(lds_s16(bb | o1), pterm[c], kMiss + 1);
+      const int32_t v1 = __viaddmin_s32_relu(lds_s16(b1 * c_s1_mul[4] + bb), pterm[c], kMiss + 1);
       if (WM == W_UNIT) {
         a32[c] += (int32_t)lds_u8(lut2_s + ((uint32_t)v0 * kS1LutSide + (uint32_t)v1));
       } else {
@@ -207,6 +209,7 @@ __device__ __forceinline__ void s1_packet_two_a(const uint4 v, uint32_t baseA, u
   const uint32_t words[4] = {v.x, v.y, v.z, v.w};
   const uint32_t oa0 = (v.x >> 7) & 0x1FEu, oa1 = (v.w >> 23) & 0x1FEu;
   const uint32_t rep = (v.x & 0xFF00u) * 0x00010001u;   // the first a at bits 8..15 and 24..31
+  const uint32_t lut2_s = smem_u32(lut2);
   int32_t p0[NC], p1[NC];
 #pragma unroll
   for (int c = 0; c < NC; ++c) {
@@ -217,14 +220,15 @@ __device__ __forceinline__ void s1_packet_two_a(const uint4 v, uint32_t baseA, u
   for (int q = 0; q < 4; ++q) {
     const uint32_t x = words[q] ^ rep;
     const bool f0 = (x & 0xFF00u) == 0u, f1 = (x & 0xFF000000u) == 0u;
-    const uint32_t o0 = (words[q] << 1) & 0x1FEu, o1 = (words[q] >> 15) & 0x1FEu;
+    const uint32_t o0 = (words[q] << 1) & 0x1FEu;
+    const uint32_t b1 = __byte_perm(words[q], 0u, 0x4442u);
 #pragma unroll
     for (int c = 0; c < NC; ++c) {
       const uint32_t bb = baseB + c * cstride;
       const int32_t v0 = __viaddmin_s32_relu(lds_s16(bb | o0), f0 ? p0[c] : p1[c], kMiss + 1);
-      const int32_t v1 = __viaddmin_s32_relu(lds_s16(bb | o1), f1 ? p0[c] : p1[c], kMiss + 1);
+      const int32_t v1 = __viaddmin_s32_relu(lds_s16(b1 * c_s1_mul[4] + bb), f1 ? p0[c] : p1[c], kMiss + 1);
       if (WM == W_UNIT) {
-        a32[c] += lut2[v0 * kS1LutSide + v1];
+        a32[c] += (int32_t)lds_u8(lut2_s + ((uint32_t)v0 * kS1LutSide + (uint32_t)v1));
       } else {
         s1_acc<WM>(lut[v0], wi[2 * q], wd[2 * q], a32[c], a64[c], ad[c]);
         s1_acc<WM>(lut[v1], wi[2 * q + 1], wd[2 * q + 1], a32[c], a64[c], ad[c]);

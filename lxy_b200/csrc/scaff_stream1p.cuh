@@ -36,12 +36,13 @@ __device__ __forceinline__ void s1p_packet_same_a(const uint4 v, uint32_t baseA,
   for (int j = 0; j < NP; ++j) A[j] = __vsub2(kS1pBias, lds_u32((baseA + j * pstride) | oa));
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
-    const uint32_t o0 = (words[q] << 2) & 0x3FCu, o1 = (words[q] >> 14) & 0x3FCu;
+    const uint32_t o0 = (words[q] << 2) & 0x3FCu;
+    const uint32_t b1 = __byte_perm(words[q], 0u, 0x4442u);   // PRMT + IMAD instead of SHF + LOP3 (see scaff_stream1.cuh)
 #pragma unroll
     for (int j = 0; j < NP; ++j) {
       const uint32_t bb = baseB + j * pstride;
       p32[j] += s1p_pair(A[j], lds_u32(bb | o0), lutc);
-      p32[j] += s1p_pair(A[j], lds_u32(bb | o1), lutc);
+      p32[j] += s1p_pair(A[j], lds_u32(b1 * c_s1_mul[5] + bb), lutc);
     }
   }
 }
@@ -63,12 +64,13 @@ __device__ __forceinline__ void s1p_packet_two_a(const uint4 v, uint32_t baseA, 
   for (int q = 0; q < 4; ++q) {
     const uint32_t x = words[q] ^ rep;
     const bool f0 = (x & 0xFF00u) == 0u, f1 = (x & 0xFF000000u) == 0u;
-    const uint32_t o0 = (words[q] << 2) & 0x3FCu, o1 = (words[q] >> 14) & 0x3FCu;
+    const uint32_t o0 = (words[q] << 2) & 0x3FCu;
+    const uint32_t b1 = __byte_perm(words[q], 0u, 0x4442u);
 #pragma unroll
     for (int j = 0; j < NP; ++j) {
       const uint32_t bb = baseB + j * pstride;
       p32[j] += s1p_pair(f0 ? A0[j] : A1[j], lds_u32(bb | o0), lutc);
-      p32[j] += s1p_pair(f1 ? A0[j] : A1[j], lds_u32(bb | o1), lutc);
+      p32[j] += s1p_pair(f1 ? A0[j] : A1[j], lds_u32(b1 * c_s1_mul[5] + bb), lutc);
     }
   }
 }
