@@ -50,5 +50,34 @@ for case in range(cases):
     except Exception as e:   # noqa: BLE001
         fails += 1
         print("FAIL case", case, dict(n=n, L=len(a), P=P, w=wm, flags=flags), repr(e)[:200], flush=True)
+# ---- G-profile (lengths, orientations, in-contig offsets): unit weights take k_scaffg2r_score ----
+gcases = cases // 3
+for case in range(gcases):
+    n = int(rng.choice([2, 5, 60, 255, 257, 700, 3000]))
+    L = int(rng.choice([1, 8, 9, 127, 129, 2000, 4097, 50000, 300000]))
+    P = int(rng.choice([1, 3, 33, 64, 127, 128, 129, 200]))
+    unit = int(rng.choice([2, 3, 1000, 13972, 13973, 250000, 777777, 1 << 20]))
+    wm = str(rng.choice(["unit", "unit", "int"]))
+    seed = int(rng.integers(1, 1 << 30))
+    lens = S.contig_lengths(n, seed)
+    a, xa, b, xb, w = S.scaffg_links(n, L, seed, lens)
+    if len(a) == 0:
+        continue
+    if wm == "int":
+        w = rng.integers(1, 9, len(a)).astype(np.float64)
+    perms = S.scaff_population(n, P, seed + 1)
+    oris = S.orientations(n, P, seed) if rng.random() < 0.7 else None
+    want, ox100 = O.scaffg_score_links_batch(lens, unit, a, xa, b, xb, w, perms, oris, nthreads=8)
+    try:
+        with N.Context(0) as c:
+            c.set_links_g(lens, unit, a, xa, b, xb, None if wm == "unit" else w)
+            for rep in range(2):
+                got, x100 = c.scaffg_score_batch(perms, oris, want_x100=True)
+                if x100.tolist() != ox100.tolist():
+                    raise AssertionError("G scores differ (call %d)" % rep)
+    except Exception as e:   # noqa: BLE001
+        fails += 1
+        print("FAIL G case", case, dict(n=n, L=len(a), P=P, unit=unit, w=wm), repr(e)[:200], flush=True)
+cases += gcases
 print("stress_scaff: %d cases, %d failures" % (cases, fails))
 sys.exit(1 if fails else 0)
