@@ -153,8 +153,6 @@ struct ScoreParams {
   int64_t L;
   int32_t n, nblk;
   int32_t groups, splits;     // units = groups * splits
-  int32_t prefetch;           // ask the record stream into L2 ahead of the warps (few groups share it)
-  int32_t ring;               // records through the per-warp bulk-copy ring (contiguous packets per warp)
 };
 
 // Per-lane state of the streaming loop: CPL candidates, their running sums.
@@ -375,7 +373,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
   uint64_t* bar = (uint64_t*)(smem + 2 * TABB + 64 + 8 * kLutLen);
   uint32_t* s_lut2 = (uint32_t*)(smem + 2 * TABB + 64 + 8 * kLutLen + 16);  // [kLutLen][kLut2Stride]
   const uint32_t lut2 = smem_u32(s_lut2);
-  // per-warp record ring: two slots of kRingPackets packets and their mbarriers (prm.ring)
+  // per-warp record ring: two slots of kRingPackets packets and their mbarriers
   const uint32_t ring_w = smem_u32(s_lut2 + kLut2Words) + (uint32_t)(threadIdx.x >> 5) * (2 * kRingBytes);
   const uint32_t ring_bar = smem_u32(s_lut2 + kLut2Words) + (uint32_t)kWarps * (2 * kRingBytes) + (uint32_t)(threadIdx.x >> 5) * 16;
 
@@ -495,93 +493,53 @@ __global__ void __launch_bounds__(kThreads, 1) k_scaff_score(ScoreParams prm) {
         if (nfull > 0) {
           const uint16_t* recp = prm.rec + f0 * kPacket;
           const int64_t wbase = f0 * kPacket;
-          if (prm.ring) {
-            // Every warp takes a CONTIGUOUS run of the segment's packets, in slices of kRingPackets that
-            // arrive in its own two-slot ring, each by one bulk copy (UBLKCP) counted on the slot's
-            // mbarrier: a slice lasts the warp ~30 us, so the next one is in shared memory long before
-            // it is needed, with no other candidate group walking the same stretch (one group per GPU at
-            // 8 GPUs: 3.57 ms against 3.37 per group when four groups share the stream through L2).
-            const int64_t w_lo = nfull * warp / kWarps, w_hi = nfull * (warp + 1) / kWarps;
-            const int64_t nsl = (w_hi - w_lo + kRingPackets - 1) / kRingPackets;
-            auto fill = [&](int64_t sl) {   // lane 0
-              const int64_t p0 = w_lo + sl * kRingPackets;
-              const uint32_t bytes = (uint32_t)min((int64_t)kRingPackets, w_hi - p0) * 16u;
-              const uint32_t b = ring_bar + (uint32_t)(sl & 1) * 8, dst = ring_w + (uint32_t)(sl & 1) * kRingBytes;
-              asm volatile(
-                  "mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %3;\n\t"
-                  "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%1], [%2], %3, [%0];" ::"r"(b),
-                  "r"(dst), "l"(recp + p0 * kPacket), "r"(bytes)
-                  : "memory");
-            };
-            if (lane == 0) {
-              if (nsl > 0) fill(0);
-              if (nsl > 1) fill(1);
-            }
-            int32_t unflushed = 0;   // slices since the 32-bit sums went to 64 bits: 1024 * 64 * 8 * 100 < 2^31
-#pragma unroll 1
-            for (int64_t sl = 0; sl < nsl; ++sl) {
-              const uint32_t sb = (uint32_t)(sl & 1);
-              mbar_wait_u32(ring_bar + sb * 8, (ring_ph >> sb) & 1u);
-              ring_ph ^= 1u << sb;
-              const int64_t p0 = w_lo + sl * kRingPackets;
-              const int32_t cnt = (int32_t)min((int64_t)kRingPackets, w_hi - p0);
-              const uint32_t slot = ring_w + sb * kRingBytes + (uint32_t)lane * 4;
-              uint32_t mine_n = lane < 4 ? lds_u32s(slot) : 0u;
-#pragma unroll 1
-              for (int32_t k = 0; k < cnt; ++k) {
-                const uint4 v = warp_packet(mine_n, lane);
-                if (k + 1 < cnt && lane < 4) mine_n = lds_u32s(slot + (uint32_t)(k + 1) * 16);
-                load_weights<WM>(prm.w, wbase + (p0 + k) * kPacket, wi, wd);
-                if (((v.x >> 8) & 0xFFu) == (v.w >> 24))
-                  eval_packet<CPL, WIDE, WM, true>(v, laneA, laneB, lane_off, s_lut, s_lutd, lut2, wi, wd, 0, kPacket, acc);
-                else
-                  eval_packet<CPL, WIDE, WM, false>(v, laneA, laneB, lane_off, s_lut, s_lutd, lut2, wi, wd, 0, kPacket, acc);
-              }
-              // the slot's packets are all in registers (REDUX consumed the last one): hand it back
-              if (lane == 0 && sl + 2 < nsl) fill(sl + 2);
-              acc.flush16();   // kRingPackets * 8 * 100 < 2^16
-              if (++unflushed == 1024) { acc.flush(); unflushed = 0; }
-            }
-            acc.flush();
-          } else {
-            // chunks bound the int32 accumulators: 2^16 packets * 8 records * 100 < 2^31
-            for (int64_t c0 = 0; c0 < nfull; c0 += (int64_t)kWarps << 16) {
-              const int32_t cnt = (int32_t)min((int64_t)kWarps << 16, nfull - c0);
-              const uint16_t* rp = recp + c0 * kPacket;
-              int32_t it = warp;
-              uint32_t mine_n = 0;
-              if (it < cnt) mine_n = ldg_stream_word(rp + (size_t)it * kPacket, lane);
-              // A warp takes a packet every ~0.5 us and asks for it one round ahead, which does not cover a
-              // DRAM miss.  With 8 candidate groups the four groups that walk a stretch of the stream at the
-              // same time hide each other's misses in L2 (measured: a prefetch then only costs); with fewer
-              // groups the 128-byte line kPfAhead rounds further on is asked into L2.  Consecutive packets go
-              // to consecutive warps and kWarps is a multiple of 8, so warps 0, 8 and 16 between them see every
-              // line exactly once.  (A deeper register pipeline is slower: the loads share one scoreboard.)
-              static_assert(kWarps % 8 == 0, "a packet's line index must be fixed per warp");
-  #ifndef LXY_PF_AHEAD
-  #define LXY_PF_AHEAD 6
-  #endif
-              constexpr int kPfAhead = LXY_PF_AHEAD;
-              const bool pf_warp = prm.prefetch && (warp & 7) == 0;
-              int32_t since = 0;  // packets since the 16-bit pair sums were unpacked: 64 * 8 * 100 < 2^16
-  #pragma unroll 1
-              for (; it < cnt; it += kWarps) {
-                if (PairLut<CPL, WIDE, WM>::on && WM == W_UNIT && ++since == 64) { acc.flush16(); since = 0; }
-                const uint4 v = warp_packet(mine_n, lane);
-                if (it + kWarps < cnt) mine_n = ldg_stream_word(rp + (size_t)(it + kWarps) * kPacket, lane);
-                if (pf_warp && it + kPfAhead * kWarps < cnt)
-                  asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + (size_t)(it + kPfAhead * kWarps) * kPacket));
-                load_weights<WM>(prm.w, wbase + (c0 + it) * kPacket, wi, wd);
-                // sorted by (a, b): first a == last a  <=>  one a for the whole packet (warp-uniform)
-                if (((v.x >> 8) & 0xFFu) == (v.w >> 24))
-                  eval_packet<CPL, WIDE, WM, true>(v, laneA, laneB, lane_off, s_lut, s_lutd, lut2, wi, wd, 0, kPacket, acc);
-                else
-                  eval_packet<CPL, WIDE, WM, false>(v, laneA, laneB, lane_off, s_lut, s_lutd, lut2, wi, wd, 0, kPacket, acc);
-              }
-              acc.flush16();
-              acc.flush();
-            }
+          // Every warp takes a CONTIGUOUS run of the segment's packets, in slices of kRingPackets that
+          // arrive in its own two-slot ring, each by one bulk copy (UBLKCP) counted on the slot's
+          // mbarrier: a slice lasts the warp ~30 us, so the next one is in shared memory long before
+          // it is needed, with no other candidate group walking the same stretch (one group per GPU at
+          // 8 GPUs: 3.57 ms against 3.37 per group when four groups share the stream through L2).
+          const int64_t w_lo = nfull * warp / kWarps, w_hi = nfull * (warp + 1) / kWarps;
+          const int64_t nsl = (w_hi - w_lo + kRingPackets - 1) / kRingPackets;
+          auto fill = [&](int64_t sl) {   // lane 0
+            const int64_t p0 = w_lo + sl * kRingPackets;
+            const uint32_t bytes = (uint32_t)min((int64_t)kRingPackets, w_hi - p0) * 16u;
+            const uint32_t b = ring_bar + (uint32_t)(sl & 1) * 8, dst = ring_w + (uint32_t)(sl & 1) * kRingBytes;
+            asm volatile(
+                "mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %3;\n\t"
+                "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%1], [%2], %3, [%0];" ::"r"(b),
+                "r"(dst), "l"(recp + p0 * kPacket), "r"(bytes)
+                : "memory");
+          };
+          if (lane == 0) {
+            if (nsl > 0) fill(0);
+            if (nsl > 1) fill(1);
           }
+          int32_t unflushed = 0;   // slices since the 32-bit sums went to 64 bits: 1024 * 64 * 8 * 100 < 2^31
+#pragma unroll 1
+          for (int64_t sl = 0; sl < nsl; ++sl) {
+            const uint32_t sb = (uint32_t)(sl & 1);
+            mbar_wait_u32(ring_bar + sb * 8, (ring_ph >> sb) & 1u);
+            ring_ph ^= 1u << sb;
+            const int64_t p0 = w_lo + sl * kRingPackets;
+            const int32_t cnt = (int32_t)min((int64_t)kRingPackets, w_hi - p0);
+            const uint32_t slot = ring_w + sb * kRingBytes + (uint32_t)lane * 4;
+            uint32_t mine_n = lane < 4 ? lds_u32s(slot) : 0u;
+#pragma unroll 1
+            for (int32_t k = 0; k < cnt; ++k) {
+              const uint4 v = warp_packet(mine_n, lane);
+              if (k + 1 < cnt && lane < 4) mine_n = lds_u32s(slot + (uint32_t)(k + 1) * 16);
+              load_weights<WM>(prm.w, wbase + (p0 + k) * kPacket, wi, wd);
+              if (((v.x >> 8) & 0xFFu) == (v.w >> 24))
+                eval_packet<CPL, WIDE, WM, true>(v, laneA, laneB, lane_off, s_lut, s_lutd, lut2, wi, wd, 0, kPacket, acc);
+              else
+                eval_packet<CPL, WIDE, WM, false>(v, laneA, laneB, lane_off, s_lut, s_lutd, lut2, wi, wd, 0, kPacket, acc);
+            }
+            // the slot's packets are all in registers (REDUX consumed the last one): hand it back
+            if (lane == 0 && sl + 2 < nsl) fill(sl + 2);
+            acc.flush16();   // kRingPackets * 8 * 100 < 2^16
+            if (++unflushed == 1024) { acc.flush(); unflushed = 0; }
+          }
+          acc.flush();
         }
         cur = seg_end;
       }
@@ -1092,9 +1050,6 @@ static int scaff_enqueue_batch(lxy_ctx* c, const int32_t* perm_dev, int32_t P, d
   prm.nblk = S.nblk;
   prm.groups = groups;
   prm.splits = splits;
-  prm.prefetch = (groups <= 4 && 2 * S.L > ((int64_t)96 << 20)) ? 1 : 0;   // a stream that stays in L2 needs none
-  static const char* ring_env = getenv("LXY_RING");   // experiments: 0 = the round-2 register pipeline (+ L2 prefetch)
-  prm.ring = ring_env ? atoi(ring_env) : 1;
   int rc;
   if (tm == 1) {
     rc = S.wmode == W_UNIT ? launch_score_cpl<1, W_UNIT>(c, cpl, prm, grid)

@@ -5,8 +5,8 @@
 // (/root/reference/src/lxy/scaff/genome.go:153-159 -> scaff.go:246-310).  With a single candidate
 // there is no cross-candidate reuse of a record, so the pass is bound by HBM: every 2-byte record
 // is read once and scored once.  The mapping is therefore turned around with respect to
-// k_scaff_score: lane = record (8 consecutive records per lane per 128-bit load, a warp reads 512
-// contiguous bytes), and the whole placement table pos[] of each candidate (u16, n <= 65536) sits in
+// k_scaff_score: lane = record (8 consecutive records per lane per 128-bit shared-memory load; the
+// records arrive through a per-warp ring of 2 KB bulk copies), and the whole placement table pos[] of each candidate (u16, n <= 65536) sits in
 // shared memory for the lifetime of the CTA, built in the kernel from the ordering itself
 // (pos[perm[i]] = i: the exclusive prefix scan of unit lengths is the ordering index).
 //   per record:  d = |pos[a] - pos[b]|,  acc += 100*T[min(d, 21)]      (T of scaff.go:252-302)
@@ -20,25 +20,13 @@
 constexpr int kS1Threads = LXY_S1_THREADS;
 constexpr int kS1MinBlocks = kS1Threads > 512 ? 1 : 2;
 constexpr int kS1Warps = kS1Threads / 32;
-#ifndef LXY_S1_DEPTH
-#define LXY_S1_DEPTH 8
-#endif
-constexpr int kS1Depth = LXY_S1_DEPTH;     // 16-byte record copies in flight per lane
-constexpr int kS1DepthLog2 = kS1Depth == 8 ? 3 : kS1Depth == 4 ? 2 : kS1Depth == 16 ? 4 : -1;
-static_assert(kS1DepthLog2 > 0, "ring depth");
-constexpr int kS1Stage = kS1Threads * 16;  // bytes of one ring stage (one packet per thread)
-// Ring geometry of k_scaff_stream1: every warp owns kS1Sub packets per lane (2 KB) of each chunk and
+// Ring geometry of the streaming kernels: every warp owns kS1Sub packets per lane (2 KB) of each chunk and
 // keeps `stages` such slices in flight, each filled by ONE bulk copy (UBLKCP) counted on the warp's own
 // mbarrier of that stage: warps stay independent of each other (a ring stage shared by the CTA couples
 // them to the slowest, measured 100 us against 82), and the copy engine sees 2 KB requests (512-byte
 // ones cost 158 us: its cost is per request).
 constexpr int kS1Sub = 4;
 constexpr int kS1WarpStage = kS1Sub * 512;             // bytes per warp and ring stage
-#ifndef LXY_S1_BLOCK
-#define LXY_S1_BLOCK 4
-#endif
-constexpr int kS1BlockMax = LXY_S1_BLOCK;     // chunks per unrolled block of the hot loop (divides kS1Depth)
-static_assert(kS1Depth % kS1BlockMax == 0, "ring blocks");
 // Unit weights: the two records of a 32-bit word share ONE decay look-up, lut2[v0 * 43 + v1] =
 // 100*T[v0] + 100*T[v1] (<= 200: a byte).  Saves one of the two look-ups, one add and moves the index
 // arithmetic to an IMAD (the FMA pipe idles in this kernel): 25 -> 21 shared-pipe wavefronts per packet.
@@ -109,18 +97,6 @@ __device__ __forceinline__ int32_t lds_s16(uint32_t addr) {
   return v;
 }
 
-__device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void* src) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
-}
-// Branch-free conditional copy: with src-size 0 nothing is read and the 16 bytes are zero-filled.
-__device__ __forceinline__ void cp_async16_zfill(uint32_t dst_smem, const void* src, bool pred) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst_smem), "l"(src), "r"(pred ? 16u : 0u) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() {
-  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-}
 __device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
   uint4 r;
   asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
@@ -255,9 +231,6 @@ __device__ __forceinline__ void s1_bar_wait(uint32_t bar_smem, uint32_t parity) 
       "r"(parity)
       : "memory");
 }
-
-struct S1Yes { static constexpr bool value = true; };
-struct S1No { static constexpr bool value = false; };
 
 struct S1Tile {  // a tile cursor: tile t = (I, J) holds records [.., end)
   int64_t t, end;

@@ -2,7 +2,7 @@
 // the placement tables of TWO orderings are interleaved as one 32-bit word per contig.
 // (included by scaff_kernels.cu inside its anonymous namespace, after scaff_stream1.cuh)
 //
-// Same boundary, mapping (lane = record, cp.async ring, runs of chunks) and integers as
+// Same boundary, mapping (lane = record, per-warp ring of bulk copies, runs of chunks) and integers as
 // k_scaff_stream1 (scaff.go:246-310 through DESIGN.md §2); what changes is the cost per evaluation.
 //   table word of pair j at contig x:  (-pos_{2j}[x] mod 2^16) | (-pos_{2j+1}[x] mod 2^16) << 16
 //   per packet:   A_j = (21 | 21 << 16) - word_j[a]      (per half-word: pos a + 21)
