@@ -10,6 +10,9 @@
 //    block J lives in shared memory; row a — constant over the run of records with the same first
 //    contig, records being sorted by (a, b) inside a tile — is read from global memory (L2) into
 //    registers, one packet ahead.
+//  * records and offsets (10 bytes per record in three arrays) arrive through a per-warp ring of bulk
+//    copies and are read from shared memory two records at a time: 64 registers, 32 warps per SM
+//    (the first version kept two whole packets per warp in registers: 128 registers, 16 warps, 6 % slower).
 //  * per evaluation: table entry e = -start (forward) or start + len - 1 (reversed), so that
 //    coord = |x - e| is ONE VABSDIFF (the absolute value handles the orientation), d = |coord a - coord b|
 //    a second one; d is clamped to 22 * unit - 1 (VIMNMX) and divided by one IMAD.HI + shift:
@@ -32,11 +35,6 @@ constexpr int kFirst2 = kBlk * kFirstRow2;
 constexpr int kQ2 = 22;                    // bucket indices 0..21; 21 = far (T = 0)
 constexpr int kLutG2Stride = 23;
 constexpr int kLutG2Words = kQ2 * kLutG2Stride;
-#ifndef LXY_G2_THREADS
-#define LXY_G2_THREADS 512
-#endif
-constexpr int kG2Threads = LXY_G2_THREADS;
-constexpr int kG2Warps = kG2Threads / 32;
 constexpr int kG2Flush = 64;               // packets between flushes of the packed sums: 64 * 8 * 100 < 2^16
 constexpr int kG2Smem = kTab2 + kFirst2 + 4 * ((kLutG2Words + 3) & ~3) + 64;
 
@@ -226,175 +224,7 @@ __device__ __forceinline__ void g2_eval_records(const G2Packet& pk, int k0, int 
   }
 }
 
-template <bool SH0>
-__global__ void __launch_bounds__(kG2Threads, 1) k_scaffg2_score(G2Params prm) {
-  extern __shared__ __align__(128) uint8_t smem[];
-  uint8_t* sB = smem;
-  uint8_t* sFirstB = smem + kTab2;
-  uint32_t* s_lut2 = (uint32_t*)(sFirstB + kFirst2);
-  uint64_t* bar = (uint64_t*)(s_lut2 + ((kLutG2Words + 3) & ~3));
-  const uint32_t lut = smem_u32(s_lut2);
-
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int i = tid; i < kLutG2Words; i += kG2Threads) {
-    const int q1 = i / kLutG2Stride, q0 = i - q1 * kLutG2Stride;
-    s_lut2[i] = (q0 < kQ2 ? (uint32_t)c_lutg[q0] : 0u) | ((uint32_t)c_lutg[q1] << 16);
-  }
-  if (tid == 0) {
-    mbar_init(bar, 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  __syncthreads();
-  uint32_t parity = 0;
-
-  const int units = prm.groups * prm.splits;
-  const int64_t npk_all = (prm.L + kPacket - 1) / kPacket;
-  const int64_t ntiles = (int64_t)prm.nblk * (prm.nblk + 1) / 2;
-  for (int u = blockIdx.x; u < units; u += gridDim.x) {
-    const int g = u / prm.splits, s = u - g * prm.splits;
-    const int64_t lo = (npk_all * s / prm.splits) * kPacket;
-    const int64_t hi = min((npk_all * (s + 1) / prm.splits) * kPacket, prm.L);
-    G2Acc acc;
-    acc.clear();
-    int32_t loadedJ = -1;
-    if (lo < hi) {
-      int64_t tl = 0, th = ntiles;
-      while (th - tl > 1) {
-        const int64_t mid = (tl + th) >> 1;
-        if (prm.tile_start[mid] <= lo) tl = mid; else th = mid;
-      }
-      int64_t t = tl;
-      int32_t I = 0;
-      {
-        int32_t a = 0, b = prm.nblk;
-        while (b - a > 1) {
-          const int32_t m = (a + b) >> 1;
-          if (tile_row_start(m, prm.nblk) <= t) a = m; else b = m;
-        }
-        I = a;
-      }
-      int32_t J = I + (int32_t)(t - tile_row_start(I, prm.nblk));
-      int64_t cur = lo;
-      while (cur < hi) {
-        const int64_t tend = prm.tile_start[t + 1];
-        if (tend <= cur) {
-          ++t; ++J;
-          if (J == prm.nblk) { ++I; J = I; }
-          continue;
-        }
-        const int64_t seg_end = min(hi, tend);
-        if (J != loadedJ) {   // stage block J of the origin table, its first-bits and any-first bytes
-          __syncthreads();
-          if (tid == 0) {
-            const int rowsB = min(kBlk, prm.n - J * kBlk);
-            const size_t rb = (size_t)g * prm.n + (size_t)J * kBlk;
-            fence_proxy_async();
-            mbar_expect_tx(bar, (uint32_t)rowsB * (kRow2 + kFirstRow2));
-            tma_bulk_g2s(sB, prm.origin + rb * kCand2, (uint32_t)rowsB * kRow2, bar);
-            tma_bulk_g2s(sFirstB, prm.firstw + rb * 8, (uint32_t)rowsB * kFirstRow2, bar);
-          }
-          loadedJ = J;
-          mbar_wait(bar, parity);
-          parity ^= 1;
-        }
-        const size_t rowA0 = (size_t)g * prm.n + (size_t)I * kBlk;
-
-        const int64_t p_first = cur / kPacket, p_last = (seg_end - 1) / kPacket;
-        const bool head_partial = (p_first * kPacket < cur);
-        const bool tail_partial = ((p_last + 1) * kPacket > seg_end);
-        if (head_partial && warp == 0) {   // boundary packets: masked, one warp each
-          const int64_t base = p_first * kPacket;
-          const G2Packet pk = g2_load_packet(prm, base);
-          g2_eval_records<SH0>(pk, (int)(cur - base), (int)min((int64_t)kPacket, seg_end - base), rowA0, sB, sFirstB,
-                          lut, lane, prm, acc);
-          acc.flush16();
-        }
-        if (tail_partial && warp == 1 && !(head_partial && p_last == p_first)) {
-          const int64_t base = p_last * kPacket;
-          const G2Packet pk = g2_load_packet(prm, base);
-          g2_eval_records<SH0>(pk, 0, (int)(seg_end - base), rowA0, sB, sFirstB, lut, lane, prm, acc);
-          acc.flush16();
-        }
-        const int64_t f0 = p_first + (head_partial ? 1 : 0);
-        const int64_t f1 = p_last - (tail_partial ? 1 : 0);  // inclusive
-        const int64_t nfull = f1 - f0 + 1;
-        if (nfull > 0) {
-          for (int64_t c0 = 0; c0 < nfull; c0 += (int64_t)kG2Warps << 16) {
-            const int32_t cnt = (int32_t)min((int64_t)kG2Warps << 16, nfull - c0);
-            const int64_t pbase = (f0 + c0) * kPacket;
-            int32_t it = warp;
-            // Two packets per iteration, ping-pong (no register rotation): while one is scored the other's
-            // records are in flight.  Row a of a packet must be requested a whole packet ahead of its use,
-            // but the row index is in the packet itself - so the FIRST WORD of each packet is fetched one
-            // step earlier still (w_next), and the row request goes out together with the packet's loads.
-            const uint16_t* rbase = prm.rec + pbase;
-            auto first_word = [&](int32_t i) -> uint32_t {
-              return i < cnt ? __ldg(reinterpret_cast<const uint32_t*>(rbase + (int64_t)i * kPacket)) : 0u;
-            };
-            G2Packet pkA, pkB;
-            G2RowA RA, RB;
-            RA.e = RB.e = make_int4(0, 0, 0, 0); RA.fw = RB.fw = RA.any = RB.any = 0;
-            if (it < cnt) {
-              pkA = g2_load_packet(prm, pbase + (int64_t)it * kPacket);
-              RA = g2_load_row_a(prm, rowA0 + ((first_word(it) >> 8) & 0xFFu), lane);
-            }
-            if (it + kG2Warps < cnt) {
-              pkB = g2_load_packet(prm, pbase + (int64_t)(it + kG2Warps) * kPacket);
-              RB = g2_load_row_a(prm, rowA0 + ((first_word(it + kG2Warps) >> 8) & 0xFFu), lane);
-            }
-            uint32_t w_next = first_word(it + 2 * kG2Warps);
-            int32_t since = 0;
-#pragma unroll 1
-            for (; it < cnt; it += 2 * kG2Warps) {
-              // sorted by (a, b): first a == last a  <=>  one a for the whole packet (warp-uniform)
-              if (((pkA.rec.x >> 8) & 0xFFu) == (pkA.rec.w >> 24))
-                g2_eval_packet<SH0>(pkA, RA, sB, sFirstB, lut, lane, prm, acc);
-              else
-                g2_eval_records<SH0>(pkA, 0, kPacket, rowA0, sB, sFirstB, lut, lane, prm, acc);
-              if (it + 2 * kG2Warps < cnt) {
-                pkA = g2_load_packet(prm, pbase + (int64_t)(it + 2 * kG2Warps) * kPacket);
-                RA = g2_load_row_a(prm, rowA0 + ((w_next >> 8) & 0xFFu), lane);
-              }
-              w_next = first_word(it + 3 * kG2Warps);
-              if (it + kG2Warps < cnt) {
-                if (((pkB.rec.x >> 8) & 0xFFu) == (pkB.rec.w >> 24))
-                  g2_eval_packet<SH0>(pkB, RB, sB, sFirstB, lut, lane, prm, acc);
-                else
-                  g2_eval_records<SH0>(pkB, 0, kPacket, rowA0, sB, sFirstB, lut, lane, prm, acc);
-              }
-              if (it + 3 * kG2Warps < cnt) {
-                pkB = g2_load_packet(prm, pbase + (int64_t)(it + 3 * kG2Warps) * kPacket);
-                RB = g2_load_row_a(prm, rowA0 + ((w_next >> 8) & 0xFFu), lane);
-              }
-              w_next = first_word(it + 4 * kG2Warps);
-              since += 2;
-              if (since >= kG2Flush - 1) { acc.flush16(); since = 0; }
-            }
-            acc.flush16();
-          }
-        }
-        cur = seg_end;
-      }
-    }
-    acc.flush16();
-    __syncthreads();
-    loadedJ = -1;                        // the table area is reused by the reduction
-    int64_t* red = (int64_t*)smem;       // [kG2Warps][2][128]
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      red[(warp * 2 + 0) * kCand2 + lane * 4 + j] = acc.s32[j];
-      red[(warp * 2 + 1) * kCand2 + lane * 4 + j] = acc.h32[j];
-    }
-    __syncthreads();
-    if (tid < 2 * kCand2) {
-      int64_t sum = 0;
-      for (int wq = 0; wq < kG2Warps; ++wq) sum += red[wq * 2 * kCand2 + tid];
-      prm.partial[(size_t)u * 2 * kCand2 + tid] = sum;
-    }
-  }
-}
-
-// ---- k_scaffg2r_score: the same scorer with the records arriving through a per-warp ring of bulk copies ----
+// ---- k_scaffg2r_score: the scorer; records and offsets arrive through a per-warp ring of bulk copies ----
 #ifndef LXY_G2R_THREADS
 #define LXY_G2R_THREADS 1024
 #endif

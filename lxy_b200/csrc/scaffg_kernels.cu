@@ -537,23 +537,14 @@ static int scaffg2_score(lxy_ctx* c, const int32_t* perm_dev, const uint8_t* ori
     {
       std::lock_guard<std::mutex> cfg_lock(config_mutex());
       if (!configured[c->cfg.device & 63]) {
-        LXY_CUDA(cudaFuncSetAttribute(k_scaffg2_score<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kG2Smem));
-        LXY_CUDA(cudaFuncSetAttribute(k_scaffg2_score<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kG2Smem));
         LXY_CUDA(cudaFuncSetAttribute(k_scaffg2r_score<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kG2RSmem));
         LXY_CUDA(cudaFuncSetAttribute(k_scaffg2r_score<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kG2RSmem));
         configured[c->cfg.device & 63] = true;
       }
     }
     prm.shmul = sh ? (1u << (32 - sh)) : 0u;
-    static const char* g2_ring_env = getenv("LXY_G2_RING");   // experiments: 0 = packets in registers (512 threads)
-    const bool ring = g2_ring_env ? atoi(g2_ring_env) != 0 : true;
-    if (ring) {
-      if (sh == 0) k_scaffg2r_score<true><<<grid, kG2RThreads, kG2RSmem, st>>>(prm);
-      else k_scaffg2r_score<false><<<grid, kG2RThreads, kG2RSmem, st>>>(prm);
-    } else {
-      if (sh == 0) k_scaffg2_score<true><<<grid, kG2Threads, kG2Smem, st>>>(prm);
-      else k_scaffg2_score<false><<<grid, kG2Threads, kG2Smem, st>>>(prm);
-    }
+    if (sh == 0) k_scaffg2r_score<true><<<grid, kG2RThreads, kG2RSmem, st>>>(prm);
+    else k_scaffg2r_score<false><<<grid, kG2RThreads, kG2RSmem, st>>>(prm);
     LXY_CUDA(cudaGetLastError());
     ++launches;
   } else {

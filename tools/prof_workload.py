@@ -36,7 +36,7 @@ if mode in ("r3", "r4"):   # r3: the bench default (config 3, population 1024, b
             ctx.scaff_score_batch_dev(perms.data_ptr(), P, out.data_ptr(), None)
         print(ctx.timing())
     sys.exit(0)
-if mode == "g3":      # G-profile at config-3 size (bench.py's g_profile inputs): k_scaffg2_score
+if mode == "g3":      # G-profile at config-3 size (bench.py's g_profile inputs): k_scaffg2r_score
     import torch
     import bench
     n, L, P = 5000, int(float(os.environ.get("G3_L", "2e8"))), 1024
