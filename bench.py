@@ -715,6 +715,18 @@ def main():
                                                                      x100_dev.data_ptr()),
                        lambda: pctx.scaff_score_batch(perms), args.steps, args.warmup)
         same = bool((x100_dev == stream_x100).all().item())
+        e2e_u16 = None
+        if n <= 65536:      # the same call with 16-bit genes: half the bytes over PCIe
+            perms16 = pinned(perms.astype(np.uint16))
+            for _ in range(2):
+                pctx.scaff_score_batch_u16(perms16)
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                _, x16 = pctx.scaff_score_batch_u16(perms16, want_x100=True)
+            ms16 = 1e3 * (time.perf_counter() - t0) / args.steps
+            e2e_u16 = {"entry_point": "lxy_scaff_score_batch_u16", "ms_per_step": ms16,
+                       "candidates_per_sec": float(P) / (ms16 * 1e-3), "h2d_bytes_per_step": int(perms16.nbytes),
+                       "identical_x100": bool((x16 == stream_x100.cpu().numpy()).all())}
         ga_auto = measure_ga(pctx, N, torch, dist, dev, P, n, L, rank, world, max(args.steps, 5))
         pctx.close()
         extras["best_exact_path"] = {
@@ -730,6 +742,7 @@ def main():
             "e2e": {"value": float(P) * L * args.steps / (pr["ms_e2e"] * 1e-3), "unit": UNIT,
                     "candidates_per_sec": float(P) * args.steps / (pr["ms_e2e"] * 1e-3),
                     "ms_per_step": pr["ms_e2e"] / args.steps},
+            "e2e_u16": e2e_u16,
             "kernel_ms": pr["kernel_ms"], "table_bytes": 4 * n * n, "set_links_s": round(t_pbuild, 3),
             "identical_x100": same, "ga": ga_auto}
 

@@ -125,6 +125,11 @@ int lxy_scaff_score_batch(lxy_ctx* ctx, const int32_t* perm, int32_t P, double* 
                           int64_t* x100);
 int lxy_scaff_score_batch_dev(lxy_ctx* ctx, const int32_t* perm_dev, int32_t P, double* out_dev,
                               int64_t* x100_dev);
+/* The same scores from 16-bit gene values (n_ids <= 65,536, else LXY_ERR_RANGE): half the bytes over PCIe
+ * for a caller whose orderings live in host memory - scaff/genome.go keeps them as []int, so the shim
+ * narrows while it copies the rows it copies anyway (go/scaff/gpu.go).  On the dense pair-table path
+ * (LXY_PATH_AUTO at BASELINE config 3) the copy is most of a call. */
+int lxy_scaff_score_batch_u16(lxy_ctx* ctx, const uint16_t* perm, int32_t P, double* out, int64_t* x100);
 /* Integer checks: pos[P][n_ids] (placement offset of every contig = its ordering index in the
  * R-profile) and, for ONE candidate, |pos a - pos b| of caller-supplied records in their order. */
 int lxy_scaff_positions(lxy_ctx* ctx, const int32_t* perm, int32_t P, int32_t* pos);

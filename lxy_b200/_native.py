@@ -40,7 +40,7 @@ SYMBOLS = [
     "lxy_comm_unique_id", "lxy_comm_init_rank", "lxy_comm_init_all", "lxy_comm_destroy", "lxy_comm_info",
     "lxy_comm_slice", "lxy_scaff_score_sharded", "lxy_scaff_score_sharded_dev", "lxy_ga_set_sharding",
     "lxy_links_tabulate_varblocks", "lxy_comm_link_owners",
-    "lxy_phase_score_batch_bits_noalloc_dev",
+    "lxy_phase_score_batch_bits_noalloc_dev", "lxy_scaff_score_batch_u16",
 ]
 
 ACC_AUTO, ACC_F64, ACC_INT = 0, 1, 2
@@ -214,6 +214,7 @@ def lib():
         "lxy_phase_score_batch_bits": (i32, [vp, vp, i32, vp, vp]),
         "lxy_phase_score_batch_bits_dev": (i32, [vp, vp, i32, vp, vp]),
         "lxy_phase_score_batch_bits_noalloc_dev": (i32, [vp, vp, i32, vp, vp]),
+        "lxy_scaff_score_batch_u16": (i32, [vp, vp, i32, vp, vp]),
         "lxy_comm_unique_id": (i32, [vp]),
         "lxy_comm_init_rank": (i32, [vp, i32, i32, vp]),
         "lxy_comm_init_all": (i32, [C.POINTER(vp), i32]),
@@ -395,6 +396,17 @@ class Context:
         out = np.zeros(P, np.float64)
         x100 = np.zeros(P, np.int64)
         _check(lib().lxy_scaff_score_batch(self._h, _p(perms), P, _p(out), _p(x100)))
+        return (out, x100) if want_x100 else out
+
+    def scaff_score_batch_u16(self, perms, want_x100=False):
+        """perms[P][n] as uint16 (n <= 65,536): half the bytes over PCIe, identical scores."""
+        perms = _c(perms, np.uint16)
+        if perms.ndim != 2 or perms.shape[1] != self.n:
+            raise ValueError(f"perms must be [P][{self.n}]")
+        P = perms.shape[0]
+        out = np.zeros(P, np.float64)
+        x100 = np.zeros(P, np.int64)
+        _check(lib().lxy_scaff_score_batch_u16(self._h, _p(perms), P, _p(out), _p(x100)))
         return (out, x100) if want_x100 else out
 
     def scaff_score_batch_dev(self, perm_ptr, P, out_ptr, x100_ptr=None):

@@ -131,6 +131,14 @@ int read_flags(lxy_ctx* c, const char* what, const char* where) {
 }
 }  // namespace lxy
 
+namespace lxy {
+__global__ void k_widen_u16(const uint16_t* __restrict__ in, int64_t count, int32_t* __restrict__ out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < count; i += stride) out[i] = (int32_t)in[i];
+}
+}  // namespace lxy
+
 // The scorer of the context's R-profile store: the dense pair table when the store has one
 // (LXY_PATH_PAIRS, or LXY_PATH_AUTO's choice), else the record stream.
 namespace lxy {
@@ -337,6 +345,38 @@ int lxy_scaff_score_batch(lxy_ctx* c, const int32_t* perm, int32_t P, double* ou
   LXY_TRY(stage_h2d(c, c->d_perm.p, perm, pbytes, 0));
   LXY_TRY(scaff_dispatch(c, c->d_perm.as<int32_t>(), P, c->d_out.as<double>(), c->d_x100.as<int64_t>()));
   char* hout = (char*)c->h_pin + pbytes;
+  LXY_CUDA(cudaMemcpyAsync(hout, c->d_out.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, c->stream));
+  LXY_CUDA(cudaMemcpyAsync(hout + 8 * (size_t)P, c->d_x100.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, c->stream));
+  LXY_CUDA(cudaEventRecord(c->ev[5], c->stream));
+  c->timing_pending = 2;
+  LXY_TRY(finish_flags(c, "scaff score"));
+  std::memcpy(out, hout, 8 * (size_t)P);
+  if (x100) std::memcpy(x100, hout + 8 * (size_t)P, 8 * (size_t)P);
+  return LXY_OK;
+}
+
+// 16-bit genes (n_ids <= 65,536): half the bytes over PCIe; widened to the kernels' int32 on the device.
+int lxy_scaff_score_batch_u16(lxy_ctx* c, const uint16_t* perm, int32_t P, double* out, int64_t* x100) {
+  CHECK_CTX(c);
+  if (P < 0 || (P > 0 && (!perm || !out))) { set_error("score_batch_u16: bad argument"); return LXY_ERR_ARG; }
+  if (!c->scaff.ready) { set_error("score_batch_u16: links not set"); return LXY_ERR_STATE; }
+  if (c->scaff.n > 65536) { set_error("score_batch_u16: %d ids do not fit 16-bit genes", c->scaff.n); return LXY_ERR_RANGE; }
+  if (P == 0) return LXY_OK;
+  const size_t cnt = (size_t)c->scaff.n * (size_t)P;
+  const size_t pbytes = sizeof(uint16_t) * cnt;
+  const size_t poff = (pbytes + 15) & ~(size_t)15;
+  LXY_TRY(pin_reserve(c, poff + 16 * (size_t)P));
+  LXY_TRY(c->d_tmp3.reserve(pbytes));
+  LXY_TRY(c->d_perm.reserve(sizeof(int32_t) * cnt));
+  LXY_TRY(c->d_out.reserve(8 * (size_t)P));
+  LXY_TRY(c->d_x100.reserve(8 * (size_t)P));
+  LXY_CUDA(cudaEventRecord(c->ev[4], c->stream));
+  LXY_TRY(stage_h2d(c, c->d_tmp3.p, perm, pbytes, 0));
+  lxy::k_widen_u16<<<(unsigned)std::min<size_t>((cnt + 255) / 256, (size_t)c->sm_count * 16), 256, 0, c->stream>>>(c->d_tmp3.as<uint16_t>(), (int64_t)cnt,
+                                                                                     c->d_perm.as<int32_t>());
+  LXY_CUDA(cudaGetLastError());
+  LXY_TRY(scaff_dispatch(c, c->d_perm.as<int32_t>(), P, c->d_out.as<double>(), c->d_x100.as<int64_t>()));
+  char* hout = (char*)c->h_pin + poff;
   LXY_CUDA(cudaMemcpyAsync(hout, c->d_out.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, c->stream));
   LXY_CUDA(cudaMemcpyAsync(hout + 8 * (size_t)P, c->d_x100.p, 8 * (size_t)P, cudaMemcpyDeviceToHost, c->stream));
   LXY_CUDA(cudaEventRecord(c->ev[5], c->stream));

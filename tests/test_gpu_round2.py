@@ -273,3 +273,31 @@ def test_deferred_errors_are_reported_by_the_next_sync():
             c.scaff_score_batch(bad)
         assert e.value.status == -4
         assert c.scaff_score_batch(perms, want_x100=True)[1].tolist() == ox100.tolist()
+
+
+@pytest.mark.parametrize("path", [N.PATH_AUTO, N.PATH_STREAM])
+def test_sixteen_bit_genes_entry_point(path):
+    """lxy_scaff_score_batch_u16: the orderings as uint16 (half the PCIe bytes), same integers as the
+    int32 entry point and the oracle on both scoring paths; a bad row is reported; n > 65,536 is refused."""
+    n, P = 700, 150
+    a, b = _dup_links(n, 40_000, 6, 13)                       # dense enough for the pair table under AUTO
+    perms = S.scaff_population(n, P, 113)
+    _, ox100 = O.scaff_score_links_batch(n, a, b, np.ones(len(a)), perms, nthreads=4)
+    with N.Context(0, path=path) as c:
+        c.set_links(n, a, b, None)
+        s32, x32 = c.scaff_score_batch(perms, want_x100=True)
+        for _ in range(3):                                     # repeated calls: the captured graph is replayed
+            s16, x16 = c.scaff_score_batch_u16(perms.astype(np.uint16), want_x100=True)
+            assert x16.tolist() == x32.tolist() == ox100.tolist() and s16.tolist() == s32.tolist()
+        bad = perms.astype(np.uint16)
+        bad[149, 3] = bad[149, 4]
+        with pytest.raises(N.LxyError) as e:
+            c.scaff_score_batch_u16(bad)
+        assert e.value.status == -4
+    big = 65_537
+    ab = np.arange(big - 1, dtype=np.uint32)
+    with N.Context(0, path=N.PATH_STREAM) as c:
+        c.set_links(big, ab, ab + 1, None)
+        with pytest.raises(N.LxyError) as e:
+            c.scaff_score_batch_u16(np.zeros((1, big), np.uint16))
+        assert e.value.status == -5
