@@ -544,9 +544,12 @@ def run_scoring(job, name, steps, warmup, sample_clocks, check):
     x100_dev = torch.zeros(P, dtype=torch.int64, device=dev)
     torch.cuda.synchronize()
     mode = N.SHARD_LINKS if link_mode else N.SHARD_POPULATION
+    perms16 = pinned(perms_all.astype(np.uint16)) if (world == 1 and n <= 65536) else None
     if world == 1:
         dev_call = lambda: ctx.scaff_score_batch_dev(perm_dev.data_ptr(), P, out_dev.data_ptr(), x100_dev.data_ptr())
-        host_call = lambda: ctx.scaff_score_batch(perms, want_x100=True)
+        # the call the cgo shim makes (go/scaff/gpu.go): 16-bit genes while the contig ids fit them
+        host_call = (lambda: ctx.scaff_score_batch_u16(perms16, want_x100=True)) if perms16 is not None else \
+                    (lambda: ctx.scaff_score_batch(perms, want_x100=True))
     else:
         dev_call = lambda: ctx.scaff_score_sharded_dev(mode, perm_dev.data_ptr(), P, out_dev.data_ptr(), x100_dev.data_ptr())
         host_call = lambda: ctx.scaff_score_sharded(mode, perms, want_x100=True)
@@ -554,6 +557,9 @@ def run_scoring(job, name, steps, warmup, sample_clocks, check):
     res = {"name": name, "n": n, "L": L, "L_loc": L_loc, "P": P, "seed": seed, "pseed": pseed,
            "link_mode": link_mode, "ctx": ctx, "a": a, "b": b, "perms_all": perms_all, "perms": perms,
            "perm_dev": perm_dev, "out_dev": out_dev, "x100_dev": x100_dev, "t_build": t_build, "main": main,
+           "h2d_bytes": int(perms16.nbytes if perms16 is not None else perms.nbytes),
+           "host_entry": "lxy_scaff_score_batch_u16 (16-bit genes, as the cgo shim passes them)" if perms16 is not None
+                         else ("lxy_scaff_score_sharded" if world > 1 else "lxy_scaff_score_batch"),
            "P_loc": P if link_mode else N.comm_slice(P, world, rank)[1]}
     L_total = (L // world) * world if link_mode else L
     evals = float(P) * float(L_total)
@@ -626,11 +632,13 @@ def main():
     # stages it through its pinned buffer with a few host threads
     ms_e2e_pageable = None
     if world == 1:
-        perms_pageable = np.array(perms, copy=True)
-        ctx.scaff_score_batch(perms_pageable)
+        narrow = n <= 65536                      # the same entry point as the e2e leg, caller memory pageable
+        perms_pageable = np.array(perms.astype(np.uint16) if narrow else perms, copy=True)
+        call_pageable = ctx.scaff_score_batch_u16 if narrow else ctx.scaff_score_batch
+        call_pageable(perms_pageable)
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            ctx.scaff_score_batch(perms_pageable)
+            call_pageable(perms_pageable)
         ms_e2e_pageable = 1e3 * (time.perf_counter() - t0) / args.steps
         del perms_pageable
 
@@ -939,7 +947,8 @@ def main():
             "candidates_per_sec": P * args.steps / (ms_dev * 1e-3),
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                     "candidates_per_sec": P * args.steps / (ms_e2e * 1e-3),
-                    "h2d_bytes_per_step": int(perms.nbytes), "d2h_bytes_per_step": int(16 * P) * world,
+                    "h2d_bytes_per_step": R["h2d_bytes"], "d2h_bytes_per_step": int(16 * P) * world,
+                    "entry_point": R["host_entry"],
                     "host_memory": "pinned (page-locked caller buffers go straight to the copy engine)",
                     "pageable_ms_per_step": ms_e2e_pageable},
             "gpu_launches": int(launches),
